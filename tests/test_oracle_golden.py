@@ -1,0 +1,115 @@
+"""CPU: the oracle restatement against the committed golden vectors.
+
+ref_*.npz were produced by the UNMODIFIED reference (tests/golden/make_golden.py), so these
+checks pin oracle/macbf_oracle.py to the reference: LITERAL CBF.forward (cbf.py:21-45),
+Controller.forward (controller.py:31-63), top-k (core.py:234-250), dynamics (core.py:74-86)
+and the dense TTC predicate (core.py:212-231).
+Tolerance: bit-exact for indices/masks; 1e-6 relative-to-scale for h/u because the CPU
+conv/matmul kernels (MKL-DNN) may differ in summation order between machines.
+"""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import macbf_oracle as O
+
+
+def load(path):
+    z = np.load(path)
+    return {k: z[k] for k in z.files}
+
+
+def params_from(z, prefix):
+    return {k[len(prefix):]: torch.from_numpy(v) for k, v in z.items() if k.startswith(prefix)}
+
+
+def close(a, b, rtol):
+    a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
+    scale = max(np.abs(b).max(), 1e-30)
+    return np.abs(a - b).max() <= rtol * scale
+
+
+REF_CASES = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "ref_*_*vel.npz"))) + \
+    [os.path.join(os.path.dirname(__file__), "golden", "ref_c1_n32.npz")]
+
+
+@pytest.mark.parametrize("path", REF_CASES, ids=[os.path.basename(p) for p in REF_CASES])
+def test_literal_matches_reference(path):
+    z = load(path)
+    s, g = torch.from_numpy(z["states"]), torch.from_numpy(z["goals"])
+    p_cbf, p_ctrl = params_from(z, "cbf/"), params_from(z, "ctrl/")
+    idx = O.neighbor_indices(s, 12)
+    assert np.array_equal(idx.reshape(-1).numpy(), z["idx"][:, 1])
+    assert np.array_equal(z["idx"][:, 0], np.repeat(np.arange(s.shape[0]), 12))
+    h = O.cbf_forward(p_cbf, s, O.LITERAL)
+    u = O.controller_forward(p_ctrl, s, g, O.LITERAL)
+    assert h.shape == z["h"].shape and u.shape == z["u"].shape
+    assert close(h.numpy(), z["h"], 1e-6)
+    # LITERAL controller pools arg-max indices: a flipped near-tie moves u by O(1); require the
+    # bulk of agents to agree (all of them do on the machine that made the fixture)
+    du = np.abs(u.numpy() - z["u"]).max(axis=1)
+    assert (du <= 1e-5 * max(np.abs(z["u"]).max(), 1.0)).mean() >= 0.97
+    assert np.array_equal(O.dynamics(s, torch.from_numpy(z["u"])).numpy(), z["dsdt"])
+    assert np.array_equal(O.ttc_dangerous_mask_dense_np(z["states"]), z["ttc_np"])
+    # slot 0 is the agent itself, neighbours sorted by ascending distance (Appendix B)
+    assert np.array_equal(idx[:, 0].numpy(), np.arange(s.shape[0]))
+
+
+ORACLE_CASES = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "oracle_*.npz")))
+
+
+@pytest.mark.parametrize("path", ORACLE_CASES, ids=[os.path.basename(p) for p in ORACLE_CASES])
+def test_repaired_matches_golden(path):
+    z = load(path)
+    if z["states"].shape[0] > 400:
+        pytest.skip("large case is exercised by the GPU parity tests")
+    s, g = torch.from_numpy(z["states"]), torch.from_numpy(z["goals"])
+    obs = torch.from_numpy(z["obstacles"]) if z["obstacles"].shape[0] else None
+    k = int(z["k"])
+    p_cbf = dict(zip(O.CBF_KEYS, [t.reshape(shp) for t, shp in zip(
+        torch.split(torch.from_numpy(z["cbf_flat"]), [int(np.prod(sh)) for sh in O.CBF_SHAPES]), O.CBF_SHAPES)]))
+    p_ctrl = dict(zip(O.CTRL_KEYS, [t.reshape(shp) for t, shp in zip(
+        torch.split(torch.from_numpy(z["ctrl_flat"]), [int(np.prod(sh)) for sh in O.CTRL_SHAPES]), O.CTRL_SHAPES)]))
+    out = O.full_step(p_cbf, p_ctrl, s, g, obs, k, O.REPAIRED, with_grad=True)
+    assert np.array_equal(O.neighbor_indices(s, k, obs).numpy(), z["idx"])
+    assert np.array_equal(out["ttc_mask"].numpy(), z["ttc_mask"])
+    for name in ("u", "h", "h_next", "scalars", "grad_cbf", "grad_ctrl"):
+        assert close(out[name].numpy(), z[name], 2e-5), name
+
+
+def test_repaired_differs_from_literal_only_by_repairs():
+    """F1/F2: with K = 1 channel permutation is the identity, so the CBF forwards coincide."""
+    p_cbf, _ = O.init_params(7)
+    s, _ = O.synthetic_swarm(1, 50, 3)
+    a = O.cbf_forward(p_cbf, s[0], O.LITERAL, k=1)
+    b = O.cbf_forward(p_cbf, s[0], O.REPAIRED, k=1)
+    assert close(a.numpy(), b.numpy(), 1e-6)   # same data, possibly another conv kernel
+
+
+def test_row_chunked_topk_identical():
+    s, _ = O.synthetic_swarm(1, 777, 5)
+    assert torch.equal(O.neighbor_indices(s[0], 12), O.neighbor_indices(s[0], 12, row_chunk=100))
+
+
+def test_small_n_no_topk():
+    s, _ = O.synthetic_swarm(1, 8, 5)
+    idx = O.neighbor_indices(s[0], 12)
+    assert idx.shape == (8, 8) and torch.equal(idx[3], torch.arange(8))
+    p_cbf, p_ctrl = O.init_params(1)
+    assert O.cbf_forward(p_cbf, s[0]).shape == (8, 1, 8)
+
+
+def test_ttc_topk_matches_dense_predicate():
+    """A9 on the top-k edges equals the dense numpy predicate (core.py:212-231) gathered at
+    the same edges when both use the training constants."""
+    s, _ = O.synthetic_swarm(1, 128, 9)
+    s = s[0]
+    idx = O.neighbor_indices(s, 12)
+    dense = O.ttc_dangerous_mask_dense_np(s.numpy().astype(np.float32), r=0.07, ttc=2.0)
+    m = O.ttc_dangerous_mask(s).numpy()[:, :, 0]
+    # dense numpy path promotes through float64 eye; compare away from the decision boundary
+    gathered = dense[np.arange(128)[:, None], idx.numpy(), 0]
+    assert (m == gathered).mean() > 0.995
