@@ -1,0 +1,146 @@
+/*
+ * macbf_b200.h - C ABI of libmacbf_b200.so: the B200 (sm_100a) implementation of
+ * macbf-gnn's per-step safety-certificate path.
+ *
+ * The reference (lucaballotta/macbf-gnn) has no FFI: its "operator API" is the Python call
+ * surface of core.py / cbf.py / controller.py.  Each entry point below replaces the torch
+ * op groups behind one of those functions; the reference lines are cited per function.
+ * The Python drop-in modules (macbf-gnn_b200/{core,cbf,controller}.py) bind these through
+ * ctypes; INTEGRATION.md shows the stub a maintainer of the reference would add.
+ *
+ * Conventions
+ *  - All pointers are DEVICE pointers unless named host_*; fp32, row-major, contiguous.
+ *  - Extents: B independent environments, N agents per env, M obstacle points per env
+ *    (0 allowed; `obstacles` may then be NULL), K = neighbours per agent actually stored
+ *    (K_eff = min(TOP_K, N + M), see macbf_neighbor_count).
+ *  - states  [B,N,4] = (x, y, vx, vy);  goals [B,N,2];  obstacles [B,M,2];
+ *    idx [B,N,K] int32, env-local candidate index in [0, N+M): j < N is agent j, j >= N is
+ *    obstacle point j-N (candidate state (ox, oy, 0, 0), identity indicator 0).
+ *  - `stream` is a cudaStream_t passed as void* (0 = default stream).  Calls enqueue work
+ *    and return; nothing synchronises.
+ *  - The library allocates nothing: outputs and scratch are caller-owned.
+ *  - Return value: 0 on success, non-zero on error; macbf_last_error() gives the text
+ *    (thread-local).  No exceptions cross the boundary.
+ *  - `semantics`: MACBF_LITERAL reproduces the reference's forwards bug for bug
+ *    (reshape-as-transpose cbf.py:40 / controller.py:43, arg-max-index pooling
+ *    controller.py:46); MACBF_REPAIRED applies SURVEY Appendix A (F1, F2).
+ *  - Parameters are flat fp32 buffers in state_dict order:
+ *      CBF  (17089): cbf_net.{0,2,4,6}.{weight,bias}                (cbf.py:13-19)
+ *      CTRL (34052): controller_centr_net.{0,2}.{weight,bias},
+ *                    controller_dec_net.{0,2,4,6}.{weight,bias}      (controller.py:16-29)
+ */
+#ifndef MACBF_B200_H
+#define MACBF_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MACBF_LITERAL 0
+#define MACBF_REPAIRED 1
+
+#define MACBF_CBF_PARAMS 17089
+#define MACBF_CTRL_PARAMS 34052
+#define MACBF_POOL_DIM 128
+#define MACBF_MAX_K 128
+#define MACBF_NUM_SCALARS 12
+
+/* ---- housekeeping ------------------------------------------------------------------ */
+const char* macbf_last_error(void);
+int macbf_version(void);
+/* K_eff = min(top_k, N + M): core.py:236-237 returns all candidates when there are <= k. */
+int macbf_neighbor_count(int N, int M, int top_k);
+
+/* ---- A3: neighbour graph  (core.py:234-250 remove_distant_agents; key core.py:238) ----
+ * idx[b,i,:] = the K candidates with the smallest key
+ *   sqrt((dx^2 + 1e-6) + (dy^2 + 1e-6)), ascending, ties by ascending candidate index;
+ * slot 0 is the agent itself.  If N + M <= top_k: idx[b,i,e] = e (no selection, index order).
+ * The dense (N,N,C) tensor of cbf.py:23 / controller.py:33 / core.py:188 is never built. */
+int macbf_neighbor_topk(const float* states, const float* obstacles, int B, int N, int M,
+                        int top_k, int32_t* idx, void* stream);
+
+/* ---- A2,A4,A5: CBF head  (cbf.py:21-45) ------------------------------------------------
+ * h[b,i,k] = mask * MLP_cbf([dx,dy,dvx,dvy,eye, d - dist_min_thres]),
+ * d = sqrt((dx^2+1e-4)+(dy^2+1e-4)), mask = d <= obs_radius.  h is [B,N,K] (the reference's
+ * (N,1,K) with the unit dim dropped). */
+int macbf_cbf_forward(const float* states, const float* obstacles, const int32_t* idx,
+                      const float* cbf_params, int B, int N, int M, int K, int semantics,
+                      double dist_min_thres, double obs_radius, float* h, void* stream);
+
+/* ---- A6,A7,A8: controller + Euler step  (controller.py:31-63, core.py:74-86, train.py:70)
+ * pool [B,N,128]: masked max over the K edge embeddings (LITERAL: arg-max slot as float);
+ * u [B,N,2]: action; s_next [B,N,4] = states + [v, u] * dt (may be NULL). */
+int macbf_controller_forward(const float* states, const float* goals, const float* obstacles,
+                             const int32_t* idx, const float* ctrl_params, int B, int N, int M,
+                             int K, int semantics, double obs_radius, double dt, float* pool,
+                             float* u, float* s_next, void* stream);
+
+/* ---- A9: time-to-collision mask  (core.py:187-209) -------------------------------------
+ * mask[b,i,k] in {0,1}. */
+int macbf_ttc_mask(const float* states, const float* obstacles, const int32_t* idx, int B, int N,
+                   int M, int K, double dist_min_thres, double ttc, uint8_t* mask, void* stream);
+
+/* ---- A10,A11,A12,A13: losses  (core.py:89-184, train.py:93-98) --------------------------
+ * scalars [B,12] per env: 0 loss_dang, 1 loss_safe, 2 acc_dang, 3 acc_safe,
+ *   4 loss_dang_deriv, 5 loss_safe_deriv, 6 acc_dang_deriv, 7 acc_safe_deriv, 8 loss_action,
+ *   9 total = 10*(2*l0 + l1 + 2*l4 + l5 + 0.01*l8), 10 n_dang, 11 n_safe.
+ * h_next may be NULL (derivative terms = 0), u/goals may be NULL (action term = 0).
+ * ttc_mask [B,N,K] is written (A9 is evaluated inside).  scratch: macbf_loss_scratch_bytes. */
+size_t macbf_loss_scratch_bytes(int B, int N, int K);
+int macbf_loss_forward(const float* states, const float* goals, const float* obstacles,
+                       const int32_t* idx, const float* h, const float* h_next, const float* u,
+                       int B, int N, int M, int K, double dist_min_thres, double ttc, double dt,
+                       double alpha, uint8_t* ttc_mask, float* scalars, void* scratch,
+                       size_t scratch_bytes, void* stream);
+
+/* Seeds of the backward pass: given d(objective)/d(scalars) [B,12] (only entries 0,1,4,5,8 are
+ * differentiable; the rest are ignored) produce dL/dh, dL/dh_next [B,N,K] and dL/du [B,N,2]
+ * (any output may be NULL).  Uses ttc_mask and scalars[.,10:12] from macbf_loss_forward. */
+int macbf_loss_backward(const float* states, const float* goals, const float* h, const float* h_next,
+                        const float* u, const uint8_t* ttc_mask, const float* scalars,
+                        const float* grad_scalars, int B, int N, int K, double dt, double alpha,
+                        float* grad_h, float* grad_h_next, float* grad_u, void* stream);
+
+/* ---- backward of A5 (autograd of cbf.py:21-45) ------------------------------------------
+ * grad_params [17089] is ACCUMULATED into (caller zeroes it); grad_states [B,N,4] is
+ * accumulated into when non-NULL (caller zeroes it).  Activations are recomputed from
+ * states + idx; nothing from the forward needs to be kept.  REPAIRED semantics only. */
+size_t macbf_cbf_backward_scratch_bytes(int B, int N, int K);
+int macbf_cbf_backward(const float* states, const float* obstacles, const int32_t* idx,
+                       const float* cbf_params, const float* grad_h, int B, int N, int M, int K,
+                       double dist_min_thres, double obs_radius, float* grad_params,
+                       float* grad_states, void* scratch, size_t scratch_bytes, void* stream);
+
+/* ---- backward of A6-A8 (autograd of controller.py:31-63 + Euler step) --------------------
+ * grad_u [B,N,2] and (optional) grad_s_next [B,N,4] are the incoming gradients; grad_params
+ * [34052] and (optional) grad_states [B,N,4], grad_goals [B,N,2] are accumulated into. */
+size_t macbf_controller_backward_scratch_bytes(int B, int N, int K);
+int macbf_controller_backward(const float* states, const float* goals, const float* obstacles,
+                              const int32_t* idx, const float* ctrl_params, const float* grad_u,
+                              const float* grad_s_next, int B, int N, int M, int K,
+                              double obs_radius, double dt, float* grad_params, float* grad_states,
+                              float* grad_goals, void* scratch, size_t scratch_bytes, void* stream);
+
+/* ---- the whole per-step path in one call (what bench.py times) ---------------------------
+ * graph(S) -> u, S' -> graph(S') -> h(S), h(S') -> TTC mask -> scalars.  Workspace layout is
+ * private; size it with macbf_step_workspace_bytes.  Outputs u, s_next, h, h_next, idx,
+ * idx_next, ttc_mask, scalars as documented above (idx_next/h_next/ttc_mask may not be NULL). */
+size_t macbf_step_workspace_bytes(int B, int N, int M, int top_k);
+int macbf_step_forward(const float* states, const float* goals, const float* obstacles,
+                       const float* cbf_params, const float* ctrl_params, int B, int N, int M,
+                       int top_k, int semantics, double dist_min_thres, double obs_radius, double ttc,
+                       double dt, double alpha, int32_t* idx, int32_t* idx_next, float* u,
+                       float* s_next, float* h, float* h_next, uint8_t* ttc_mask, float* scalars,
+                       void* workspace, size_t workspace_bytes, void* stream);
+
+/* Kernel launches issued by this library on the calling thread since load (bench.py reports
+ * the per-step delta as gpu_launches). */
+long long macbf_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MACBF_B200_H */

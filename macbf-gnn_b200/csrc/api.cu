@@ -1,0 +1,206 @@
+// extern "C" surface of libmacbf_b200.so (declared in include/macbf_b200.h).
+#include <stdarg.h>
+
+#include "common.cuh"
+
+namespace macbf {
+
+static thread_local char g_err[512] = "";
+static thread_local long long g_launches = 0;
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+void count_launch(int n) { g_launches += n; }
+
+// implemented in the kernel translation units
+int neighbor_topk(const float*, const float*, int, int, int, int, int32_t*, cudaStream_t);
+int cbf_forward(const float*, const float*, const int32_t*, const float*, int, int, int, int, int, double, double,
+                float*, cudaStream_t);
+int controller_forward(const float*, const float*, const float*, const int32_t*, const float*, int, int, int, int,
+                       int, double, double, float*, float*, float*, cudaStream_t);
+int ttc_mask(const float*, const float*, const int32_t*, int, int, int, int, double, double, uint8_t*, cudaStream_t);
+size_t loss_scratch_bytes(int, int, int);
+int loss_forward(const float*, const float*, const float*, const int32_t*, const float*, const float*, const float*,
+                 int, int, int, int, double, double, double, double, uint8_t*, float*, void*, size_t, cudaStream_t);
+int loss_backward(const float*, const float*, const float*, const float*, const float*, const uint8_t*, const float*,
+                  const float*, int, int, int, double, double, float*, float*, float*, cudaStream_t);
+size_t cbf_backward_scratch_bytes(int, int, int);
+int cbf_backward(const float*, const float*, const int32_t*, const float*, const float*, int, int, int, int, double,
+                 double, float*, float*, void*, size_t, cudaStream_t);
+size_t controller_backward_scratch_bytes(int, int, int);
+int controller_backward(const float*, const float*, const float*, const int32_t*, const float*, const float*,
+                        const float*, int, int, int, int, double, double, float*, float*, float*, void*, size_t,
+                        cudaStream_t);
+
+static int check_dims(const char* fn, int B, int N, int M, int K) {
+  MACBF_CHECK_ARG(B >= 1 && B <= 65535, "%s: B=%d out of range [1,65535]", fn, B);
+  MACBF_CHECK_ARG(N >= 1, "%s: N=%d must be >= 1", fn, N);
+  MACBF_CHECK_ARG(M >= 0, "%s: M=%d must be >= 0", fn, M);
+  MACBF_CHECK_ARG(K >= 1 && K <= MACBF_MAX_K, "%s: K=%d out of range [1,%d]", fn, K, MACBF_MAX_K);
+  MACBF_CHECK_ARG(K <= N + M, "%s: K=%d exceeds the candidate count N+M=%d", fn, K, N + M);
+  MACBF_CHECK_ARG((long long)B * N * K < (1ll << 40), "%s: problem too large", fn);
+  return 0;
+}
+#define REQ_PTR(fn, p) MACBF_CHECK_ARG((p) != nullptr, "%s: %s is NULL", fn, #p)
+#define REQ_A16(fn, p) MACBF_CHECK_ARG((((uintptr_t)(p)) & 15) == 0, "%s: %s must be 16-byte aligned", fn, #p)
+
+static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+}  // namespace macbf
+
+using namespace macbf;
+
+extern "C" {
+
+const char* macbf_last_error(void) { return g_err; }
+int macbf_version(void) { return 100; }
+long long macbf_launch_count(void) { return g_launches; }
+int macbf_neighbor_count(int N, int M, int top_k) { return (N + M) < top_k ? (N + M) : top_k; }
+
+int macbf_neighbor_topk(const float* states, const float* obstacles, int B, int N, int M, int top_k, int32_t* idx,
+                        void* stream) {
+  const char* fn = "macbf_neighbor_topk";
+  MACBF_CHECK_ARG(top_k >= 1 && top_k <= MACBF_MAX_K, "%s: top_k=%d out of range [1,%d]", fn, top_k, MACBF_MAX_K);
+  if (check_dims(fn, B, N, M, macbf_neighbor_count(N, M, top_k))) return 1;
+  REQ_PTR(fn, states); REQ_PTR(fn, idx); REQ_A16(fn, states);
+  MACBF_CHECK_ARG(M == 0 || obstacles != nullptr, "%s: obstacles is NULL but M=%d", fn, M);
+  return neighbor_topk(states, obstacles, B, N, M, top_k, idx, (cudaStream_t)stream);
+}
+
+int macbf_cbf_forward(const float* states, const float* obstacles, const int32_t* idx, const float* cbf_params, int B,
+                      int N, int M, int K, int semantics, double dist_min_thres, double obs_radius, float* h,
+                      void* stream) {
+  const char* fn = "macbf_cbf_forward";
+  if (check_dims(fn, B, N, M, K)) return 1;
+  REQ_PTR(fn, states); REQ_PTR(fn, idx); REQ_PTR(fn, cbf_params); REQ_PTR(fn, h); REQ_A16(fn, states);
+  MACBF_CHECK_ARG(M == 0 || obstacles != nullptr, "%s: obstacles is NULL but M=%d", fn, M);
+  MACBF_CHECK_ARG(semantics == MACBF_LITERAL || semantics == MACBF_REPAIRED, "%s: bad semantics %d", fn, semantics);
+  return cbf_forward(states, obstacles, idx, cbf_params, B, N, M, K, semantics, dist_min_thres, obs_radius, h,
+                     (cudaStream_t)stream);
+}
+
+int macbf_controller_forward(const float* states, const float* goals, const float* obstacles, const int32_t* idx,
+                             const float* ctrl_params, int B, int N, int M, int K, int semantics, double obs_radius,
+                             double dt, float* pool, float* u, float* s_next, void* stream) {
+  const char* fn = "macbf_controller_forward";
+  if (check_dims(fn, B, N, M, K)) return 1;
+  REQ_PTR(fn, states); REQ_PTR(fn, goals); REQ_PTR(fn, idx); REQ_PTR(fn, ctrl_params); REQ_PTR(fn, pool);
+  REQ_PTR(fn, u); REQ_A16(fn, states); REQ_A16(fn, pool);
+  MACBF_CHECK_ARG(M == 0 || obstacles != nullptr, "%s: obstacles is NULL but M=%d", fn, M);
+  MACBF_CHECK_ARG(semantics == MACBF_LITERAL || semantics == MACBF_REPAIRED, "%s: bad semantics %d", fn, semantics);
+  return controller_forward(states, goals, obstacles, idx, ctrl_params, B, N, M, K, semantics, obs_radius, dt, pool,
+                            u, s_next, (cudaStream_t)stream);
+}
+
+int macbf_ttc_mask(const float* states, const float* obstacles, const int32_t* idx, int B, int N, int M, int K,
+                   double dist_min_thres, double ttc, uint8_t* mask, void* stream) {
+  const char* fn = "macbf_ttc_mask";
+  if (check_dims(fn, B, N, M, K)) return 1;
+  REQ_PTR(fn, states); REQ_PTR(fn, idx); REQ_PTR(fn, mask); REQ_A16(fn, states);
+  MACBF_CHECK_ARG(M == 0 || obstacles != nullptr, "%s: obstacles is NULL but M=%d", fn, M);
+  return ttc_mask(states, obstacles, idx, B, N, M, K, dist_min_thres, ttc, mask, (cudaStream_t)stream);
+}
+
+size_t macbf_loss_scratch_bytes(int B, int N, int K) { return loss_scratch_bytes(B, N, K); }
+
+int macbf_loss_forward(const float* states, const float* goals, const float* obstacles, const int32_t* idx,
+                       const float* h, const float* h_next, const float* u, int B, int N, int M, int K,
+                       double dist_min_thres, double ttc, double dt, double alpha, uint8_t* ttc_mask_out,
+                       float* scalars, void* scratch, size_t scratch_bytes, void* stream) {
+  const char* fn = "macbf_loss_forward";
+  if (check_dims(fn, B, N, M, K)) return 1;
+  REQ_PTR(fn, states); REQ_PTR(fn, idx); REQ_PTR(fn, h); REQ_PTR(fn, ttc_mask_out); REQ_PTR(fn, scalars);
+  REQ_PTR(fn, scratch); REQ_A16(fn, states);
+  MACBF_CHECK_ARG(M == 0 || obstacles != nullptr, "%s: obstacles is NULL but M=%d", fn, M);
+  return loss_forward(states, goals, obstacles, idx, h, h_next, u, B, N, M, K, dist_min_thres, ttc, dt, alpha,
+                      ttc_mask_out, scalars, scratch, scratch_bytes, (cudaStream_t)stream);
+}
+
+int macbf_loss_backward(const float* states, const float* goals, const float* h, const float* h_next, const float* u,
+                        const uint8_t* ttc_mask_in, const float* scalars, const float* grad_scalars, int B, int N,
+                        int K, double dt, double alpha, float* grad_h, float* grad_h_next, float* grad_u,
+                        void* stream) {
+  const char* fn = "macbf_loss_backward";
+  MACBF_CHECK_ARG(B >= 1 && B <= 65535 && N >= 1 && K >= 1 && K <= MACBF_MAX_K, "%s: bad extents B=%d N=%d K=%d", fn, B, N, K);
+  REQ_PTR(fn, h); REQ_PTR(fn, ttc_mask_in); REQ_PTR(fn, scalars); REQ_PTR(fn, grad_scalars);
+  MACBF_CHECK_ARG(grad_u == nullptr || u == nullptr || (states != nullptr && goals != nullptr),
+                  "%s: grad_u needs states and goals", fn);
+  return loss_backward(states, goals, h, h_next, u, ttc_mask_in, scalars, grad_scalars, B, N, K, dt, alpha, grad_h,
+                       grad_h_next, grad_u, (cudaStream_t)stream);
+}
+
+size_t macbf_cbf_backward_scratch_bytes(int B, int N, int K) { return cbf_backward_scratch_bytes(B, N, K); }
+
+int macbf_cbf_backward(const float* states, const float* obstacles, const int32_t* idx, const float* cbf_params,
+                       const float* grad_h, int B, int N, int M, int K, double dist_min_thres, double obs_radius,
+                       float* grad_params, float* grad_states, void* scratch, size_t scratch_bytes, void* stream) {
+  const char* fn = "macbf_cbf_backward";
+  if (check_dims(fn, B, N, M, K)) return 1;
+  REQ_PTR(fn, states); REQ_PTR(fn, idx); REQ_PTR(fn, cbf_params); REQ_PTR(fn, grad_h); REQ_PTR(fn, grad_params);
+  REQ_PTR(fn, scratch); REQ_A16(fn, states);
+  MACBF_CHECK_ARG(M == 0 || obstacles != nullptr, "%s: obstacles is NULL but M=%d", fn, M);
+  return cbf_backward(states, obstacles, idx, cbf_params, grad_h, B, N, M, K, dist_min_thres, obs_radius, grad_params,
+                      grad_states, scratch, scratch_bytes, (cudaStream_t)stream);
+}
+
+size_t macbf_controller_backward_scratch_bytes(int B, int N, int K) {
+  return controller_backward_scratch_bytes(B, N, K);
+}
+
+int macbf_controller_backward(const float* states, const float* goals, const float* obstacles, const int32_t* idx,
+                              const float* ctrl_params, const float* grad_u, const float* grad_s_next, int B, int N,
+                              int M, int K, double obs_radius, double dt, float* grad_params, float* grad_states,
+                              float* grad_goals, void* scratch, size_t scratch_bytes, void* stream) {
+  const char* fn = "macbf_controller_backward";
+  if (check_dims(fn, B, N, M, K)) return 1;
+  REQ_PTR(fn, states); REQ_PTR(fn, goals); REQ_PTR(fn, idx); REQ_PTR(fn, ctrl_params); REQ_PTR(fn, grad_params);
+  REQ_PTR(fn, scratch); REQ_A16(fn, states);
+  MACBF_CHECK_ARG(grad_u != nullptr || grad_s_next != nullptr, "%s: no incoming gradient", fn);
+  MACBF_CHECK_ARG(M == 0 || obstacles != nullptr, "%s: obstacles is NULL but M=%d", fn, M);
+  return controller_backward(states, goals, obstacles, idx, ctrl_params, grad_u, grad_s_next, B, N, M, K, obs_radius,
+                             dt, grad_params, grad_states, grad_goals, scratch, scratch_bytes, (cudaStream_t)stream);
+}
+
+// workspace: [pool (B*N*128 f32)] [loss scratch]
+size_t macbf_step_workspace_bytes(int B, int N, int M, int top_k) {
+  const int K = macbf_neighbor_count(N, M, top_k);
+  return align256((size_t)B * N * MACBF_POOL_DIM * sizeof(float)) + align256(loss_scratch_bytes(B, N, K));
+}
+
+int macbf_step_forward(const float* states, const float* goals, const float* obstacles, const float* cbf_params,
+                       const float* ctrl_params, int B, int N, int M, int top_k, int semantics, double dist_min_thres,
+                       double obs_radius, double ttc, double dt, double alpha, int32_t* idx, int32_t* idx_next,
+                       float* u, float* s_next, float* h, float* h_next, uint8_t* ttc_mask_out, float* scalars,
+                       void* workspace, size_t workspace_bytes, void* stream) {
+  const char* fn = "macbf_step_forward";
+  MACBF_CHECK_ARG(top_k >= 1 && top_k <= MACBF_MAX_K, "%s: top_k=%d out of range [1,%d]", fn, top_k, MACBF_MAX_K);
+  const int K = macbf_neighbor_count(N, M, top_k);
+  if (check_dims(fn, B, N, M, K)) return 1;
+  REQ_PTR(fn, states); REQ_PTR(fn, goals); REQ_PTR(fn, cbf_params); REQ_PTR(fn, ctrl_params); REQ_PTR(fn, idx);
+  REQ_PTR(fn, idx_next); REQ_PTR(fn, u); REQ_PTR(fn, s_next); REQ_PTR(fn, h); REQ_PTR(fn, h_next);
+  REQ_PTR(fn, ttc_mask_out); REQ_PTR(fn, scalars); REQ_PTR(fn, workspace);
+  REQ_A16(fn, states); REQ_A16(fn, s_next); REQ_A16(fn, workspace);
+  MACBF_CHECK_ARG(M == 0 || obstacles != nullptr, "%s: obstacles is NULL but M=%d", fn, M);
+  MACBF_CHECK_ARG(workspace_bytes >= macbf_step_workspace_bytes(B, N, M, top_k), "%s: workspace too small (%zu < %zu)",
+                  fn, workspace_bytes, macbf_step_workspace_bytes(B, N, M, top_k));
+  cudaStream_t st = (cudaStream_t)stream;
+  float* pool = (float*)workspace;
+  void* lscratch = (char*)workspace + align256((size_t)B * N * MACBF_POOL_DIM * sizeof(float));
+  int rc;
+  if ((rc = neighbor_topk(states, obstacles, B, N, M, top_k, idx, st))) return rc;
+  if ((rc = controller_forward(states, goals, obstacles, idx, ctrl_params, B, N, M, K, semantics, obs_radius, dt, pool,
+                               u, s_next, st))) return rc;
+  if ((rc = neighbor_topk(s_next, obstacles, B, N, M, top_k, idx_next, st))) return rc;   // core.py:137: fresh top-k
+  if ((rc = cbf_forward(states, obstacles, idx, cbf_params, B, N, M, K, semantics, dist_min_thres, obs_radius, h, st)))
+    return rc;
+  if ((rc = cbf_forward(s_next, obstacles, idx_next, cbf_params, B, N, M, K, semantics, dist_min_thres, obs_radius,
+                        h_next, st))) return rc;
+  return loss_forward(states, goals, obstacles, idx, h, h_next, u, B, N, M, K, dist_min_thres, ttc, dt, alpha,
+                      ttc_mask_out, scalars, lscratch, loss_scratch_bytes(B, N, K), st);
+}
+
+}  // extern "C"

@@ -1,0 +1,235 @@
+// K5 - time-to-collision mask (core.py:187-209) and the barrier / derivative / action loss
+// reductions (core.py:89-184), plus the analytic seeds of the backward pass.
+//
+// Reduction is two-stage and deterministic: each CTA reduces a fixed chunk of one env's
+// (agent, slot) rows to 10 partial sums in caller-provided scratch, a second single-CTA-per-env
+// kernel adds the partials in index order and forms the 12 scalars.  HBM-bound: per edge it
+// reads idx (4 B), h and h' (8 B) and writes the mask (1 B).
+#include "common.cuh"
+
+namespace macbf {
+
+constexpr int LOSS_THREADS = 256;
+constexpr int LOSS_ROWS_PER_CTA = 4096;
+constexpr int LOSS_NACC = 10;
+
+static inline int loss_chunks(int N, int K) {
+  long long rows = (long long)N * K;
+  return (int)((rows + LOSS_ROWS_PER_CTA - 1) / LOSS_ROWS_PER_CTA);
+}
+
+__global__ void ttc_mask_kernel(const float* __restrict__ states, const float* __restrict__ obstacles,
+                                const int32_t* __restrict__ idx, int N, int M, int K, long long edges,
+                                float r2, float ttc, uint8_t* __restrict__ mask) {
+  const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= edges) return;
+  const long long ga = e / K;
+  const int b = (int)(ga / N), i = (int)(ga % N);
+  const int j = __ldg(idx + e);
+  const float4 si = __ldg(reinterpret_cast<const float4*>(states) + ga);
+  const float4 sj = load_candidate(states, obstacles, b, j, N, M);
+  mask[e] = ttc_dangerous(edge_geom(si, sj, i, j), r2, ttc) ? 1 : 0;
+}
+
+// acc: 0 sum_dang relu(h+1e-3) | 1 sum_safe relu(-h) | 2 cnt_dang[h<=0] | 3 cnt_safe[h>0]
+//      4 sum_dang relu(-d+1e-3) | 5 sum_safe relu(-d) | 6 cnt_dang[d>=0] | 7 cnt_safe[d>0]
+//      8 n_dang | 9 sum_i | |a|^2 - |a_ref|^2 |
+__global__ void __launch_bounds__(LOSS_THREADS)
+loss_partial_kernel(const float* __restrict__ states, const float* __restrict__ goals,
+                    const float* __restrict__ obstacles, const int32_t* __restrict__ idx,
+                    const float* __restrict__ h, const float* __restrict__ h_next, const float* __restrict__ u,
+                    int N, int M, int K, float r2, float ttc, float dt_alpha, uint8_t* __restrict__ mask,
+                    float* __restrict__ partial) {
+  const int b = blockIdx.y, chunk = blockIdx.x, nchunks = gridDim.x;
+  const long long rows_env = (long long)N * K;
+  const long long r_begin = (long long)chunk * LOSS_ROWS_PER_CTA;
+  const long long r_end = min(rows_env, r_begin + LOSS_ROWS_PER_CTA);
+  float acc[LOSS_NACC];
+#pragma unroll
+  for (int q = 0; q < LOSS_NACC; ++q) acc[q] = 0.f;
+
+  for (long long r = r_begin + threadIdx.x; r < r_end; r += LOSS_THREADS) {
+    const int i = (int)(r / K);
+    const long long e = (long long)b * rows_env + r;
+    const int j = __ldg(idx + e);
+    const float4 si = __ldg(reinterpret_cast<const float4*>(states) + (size_t)b * N + i);
+    const float4 sj = load_candidate(states, obstacles, b, j, N, M);
+    const bool dang = ttc_dangerous(edge_geom(si, sj, i, j), r2, ttc);
+    mask[e] = dang ? 1 : 0;
+    const float hv = __ldg(h + e);
+    if (dang) {
+      acc[8] += 1.f;
+      acc[0] += fmaxf(xadd(hv, 1e-3f), 0.f);   // core.py:114-115
+      acc[2] += (hv <= 0.f) ? 1.f : 0.f;       // core.py:119-120
+    } else {
+      acc[1] += fmaxf(-hv, 0.f);               // core.py:116-117
+      acc[3] += (hv > 0.f) ? 1.f : 0.f;        // core.py:121-122 (repair L6)
+    }
+    if (h_next != nullptr) {
+      // core.py:139: h_next - h + TIME_STEP * ALPHA_CBF * h
+      const float d = xadd(xsub(__ldg(h_next + e), hv), xmul(dt_alpha, hv));
+      if (dang) {
+        acc[4] += fmaxf(xadd(-d, 1e-3f), 0.f);
+        acc[6] += (d >= 0.f) ? 1.f : 0.f;
+      } else {
+        acc[5] += fmaxf(-d, 0.f);
+        acc[7] += (d > 0.f) ? 1.f : 0.f;
+      }
+    }
+  }
+  if (u != nullptr) {
+    // core.py:174-184: a_ref = -(p - g) - sqrt(3) v, agents striped over the env's chunks
+    const float s3 = 1.7320508075688772f;
+    for (int i = chunk * LOSS_THREADS + threadIdx.x; i < N; i += nchunks * LOSS_THREADS) {
+      const float4 s = __ldg(reinterpret_cast<const float4*>(states) + (size_t)b * N + i);
+      const float2 g = __ldg(reinterpret_cast<const float2*>(goals) + (size_t)b * N + i);
+      const float2 a = __ldg(reinterpret_cast<const float2*>(u) + (size_t)b * N + i);
+      const float rx = -(s.x - g.x) - s3 * s.z, ry = -(s.y - g.y) - s3 * s.w;
+      acc[9] += fabsf((a.x * a.x + a.y * a.y) - (rx * rx + ry * ry));
+    }
+  }
+  __shared__ float red[LOSS_THREADS / 32][LOSS_NACC];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int q = 0; q < LOSS_NACC; ++q) {
+    float v = warp_sum(acc[q]);
+    if (lane == 0) red[warp][q] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < LOSS_NACC) {
+    float v = 0.f;
+    for (int w = 0; w < LOSS_THREADS / 32; ++w) v += red[w][threadIdx.x];
+    partial[((size_t)b * nchunks + chunk) * LOSS_NACC + threadIdx.x] = v;
+  }
+}
+
+__global__ void loss_final_kernel(const float* __restrict__ partial, int nchunks, int N, int K,
+                                  int has_next, int has_u, float* __restrict__ scalars) {
+  const int b = blockIdx.x;
+  __shared__ double acc[LOSS_NACC];
+  if (threadIdx.x < LOSS_NACC) {
+    double v = 0.0;
+    for (int c = 0; c < nchunks; ++c) v += (double)partial[((size_t)b * nchunks + c) * LOSS_NACC + threadIdx.x];
+    acc[threadIdx.x] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const float nd = (float)acc[8];
+    const float ns = (float)((double)N * K - acc[8]);
+    const float dd = 1e-5f + nd, ds = 1e-5f + ns;   // core.py:114-117 denominators
+    float* o = scalars + (size_t)b * MACBF_NUM_SCALARS;
+    o[0] = (float)acc[0] / dd;
+    o[1] = (float)acc[1] / ds;
+    o[2] = nd > 0.f ? (float)acc[2] / dd : -1.f;     // core.py:124-127 (repair L7)
+    o[3] = ns > 0.f ? (float)acc[3] / ds : -1.f;
+    o[4] = has_next ? (float)acc[4] / dd : 0.f;
+    o[5] = has_next ? (float)acc[5] / ds : 0.f;
+    o[6] = has_next ? (nd > 0.f ? (float)acc[6] / dd : -1.f) : 0.f;
+    o[7] = has_next ? (ns > 0.f ? (float)acc[7] / ds : -1.f) : 0.f;
+    o[8] = has_u ? (float)(acc[9] / (double)N) : 0.f;
+    o[9] = 10.f * (2.f * o[0] + o[1] + 2.f * o[4] + o[5] + 0.01f * o[8]);  // train.py:93,98
+    o[10] = nd;
+    o[11] = ns;
+  }
+}
+
+// dL/dh, dL/dh_next, dL/du from d(objective)/d(scalars).  Hinge subgradients follow torch:
+// clamp(min=0) passes the gradient where its argument >= 0, abs' = sign.
+__global__ void loss_backward_kernel(const float* __restrict__ states, const float* __restrict__ goals,
+                                     const float* __restrict__ h, const float* __restrict__ h_next,
+                                     const float* __restrict__ u, const uint8_t* __restrict__ mask,
+                                     const float* __restrict__ scalars, const float* __restrict__ gs, int N,
+                                     int K, float dt_alpha, float* __restrict__ gh, float* __restrict__ ghn,
+                                     float* __restrict__ gu) {
+  const int b = blockIdx.y;
+  const long long rows_env = (long long)N * K;
+  const float* sc = scalars + (size_t)b * MACBF_NUM_SCALARS;
+  const float* g = gs + (size_t)b * MACBF_NUM_SCALARS;
+  const float inv_d = 1.f / (1e-5f + sc[10]), inv_s = 1.f / (1e-5f + sc[11]);
+  const float g0 = g[0] * inv_d, g1 = g[1] * inv_s, g4 = g[4] * inv_d, g5 = g[5] * inv_s, g8 = g[8] / (float)N;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < rows_env; r += stride) {
+    const long long e = (long long)b * rows_env + r;
+    const bool dang = mask[e] != 0;
+    const float hv = h[e];
+    float dh = 0.f;
+    if (dang) dh += (xadd(hv, 1e-3f) >= 0.f) ? g0 : 0.f;
+    else      dh += (-hv >= 0.f) ? -g1 : 0.f;
+    if (h_next != nullptr) {
+      const float d = xadd(xsub(h_next[e], hv), xmul(dt_alpha, hv));
+      float gd;
+      if (dang) gd = (xadd(-d, 1e-3f) >= 0.f) ? -g4 : 0.f;
+      else      gd = (-d >= 0.f) ? -g5 : 0.f;
+      if (ghn != nullptr) ghn[e] = gd;
+      dh += gd * (dt_alpha - 1.f);
+    } else if (ghn != nullptr) {
+      ghn[e] = 0.f;
+    }
+    if (gh != nullptr) gh[e] = dh;
+  }
+  if (gu != nullptr) {
+    const float s3 = 1.7320508075688772f;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += stride) {
+      float2 o = make_float2(0.f, 0.f);
+      if (u != nullptr) {
+        const float4 s = __ldg(reinterpret_cast<const float4*>(states) + (size_t)b * N + i);
+        const float2 gl = __ldg(reinterpret_cast<const float2*>(goals) + (size_t)b * N + i);
+        const float2 a = __ldg(reinterpret_cast<const float2*>(u) + (size_t)b * N + i);
+        const float rx = -(s.x - gl.x) - s3 * s.z, ry = -(s.y - gl.y) - s3 * s.w;
+        const float diff = (a.x * a.x + a.y * a.y) - (rx * rx + ry * ry);
+        const float sg = diff > 0.f ? 1.f : (diff < 0.f ? -1.f : 0.f);
+        o = make_float2(g8 * sg * 2.f * a.x, g8 * sg * 2.f * a.y);
+      }
+      reinterpret_cast<float2*>(gu)[(size_t)b * N + i] = o;
+    }
+  }
+}
+
+int ttc_mask(const float* states, const float* obstacles, const int32_t* idx, int B, int N, int M, int K,
+             double dist_min, double ttc, uint8_t* mask, cudaStream_t st) {
+  const long long edges = (long long)B * N * K;
+  const float r2 = (float)(dist_min * dist_min);  // python: DIST_MIN_THRES ** 2 in double, then cast
+  ttc_mask_kernel<<<(unsigned)((edges + 255) / 256), 256, 0, st>>>(states, obstacles, idx, N, M, K, edges, r2,
+                                                                  (float)ttc, mask);
+  MACBF_CHECK_LAUNCH("ttc_mask_kernel");
+  return 0;
+}
+
+size_t loss_scratch_bytes(int B, int N, int K) {
+  return (size_t)B * loss_chunks(N, K) * LOSS_NACC * sizeof(float);
+}
+
+int loss_forward(const float* states, const float* goals, const float* obstacles, const int32_t* idx,
+                 const float* h, const float* h_next, const float* u, int B, int N, int M, int K,
+                 double dist_min, double ttc, double dt, double alpha, uint8_t* mask, float* scalars,
+                 void* scratch, size_t scratch_bytes, cudaStream_t st) {
+  const int nchunks = loss_chunks(N, K);
+  MACBF_CHECK_ARG(scratch_bytes >= loss_scratch_bytes(B, N, K), "loss_forward: scratch too small (%zu < %zu)",
+                  scratch_bytes, loss_scratch_bytes(B, N, K));
+  const float r2 = (float)(dist_min * dist_min);
+  const float dt_alpha = (float)(dt * alpha);     // python: TIME_STEP * ALPHA_CBF in double, then cast
+  dim3 grid(nchunks, B);
+  loss_partial_kernel<<<grid, LOSS_THREADS, 0, st>>>(states, goals, obstacles, idx, h, h_next,
+                                                    (goals != nullptr) ? u : nullptr, N, M, K, r2, (float)ttc,
+                                                    dt_alpha, mask, (float*)scratch);
+  MACBF_CHECK_LAUNCH("loss_partial_kernel");
+  loss_final_kernel<<<B, 32, 0, st>>>((const float*)scratch, nchunks, N, K, h_next != nullptr,
+                                      (u != nullptr && goals != nullptr), scalars);
+  MACBF_CHECK_LAUNCH("loss_final_kernel");
+  return 0;
+}
+
+int loss_backward(const float* states, const float* goals, const float* h, const float* h_next, const float* u,
+                  const uint8_t* mask, const float* scalars, const float* grad_scalars, int B, int N, int K,
+                  double dt, double alpha, float* gh, float* ghn, float* gu, cudaStream_t st) {
+  const long long rows_env = (long long)N * K;
+  int gx = (int)(((rows_env + 255) / 256) < 4ll * NUM_SMS ? ((rows_env + 255) / 256) : 4ll * NUM_SMS);
+  if (gx < 1) gx = 1;
+  dim3 grid(gx, B);
+  loss_backward_kernel<<<grid, 256, 0, st>>>(states, goals, h, h_next, (goals != nullptr) ? u : nullptr, mask,
+                                            scalars, grad_scalars, N, K, (float)(dt * alpha), gh, ghn, gu);
+  MACBF_CHECK_LAUNCH("loss_backward_kernel");
+  return 0;
+}
+
+}  // namespace macbf

@@ -1,0 +1,130 @@
+"""torch.autograd bridges: the reference's call surface (cbf.py / controller.py / core.py) expressed
+as autograd Functions whose forward AND backward run in libmacbf_b200.so.
+
+Neighbour indices and masks are piecewise-constant in the states, so - exactly as in the
+reference's eager autograd (topk indices / comparisons carry no gradient) - they are treated
+as constants of the backward pass.
+"""
+from typing import Optional, Sequence
+
+import torch
+
+from . import ops
+
+_pack_cache = {}
+
+
+def pack_params(params: Sequence[torch.Tensor]) -> torch.Tensor:
+    """state_dict-ordered parameters -> one flat fp32 buffer (the C ABI's layout).  Cached on
+    (storage, version) so an unchanged module is not repacked on every call."""
+    key = tuple((p.data_ptr(), p._version) for p in params)
+    slot = id(params[0])
+    hit = _pack_cache.get(slot)
+    if hit is not None and hit[0] == key:
+        return hit[1]
+    flat = torch.cat([p.detach().reshape(-1) for p in params]).contiguous()
+    _pack_cache[slot] = (key, flat)
+    return flat
+
+
+def _split_like(flat: torch.Tensor, params: Sequence[torch.Tensor]):
+    out, off = [], 0
+    for p in params:
+        n = p.numel()
+        out.append(flat[off:off + n].view_as(p))
+        off += n
+    return out
+
+
+def _batched(t: torch.Tensor, last: int):
+    """[N,last] -> ([1,N,last], True);  [B,N,last] -> (t, False)."""
+    if t.dim() == 2:
+        return t.unsqueeze(0), True
+    assert t.dim() == 3 and t.shape[-1] == last
+    return t, False
+
+
+class CBFFunction(torch.autograd.Function):
+    """h = CBF(states) on a fixed neighbour graph (cbf.py:21-45)."""
+
+    @staticmethod
+    def forward(ctx, states, obstacles, idx, semantics, *params):
+        flat = pack_params(params)
+        h = ops.cbf_forward(states, idx, flat, obstacles, semantics)
+        ctx.save_for_backward(states, idx, flat, obstacles if obstacles is not None else states.new_empty(0))
+        ctx.has_obs = obstacles is not None
+        ctx.semantics = semantics
+        ctx.nparams = len(params)
+        ctx.param_shapes = [p.shape for p in params]
+        return h
+
+    @staticmethod
+    def backward(ctx, grad_h):
+        if ctx.semantics != ops.REPAIRED:
+            raise RuntimeError("LITERAL semantics is forward-only (the reference's losses do not run; SURVEY App. A)")
+        states, idx, flat, obs = ctx.saved_tensors
+        obs = obs if ctx.has_obs else None
+        gp, gs = ops.cbf_backward(states, idx, flat, grad_h.contiguous(), obs, want_grad_states=ctx.needs_input_grad[0])
+        grads, off = [], 0
+        for shp in ctx.param_shapes:
+            n = int(torch.Size(shp).numel())
+            grads.append(gp[off:off + n].view(shp))
+            off += n
+        return (gs, None, None, None, *grads)
+
+
+class ControllerFunction(torch.autograd.Function):
+    """u = Controller(states, goals) on a fixed neighbour graph (controller.py:31-63)."""
+
+    @staticmethod
+    def forward(ctx, states, goals, obstacles, idx, semantics, *params):
+        flat = pack_params(params)
+        u, _, _ = ops.controller_forward(states, goals, idx, flat, obstacles, semantics, want_next=False)
+        ctx.save_for_backward(states, goals, idx, flat, obstacles if obstacles is not None else states.new_empty(0))
+        ctx.has_obs = obstacles is not None
+        ctx.semantics = semantics
+        ctx.param_shapes = [p.shape for p in params]
+        return u
+
+    @staticmethod
+    def backward(ctx, grad_u):
+        if ctx.semantics != ops.REPAIRED:
+            raise RuntimeError("LITERAL semantics is forward-only (the reference's losses do not run; SURVEY App. A)")
+        states, goals, idx, flat, obs = ctx.saved_tensors
+        obs = obs if ctx.has_obs else None
+        gp, gs, gg = ops.controller_backward(states, goals, idx, flat, grad_u.contiguous(), None, obs,
+                                             want_grad_states=ctx.needs_input_grad[0],
+                                             want_grad_goals=ctx.needs_input_grad[1])
+        grads, off = [], 0
+        for shp in ctx.param_shapes:
+            n = int(torch.Size(shp).numel())
+            grads.append(gp[off:off + n].view(shp))
+            off += n
+        return (gs, gg, None, None, None, *grads)
+
+
+class HingeLossFunction(torch.autograd.Function):
+    """The 9 loss/accuracy scalars of core.py:89-184 for one batch of envs.
+    Inputs h, h_next [B,N,K] (h_next optional), u [B,N,2] (optional); states/goals/idx are data.
+    Output scalars [B,12] (layout: include/macbf_b200.h)."""
+
+    @staticmethod
+    def forward(ctx, h, h_next, u, states, goals, obstacles, idx):
+        scalars, mask = ops.loss_forward(states, idx, h, h_next, u, goals, obstacles)
+        ctx.save_for_backward(h, h_next if h_next is not None else h.new_empty(0),
+                              u if u is not None else h.new_empty(0), states,
+                              goals if goals is not None else h.new_empty(0), mask, scalars)
+        ctx.flags = (h_next is not None, u is not None, goals is not None)
+        ctx.mark_non_differentiable(mask)
+        return scalars, mask
+
+    @staticmethod
+    def backward(ctx, grad_scalars, _grad_mask):
+        h, h_next, u, states, goals, mask, scalars = ctx.saved_tensors
+        has_next, has_u, has_goals = ctx.flags
+        gh, ghn, gu = ops.loss_backward(states, goals if has_goals else None, h, h_next if has_next else None,
+                                        u if has_u else None, mask, scalars, grad_scalars.contiguous(),
+                                        want_h=ctx.needs_input_grad[0],
+                                        want_h_next=has_next and ctx.needs_input_grad[1],
+                                        want_u=has_u and ctx.needs_input_grad[2])
+        return gh, ghn, gu, None, None, None, None

@@ -1,0 +1,243 @@
+"""Tensor-level wrappers over the C ABI (include/macbf_b200.h).
+
+torch is used for device memory, streams and shapes only; all arithmetic happens in
+libmacbf_b200.so.  Every function takes CUDA fp32 tensors with a leading env-batch dim
+(states [B,N,4], goals [B,N,2], obstacles [B,M,2] or None) and launches on the current stream.
+"""
+from typing import Optional, Tuple
+
+import torch
+
+from . import lib as _lib
+
+LITERAL = 0
+REPAIRED = 1
+CBF_PARAMS = 17089
+CTRL_PARAMS = 34052
+NUM_SCALARS = 12
+
+# defaults = the reference's config.py
+DIST_MIN_THRES = 0.07
+OBS_RADIUS = 1.0
+TOP_K = 12
+TIME_TO_COLLISION = 2.0
+TIME_STEP = 0.1
+ALPHA_CBF = 1.0
+
+
+def _need_cuda(*tensors):
+    for t in tensors:
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise _lib.MacbfError("macbf_b200 has no CPU path: tensors must live on a CUDA device")
+        if t.dtype not in (torch.float32, torch.int32, torch.uint8):
+            raise _lib.MacbfError(f"unsupported dtype {t.dtype}")
+
+
+def _c(t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+    return None if t is None else (t if t.is_contiguous() else t.contiguous())
+
+
+def _p(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _dims(states, obstacles):
+    B, N, four = states.shape
+    assert four == 4, "states must be [B,N,4]"
+    M = 0
+    if obstacles is not None:
+        assert obstacles.dim() == 3 and obstacles.shape[0] == B and obstacles.shape[2] == 2, "obstacles must be [B,M,2]"
+        M = obstacles.shape[1]
+        if M == 0:
+            obstacles = None
+    return B, N, M, obstacles
+
+
+def neighbor_count(N: int, M: int, top_k: int) -> int:
+    return min(top_k, N + M)
+
+
+def neighbor_topk(states: torch.Tensor, top_k: int = TOP_K, obstacles: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """core.py:234-250 -> idx [B,N,K_eff] int32."""
+    _need_cuda(states, obstacles)
+    states, obstacles = _c(states), _c(obstacles)
+    B, N, M, obstacles = _dims(states, obstacles)
+    K = neighbor_count(N, M, top_k)
+    idx = torch.empty((B, N, K), dtype=torch.int32, device=states.device)
+    L = _lib.load()
+    _lib.check(L.macbf_neighbor_topk(_p(states), _p(obstacles), B, N, M, top_k, _p(idx), _stream()), "macbf_neighbor_topk")
+    return idx
+
+
+def cbf_forward(states, idx, cbf_params, obstacles=None, semantics=REPAIRED, dist_min_thres=DIST_MIN_THRES,
+                obs_radius=OBS_RADIUS) -> torch.Tensor:
+    """cbf.py:21-45 -> h [B,N,K]."""
+    _need_cuda(states, idx, cbf_params, obstacles)
+    states, idx, cbf_params, obstacles = _c(states), _c(idx), _c(cbf_params), _c(obstacles)
+    B, N, M, obstacles = _dims(states, obstacles)
+    K = idx.shape[2]
+    assert cbf_params.numel() == CBF_PARAMS and idx.dtype == torch.int32
+    h = torch.empty((B, N, K), dtype=torch.float32, device=states.device)
+    L = _lib.load()
+    _lib.check(L.macbf_cbf_forward(_p(states), _p(obstacles), _p(idx), _p(cbf_params), B, N, M, K, semantics,
+                                   dist_min_thres, obs_radius, _p(h), _stream()), "macbf_cbf_forward")
+    return h
+
+
+def controller_forward(states, goals, idx, ctrl_params, obstacles=None, semantics=REPAIRED, obs_radius=OBS_RADIUS,
+                       dt=TIME_STEP, want_next=True) -> Tuple[torch.Tensor, Optional[torch.Tensor], torch.Tensor]:
+    """controller.py:31-63 + train.py:70 -> (u [B,N,2], s_next [B,N,4] | None, pool [B,N,128])."""
+    _need_cuda(states, goals, idx, ctrl_params, obstacles)
+    states, goals, idx, ctrl_params, obstacles = _c(states), _c(goals), _c(idx), _c(ctrl_params), _c(obstacles)
+    B, N, M, obstacles = _dims(states, obstacles)
+    K = idx.shape[2]
+    assert ctrl_params.numel() == CTRL_PARAMS and idx.dtype == torch.int32
+    dev = states.device
+    pool = torch.empty((B, N, 128), dtype=torch.float32, device=dev)
+    u = torch.empty((B, N, 2), dtype=torch.float32, device=dev)
+    s_next = torch.empty((B, N, 4), dtype=torch.float32, device=dev) if want_next else None
+    L = _lib.load()
+    _lib.check(L.macbf_controller_forward(_p(states), _p(goals), _p(obstacles), _p(idx), _p(ctrl_params), B, N, M, K,
+                                          semantics, obs_radius, dt, _p(pool), _p(u), _p(s_next), _stream()),
+               "macbf_controller_forward")
+    return u, s_next, pool
+
+
+def ttc_mask(states, idx, obstacles=None, dist_min_thres=DIST_MIN_THRES, ttc=TIME_TO_COLLISION) -> torch.Tensor:
+    """core.py:187-209 -> uint8 [B,N,K]."""
+    _need_cuda(states, idx, obstacles)
+    states, idx, obstacles = _c(states), _c(idx), _c(obstacles)
+    B, N, M, obstacles = _dims(states, obstacles)
+    K = idx.shape[2]
+    mask = torch.empty((B, N, K), dtype=torch.uint8, device=states.device)
+    L = _lib.load()
+    _lib.check(L.macbf_ttc_mask(_p(states), _p(obstacles), _p(idx), B, N, M, K, dist_min_thres, ttc, _p(mask),
+                                _stream()), "macbf_ttc_mask")
+    return mask
+
+
+def loss_forward(states, idx, h, h_next=None, u=None, goals=None, obstacles=None, dist_min_thres=DIST_MIN_THRES,
+                 ttc=TIME_TO_COLLISION, dt=TIME_STEP, alpha=ALPHA_CBF):
+    """core.py:89-184 -> (scalars [B,12], ttc_mask uint8 [B,N,K]).  Scalar layout: macbf_b200.h."""
+    _need_cuda(states, idx, h, h_next, u, goals, obstacles)
+    states, idx, h, h_next, u, goals, obstacles = map(_c, (states, idx, h, h_next, u, goals, obstacles))
+    B, N, M, obstacles = _dims(states, obstacles)
+    K = idx.shape[2]
+    dev = states.device
+    L = _lib.load()
+    nbytes = L.macbf_loss_scratch_bytes(B, N, K)
+    scratch = torch.empty((max(nbytes, 256),), dtype=torch.uint8, device=dev)
+    mask = torch.empty((B, N, K), dtype=torch.uint8, device=dev)
+    scalars = torch.empty((B, NUM_SCALARS), dtype=torch.float32, device=dev)
+    _lib.check(L.macbf_loss_forward(_p(states), _p(goals), _p(obstacles), _p(idx), _p(h), _p(h_next), _p(u), B, N, M,
+                                    K, dist_min_thres, ttc, dt, alpha, _p(mask), _p(scalars), _p(scratch),
+                                    scratch.numel(), _stream()), "macbf_loss_forward")
+    return scalars, mask
+
+
+def loss_backward(states, goals, h, h_next, u, mask, scalars, grad_scalars, dt=TIME_STEP, alpha=ALPHA_CBF,
+                  want_h=True, want_h_next=True, want_u=True):
+    """Seeds dL/dh, dL/dh_next [B,N,K] and dL/du [B,N,2] from dL/dscalars [B,12]."""
+    _need_cuda(states, goals, h, h_next, u, mask, scalars, grad_scalars)
+    states, goals, h, h_next, u, mask, scalars, grad_scalars = map(
+        _c, (states, goals, h, h_next, u, mask, scalars, grad_scalars))
+    B, N, K = h.shape
+    dev = h.device
+    gh = torch.empty_like(h) if want_h else None
+    ghn = torch.empty_like(h) if (want_h_next and h_next is not None) else None
+    gu = torch.empty((B, N, 2), dtype=torch.float32, device=dev) if (want_u and u is not None) else None
+    L = _lib.load()
+    _lib.check(L.macbf_loss_backward(_p(states), _p(goals), _p(h), _p(h_next), _p(u), _p(mask), _p(scalars),
+                                     _p(grad_scalars), B, N, K, dt, alpha, _p(gh), _p(ghn), _p(gu), _stream()),
+               "macbf_loss_backward")
+    return gh, ghn, gu
+
+
+def cbf_backward(states, idx, cbf_params, grad_h, obstacles=None, dist_min_thres=DIST_MIN_THRES,
+                 obs_radius=OBS_RADIUS, grad_params=None, want_grad_states=False):
+    """Autograd of cbf.py:21-45 -> (grad_params [17089] (accumulated if given), grad_states [B,N,4] | None)."""
+    _need_cuda(states, idx, cbf_params, grad_h, obstacles, grad_params)
+    states, idx, cbf_params, grad_h, obstacles = map(_c, (states, idx, cbf_params, grad_h, obstacles))
+    B, N, M, obstacles = _dims(states, obstacles)
+    K = idx.shape[2]
+    dev = states.device
+    if grad_params is None:
+        grad_params = torch.zeros((CBF_PARAMS,), dtype=torch.float32, device=dev)
+    gs = torch.zeros((B, N, 4), dtype=torch.float32, device=dev) if want_grad_states else None
+    L = _lib.load()
+    nbytes = L.macbf_cbf_backward_scratch_bytes(B, N, K)
+    scratch = torch.empty((max(nbytes, 256),), dtype=torch.uint8, device=dev)
+    _lib.check(L.macbf_cbf_backward(_p(states), _p(obstacles), _p(idx), _p(cbf_params), _p(grad_h), B, N, M, K,
+                                    dist_min_thres, obs_radius, _p(grad_params), _p(gs), _p(scratch), scratch.numel(),
+                                    _stream()), "macbf_cbf_backward")
+    return grad_params, gs
+
+
+def controller_backward(states, goals, idx, ctrl_params, grad_u, grad_s_next=None, obstacles=None,
+                        obs_radius=OBS_RADIUS, dt=TIME_STEP, grad_params=None, want_grad_states=False,
+                        want_grad_goals=False):
+    """Autograd of controller.py:31-63 (+ Euler step) -> (grad_params [34052], grad_states | None, grad_goals | None)."""
+    _need_cuda(states, goals, idx, ctrl_params, grad_u, grad_s_next, obstacles, grad_params)
+    states, goals, idx, ctrl_params, grad_u, grad_s_next, obstacles = map(
+        _c, (states, goals, idx, ctrl_params, grad_u, grad_s_next, obstacles))
+    B, N, M, obstacles = _dims(states, obstacles)
+    K = idx.shape[2]
+    dev = states.device
+    if grad_params is None:
+        grad_params = torch.zeros((CTRL_PARAMS,), dtype=torch.float32, device=dev)
+    gs = torch.zeros((B, N, 4), dtype=torch.float32, device=dev) if want_grad_states else None
+    gg = torch.zeros((B, N, 2), dtype=torch.float32, device=dev) if want_grad_goals else None
+    L = _lib.load()
+    nbytes = L.macbf_controller_backward_scratch_bytes(B, N, K)
+    scratch = torch.empty((max(nbytes, 256),), dtype=torch.uint8, device=dev)
+    _lib.check(L.macbf_controller_backward(_p(states), _p(goals), _p(obstacles), _p(idx), _p(ctrl_params), _p(grad_u),
+                                           _p(grad_s_next), B, N, M, K, obs_radius, dt, _p(grad_params), _p(gs),
+                                           _p(gg), _p(scratch), scratch.numel(), _stream()),
+               "macbf_controller_backward")
+    return grad_params, gs, gg
+
+
+class StepBuffers:
+    """Pre-allocated outputs + workspace for macbf_step_forward: the timed loop allocates nothing."""
+
+    def __init__(self, B: int, N: int, M: int, top_k: int, device):
+        L = _lib.load()
+        self.B, self.N, self.M, self.top_k = B, N, M, top_k
+        self.K = K = neighbor_count(N, M, top_k)
+        f32, dev = torch.float32, device
+        self.idx = torch.empty((B, N, K), dtype=torch.int32, device=dev)
+        self.idx_next = torch.empty((B, N, K), dtype=torch.int32, device=dev)
+        self.u = torch.empty((B, N, 2), dtype=f32, device=dev)
+        self.s_next = torch.empty((B, N, 4), dtype=f32, device=dev)
+        self.h = torch.empty((B, N, K), dtype=f32, device=dev)
+        self.h_next = torch.empty((B, N, K), dtype=f32, device=dev)
+        self.ttc_mask = torch.empty((B, N, K), dtype=torch.uint8, device=dev)
+        self.scalars = torch.empty((B, NUM_SCALARS), dtype=f32, device=dev)
+        self.workspace = torch.empty((L.macbf_step_workspace_bytes(B, N, M, top_k),), dtype=torch.uint8, device=dev)
+
+
+def step_forward(states, goals, cbf_params, ctrl_params, buf: StepBuffers, obstacles=None, semantics=REPAIRED,
+                 dist_min_thres=DIST_MIN_THRES, obs_radius=OBS_RADIUS, ttc=TIME_TO_COLLISION, dt=TIME_STEP,
+                 alpha=ALPHA_CBF):
+    """The whole per-step path (graph -> u, S' -> graph' -> h, h' -> TTC mask -> scalars) in one C call."""
+    _need_cuda(states, goals, cbf_params, ctrl_params, obstacles)
+    B, N, M, obstacles = _dims(states, obstacles)
+    assert (B, N, M) == (buf.B, buf.N, buf.M), "StepBuffers were sized for another problem"
+    assert states.is_contiguous() and goals.is_contiguous() and cbf_params.is_contiguous() and ctrl_params.is_contiguous()
+    L = _lib.load()
+    _lib.check(L.macbf_step_forward(_p(states), _p(goals), _p(obstacles), _p(cbf_params), _p(ctrl_params), B, N, M,
+                                    buf.top_k, semantics, dist_min_thres, obs_radius, ttc, dt, alpha, _p(buf.idx),
+                                    _p(buf.idx_next), _p(buf.u), _p(buf.s_next), _p(buf.h), _p(buf.h_next),
+                                    _p(buf.ttc_mask), _p(buf.scalars), _p(buf.workspace), buf.workspace.numel(),
+                                    _stream()), "macbf_step_forward")
+    return buf
+
+
+def launch_count() -> int:
+    return int(_lib.load().macbf_launch_count())

@@ -1,0 +1,205 @@
+"""GPU parity (forward): CUDA path through the C ABI vs golden vectors / the oracle.
+
+Bit-exact: neighbour indices, CBF/controller/TTC masks.  h, u, s', losses: 1e-5 scale-relative
+(tests/helpers.py:RTOL), the tolerance BASELINE.json's north_star states.
+"""
+import numpy as np
+import pytest
+import torch
+
+from helpers import RTOL, assert_close, dev, flat_params_from_ref, load_npz, oracle_cases, ref_cases, rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ops():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from macbf_b200 import ops as _ops
+    return _ops
+
+
+def _inputs(z):
+    s = dev(z["states"]).unsqueeze(0)
+    g = dev(z["goals"]).unsqueeze(0)
+    obs = dev(z["obstacles"]).unsqueeze(0) if z["obstacles"].shape[0] else None
+    return s, g, obs
+
+
+@pytest.mark.parametrize("case", oracle_cases())
+def test_neighbor_topk_bit_exact(ops, case):
+    z = load_npz(case)
+    s, g, obs = _inputs(z)
+    k = int(z["k"])
+    idx = ops.neighbor_topk(s, k, obs)[0].cpu().numpy()
+    assert idx.shape == z["idx"].shape
+    dec = z["decidable"]
+    assert np.array_equal(idx[dec], z["idx"][dec])
+    assert dec.mean() == 1.0  # fixtures were chosen tie-free; the classifier is exercised below
+    idx_next = ops.neighbor_topk(dev(z["s_next"]).unsqueeze(0), k, obs)[0].cpu().numpy()
+    assert np.array_equal(idx_next, z["idx_next"])
+
+
+@pytest.mark.parametrize("case", oracle_cases())
+def test_cbf_forward_repaired(ops, case):
+    z = load_npz(case)
+    s, g, obs = _inputs(z)
+    idx = dev(z["idx"]).unsqueeze(0)
+    h = ops.cbf_forward(s, idx, dev(z["cbf_flat"]), obs)[0].cpu().numpy()
+    assert_close(h, z["h"][:, 0, :], RTOL, "h")
+    # mask bits: h is exactly 0 where the reference masked it
+    assert np.array_equal(h == 0.0, z["h"][:, 0, :] == 0.0)
+    hn = ops.cbf_forward(dev(z["s_next"]).unsqueeze(0), dev(z["idx_next"]).unsqueeze(0), dev(z["cbf_flat"]), obs)
+    assert_close(hn[0].cpu().numpy(), z["h_next"][:, 0, :], RTOL, "h_next")
+
+
+@pytest.mark.parametrize("case", oracle_cases())
+def test_controller_forward_repaired(ops, case):
+    z = load_npz(case)
+    s, g, obs = _inputs(z)
+    idx = dev(z["idx"]).unsqueeze(0)
+    u, s_next, pool = ops.controller_forward(s, g, idx, dev(z["ctrl_flat"]), obs)
+    assert_close(pool[0].cpu().numpy(), z["pool"], RTOL, "pool")
+    assert_close(u[0].cpu().numpy(), z["u"], RTOL, "u")
+    assert_close(s_next[0].cpu().numpy(), z["s_next"], RTOL, "s_next")
+
+
+@pytest.mark.parametrize("case", oracle_cases())
+def test_ttc_mask_and_losses(ops, case):
+    z = load_npz(case)
+    s, g, obs = _inputs(z)
+    idx = dev(z["idx"]).unsqueeze(0)
+    m = ops.ttc_mask(s, idx, obs)[0].cpu().numpy().astype(bool)
+    assert np.array_equal(m, z["ttc_mask"][:, :, 0])
+    h = dev(z["h"][:, 0, :]).unsqueeze(0)
+    hn = dev(z["h_next"][:, 0, :]).unsqueeze(0)
+    u = dev(z["u"]).unsqueeze(0)
+    scal, m2 = ops.loss_forward(s, idx, h, hn, u, g, obs)
+    scal = scal[0].cpu().numpy()
+    assert np.array_equal(m2[0].cpu().numpy().astype(bool), m)
+    for q in range(9):
+        ref = float(z["scalars"][q])
+        assert abs(float(scal[q]) - ref) <= RTOL * max(abs(ref), 1e-3), (q, scal[q], ref)
+    assert abs(scal[9] - float(z["total"])) <= RTOL * max(abs(float(z["total"])), 1e-3)
+    assert scal[10] == z["ttc_mask"].sum() and scal[10] + scal[11] == z["ttc_mask"].size
+
+
+@pytest.mark.parametrize("case", oracle_cases())
+def test_step_forward_fused(ops, case):
+    """The one-call path (what bench.py times) against the same golden."""
+    z = load_npz(case)
+    s, g, obs = _inputs(z)
+    k = int(z["k"])
+    B, N = 1, s.shape[1]
+    M = 0 if obs is None else obs.shape[1]
+    buf = ops.StepBuffers(B, N, M, k, s.device)
+    ops.step_forward(s, g, dev(z["cbf_flat"]), dev(z["ctrl_flat"]), buf, obs)
+    torch.cuda.synchronize()
+    assert np.array_equal(buf.idx[0].cpu().numpy(), z["idx"])
+    assert_close(buf.u[0].cpu().numpy(), z["u"], RTOL, "u")
+    assert_close(buf.h[0].cpu().numpy(), z["h"][:, 0, :], RTOL, "h")
+    # s' comes from the GPU's own u (1 ulp away from the oracle's): the S' graph may differ on rows
+    # whose K-th/K+1-th keys are within a few ulp; compare h' on rows with identical neighbour sets
+    same = (buf.idx_next[0].cpu().numpy() == z["idx_next"]).all(axis=1)
+    assert same.mean() > 0.99
+    assert_close(buf.h_next[0].cpu().numpy()[same], z["h_next"][:, 0, :][same], 2 * RTOL, "h_next")
+    if same.all():
+        sc = buf.scalars[0].cpu().numpy()
+        for q in range(9):
+            ref = float(z["scalars"][q])
+            assert abs(float(sc[q]) - ref) <= 2 * RTOL * max(abs(ref), 1e-3), (q, sc[q], ref)
+
+
+@pytest.mark.parametrize("case", ref_cases())
+def test_literal_forwards_match_reference(ops, case):
+    """LITERAL mode against vectors produced by the unmodified reference (cbf.py / controller.py)."""
+    from oracle import macbf_oracle as O
+    z = load_npz(case)
+    s = dev(z["states"]).unsqueeze(0)
+    g = dev(z["goals"]).unsqueeze(0)
+    idx = ops.neighbor_topk(s, 12)
+    assert np.array_equal(idx[0].cpu().numpy().reshape(-1), z["idx"][:, 1])
+    cbf_flat = dev(flat_params_from_ref(z, "cbf/", O.CBF_KEYS))
+    ctrl_flat = dev(flat_params_from_ref(z, "ctrl/", O.CTRL_KEYS))
+    h = ops.cbf_forward(s, idx, cbf_flat, semantics=ops.LITERAL)[0].cpu().numpy()
+    assert_close(h, z["h"][:, 0, :], RTOL, "h literal")
+    u, _, pool = ops.controller_forward(s, g, idx, ctrl_flat, semantics=ops.LITERAL)
+    # arg-max pooling is discontinuous: an agent whose two best slots differ by ~1 ulp may flip
+    du = np.abs(u[0].cpu().numpy() - z["u"]).max(axis=1)
+    ok = du <= RTOL * max(np.abs(z["u"]).max(), 1.0)
+    assert ok.mean() >= 0.95, ok.mean()
+    # dynamics (core.py:74-86) + Euler step from the reference's own u
+    dsdt = z["dsdt"]
+    assert np.array_equal(dsdt[:, :2], z["states"][:, 2:])
+
+
+def test_batched_equals_per_env(ops):
+    """The leading env dim is defined as the per-env function applied independently."""
+    from oracle import macbf_oracle as O
+    s, g = O.synthetic_swarm(5, 130, seed=77)
+    p_cbf, p_ctrl = O.init_params(3)
+    cf, tf = dev(O.flatten_params(p_cbf, O.CBF_KEYS).numpy()), dev(O.flatten_params(p_ctrl, O.CTRL_KEYS).numpy())
+    sd, gd = s.cuda(), g.cuda()
+    idx = ops.neighbor_topk(sd, 12)
+    h = ops.cbf_forward(sd, idx, cf)
+    u, sn, _ = ops.controller_forward(sd, gd, idx, tf)
+    for b in range(5):
+        idx_b = ops.neighbor_topk(sd[b:b + 1], 12)
+        assert torch.equal(idx_b[0], idx[b])
+        assert torch.equal(ops.cbf_forward(sd[b:b + 1], idx_b, cf)[0], h[b])
+        ub, snb, _ = ops.controller_forward(sd[b:b + 1], gd[b:b + 1], idx_b, tf)
+        assert torch.equal(ub[0], u[b]) and torch.equal(snb[0], sn[b])
+        ref_idx = O.neighbor_indices(s[b], 12).numpy()
+        assert np.array_equal(idx[b].cpu().numpy(), ref_idx)
+
+
+@pytest.mark.parametrize("k", [8, 32, 64, 128])
+def test_topk_density_sweep_sizes(ops, k):
+    """Config-5 neighbour counts (register slots 1, 1, 2, 4 per lane) against torch.topk."""
+    from oracle import macbf_oracle as O
+    s, _ = O.synthetic_swarm(1, 1500, seed=200 + k)
+    idx = ops.neighbor_topk(s.cuda(), k)[0].cpu().numpy()
+    ref = O.neighbor_indices(s[0], k).numpy()
+    dec = O.decidable_rows(s[0], k).numpy()
+    assert np.array_equal(idx[dec], ref[dec])
+    assert dec.mean() > 0.99
+    # undecidable rows: same neighbour SET up to the tied candidates (Appendix B)
+    for r in np.where(~dec)[0]:
+        assert len(set(idx[r]) ^ set(ref[r])) <= 2
+
+
+def test_ties_break_by_index(ops):
+    """Exact duplicates: lexicographic (key, index) order."""
+    s = torch.zeros(1, 40, 4)
+    s[0, :, 0] = torch.arange(40) // 4  # groups of 4 coincident agents along x, spacing 1
+    idx = ops.neighbor_topk(s.cuda(), 4)[0].cpu().numpy()
+    for i in range(40):
+        base = (i // 4) * 4
+        assert list(idx[i]) == [base, base + 1, base + 2, base + 3]
+
+
+def test_c2_shape_against_oracle_sample(ops):
+    """BASELINE config 2 (1024 agents x 64 envs): full fused step; 2 envs checked against the oracle."""
+    from oracle import macbf_oracle as O
+    B, N = 64, 1024
+    s, g = O.synthetic_swarm(B, N, seed=1234 + 2000)
+    p_cbf, p_ctrl = O.init_params(5)
+    cf, tf = dev(O.flatten_params(p_cbf, O.CBF_KEYS).numpy()), dev(O.flatten_params(p_ctrl, O.CTRL_KEYS).numpy())
+    buf = ops.StepBuffers(B, N, 0, 12, "cuda")
+    ops.step_forward(s.cuda(), g.cuda(), cf, tf, buf)
+    torch.cuda.synchronize()
+    for b in (0, 63):
+        out = O.full_step(p_cbf, p_ctrl, s[b], g[b])
+        assert np.array_equal(buf.idx[b].cpu().numpy(), O.neighbor_indices(s[b], 12).numpy())
+        assert_close(buf.u[b].cpu().numpy(), out["u"].numpy(), RTOL, "u")
+        assert_close(buf.h[b].cpu().numpy(), out["h"][:, 0, :].numpy(), RTOL, "h")
+        assert np.array_equal(buf.ttc_mask[b].cpu().numpy().astype(bool), out["ttc_mask"][:, :, 0].numpy())
+    # size-independent properties over the whole batch
+    idx = buf.idx.cpu().numpy()
+    assert (idx[:, :, 0] == np.arange(N)[None, :]).all()          # slot 0 is the agent itself
+    assert idx.min() >= 0 and idx.max() < N
+    srt = np.sort(idx, axis=2)
+    assert (srt[:, :, 1:] != srt[:, :, :-1]).all()                 # no duplicate neighbours
+    sc = buf.scalars.cpu().numpy()
+    assert np.isfinite(sc).all() and (sc[:, 10] + sc[:, 11] == N * 12).all()
