@@ -217,6 +217,22 @@ ctrl_node_kernel(const float* __restrict__ states, const float* __restrict__ goa
   }
 }
 
+// edge kernel only (REPAIRED): rebuilds the pooled features for the backward pass
+int controller_forward_pool_only(const float* states, const float* obstacles, const int32_t* idx,
+                                 const float* params, int B, int N, int M, int K, double obs_radius, float* pool,
+                                 cudaStream_t st) {
+  const long long agents = (long long)B * N;
+  const int TA = max(1, ce_smem::R / K);
+  const long long ntiles = (agents + TA - 1) / TA;
+  const int grid = (int)(ntiles < NUM_SMS ? ntiles : (long long)NUM_SMS);
+  const size_t smem = ce_smem::total * sizeof(float);
+  MACBF_CHECK_CUDA(cudaFuncSetAttribute(ctrl_edge_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  ctrl_edge_kernel<false><<<grid, MLP_THREADS, smem, st>>>(states, obstacles, idx, params, N, M, K, agents, TA,
+                                                          (float)obs_radius, pool);
+  MACBF_CHECK_LAUNCH("ctrl_edge_kernel");
+  return 0;
+}
+
 int controller_forward(const float* states, const float* goals, const float* obstacles, const int32_t* idx,
                        const float* params, int B, int N, int M, int K, int semantics, double obs_radius,
                        double dt, float* pool, float* u, float* s_next, cudaStream_t st) {

@@ -122,17 +122,18 @@ __device__ __forceinline__ void layer_kn(const float* __restrict__ Dout, const f
   }
 }
 
-// Weight-gradient GEMM: dW[n][k] += sum_r D[n][r] * A[k][r]  (n < NOUT, k < KIN), accumulated
-// into a shared-memory buffer dW[n * WS + k]; also db[n] += sum_r D[n][r].
-// Rows beyond `rows_valid` must hold D == 0 (they do: padded rows carry zero gradient).
-template <int R, int KIN, int NOUT, int RS_D, int RS_A, int WS>
+// Weight-gradient GEMM: dW[n][k] += sum_r D[n][r] * A[k][r]  (n < NOUT, k < KVALID <= KIN), both
+// operands channel-major in shared memory.  dW is the CTA's private slice of the global partial
+// buffer in the flat state_dict layout (row stride WS_OUT = true fan-in): every element is
+// owned by exactly one thread, so the read-modify-write needs no atomics and the summation
+// order is fixed.  Also db[n] += sum_r D[n][r].  Padded rows must hold D == 0 (they do).
+template <int R, int KIN, int NOUT, int RS_D, int RS_A, int WS_OUT, int KVALID>
 __device__ __forceinline__ void grad_w(const float* __restrict__ D, const float* __restrict__ A,
                                        float* __restrict__ dW, float* __restrict__ db) {
-  // thread tile: NT n's x KT k's with NT*KT*256 = NOUT*KIN
   constexpr int KB = 16;             // threads along k
   constexpr int NB = 16;             // threads along n
-  constexpr int KT = KIN / KB;       // 4 (KIN=64) or 8 (KIN=128)
-  constexpr int NT = NOUT / NB;      // 8 or 4
+  constexpr int KT = KIN / KB;
+  constexpr int NT = NOUT / NB;
   static_assert(KIN % KB == 0 && NOUT % NB == 0, "shape");
   const int kb = threadIdx.x & 15, nb = threadIdx.x >> 4;
   float acc[NT][KT];
@@ -152,7 +153,7 @@ __device__ __forceinline__ void grad_w(const float* __restrict__ D, const float*
     for (int i = 0; i < KT; ++i) a[i] = *reinterpret_cast<const float4*>(A + (kb + KB * i) * RS_A + r);
 #pragma unroll
     for (int j = 0; j < NT; ++j) {
-      if (kb == 0) bsum[j] += (d[j].x + d[j].y) + (d[j].z + d[j].w);
+      bsum[j] += (d[j].x + d[j].y) + (d[j].z + d[j].w);
 #pragma unroll
       for (int i = 0; i < KT; ++i) {
         acc[j][i] = fmaf(d[j].x, a[i].x, acc[j][i]);
@@ -166,7 +167,10 @@ __device__ __forceinline__ void grad_w(const float* __restrict__ D, const float*
   for (int j = 0; j < NT; ++j) {
     const int n = nb + NB * j;
 #pragma unroll
-    for (int i = 0; i < KT; ++i) dW[n * WS + kb + KB * i] += acc[j][i];
+    for (int i = 0; i < KT; ++i) {
+      const int k = kb + KB * i;
+      if (k < KVALID) dW[n * WS_OUT + k] += acc[j][i];
+    }
     if (kb == 0) db[n] += bsum[j];
   }
 }

@@ -1,0 +1,96 @@
+"""One fused training step of the safety-certificate path on a batch of independent envs.
+
+forward  : macbf_step_forward (graph(S) -> u, S' -> graph(S') -> h, h' -> TTC mask -> scalars)
+objective: mean over envs of the per-env reference loss
+           10 * (2 l_dang + l_safe + 2 l_dang' + l_safe' + 0.01 l_act)        (train.py:93,98)
+backward : loss seeds -> CBF backward on (S', graph') and on (S, graph) -> controller backward with
+           d/du = d l_act/du + dt * d/dS'[v]  (S' = S + [v,u] dt couples the CBF and controller
+           gradients, core.py:133-137)
+sync     : one all-reduce (sum) of the flat 51,141-float gradient buffer across ranks, after
+           which every rank holds the gradient of the global env-mean.
+All arithmetic runs in libmacbf_b200.so; torch provides buffers, the stream and NCCL.
+"""
+from typing import Optional
+
+import torch
+
+from . import lib as _lib
+from . import ops
+
+# d(objective)/d(scalars) for one env, before the 1/B_global env mean (train.py:93: weights 2,1,2,1,0.01; x10)
+_LOSS_WEIGHTS = {0: 20.0, 1: 10.0, 4: 20.0, 5: 10.0, 8: 0.1}
+
+
+class TrainStep:
+    def __init__(self, B: int, N: int, M: int, top_k: int, device, world_size: int = 1, process_group=None):
+        self.B, self.N, self.M, self.top_k = B, N, M, top_k
+        self.world_size = world_size
+        self.group = process_group
+        self.device = torch.device(device)
+        self.buf = ops.StepBuffers(B, N, M, top_k, device)
+        K = self.buf.K
+        L = _lib.load()
+        f32 = torch.float32
+        dev = device
+        # one flat gradient buffer [cbf | ctrl] so a single collective moves everything
+        self.grad = torch.zeros((ops.CBF_PARAMS + ops.CTRL_PARAMS,), dtype=f32, device=dev)
+        self.grad_cbf = self.grad[:ops.CBF_PARAMS]
+        self.grad_ctrl = self.grad[ops.CBF_PARAMS:]
+        self.gh = torch.empty((B, N, K), dtype=f32, device=dev)
+        self.ghn = torch.empty((B, N, K), dtype=f32, device=dev)
+        self.gu = torch.empty((B, N, 2), dtype=f32, device=dev)
+        self.gs_next = torch.zeros((B, N, 4), dtype=f32, device=dev)
+        gsc = torch.zeros((B, ops.NUM_SCALARS), dtype=f32)
+        for c, w in _LOSS_WEIGHTS.items():
+            gsc[:, c] = w / (B * world_size)
+        self.grad_scalars = gsc.to(dev)
+        nb = max(L.macbf_cbf_backward_scratch_bytes(B, N, K), L.macbf_controller_backward_scratch_bytes(B, N, K), 256)
+        self.scratch = torch.empty((nb,), dtype=torch.uint8, device=dev)
+
+    def forward_backward(self, states, goals, cbf_params, ctrl_params, obstacles: Optional[torch.Tensor] = None,
+                         all_reduce: bool = True):
+        """Returns (scalars [B,12], grad [51141] = [grad_cbf | grad_ctrl] of the env-mean objective)."""
+        L = _lib.load()
+        b = self.buf
+        B, N, M, K = self.B, self.N, self.M, b.K
+        ops.step_forward(states, goals, cbf_params, ctrl_params, b, obstacles)
+        st = torch.cuda.current_stream().cuda_stream
+        p = ops._p
+        obs = obstacles if (obstacles is not None and M > 0) else None
+        _lib.check(L.macbf_loss_backward(p(states), p(goals), p(b.h), p(b.h_next), p(b.u), p(b.ttc_mask), p(b.scalars),
+                                         p(self.grad_scalars), B, N, K, ops.TIME_STEP, ops.ALPHA_CBF, p(self.gh),
+                                         p(self.ghn), p(self.gu), st), "macbf_loss_backward")
+        self.grad.zero_()
+        self.gs_next.zero_()
+        # h' = CBF(S') on its own graph: parameter gradient + d/dS'
+        _lib.check(L.macbf_cbf_backward(p(b.s_next), p(obs), p(b.idx_next), p(cbf_params), p(self.ghn), B, N, M, K,
+                                        ops.DIST_MIN_THRES, ops.OBS_RADIUS, p(self.grad_cbf), p(self.gs_next),
+                                        p(self.scratch), self.scratch.numel(), st), "macbf_cbf_backward(S')")
+        # h = CBF(S): S is the data of this step, only the parameter gradient is needed
+        _lib.check(L.macbf_cbf_backward(p(states), p(obs), p(b.idx), p(cbf_params), p(self.gh), B, N, M, K,
+                                        ops.DIST_MIN_THRES, ops.OBS_RADIUS, p(self.grad_cbf), None,
+                                        p(self.scratch), self.scratch.numel(), st), "macbf_cbf_backward(S)")
+        # controller: d/du from the action loss, plus dt * d/dS'[v] through the Euler step
+        _lib.check(L.macbf_controller_backward(p(states), p(goals), p(obs), p(b.idx), p(ctrl_params), p(self.gu),
+                                               p(self.gs_next), B, N, M, K, ops.OBS_RADIUS, ops.TIME_STEP,
+                                               p(self.grad_ctrl), None, None, p(self.scratch), self.scratch.numel(),
+                                               st), "macbf_controller_backward")
+        if all_reduce and self.world_size > 1:
+            import torch.distributed as dist
+            dist.all_reduce(self.grad, op=dist.ReduceOp.SUM, group=self.group)
+        return b.scalars, self.grad
+
+
+def shard_envs(n_envs: int, world_size: int, rank: int):
+    """Contiguous env shard [lo, hi) of rank `rank` (envs are independent)."""
+    base, rem = divmod(n_envs, world_size)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def env_mean_grad_scalars(n_local: int, n_global: int, device=None) -> torch.Tensor:
+    """d(objective)/d(scalars) [n_local,12] for the global env-mean objective."""
+    g = torch.zeros((n_local, ops.NUM_SCALARS), dtype=torch.float32, device=device)
+    for c, w in _LOSS_WEIGHTS.items():
+        g[:, c] = w / n_global
+    return g
