@@ -97,12 +97,14 @@ int macbf_loss_forward(const float* states, const float* goals, const float* obs
                        size_t scratch_bytes, void* stream);
 
 /* Seeds of the backward pass: given d(objective)/d(scalars) [B,12] (only entries 0,1,4,5,8 are
- * differentiable; the rest are ignored) produce dL/dh, dL/dh_next [B,N,K] and dL/du [B,N,2]
- * (any output may be NULL).  Uses ttc_mask and scalars[.,10:12] from macbf_loss_forward. */
+ * differentiable; the rest are ignored) produce dL/dh, dL/dh_next [B,N,K], dL/du [B,N,2] and the
+ * action-loss part of dL/dstates [B,N,4] (a_ref depends on the states, core.py:177-178); any
+ * output may be NULL, all are overwritten.  Uses ttc_mask and scalars[.,10:12] of the forward. */
 int macbf_loss_backward(const float* states, const float* goals, const float* h, const float* h_next,
                         const float* u, const uint8_t* ttc_mask, const float* scalars,
                         const float* grad_scalars, int B, int N, int K, double dt, double alpha,
-                        float* grad_h, float* grad_h_next, float* grad_u, void* stream);
+                        float* grad_h, float* grad_h_next, float* grad_u, float* grad_states,
+                        void* stream);
 
 /* ---- backward of A5 (autograd of cbf.py:21-45) ------------------------------------------
  * grad_params [17089] is ACCUMULATED into (caller zeroes it); grad_states [B,N,4] is

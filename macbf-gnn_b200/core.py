@@ -173,5 +173,5 @@ def loss_actions(s, g, a):
     idx = torch.zeros((sb.shape[0], sb.shape[1], k_eff), dtype=torch.int32, device=sb.device)
     idx += torch.arange(sb.shape[1], dtype=torch.int32, device=sb.device).view(1, -1, 1)
     dummy_h = torch.zeros((sb.shape[0], sb.shape[1], k_eff), dtype=torch.float32, device=sb.device)
-    scalars, _ = _F.HingeLossFunction.apply(dummy_h, None, ab.contiguous(), sb.detach(), gb.detach(), None, idx)
+    scalars, _ = _F.HingeLossFunction.apply(dummy_h, None, ab.contiguous(), sb.contiguous(), gb.detach(), None, idx)
     return scalars[:, 8].mean()

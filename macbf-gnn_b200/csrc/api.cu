@@ -27,7 +27,7 @@ size_t loss_scratch_bytes(int, int, int);
 int loss_forward(const float*, const float*, const float*, const int32_t*, const float*, const float*, const float*,
                  int, int, int, int, double, double, double, double, uint8_t*, float*, void*, size_t, cudaStream_t);
 int loss_backward(const float*, const float*, const float*, const float*, const float*, const uint8_t*, const float*,
-                  const float*, int, int, int, double, double, float*, float*, float*, cudaStream_t);
+                  const float*, int, int, int, double, double, float*, float*, float*, float*, cudaStream_t);
 size_t cbf_backward_scratch_bytes(int, int, int);
 int cbf_backward(const float*, const float*, const int32_t*, const float*, const float*, int, int, int, int, double,
                  double, float*, float*, void*, size_t, cudaStream_t);
@@ -123,14 +123,15 @@ int macbf_loss_forward(const float* states, const float* goals, const float* obs
 int macbf_loss_backward(const float* states, const float* goals, const float* h, const float* h_next, const float* u,
                         const uint8_t* ttc_mask_in, const float* scalars, const float* grad_scalars, int B, int N,
                         int K, double dt, double alpha, float* grad_h, float* grad_h_next, float* grad_u,
-                        void* stream) {
+                        float* grad_states, void* stream) {
   const char* fn = "macbf_loss_backward";
   MACBF_CHECK_ARG(B >= 1 && B <= 65535 && N >= 1 && K >= 1 && K <= MACBF_MAX_K, "%s: bad extents B=%d N=%d K=%d", fn, B, N, K);
   REQ_PTR(fn, h); REQ_PTR(fn, ttc_mask_in); REQ_PTR(fn, scalars); REQ_PTR(fn, grad_scalars);
-  MACBF_CHECK_ARG(grad_u == nullptr || u == nullptr || (states != nullptr && goals != nullptr),
-                  "%s: grad_u needs states and goals", fn);
+  MACBF_CHECK_ARG((grad_u == nullptr && grad_states == nullptr) || u == nullptr ||
+                      (states != nullptr && goals != nullptr),
+                  "%s: grad_u / grad_states need states and goals", fn);
   return loss_backward(states, goals, h, h_next, u, ttc_mask_in, scalars, grad_scalars, B, N, K, dt, alpha, grad_h,
-                       grad_h_next, grad_u, (cudaStream_t)stream);
+                       grad_h_next, grad_u, grad_states, (cudaStream_t)stream);
 }
 
 size_t macbf_cbf_backward_scratch_bytes(int B, int N, int K) { return cbf_backward_scratch_bytes(B, N, K); }

@@ -140,7 +140,7 @@ __global__ void loss_backward_kernel(const float* __restrict__ states, const flo
                                      const float* __restrict__ u, const uint8_t* __restrict__ mask,
                                      const float* __restrict__ scalars, const float* __restrict__ gs, int N,
                                      int K, float dt_alpha, float* __restrict__ gh, float* __restrict__ ghn,
-                                     float* __restrict__ gu) {
+                                     float* __restrict__ gu, float* __restrict__ gst) {
   const int b = blockIdx.y;
   const long long rows_env = (long long)N * K;
   const float* sc = scalars + (size_t)b * MACBF_NUM_SCALARS;
@@ -167,10 +167,11 @@ __global__ void loss_backward_kernel(const float* __restrict__ states, const flo
     }
     if (gh != nullptr) gh[e] = dh;
   }
-  if (gu != nullptr) {
+  if (gu != nullptr || gst != nullptr) {
     const float s3 = 1.7320508075688772f;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += stride) {
       float2 o = make_float2(0.f, 0.f);
+      float4 os = make_float4(0.f, 0.f, 0.f, 0.f);
       if (u != nullptr) {
         const float4 s = __ldg(reinterpret_cast<const float4*>(states) + (size_t)b * N + i);
         const float2 gl = __ldg(reinterpret_cast<const float2*>(goals) + (size_t)b * N + i);
@@ -179,8 +180,11 @@ __global__ void loss_backward_kernel(const float* __restrict__ states, const flo
         const float diff = (a.x * a.x + a.y * a.y) - (rx * rx + ry * ry);
         const float sg = diff > 0.f ? 1.f : (diff < 0.f ? -1.f : 0.f);
         o = make_float2(g8 * sg * 2.f * a.x, g8 * sg * 2.f * a.y);
+        // d|a_ref|^2/dp = -2 a_ref, d/dv = -2 sqrt(3) a_ref; the loss carries -|a_ref|^2
+        os = make_float4(g8 * sg * 2.f * rx, g8 * sg * 2.f * ry, g8 * sg * 2.f * s3 * rx, g8 * sg * 2.f * s3 * ry);
       }
-      reinterpret_cast<float2*>(gu)[(size_t)b * N + i] = o;
+      if (gu != nullptr) reinterpret_cast<float2*>(gu)[(size_t)b * N + i] = o;
+      if (gst != nullptr) reinterpret_cast<float4*>(gst)[(size_t)b * N + i] = os;
     }
   }
 }
@@ -221,13 +225,13 @@ int loss_forward(const float* states, const float* goals, const float* obstacles
 
 int loss_backward(const float* states, const float* goals, const float* h, const float* h_next, const float* u,
                   const uint8_t* mask, const float* scalars, const float* grad_scalars, int B, int N, int K,
-                  double dt, double alpha, float* gh, float* ghn, float* gu, cudaStream_t st) {
+                  double dt, double alpha, float* gh, float* ghn, float* gu, float* gst, cudaStream_t st) {
   const long long rows_env = (long long)N * K;
   int gx = (int)(((rows_env + 255) / 256) < 4ll * NUM_SMS ? ((rows_env + 255) / 256) : 4ll * NUM_SMS);
   if (gx < 1) gx = 1;
   dim3 grid(gx, B);
   loss_backward_kernel<<<grid, 256, 0, st>>>(states, goals, h, h_next, (goals != nullptr) ? u : nullptr, mask,
-                                            scalars, grad_scalars, N, K, (float)(dt * alpha), gh, ghn, gu);
+                                            scalars, grad_scalars, N, K, (float)(dt * alpha), gh, ghn, gu, gst);
   MACBF_CHECK_LAUNCH("loss_backward_kernel");
   return 0;
 }

@@ -122,9 +122,10 @@ class HingeLossFunction(torch.autograd.Function):
     def backward(ctx, grad_scalars, _grad_mask):
         h, h_next, u, states, goals, mask, scalars = ctx.saved_tensors
         has_next, has_u, has_goals = ctx.flags
-        gh, ghn, gu = ops.loss_backward(states, goals if has_goals else None, h, h_next if has_next else None,
-                                        u if has_u else None, mask, scalars, grad_scalars.contiguous(),
-                                        want_h=ctx.needs_input_grad[0],
-                                        want_h_next=has_next and ctx.needs_input_grad[1],
-                                        want_u=has_u and ctx.needs_input_grad[2])
-        return gh, ghn, gu, None, None, None, None
+        gh, ghn, gu, gst = ops.loss_backward(states, goals if has_goals else None, h, h_next if has_next else None,
+                                             u if has_u else None, mask, scalars, grad_scalars.contiguous(),
+                                             want_h=ctx.needs_input_grad[0],
+                                             want_h_next=has_next and ctx.needs_input_grad[1],
+                                             want_u=has_u and ctx.needs_input_grad[2],
+                                             want_states=has_u and ctx.needs_input_grad[3])
+        return gh, ghn, gu, gst, None, None, None

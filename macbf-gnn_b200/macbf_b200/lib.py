@@ -30,7 +30,7 @@ SIGNATURES = {
     "macbf_loss_forward": (I, [c_f32p, c_f32p, c_f32p, c_i32p, c_f32p, c_f32p, c_f32p, I, I, I, I, D, D, D, D, c_u8p,
                                c_f32p, c_void, SZ, c_void]),
     "macbf_loss_backward": (I, [c_f32p, c_f32p, c_f32p, c_f32p, c_f32p, c_u8p, c_f32p, c_f32p, I, I, I, D, D, c_f32p,
-                                c_f32p, c_f32p, c_void]),
+                                c_f32p, c_f32p, c_f32p, c_void]),
     "macbf_cbf_backward_scratch_bytes": (SZ, [I, I, I]),
     "macbf_cbf_backward": (I, [c_f32p, c_f32p, c_i32p, c_f32p, c_f32p, I, I, I, I, D, D, c_f32p, c_f32p, c_void, SZ,
                                c_void]),

@@ -142,7 +142,7 @@ def loss_forward(states, idx, h, h_next=None, u=None, goals=None, obstacles=None
 
 
 def loss_backward(states, goals, h, h_next, u, mask, scalars, grad_scalars, dt=TIME_STEP, alpha=ALPHA_CBF,
-                  want_h=True, want_h_next=True, want_u=True):
+                  want_h=True, want_h_next=True, want_u=True, want_states=False):
     """Seeds dL/dh, dL/dh_next [B,N,K] and dL/du [B,N,2] from dL/dscalars [B,12]."""
     _need_cuda(states, goals, h, h_next, u, mask, scalars, grad_scalars)
     states, goals, h, h_next, u, mask, scalars, grad_scalars = map(
@@ -152,11 +152,12 @@ def loss_backward(states, goals, h, h_next, u, mask, scalars, grad_scalars, dt=T
     gh = torch.empty_like(h) if want_h else None
     ghn = torch.empty_like(h) if (want_h_next and h_next is not None) else None
     gu = torch.empty((B, N, 2), dtype=torch.float32, device=dev) if (want_u and u is not None) else None
+    gst = torch.empty((B, N, 4), dtype=torch.float32, device=dev) if (want_states and u is not None) else None
     L = _lib.load()
     _lib.check(L.macbf_loss_backward(_p(states), _p(goals), _p(h), _p(h_next), _p(u), _p(mask), _p(scalars),
-                                     _p(grad_scalars), B, N, K, dt, alpha, _p(gh), _p(ghn), _p(gu), _stream()),
-               "macbf_loss_backward")
-    return gh, ghn, gu
+                                     _p(grad_scalars), B, N, K, dt, alpha, _p(gh), _p(ghn), _p(gu), _p(gst),
+                                     _stream()), "macbf_loss_backward")
+    return gh, ghn, gu, gst
 
 
 def cbf_backward(states, idx, cbf_params, grad_h, obstacles=None, dist_min_thres=DIST_MIN_THRES,

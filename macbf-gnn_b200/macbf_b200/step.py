@@ -59,7 +59,7 @@ class TrainStep:
         obs = obstacles if (obstacles is not None and M > 0) else None
         _lib.check(L.macbf_loss_backward(p(states), p(goals), p(b.h), p(b.h_next), p(b.u), p(b.ttc_mask), p(b.scalars),
                                          p(self.grad_scalars), B, N, K, ops.TIME_STEP, ops.ALPHA_CBF, p(self.gh),
-                                         p(self.ghn), p(self.gu), st), "macbf_loss_backward")
+                                         p(self.ghn), p(self.gu), None, st), "macbf_loss_backward")
         self.grad.zero_()
         self.gs_next.zero_()
         # h' = CBF(S') on its own graph: parameter gradient + d/dS'
