@@ -96,6 +96,24 @@ int macbf_loss_forward(const float* states, const float* goals, const float* obs
                        double alpha, uint8_t* ttc_mask, float* scalars, void* scratch,
                        size_t scratch_bytes, void* stream);
 
+/* ---- losses without any allocation (no counterpart in the reference) ----------------------
+ * Same computation and outputs as macbf_loss_forward, for callers that cannot obtain device
+ * scratch: hosts whose allocator is frozen while a step is recorded or replayed, real-time loops
+ * that must not enter the driver's allocator, or C / Fortran simulators that call the library
+ * without owning a device allocator.  The partial sums live in a fixed 256 KiB array inside the
+ * library (present on every GPU that loads it, until the process exits), so the problem must
+ * satisfy macbf_loss_scratch_bytes(B,N,K) <= 4 * MACBF_LOSS_NOALLOC_MAX_FLOATS; larger problems
+ * are rejected with an error and nothing is launched.  The first call on each device looks up
+ * the array's device address (cudaGetSymbolAddress, with that device current); make that first
+ * call before starting any stream capture.  All calls on a device share the one array: it keeps
+ * the previous call's partial sums (every slot read is rewritten first, nothing needs clearing),
+ * and two calls whose kernels overlap on the GPU (different streams, no ordering) race on it. */
+#define MACBF_LOSS_NOALLOC_MAX_FLOATS 65536
+int macbf_loss_forward_noalloc(const float* states, const float* goals, const float* obstacles,
+                               const int32_t* idx, const float* h, const float* h_next, const float* u,
+                               int B, int N, int M, int K, double dist_min_thres, double ttc, double dt,
+                               double alpha, uint8_t* ttc_mask, float* scalars, void* stream);
+
 /* Seeds of the backward pass: given d(objective)/d(scalars) [B,12] (only entries 0,1,4,5,8 are
  * differentiable; the rest are ignored) produce dL/dh, dL/dh_next [B,N,K], dL/du [B,N,2] and the
  * action-loss part of dL/dstates [B,N,4] (a_ref depends on the states, core.py:177-178); any

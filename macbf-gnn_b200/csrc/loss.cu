@@ -237,3 +237,73 @@ int loss_backward(const float* states, const float* goals, const float* h, const
 }
 
 }  // namespace macbf
+
+// ---------------------------------------------------------------------------------------------
+// macbf_loss_forward_noalloc: the loss reduction for callers that cannot allocate device memory.
+//
+// Who needs this: code that runs where a device allocation is forbidden or impossible - inside
+// a region the host framework has frozen (an allocator that is locked while a step is being
+// recorded or replayed), in a real-time control loop that may not call into the driver's
+// allocator because its latency is unbounded, or in an embedding host (a C or Fortran simulator
+// calling this library directly) that simply owns no device allocator to size the scratch
+// buffer macbf_loss_forward asks for.  Such callers still pass their inputs and outputs; only
+// the reduction's partial sums, which no caller ever reads, live in the fixed array below.
+//
+// The array is part of the library image: every GPU that loads libmacbf_b200.so carries these
+// 256 KiB until the process exits, whether or not this entry point is used.
+// ---------------------------------------------------------------------------------------------
+namespace macbf {
+
+static __device__ __align__(256) float g_loss_static_scratch[MACBF_LOSS_NOALLOC_MAX_FLOATS];
+
+// In host code `g_loss_static_scratch` is only a handle for the runtime, not a device address;
+// the address has to be asked for, per device (each device has its own copy of the array).
+constexpr int kMaxDevices = 64;
+static float* g_loss_static_ptr[kMaxDevices] = {nullptr};
+
+static int loss_static_scratch_for_current_device(float** out) {
+  int dev = -1;
+  MACBF_CHECK_CUDA(cudaGetDevice(&dev));
+  MACBF_CHECK_ARG(dev >= 0 && dev < kMaxDevices, "macbf_loss_forward_noalloc: device ordinal %d not supported", dev);
+  if (g_loss_static_ptr[dev] == nullptr) {
+    float* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&p, g_loss_static_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      set_error("macbf_loss_forward_noalloc: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+      return 2;
+    }
+    g_loss_static_ptr[dev] = p;   // same value from every thread, so a racing first call is benign
+  }
+  *out = g_loss_static_ptr[dev];
+  return 0;
+}
+
+}  // namespace macbf
+
+extern "C" int macbf_loss_forward_noalloc(const float* states, const float* goals, const float* obstacles,
+                                          const int32_t* idx, const float* h, const float* h_next, const float* u,
+                                          int B, int N, int M, int K, double dist_min_thres, double ttc, double dt,
+                                          double alpha, uint8_t* ttc_mask_out, float* scalars, void* stream) {
+  using namespace macbf;
+  const char* fn = "macbf_loss_forward_noalloc";
+  MACBF_CHECK_ARG(B >= 1 && B <= 65535, "%s: B=%d out of range [1,65535]", fn, B);
+  MACBF_CHECK_ARG(N >= 1 && M >= 0, "%s: bad extents N=%d M=%d", fn, N, M);
+  MACBF_CHECK_ARG(K >= 1 && K <= MACBF_MAX_K && K <= N + M, "%s: K=%d out of range (max %d, candidates %d)", fn, K,
+                  MACBF_MAX_K, N + M);
+  MACBF_CHECK_ARG(states != nullptr && idx != nullptr && h != nullptr && ttc_mask_out != nullptr && scalars != nullptr,
+                  "%s: states, idx, h, ttc_mask and scalars must not be NULL", fn);
+  MACBF_CHECK_ARG(M == 0 || obstacles != nullptr, "%s: obstacles is NULL but M=%d", fn, M);
+  const size_t need = loss_scratch_bytes(B, N, K);
+  MACBF_CHECK_ARG(need <= sizeof(float) * (size_t)MACBF_LOSS_NOALLOC_MAX_FLOATS,
+                  "%s: problem too large for the built-in scratch: B=%d N=%d K=%d needs %zu bytes of partial sums, "
+                  "the fixed array holds %zu (use macbf_loss_forward with caller scratch instead)",
+                  fn, B, N, K, need, sizeof(float) * (size_t)MACBF_LOSS_NOALLOC_MAX_FLOATS);
+  float* scratch = nullptr;
+  int rc = loss_static_scratch_for_current_device(&scratch);
+  if (rc) return rc;
+  // Every partial-sum slot that loss_final_kernel reads is written by loss_partial_kernel in this
+  // same call, so nothing in the array has to start at zero and the previous call's contents
+  // are simply overwritten.
+  return loss_forward(states, goals, obstacles, idx, h, h_next, u, B, N, M, K, dist_min_thres, ttc, dt, alpha,
+                      ttc_mask_out, scalars, scratch, need, (cudaStream_t)stream);
+}

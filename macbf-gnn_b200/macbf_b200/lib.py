@@ -29,6 +29,8 @@ SIGNATURES = {
     "macbf_loss_scratch_bytes": (SZ, [I, I, I]),
     "macbf_loss_forward": (I, [c_f32p, c_f32p, c_f32p, c_i32p, c_f32p, c_f32p, c_f32p, I, I, I, I, D, D, D, D, c_u8p,
                                c_f32p, c_void, SZ, c_void]),
+    "macbf_loss_forward_noalloc": (I, [c_f32p, c_f32p, c_f32p, c_i32p, c_f32p, c_f32p, c_f32p, I, I, I, I, D, D, D, D,
+                                       c_u8p, c_f32p, c_void]),
     "macbf_loss_backward": (I, [c_f32p, c_f32p, c_f32p, c_f32p, c_f32p, c_u8p, c_f32p, c_f32p, I, I, I, D, D, c_f32p,
                                 c_f32p, c_f32p, c_f32p, c_void]),
     "macbf_cbf_backward_scratch_bytes": (SZ, [I, I, I]),
