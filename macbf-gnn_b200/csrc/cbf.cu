@@ -3,6 +3,8 @@
 // tiles of TA = floor(128 / K) agents (TA*K <= 128 edge rows); the per-edge feature vectors and
 // all hidden activations live in shared memory only - per edge the kernel reads 4 B of idx plus
 // two (L2-resident) states and writes 4 B of h.
+#include <stdlib.h>
+
 #include "mlp_tile.cuh"
 
 namespace macbf {
@@ -118,9 +120,20 @@ cbf_forward_kernel(const float* __restrict__ states, const float* __restrict__ o
   }
 }
 
+int cbf_forward_tc(const float* states, const float* obstacles, const int32_t* idx, const float* params, int B, int N,
+                   int M, int K, double dist_min, double obs_radius, float* h, cudaStream_t st);
+
 int cbf_forward(const float* states, const float* obstacles, const int32_t* idx, const float* params,
                 int B, int N, int M, int K, int semantics, double dist_min, double obs_radius,
                 float* h, cudaStream_t st) {
+  // REPAIRED runs on the tensor cores (cbf_tc.cu).  The FP32-FFMA kernel below serves LITERAL
+  // (its feature scramble crosses rows) and, with MACBF_CBF_FFMA=1 in the environment, A/B checks.
+  static const bool force_ffma = [] {
+    const char* e = getenv("MACBF_CBF_FFMA");
+    return e != nullptr && e[0] == '1';
+  }();
+  if (semantics == MACBF_REPAIRED && !force_ffma)
+    return cbf_forward_tc(states, obstacles, idx, params, B, N, M, K, dist_min, obs_radius, h, st);
   const long long agents = (long long)B * N;
   const int TA = max(1, cbf_smem::R / K);
   const long long ntiles = (agents + TA - 1) / TA;

@@ -1,0 +1,144 @@
+// tcgen05 / TMEM primitives (inline PTX, sm_100a) used by the tensor-core edge-MLP kernels.
+//
+// Numerics: the MLPs must match fp32 within 1e-5, which single-pass TF32 cannot.
+// Every GEMM therefore runs as a 3xTF32 split: x = hi + lo with hi = x truncated to the 19 bits
+// a kind::tf32 MMA reads (sign, 8 exponent, 10 mantissa) and lo = x - hi (exact in fp32), and
+//   A*B ~= A_hi*B_hi + A_lo*B_hi + A_hi*B_lo          (lo*lo ~ 2^-22 relative, dropped)
+// accumulated in fp32 in tensor memory.
+//
+// Operand placement: A (activations, 128 rows = 128 TMEM lanes) lives in TENSOR MEMORY, written
+// by the threads that produced it with tcgen05.st (one 32-bit column per k); B (weights, N x K,
+// K-major = the torch (out,in) layout) lives in shared memory in the canonical SWIZZLE_128B
+// K-major layout: per 32-wide K block a slab of N rows x 128 B, 16-byte chunk c of row n stored
+// at chunk position c ^ (n & 7); 8-row groups are 1024 B apart (SBO).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace macbf {
+namespace tc {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// ---- TMEM allocation (one warp; power-of-two columns >= 32) --------------------------------
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols));
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols));
+}
+__device__ __forceinline__ void fence_before_sync() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_after_sync() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// ---- mbarrier -----------------------------------------------------------------------------
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred P1;\n\t"
+      "WAIT_LOOP:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
+      "@P1 bra DONE;\n\t"
+      "bra WAIT_LOOP;\n\t"
+      "DONE:\n\t"
+      "}" ::"r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+}
+// all previously issued tcgen05.mma of this thread arrive on `bar` when they complete
+__device__ __forceinline__ void mma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+
+// ---- descriptors ----------------------------------------------------------------------------
+// K-major, SWIZZLE_128B shared-memory operand; `addr` = byte address of the first row at the
+// wanted k offset (slab base 1024-B aligned; k advances by adding bytes inside the 128-B row).
+__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((addr >> 4) & 0x3FFF);   // start address, 16-B units
+  d |= (uint64_t)1 << 16;                  // leading byte offset (unused for swizzled K-major)
+  d |= (uint64_t)(1024 >> 4) << 32;        // stride byte offset: 8 rows x 128 B
+  d |= (uint64_t)1 << 46;                  // descriptor version (Blackwell)
+  d |= (uint64_t)2 << 61;                  // layout: SWIZZLE_128B
+  return d;
+}
+// kind::tf32, fp32 accumulate, A and B K-major, M x N
+__host__ __device__ constexpr uint32_t idesc_tf32(int M, int N) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// D[tmem] (+)= A[tmem] * B[smem]^T   (issued by ONE thread)
+__device__ __forceinline__ void mma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
+                                            uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t"
+      "}\n" ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+// ---- TMEM <-> registers: 32 lanes x 32 bit, N consecutive columns per thread -----------------
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const float* v) {
+  const uint32_t* r = reinterpret_cast<const uint32_t*>(v);
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+
+// ---- 3xTF32 split ---------------------------------------------------------------------------
+// Round-to-nearest split (cvt.rna.tf32): |lo| <= 2^-11 |x| with random sign, so the dropped
+// lo*lo terms are ~2^-22 and average out; a truncating split (x & 0xFFFFE000) leaves one-sided
+// 2^-20 errors that add up coherently (measured 2e-6 vs 3e-7 scale-relative on a K=128 GEMM).
+// The result has its 13 low mantissa bits clear, so the tensor core reads it exactly.
+__device__ __forceinline__ float tf32_hi(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+// split x into (hi, lo), both exactly representable in tf32
+__device__ __forceinline__ void tf32_split(float x, float& hi, float& lo) {
+  hi = tf32_hi(x);
+  lo = tf32_hi(x - hi);
+}
+
+// Fill one SWIZZLE_128B K-major operand pair (hi, lo) from a torch-layout weight matrix
+// W[n * ld + k], n < N, k < K (K % 32 == 0): slab kb holds k in [32 kb, 32 kb + 32).
+template <int N, int K>
+__device__ __forceinline__ void fill_weight_sw128(const float* __restrict__ W, int ld, float* __restrict__ hi,
+                                                  float* __restrict__ lo) {
+  constexpr int CHUNKS = N * (K / 4);
+  for (int t = threadIdx.x; t < CHUNKS; t += blockDim.x) {
+    const int n = t / (K / 4), k4 = t % (K / 4);     // 16-byte chunk k4 of row n
+    const int kb = k4 >> 3, c = k4 & 7;
+    float w[4], h[4], l[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      w[q] = __ldg(W + (size_t)n * ld + 4 * k4 + q);
+      tf32_split(w[q], h[q], l[q]);
+    }
+    const int off = kb * (N * 32) + n * 32 + ((c ^ (n & 7)) << 2);   // in floats
+    *reinterpret_cast<float4*>(hi + off) = make_float4(h[0], h[1], h[2], h[3]);
+    *reinterpret_cast<float4*>(lo + off) = make_float4(l[0], l[1], l[2], l[3]);
+  }
+}
+
+}  // namespace tc
+}  // namespace macbf
