@@ -88,6 +88,30 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
 
   const long long ntiles = (agents_total + TA - 1) / TA;
   uint32_t parity = 0;
+  // The edge endpoints of the NEXT tile are fetched while the tensor core works on this one:
+  // idx and s_i right after layer 2 is issued, s_j (which needs idx) after layer 3 is issued.
+  int pf_j = 0, pf_b = 0, pf_i = 0;
+  bool pf_valid = false;
+  float4 pf_si = make_float4(0.f, 0.f, 0.f, 0.f), pf_sj = pf_si;
+  auto prefetch_ij = [&](long long t) {
+    pf_valid = false;
+    if (t < ntiles) {
+      const long long a0n = t * TA;
+      const int rowsn = (int)min((long long)TA, agents_total - a0n) * K;
+      if (r < rowsn) {
+        const long long ga = a0n + r / K;
+        pf_b = (int)(ga / N); pf_i = (int)(ga % N);
+        pf_j = __ldg(idx + a0n * K + r);
+        pf_si = __ldg(reinterpret_cast<const float4*>(states) + ga);
+        pf_valid = true;
+      }
+    }
+  };
+  auto prefetch_sj = [&]() {
+    if (pf_valid) pf_sj = load_candidate(states, obstacles, pf_b, pf_j, N, M);
+  };
+  prefetch_ij(blockIdx.x);
+  prefetch_sj();
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, parity ^= 1) {
     const long long a0 = tile * TA;
     const int na = (int)min((long long)TA, agents_total - a0);
@@ -97,12 +121,7 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
       float f[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
       float mk = 0.f;
       if (r < rows) {
-        const long long ga = a0 + r / K;
-        const int b = (int)(ga / N), i = (int)(ga % N);
-        const int j = __ldg(idx + a0 * K + r);
-        const float4 si = __ldg(reinterpret_cast<const float4*>(states) + ga);
-        const float4 sj = load_candidate(states, obstacles, b, j, N, M);
-        const EdgeGeom g = edge_geom(si, sj, i, j);
+        const EdgeGeom g = edge_geom(pf_si, pf_sj, pf_i, pf_j);
         const float d = cbf_dist(g.dx, g.dy);
         f[0] = g.dx; f[1] = g.dy; f[2] = g.dvx; f[3] = g.dvy; f[4] = g.eye; f[5] = xsub(d, dist_min);
         mk = (d <= obs_radius) ? 1.f : 0.f;
@@ -142,6 +161,7 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
       }
       mma_commit(&bar_d2);
     }
+    prefetch_ij(tile + gridDim.x);
     mbar_wait(&bar_d2, parity);
     fence_after_sync();
     // ---- bias + ReLU + split on this thread's 32 columns of D2 -> A3 ----
@@ -182,6 +202,7 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
       }
       mma_commit(&bar_d3);
     }
+    prefetch_sj();
     mbar_wait(&bar_d3, parity);
     fence_after_sync();
     // ---- bias + ReLU, 64 -> 1 (this thread: 16 of the 64 channels), * mask (cbf.py:43) ----

@@ -4,6 +4,8 @@
 //   kernel B (agents): [pool, p-g, v] (132) -> 64 -> 128 -> 64 -> 4, gains 2*sigmoid+0.2, action,
 //                      s' = s + [v, u] * dt.
 // FP32 FFMA path; parameters resident in shared memory of persistent CTAs.
+#include <stdlib.h>
+
 #include "mlp_tile.cuh"
 
 namespace macbf {
@@ -217,10 +219,24 @@ ctrl_node_kernel(const float* __restrict__ states, const float* __restrict__ goa
   }
 }
 
+int ctrl_edge_tc(const float* states, const float* obstacles, const int32_t* idx, const float* params, int B, int N,
+                 int M, int K, double obs_radius, float* pool, cudaStream_t st);
+
+// REPAIRED edge net runs on the tensor cores (ctrl_tc.cu); MACBF_CTRL_FFMA=1 forces the FP32-FFMA
+// kernel for A/B checks.  LITERAL always uses the FFMA kernel (row-crossing feature scramble).
+static bool ctrl_force_ffma() {
+  static const bool v = [] {
+    const char* e = getenv("MACBF_CTRL_FFMA");
+    return e != nullptr && e[0] == '1';
+  }();
+  return v;
+}
+
 // edge kernel only (REPAIRED): rebuilds the pooled features for the backward pass
 int controller_forward_pool_only(const float* states, const float* obstacles, const int32_t* idx,
                                  const float* params, int B, int N, int M, int K, double obs_radius, float* pool,
                                  cudaStream_t st) {
+  if (!ctrl_force_ffma()) return ctrl_edge_tc(states, obstacles, idx, params, B, N, M, K, obs_radius, pool, st);
   const long long agents = (long long)B * N;
   const int TA = max(1, ce_smem::R / K);
   const long long ntiles = (agents + TA - 1) / TA;
@@ -237,7 +253,10 @@ int controller_forward(const float* states, const float* goals, const float* obs
                        const float* params, int B, int N, int M, int K, int semantics, double obs_radius,
                        double dt, float* pool, float* u, float* s_next, cudaStream_t st) {
   const long long agents = (long long)B * N;
-  {
+  if (semantics == MACBF_REPAIRED && !ctrl_force_ffma()) {
+    int rc = ctrl_edge_tc(states, obstacles, idx, params, B, N, M, K, obs_radius, pool, st);
+    if (rc) return rc;
+  } else {
     const int TA = max(1, ce_smem::R / K);
     const long long ntiles = (agents + TA - 1) / TA;
     const int grid = (int)(ntiles < NUM_SMS ? ntiles : (long long)NUM_SMS);

@@ -108,10 +108,10 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const float* v) {
 // lo*lo terms are ~2^-22 and average out; a truncating split (x & 0xFFFFE000) leaves one-sided
 // 2^-20 errors that add up coherently (measured 2e-6 vs 3e-7 scale-relative on a K=128 GEMM).
 // The result has its 13 low mantissa bits clear, so the tensor core reads it exactly.
+// cvt.rna.tf32.f32 expands to ~5 instructions (NaN/Inf handling); for finite inputs the same
+// rounding (nearest, ties away from zero) is an integer add of half an ulp and a mask.
 __device__ __forceinline__ float tf32_hi(float x) {
-  uint32_t r;
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-  return __uint_as_float(r);
+  return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);
 }
 // split x into (hi, lo), both exactly representable in tf32
 __device__ __forceinline__ void tf32_split(float x, float& hi, float& lo) {
