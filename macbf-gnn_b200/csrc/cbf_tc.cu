@@ -1,29 +1,38 @@
 // K2 (tensor-core path) - fused CBF head (cbf.py:21-45, REPAIRED) on tcgen05 / TMEM.
 //
-// One persistent CTA per SM, 16 warps.  A tile is 128 edge rows (floor(128/K) agents); row r is
-// TMEM lane r.  Warp w works on lanes 32*(w%4).. (the only lanes tcgen05.ld/st lets it touch)
-// and on column group w/4 of whatever is being produced.
+// One persistent CTA per SM: 16 worker warps + 1 MMA-issue warp, decoupled by mbarriers so the
+// tensor core never waits for the CUDA cores in steady state.  A tile is 128 edge rows
+// (floor(128/K) agents); row r is TMEM lane r.  Worker warp w owns lanes 32*(w%4).. (the lanes
+// tcgen05.ld/st lets it touch) and column group w/4 of whatever is being produced.
 //
-//   features + layer 1 (6->64, FP32 FFMA)  -> split hi/lo -> tcgen05.st  A2 [128 x 64] (TMEM)
-//   layer 2: D2[128x128] = A2 * W2^T       3xTF32 tcgen05.mma, A from TMEM, B (weights) from smem
-//   bias+ReLU+split on D2 (tcgen05.ld)     -> tcgen05.st  A3 [128 x 128] (TMEM)
-//   layer 3: D3[128x64]  = A3 * W3^T       3xTF32 tcgen05.mma
-//   bias+ReLU, 64->1 dot, * mask           -> h (global)
+//   workers   features + layer 1 (6->64, FFMA) -> tf32 hi/lo -> tcgen05.st        A2   (TMEM)
+//   MMA warp  layer 2: D2[128x128] = A2 * W2^T in two 64-column chunks, 3xTF32     D2   (TMEM)
+//   workers   per chunk: tcgen05.ld, bias + ReLU, hi/lo; hi overwrites D2 in place A3   (TMEM)
+//   MMA warp  layer 3: per 64-wide K chunk, cross terms -> D3s, hi*hi -> D3        D3   (TMEM)
+//   workers   (D3 + D3s) bias + ReLU, 64 -> 1 dot, * mask                          h    (global)
 //
-// Hidden activations never leave the SM: they go registers -> TMEM -> tensor core -> TMEM ->
-// registers.  Shared memory holds only the weights (hi and lo tf32 halves of W2, W3 in the
-// canonical SWIZZLE_128B K-major layout, 128 KB) and a few hundred bytes of vectors.
-// TMEM columns: [0,64) A2_hi / later D3, [64,128) A2_lo, [128,256) D2, [256,384) A3_hi,
-// [384,512) A3_lo.
+// While the tensor core runs layer 3 of tile i the workers already build A2 of tile i+1, and
+// layer 2 of tile i+1 runs while they finish tile i, so the MMA stream is back to back.
+// Hidden activations never leave the SM (registers -> TMEM -> tensor core -> TMEM -> registers);
+// shared memory holds the weights only: hi and lo tf32 halves of W2 and W3 in the canonical
+// SWIZZLE_128B K-major layout (128 KB) plus small vectors.
+//
+// 3xTF32 ordering: the tensor core's fp32 accumulate is not round-to-nearest, so the small cross
+// terms (lo*hi, hi*lo) are accumulated where the running sum is small: first within a layer-2
+// chunk, and into their own accumulator D3s for the K-chunked layer 3 (tools/tc_probe.cu).
+//
+// TMEM columns: [0,64) A2_hi  [64,128) A2_lo  [128,256) D2 -> A3_hi (in place)
+//               [256,384) A3_lo  [384,448) D3  [448,512) D3s
 #include "common.cuh"
 #include "tc_common.cuh"
 
 namespace macbf {
 
 namespace cbftc {
-constexpr int THREADS = 512;
+constexpr int WORKERS = 512;
+constexpr int THREADS = WORKERS + 32;
 constexpr int R = 128;
-constexpr uint32_t C_A2HI = 0, C_A2LO = 64, C_D3 = 0, C_D2 = 128, C_A3HI = 256, C_A3LO = 384;
+constexpr uint32_t C_A2HI = 0, C_A2LO = 64, C_Y = 128, C_A3LO = 256, C_D3 = 384, C_D3S = 448;
 // dynamic shared memory (floats, after 1024-B alignment)
 constexpr int oW2HI = 0;
 constexpr int oW2LO = oW2HI + 128 * 64;
@@ -34,9 +43,8 @@ constexpr int oB2 = oW1 + 64 * 8;
 constexpr int oB3 = oB2 + 128;
 constexpr int oW4 = oB3 + 64;
 constexpr int oB4 = oW4 + 64;
-constexpr int oMask = oB4 + 4;
-constexpr int oHpart = oMask + R;          // [4][128]
-constexpr int total_floats = oHpart + 4 * R;
+constexpr int oHpart = oB4 + 4;            // [2][4][128]
+constexpr int total_floats = oHpart + 2 * 4 * R;
 constexpr size_t smem_bytes = (size_t)total_floats * 4 + 1024;
 }  // namespace cbftc
 
@@ -51,18 +59,18 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
   float* W2hi = sm + oW2HI; float* W2lo = sm + oW2LO;
   float* W3hi = sm + oW3HI; float* W3lo = sm + oW3LO;
   float* W1 = sm + oW1; float* B2 = sm + oB2; float* B3 = sm + oB3; float* W4 = sm + oW4; float* B4 = sm + oB4;
-  float* mask = sm + oMask; float* hpart = sm + oHpart;
-  __shared__ uint64_t bar_d2, bar_d3;
+  float* hpart = sm + oHpart;
+  // workers -> MMA: a2_full, a3_full[2], d3_free (16 arrivals: one per worker warp)
+  // MMA -> workers (tcgen05.commit): d2_full[2], d3_full
+  __shared__ uint64_t a2_full, a3_full[2], d3_free, d2_full[2], d3_full;
   __shared__ uint32_t tmem_base_s;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int q = warp & 3, cgrp = warp >> 2;
-  const int r = q * 32 + lane;
 
   if (warp == 0) tmem_alloc(&tmem_base_s, 512);
   if (threadIdx.x == 32) {
-    mbar_init(&bar_d2, 1);
-    mbar_init(&bar_d3, 1);
+    mbar_init(&a2_full, 16); mbar_init(&a3_full[0], 16); mbar_init(&a3_full[1], 16); mbar_init(&d3_free, 16);
+    mbar_init(&d2_full[0], 1); mbar_init(&d2_full[1], 1); mbar_init(&d3_full, 1);
     fence_mbar_init();
   }
   fill_weight_sw128<128, 64>(params + CBF_W2, 64, W2hi, W2lo);
@@ -82,157 +90,186 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
   __syncthreads();
   fence_after_sync();
   const uint32_t tbase = tmem_base_s;
-  const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16);
-  const uint32_t w2hi_a = smem_u32(W2hi), w2lo_a = smem_u32(W2lo), w3hi_a = smem_u32(W3hi), w3lo_a = smem_u32(W3lo);
-  constexpr uint32_t IDESC2 = idesc_tf32(128, 128), IDESC3 = idesc_tf32(128, 64);
-
   const long long ntiles = (agents_total + TA - 1) / TA;
-  uint32_t parity = 0;
-  // The edge endpoints of the NEXT tile are fetched while the tensor core works on this one:
-  // idx and s_i right after layer 2 is issued, s_j (which needs idx) after layer 3 is issued.
-  int pf_j = 0, pf_b = 0, pf_i = 0;
-  bool pf_valid = false;
-  float4 pf_si = make_float4(0.f, 0.f, 0.f, 0.f), pf_sj = pf_si;
-  auto prefetch_ij = [&](long long t) {
-    pf_valid = false;
-    if (t < ntiles) {
-      const long long a0n = t * TA;
-      const int rowsn = (int)min((long long)TA, agents_total - a0n) * K;
-      if (r < rowsn) {
-        const long long ga = a0n + r / K;
-        pf_b = (int)(ga / N); pf_i = (int)(ga % N);
-        pf_j = __ldg(idx + a0n * K + r);
-        pf_si = __ldg(reinterpret_cast<const float4*>(states) + ga);
-        pf_valid = true;
+
+  if (warp == WORKERS / 32) {
+    // =============================== MMA-issue warp ===============================
+    // Everything here is warp-uniform; only the tcgen05 instructions sit under elect_one().
+    const uint64_t d_w2hi = smem_desc_sw128(smem_u32(W2hi)), d_w2lo = smem_desc_sw128(smem_u32(W2lo));
+    const uint64_t d_w3hi = smem_desc_sw128(smem_u32(W3hi)), d_w3lo = smem_desc_sw128(smem_u32(W3lo));
+    const uint32_t tb = __shfl_sync(0xffffffffu, tbase, 0);
+    constexpr uint32_t IDESC = idesc_tf32(128, 64);
+    uint32_t par = 0;
+    int it = 0;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, par ^= 1, ++it) {
+      mbar_wait(&a2_full, par);
+      fence_after_sync();
+      // layer 2, output columns [64c, 64c+64): B rows 64c.. of every 32-wide K block
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+#pragma unroll
+        for (int term = 0; term < 3; ++term) {         // lo*hi, hi*lo, hi*hi (small terms first)
+          const uint32_t a_col = tb + (term == 0 ? C_A2LO : C_A2HI);
+          const uint64_t b_desc = desc_advance((term == 1) ? d_w2lo : d_w2hi, c * (64 * 128));
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks) {
+            const uint64_t bd = desc_advance(b_desc, (ks >> 2) * (128 * 128) + (ks & 3) * 32);
+            if (elect_one()) mma_tf32_ts(tb + C_Y + c * 64, a_col + ks * 8, bd, IDESC, (term | ks) ? 1u : 0u);
+          }
+        }
+        if (elect_one()) mma_commit(&d2_full[c]);
+      }
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        mbar_wait(&a3_full[c], par);
+        if (c == 0 && it > 0) mbar_wait(&d3_free, par ^ 1);   // previous tile's D3/D3s have been read
+        fence_after_sync();
+        // layer 3, K chunk [64c, 64c+64): cross terms -> D3s, hi*hi -> D3
+#pragma unroll
+        for (int term = 0; term < 3; ++term) {
+          const uint32_t a_col = tb + (term == 0 ? C_A3LO : C_Y) + c * 64;
+          const uint64_t b_desc = desc_advance((term == 1) ? d_w3lo : d_w3hi, (2 * c) * (64 * 128));
+          const uint32_t d = tb + (term == 2 ? C_D3 : C_D3S);
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks) {
+            const uint64_t bd = desc_advance(b_desc, (ks >> 2) * (64 * 128) + (ks & 3) * 32);
+            const uint32_t acc = (c > 0 || ks > 0 || term == 1) ? 1u : 0u;
+            if (elect_one()) mma_tf32_ts(d, a_col + ks * 8, bd, IDESC, acc);
+          }
+        }
+        if (c == 1 && elect_one()) mma_commit(&d3_full);
       }
     }
-  };
-  auto prefetch_sj = [&]() {
-    if (pf_valid) pf_sj = load_candidate(states, obstacles, pf_b, pf_j, N, M);
-  };
-  prefetch_ij(blockIdx.x);
-  prefetch_sj();
-  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, parity ^= 1) {
-    const long long a0 = tile * TA;
-    const int na = (int)min((long long)TA, agents_total - a0);
-    const int rows = na * K;
-    // ---- features (cbf.py:23-37) and layer 1 for this thread's 16 output channels ----
-    {
+  } else {
+    // ================================= worker warps =================================
+    const int q = warp & 3, cgrp = warp >> 2;
+    const int r = q * 32 + lane;
+    const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16);
+
+    // edge endpoints of upcoming tiles are fetched one phase ahead of their use
+    int pf_j = 0, pf_b = 0, pf_i = 0;
+    bool pf_valid = false;
+    float4 pf_si = make_float4(0.f, 0.f, 0.f, 0.f), pf_sj = pf_si;
+    const int a_loc = r / K;                       // agent of this row within a tile (tile-invariant)
+    auto prefetch_ij = [&](long long t) {
+      pf_valid = false;
+      if (t < ntiles) {
+        const int ga = (int)(t * TA) + a_loc;      // B*N < 2^31 is checked by the host
+        if (a_loc < TA && ga < (int)agents_total) {
+          pf_b = ga / N; pf_i = ga - pf_b * N;
+          pf_j = __ldg(idx + (size_t)(t * TA) * K + r);
+          pf_si = __ldg(reinterpret_cast<const float4*>(states) + ga);
+          pf_valid = true;
+        }
+      }
+    };
+    auto prefetch_sj = [&]() {
+      if (pf_valid) pf_sj = load_candidate(states, obstacles, pf_b, pf_j, N, M);
+    };
+    // features (cbf.py:23-37) + layer 1 for this thread's 16 channels -> A2; returns the radius mask
+    auto layer1 = [&]() -> float {
       float f[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
       float mk = 0.f;
-      if (r < rows) {
+      if (pf_valid) {
         const EdgeGeom g = edge_geom(pf_si, pf_sj, pf_i, pf_j);
         const float d = cbf_dist(g.dx, g.dy);
         f[0] = g.dx; f[1] = g.dy; f[2] = g.dvx; f[3] = g.dvy; f[4] = g.eye; f[5] = xsub(d, dist_min);
         mk = (d <= obs_radius) ? 1.f : 0.f;
       }
-      if (cgrp == 0) mask[r] = mk;
-      float hi[16], lo[16];
 #pragma unroll
-      for (int jn = 0; jn < 16; ++jn) {
-        const float4 wa = *reinterpret_cast<const float4*>(W1 + (cgrp * 16 + jn) * 8);
-        const float4 wb = *reinterpret_cast<const float4*>(W1 + (cgrp * 16 + jn) * 8 + 4);
-        float v = wa.x * f[0];
-        v = fmaf(wa.y, f[1], v); v = fmaf(wa.z, f[2], v); v = fmaf(wa.w, f[3], v);
-        v = fmaf(wb.x, f[4], v); v = fmaf(wb.y, f[5], v);
-        v = fmaxf(v + wb.z, 0.f);
-        tf32_split(v, hi[jn], lo[jn]);
+      for (int half = 0; half < 2; ++half) {       // 8 channels at a time keeps the register count down
+        float hi[8], lo[8];
+#pragma unroll
+        for (int jn = 0; jn < 8; ++jn) {
+          const int n = cgrp * 16 + half * 8 + jn;
+          const float4 wa = *reinterpret_cast<const float4*>(W1 + n * 8);
+          const float4 wb = *reinterpret_cast<const float4*>(W1 + n * 8 + 4);
+          float v = wa.x * f[0];
+          v = fmaf(wa.y, f[1], v); v = fmaf(wa.z, f[2], v); v = fmaf(wa.w, f[3], v);
+          v = fmaf(wb.x, f[4], v); v = fmaf(wb.y, f[5], v);
+          v = fmaxf(v + wb.z, 0.f);
+          tf32_split_trunc(v, hi[jn], lo[jn]);
+        }
+        tmem_st8(tlane + C_A2HI + cgrp * 16 + half * 8, hi);
+        tmem_st8(tlane + C_A2LO + cgrp * 16 + half * 8, lo);
       }
-      tmem_st16(tlane + C_A2HI + cgrp * 16, hi);
-      tmem_st16(tlane + C_A2LO + cgrp * 16, lo);
       wait_st();
-    }
-    fence_before_sync();
-    __syncthreads();
-    // ---- layer 2 on the tensor core ----
-    if (threadIdx.x == 0) {
-      fence_after_sync();
-      uint32_t acc = 0;
-#pragma unroll 1
-      for (int term = 0; term < 3; ++term) {           // lo*hi, hi*lo, hi*hi (small terms first)
-        const uint32_t a_col = tbase + (term == 0 ? C_A2LO : C_A2HI);
-        const uint32_t b_base = (term == 1) ? w2lo_a : w2hi_a;
-#pragma unroll
-        for (int ks = 0; ks < 8; ++ks) {
-          const uint32_t baddr = b_base + (ks >> 2) * (128 * 128) + (ks & 3) * 32;
-          mma_tf32_ts(tbase + C_D2, a_col + ks * 8, smem_desc_sw128(baddr), IDESC2, acc);
-          acc = 1;
-        }
-      }
-      mma_commit(&bar_d2);
-    }
-    prefetch_ij(tile + gridDim.x);
-    mbar_wait(&bar_d2, parity);
-    fence_after_sync();
-    // ---- bias + ReLU + split on this thread's 32 columns of D2 -> A3 ----
-#pragma unroll
-    for (int half = 0; half < 2; ++half) {
-      const int c0 = cgrp * 32 + half * 16;
-      float v[16], hi[16], lo[16];
-      tmem_ld16(tlane + C_D2 + c0, v);
-      wait_ld();
-#pragma unroll
-      for (int j4 = 0; j4 < 4; ++j4) {
-        const float4 bb = *reinterpret_cast<const float4*>(B2 + c0 + 4 * j4);
-        tf32_split(fmaxf(v[4 * j4 + 0] + bb.x, 0.f), hi[4 * j4 + 0], lo[4 * j4 + 0]);
-        tf32_split(fmaxf(v[4 * j4 + 1] + bb.y, 0.f), hi[4 * j4 + 1], lo[4 * j4 + 1]);
-        tf32_split(fmaxf(v[4 * j4 + 2] + bb.z, 0.f), hi[4 * j4 + 2], lo[4 * j4 + 2]);
-        tf32_split(fmaxf(v[4 * j4 + 3] + bb.w, 0.f), hi[4 * j4 + 3], lo[4 * j4 + 3]);
-      }
-      tmem_st16(tlane + C_A3HI + c0, hi);
-      tmem_st16(tlane + C_A3LO + c0, lo);
-    }
-    wait_st();
-    fence_before_sync();
-    __syncthreads();
-    // ---- layer 3 on the tensor core (D3 reuses the A2 columns: layer 2 has completed) ----
-    if (threadIdx.x == 0) {
-      fence_after_sync();
-      uint32_t acc = 0;
-#pragma unroll 1
-      for (int term = 0; term < 3; ++term) {
-        const uint32_t a_col = tbase + (term == 0 ? C_A3LO : C_A3HI);
-        const uint32_t b_base = (term == 1) ? w3lo_a : w3hi_a;
-#pragma unroll
-        for (int ks = 0; ks < 16; ++ks) {
-          const uint32_t baddr = b_base + (ks >> 2) * (64 * 128) + (ks & 3) * 32;
-          mma_tf32_ts(tbase + C_D3, a_col + ks * 8, smem_desc_sw128(baddr), IDESC3, acc);
-          acc = 1;
-        }
-      }
-      mma_commit(&bar_d3);
-    }
+      warp_arrive_after_tmem(&a2_full);
+      return mk;
+    };
+
+    prefetch_ij(blockIdx.x);
     prefetch_sj();
-    mbar_wait(&bar_d3, parity);
-    fence_after_sync();
-    // ---- bias + ReLU, 64 -> 1 (this thread: 16 of the 64 channels), * mask (cbf.py:43) ----
-    {
-      const int c0 = cgrp * 16;
-      float v[16];
-      tmem_ld16(tlane + C_D3 + c0, v);
-      wait_ld();
-      float s = 0.f;
+    float mk_next = layer1();
+    prefetch_ij((long long)blockIdx.x + gridDim.x);
+    prefetch_sj();
+
+    uint32_t par = 0;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, par ^= 1) {
+      const long long a0 = tile * TA;
+      const int rows = (int)min((long long)TA, agents_total - a0) * K;
+      const float mk = mk_next;
+      // ---- layer-2 epilogue per 64-column chunk: bias + ReLU + split; hi in place, lo aside ----
 #pragma unroll
-      for (int j4 = 0; j4 < 4; ++j4) {
-        const float4 bb = *reinterpret_cast<const float4*>(B3 + c0 + 4 * j4);
-        const float4 ww = *reinterpret_cast<const float4*>(W4 + c0 + 4 * j4);
-        s = fmaf(ww.x, fmaxf(v[4 * j4 + 0] + bb.x, 0.f), s);
-        s = fmaf(ww.y, fmaxf(v[4 * j4 + 1] + bb.y, 0.f), s);
-        s = fmaf(ww.z, fmaxf(v[4 * j4 + 2] + bb.z, 0.f), s);
-        s = fmaf(ww.w, fmaxf(v[4 * j4 + 3] + bb.w, 0.f), s);
+      for (int c = 0; c < 2; ++c) {
+        mbar_wait(&d2_full[c], par);
+        fence_after_sync();
+        const int c0 = c * 64 + cgrp * 16;
+        float v[16];
+        tmem_ld16(tlane + C_Y + c0, v);
+        wait_ld();
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          float hi[8], lo[8];
+#pragma unroll
+          for (int j4 = 0; j4 < 2; ++j4) {
+            const float4 bb = *reinterpret_cast<const float4*>(B2 + c0 + half * 8 + 4 * j4);
+            tf32_split_trunc(fmaxf(v[half * 8 + 4 * j4 + 0] + bb.x, 0.f), hi[4 * j4 + 0], lo[4 * j4 + 0]);
+            tf32_split_trunc(fmaxf(v[half * 8 + 4 * j4 + 1] + bb.y, 0.f), hi[4 * j4 + 1], lo[4 * j4 + 1]);
+            tf32_split_trunc(fmaxf(v[half * 8 + 4 * j4 + 2] + bb.z, 0.f), hi[4 * j4 + 2], lo[4 * j4 + 2]);
+            tf32_split_trunc(fmaxf(v[half * 8 + 4 * j4 + 3] + bb.w, 0.f), hi[4 * j4 + 3], lo[4 * j4 + 3]);
+          }
+          tmem_st8(tlane + C_Y + c0 + half * 8, hi);
+          tmem_st8(tlane + C_A3LO + c0 + half * 8, lo);
+        }
+        wait_st();
+        warp_arrive_after_tmem(&a3_full[c]);
       }
-      hpart[cgrp * R + r] = s;
+      // ---- layer 2 of this tile has completed (d2_full[1]): A2 is free -> next tile's layer 1 ----
+      if (tile + gridDim.x < ntiles) {
+        mk_next = layer1();
+        prefetch_ij(tile + 2 * (long long)gridDim.x);
+      }
+      // ---- layer-3 epilogue: (D3 + D3s) bias + ReLU, 64 -> 1 over this thread's 16 channels ----
+      mbar_wait(&d3_full, par);
+      fence_after_sync();
+      {
+        const int c0 = cgrp * 16;
+        float v[16], vs[16];
+        tmem_ld16(tlane + C_D3 + c0, v);
+        tmem_ld16(tlane + C_D3S + c0, vs);
+        wait_ld();
+        warp_arrive_after_tmem(&d3_free);
+        float s = 0.f;
+#pragma unroll
+        for (int j4 = 0; j4 < 4; ++j4) {
+          const float4 bb = *reinterpret_cast<const float4*>(B3 + c0 + 4 * j4);
+          const float4 ww = *reinterpret_cast<const float4*>(W4 + c0 + 4 * j4);
+          s = fmaf(ww.x, fmaxf((v[4 * j4 + 0] + vs[4 * j4 + 0]) + bb.x, 0.f), s);
+          s = fmaf(ww.y, fmaxf((v[4 * j4 + 1] + vs[4 * j4 + 1]) + bb.y, 0.f), s);
+          s = fmaf(ww.z, fmaxf((v[4 * j4 + 2] + vs[4 * j4 + 2]) + bb.z, 0.f), s);
+          s = fmaf(ww.w, fmaxf((v[4 * j4 + 3] + vs[4 * j4 + 3]) + bb.w, 0.f), s);
+        }
+        float* hp = hpart + (par * 4) * R;
+        hp[cgrp * R + r] = s;
+        named_bar_sync(1, WORKERS);
+        if (cgrp == 0 && r < rows) {
+          const float t = (hp[r] + hp[R + r]) + (hp[2 * R + r] + hp[3 * R + r]);
+          h[a0 * K + r] = (t + B4[0]) * mk;          // cbf.py:43
+        }
+      }
+      prefetch_sj();
     }
-    fence_before_sync();
-    __syncthreads();
-    fence_after_sync();
-    if (threadIdx.x < rows) {
-      const int t = threadIdx.x;
-      const float s = (hpart[t] + hpart[R + t]) + (hpart[2 * R + t] + hpart[3 * R + t]);
-      h[a0 * K + t] = (s + B4[0]) * mask[t];
-    }
-    // next tile: threads 0..127 rewrite mask[]/read hpart[] in program order; everyone else first
-    // meets a __syncthreads before hpart is written again
   }
   fence_before_sync();
   __syncthreads();

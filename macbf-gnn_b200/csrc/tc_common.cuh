@@ -50,6 +50,19 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       "}" ::"r"(smem_u32(bar)), "r"(parity)
       : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// warp-collective: every lane has finished its TMEM traffic -> one arrival per warp
+__device__ __forceinline__ void warp_arrive_after_tmem(uint64_t* bar) {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncwarp();
+  if ((threadIdx.x & 31) == 0) mbar_arrive(bar);
+}
+// named barrier among `nthreads` threads (id 1..15; id 0 is __syncthreads)
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
 // all previously issued tcgen05.mma of this thread arrive on `bar` when they complete
 __device__ __forceinline__ void mma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
@@ -72,6 +85,26 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t addr) {
 __host__ __device__ constexpr uint32_t idesc_tf32(int M, int N) {
   return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
+
+// One lane of a converged warp.  Issue tcgen05.mma / commit under `if (elect_one())` with all
+// operands computed warp-uniformly OUTSIDE the branch: the compiler then keeps descriptors and
+// TMEM addresses in uniform registers.  Under `if (lane == 0)` it cannot prove uniformity and
+// wraps every UTCHMMA in a ~16-instruction R2UR "waterfall" loop (measured: ~100 cycles per MMA,
+// which made the single issuing thread the bottleneck of the whole kernel).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred P;\n\t"
+      "elect.sync _|P, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, P;\n\t"
+      "}"
+      : "=r"(pred));
+  return pred != 0;
+}
+// descriptor of the same operand `bytes` further along (bytes % 16 == 0, no carry out of the
+// 14-bit address field for shared-memory windows < 256 KB)
+__device__ __forceinline__ uint64_t desc_advance(uint64_t d, uint32_t bytes) { return d + (uint64_t)(bytes >> 4); }
 
 // D[tmem] (+)= A[tmem] * B[smem]^T   (issued by ONE thread)
 __device__ __forceinline__ void mma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
@@ -103,6 +136,19 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const float* v) {
       : "memory");
 }
 
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, float* v) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const float* v) {
+  const uint32_t* r = reinterpret_cast<const uint32_t*>(v);
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"r"(taddr), "r"(r[0]),
+               "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+               : "memory");
+}
+
 // ---- 3xTF32 split ---------------------------------------------------------------------------
 // Round-to-nearest split (cvt.rna.tf32): |lo| <= 2^-11 |x| with random sign, so the dropped
 // lo*lo terms are ~2^-22 and average out; a truncating split (x & 0xFFFFE000) leaves one-sided
@@ -112,6 +158,14 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const float* v) {
 // rounding (nearest, ties away from zero) is an integer add of half an ulp and a mask.
 __device__ __forceinline__ float tf32_hi(float x) {
   return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);
+}
+// Cheap split for ACTIVATIONS (2 instructions): hi = x truncated to tf32, lo = x - hi (exact; the
+// tensor core reads its top 19 bits).  The weights keep the round-to-nearest split, so the
+// dropped a_lo*b_lo products still carry random signs; measured on the probe: 3.1e-7 / 5.1e-7
+// scale-relative (K = 64 / 128) against 3.1e-7 / 4.7e-7 with both operands rounded.
+__device__ __forceinline__ void tf32_split_trunc(float x, float& hi, float& lo) {
+  hi = __uint_as_float(__float_as_uint(x) & 0xFFFFE000u);
+  lo = x - hi;
 }
 // split x into (hi, lo), both exactly representable in tf32
 __device__ __forceinline__ void tf32_split(float x, float& hi, float& lo) {

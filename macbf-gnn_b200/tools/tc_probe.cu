@@ -10,7 +10,7 @@
 
 using namespace macbf::tc;
 
-template <int N, int K, int PASSES>
+template <int N, int K, int PASSES, bool TRUNC_A = false>
 __global__ void __launch_bounds__(128, 1) probe_kernel(const float* __restrict__ A, const float* __restrict__ W,
                                                        float* __restrict__ D) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(128, 1) probe_kernel(const float* __restrict__
 #pragma unroll
     for (int q = 0; q < 16; ++q) {
       float v = A[r * K + c0 + q];
-      tf32_split(v, hi[q], lo[q]);
+      if (TRUNC_A) { hi[q] = __uint_as_float(__float_as_uint(v) & 0xFFFFE000u); lo[q] = v - hi[q]; } else { tf32_split(v, hi[q], lo[q]); }
     }
     tmem_st16(tbase + lane_base + cA_hi + c0, hi);
     tmem_st16(tbase + lane_base + cA_lo + c0, lo);
@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(128, 1) probe_kernel(const float* __restrict__
   (void)lane;
 }
 
-template <int N, int K, int PASSES>
+template <int N, int K, int PASSES, bool TRUNC_A = false>
 static double run(const char* name) {
   std::vector<float> A(128 * K), W(N * K), D(128 * N);
   srand(7);
@@ -97,8 +97,8 @@ static double run(const char* name) {
   cudaMemcpy(dW, W.data(), W.size() * 4, cudaMemcpyHostToDevice);
   cudaMemset(dD, 0, D.size() * 4);
   const size_t smem = 2 * N * K * 4 + 1024;
-  cudaFuncSetAttribute(probe_kernel<N, K, PASSES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  probe_kernel<N, K, PASSES><<<1, 128, smem>>>(dA, dW, dD);
+  cudaFuncSetAttribute(probe_kernel<N, K, PASSES, TRUNC_A>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  probe_kernel<N, K, PASSES, TRUNC_A><<<1, 128, smem>>>(dA, dW, dD);
   cudaError_t e = cudaDeviceSynchronize();
   if (e != cudaSuccess) {
     printf("%s: CUDA error %s\n", name, cudaGetErrorString(e));
@@ -125,6 +125,8 @@ int main() {
   double f1 = run<64, 128, 1>("tf32x1 layer3");
   double f3 = run<64, 128, 3>("tf32x3 layer3");
   double g3 = run<128, 32, 3>("tf32x3 k32");
+  run<128, 64, 3, true>("tf32x3 layer2 truncA");
+  run<64, 128, 3, true>("tf32x3 layer3 truncA");
   bool ok = e1 < 5e-3 && f1 < 5e-3 && e3 < 2e-6 && f3 < 2e-6 && g3 < 2e-6;
   printf("%s\n", ok ? "PROBE OK" : "PROBE FAILED");
   return ok ? 0 : 1;
