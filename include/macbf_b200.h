@@ -62,6 +62,14 @@ int macbf_neighbor_count(int N, int M, int top_k);
 int macbf_neighbor_topk(const float* states, const float* obstacles, int B, int N, int M,
                         int top_k, int32_t* idx, void* stream);
 
+/* Same result through a uniform-grid search (used when top_k <= 32 and N + M >= 256; otherwise
+ * this is the brute-force kernel and needs no workspace).  workspace: macbf_neighbor_workspace_bytes
+ * bytes, 16-byte aligned, contents private. */
+size_t macbf_neighbor_workspace_bytes(int B, int N, int M, int top_k);
+int macbf_neighbor_topk_ws(const float* states, const float* obstacles, int B, int N, int M,
+                           int top_k, int32_t* idx, void* workspace, size_t workspace_bytes,
+                           void* stream);
+
 /* ---- A2,A4,A5: CBF head  (cbf.py:21-45) ------------------------------------------------
  * h[b,i,k] = mask * MLP_cbf([dx,dy,dvx,dvy,eye, d - dist_min_thres]),
  * d = sqrt((dx^2+1e-4)+(dy^2+1e-4)), mask = d <= obs_radius.  h is [B,N,K] (the reference's

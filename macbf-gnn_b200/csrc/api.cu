@@ -18,6 +18,17 @@ void count_launch(int n) { g_launches += n; }
 
 // implemented in the kernel translation units
 int neighbor_topk(const float*, const float*, int, int, int, int, int32_t*, cudaStream_t);
+size_t neighbor_grid_workspace_bytes(int, int, int);
+bool neighbor_grid_applicable(int, int, int);
+int neighbor_topk_grid(const float*, const float*, int, int, int, int, int32_t*, void*, size_t, cudaStream_t);
+
+// grid search when it applies (K <= 32, enough candidates) and workspace was given, else brute force
+static int neighbor_any(const float* states, const float* obstacles, int B, int N, int M, int top_k, int32_t* idx,
+                        void* ws, size_t ws_bytes, cudaStream_t st) {
+  if (ws != nullptr && neighbor_grid_applicable(N, M, top_k))
+    return neighbor_topk_grid(states, obstacles, B, N, M, top_k, idx, ws, ws_bytes, st);
+  return neighbor_topk(states, obstacles, B, N, M, top_k, idx, st);
+}
 int cbf_forward(const float*, const float*, const int32_t*, const float*, int, int, int, int, int, double, double,
                 float*, cudaStream_t);
 int controller_forward(const float*, const float*, const float*, const int32_t*, const float*, int, int, int, int,
@@ -69,6 +80,22 @@ int macbf_neighbor_topk(const float* states, const float* obstacles, int B, int 
   REQ_PTR(fn, states); REQ_PTR(fn, idx); REQ_A16(fn, states);
   MACBF_CHECK_ARG(M == 0 || obstacles != nullptr, "%s: obstacles is NULL but M=%d", fn, M);
   return neighbor_topk(states, obstacles, B, N, M, top_k, idx, (cudaStream_t)stream);
+}
+
+size_t macbf_neighbor_workspace_bytes(int B, int N, int M, int top_k) {
+  return neighbor_grid_applicable(N, M, top_k) ? neighbor_grid_workspace_bytes(B, N, M) : 0;
+}
+
+int macbf_neighbor_topk_ws(const float* states, const float* obstacles, int B, int N, int M, int top_k, int32_t* idx,
+                           void* workspace, size_t workspace_bytes, void* stream) {
+  const char* fn = "macbf_neighbor_topk_ws";
+  MACBF_CHECK_ARG(top_k >= 1 && top_k <= MACBF_MAX_K, "%s: top_k=%d out of range [1,%d]", fn, top_k, MACBF_MAX_K);
+  if (check_dims(fn, B, N, M, macbf_neighbor_count(N, M, top_k))) return 1;
+  REQ_PTR(fn, states); REQ_PTR(fn, idx); REQ_A16(fn, states);
+  MACBF_CHECK_ARG(M == 0 || obstacles != nullptr, "%s: obstacles is NULL but M=%d", fn, M);
+  MACBF_CHECK_ARG(workspace != nullptr || macbf_neighbor_workspace_bytes(B, N, M, top_k) == 0,
+                  "%s: workspace is NULL but %zu bytes are needed", fn, macbf_neighbor_workspace_bytes(B, N, M, top_k));
+  return neighbor_any(states, obstacles, B, N, M, top_k, idx, workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
 int macbf_cbf_forward(const float* states, const float* obstacles, const int32_t* idx, const float* cbf_params, int B,
@@ -166,10 +193,11 @@ int macbf_controller_backward(const float* states, const float* goals, const flo
                              dt, grad_params, grad_states, grad_goals, scratch, scratch_bytes, (cudaStream_t)stream);
 }
 
-// workspace: [pool (B*N*128 f32)] [loss scratch]
+// workspace: [pool (B*N*128 f32)] [loss scratch] [neighbour-grid scratch]
 size_t macbf_step_workspace_bytes(int B, int N, int M, int top_k) {
   const int K = macbf_neighbor_count(N, M, top_k);
-  return align256((size_t)B * N * MACBF_POOL_DIM * sizeof(float)) + align256(loss_scratch_bytes(B, N, K));
+  return align256((size_t)B * N * MACBF_POOL_DIM * sizeof(float)) + align256(loss_scratch_bytes(B, N, K)) +
+         align256(macbf_neighbor_workspace_bytes(B, N, M, top_k));
 }
 
 int macbf_step_forward(const float* states, const float* goals, const float* obstacles, const float* cbf_params,
@@ -191,11 +219,13 @@ int macbf_step_forward(const float* states, const float* goals, const float* obs
   cudaStream_t st = (cudaStream_t)stream;
   float* pool = (float*)workspace;
   void* lscratch = (char*)workspace + align256((size_t)B * N * MACBF_POOL_DIM * sizeof(float));
+  const size_t gbytes = macbf_neighbor_workspace_bytes(B, N, M, top_k);
+  void* gscratch = gbytes ? (char*)lscratch + align256(loss_scratch_bytes(B, N, K)) : nullptr;
   int rc;
-  if ((rc = neighbor_topk(states, obstacles, B, N, M, top_k, idx, st))) return rc;
+  if ((rc = neighbor_any(states, obstacles, B, N, M, top_k, idx, gscratch, gbytes, st))) return rc;
   if ((rc = controller_forward(states, goals, obstacles, idx, ctrl_params, B, N, M, K, semantics, obs_radius, dt, pool,
                                u, s_next, st))) return rc;
-  if ((rc = neighbor_topk(s_next, obstacles, B, N, M, top_k, idx_next, st))) return rc;   // core.py:137: fresh top-k
+  if ((rc = neighbor_any(s_next, obstacles, B, N, M, top_k, idx_next, gscratch, gbytes, st))) return rc;   // core.py:137
   if ((rc = cbf_forward(states, obstacles, idx, cbf_params, B, N, M, K, semantics, dist_min_thres, obs_radius, h, st)))
     return rc;
   if ((rc = cbf_forward(s_next, obstacles, idx_next, cbf_params, B, N, M, K, semantics, dist_min_thres, obs_radius,

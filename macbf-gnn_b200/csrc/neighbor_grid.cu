@@ -1,0 +1,309 @@
+// K1 (grid path) - exact K nearest candidates through a uniform grid (K <= 32).
+//
+// Same contract as neighbor.cu (core.py:234-250; lexicographic (key, index) order, keys computed
+// with the reference's op sequence), but a query only looks at the candidates of the grid cells
+// around it instead of all N + M:
+//
+//   grid_build_kernel  one CTA per env: bounding box -> G x G cells -> counting sort of the
+//                      candidates by cell (shared-memory histogram, scan, scatter) into
+//                      sorted[b][.] = (x, y, index) plus cell_start[b][G*G+1].
+//   knn_grid_kernel    one warp per query: ring r = 0, 1, 2, ... of cells around the query's cell.
+//                      The <= 4r cell ranges of a ring are flattened with a warp prefix sum so that
+//                      every lane evaluates one candidate per step; candidates that pass the exact
+//                      pre-filter are merged into the register-resident sorted list (entry e in
+//                      lane e) by a warp bitonic merge, or inserted one by one when only a few pass.
+//                      The search stops once the K-th key is smaller than the distance from the
+//                      query to the edge of the visited square (everything unvisited is farther).
+//
+// Exactness does not depend on how the agents are distributed: a clustered swarm only makes
+// the rings grow until the stop test holds (worst case: the whole grid = brute force).
+#include "common.cuh"
+
+namespace macbf {
+
+constexpr int GRID_GMAX = 64;                 // cells per axis (shared-memory histogram of G*G ints)
+constexpr int GRID_BUILD_THREADS = 1024;
+constexpr int GRID_QUERY_THREADS = 256;
+
+struct GridHeader {
+  float ox, oy, inv_cs, cs;
+};
+
+__device__ __forceinline__ int cell_coord(float x, float o, float inv_cs, int G) {
+  int c = (int)floorf((x - o) * inv_cs);
+  return min(max(c, 0), G - 1);
+}
+
+__global__ void __launch_bounds__(GRID_BUILD_THREADS)
+grid_build_kernel(const float* __restrict__ states, const float* __restrict__ obstacles, int N, int M, int G,
+                  float4* __restrict__ sorted, int* __restrict__ cell_start, GridHeader* __restrict__ header) {
+  __shared__ int cnt[GRID_GMAX * GRID_GMAX + 1];
+  __shared__ int cur[GRID_GMAX * GRID_GMAX];
+  __shared__ float red[4][32];
+  __shared__ int wsum[32];
+  __shared__ GridHeader hd;
+  const int b = blockIdx.x, C = N + M, cells = G * G;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // ---- bounding box ----
+  float xmin = 3.0e38f, ymin = 3.0e38f, xmax = -3.0e38f, ymax = -3.0e38f;
+  for (int t = threadIdx.x; t < C; t += GRID_BUILD_THREADS) {
+    const float4 s = load_candidate(states, obstacles, b, t, N, M);
+    xmin = fminf(xmin, s.x); xmax = fmaxf(xmax, s.x);
+    ymin = fminf(ymin, s.y); ymax = fmaxf(ymax, s.y);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    xmin = fminf(xmin, __shfl_xor_sync(0xffffffffu, xmin, o));
+    ymin = fminf(ymin, __shfl_xor_sync(0xffffffffu, ymin, o));
+    xmax = fmaxf(xmax, __shfl_xor_sync(0xffffffffu, xmax, o));
+    ymax = fmaxf(ymax, __shfl_xor_sync(0xffffffffu, ymax, o));
+  }
+  if (lane == 0) { red[0][warp] = xmin; red[1][warp] = ymin; red[2][warp] = xmax; red[3][warp] = ymax; }
+  for (int t = threadIdx.x; t <= cells; t += GRID_BUILD_THREADS) cnt[t] = 0;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < GRID_BUILD_THREADS / 32; ++w) {
+      red[0][0] = fminf(red[0][0], red[0][w]); red[1][0] = fminf(red[1][0], red[1][w]);
+      red[2][0] = fmaxf(red[2][0], red[2][w]); red[3][0] = fmaxf(red[3][0], red[3][w]);
+    }
+    float ext = fmaxf(red[2][0] - red[0][0], red[3][0] - red[1][0]);
+    float cs = ext / (float)G;
+    if (!(cs > 0.f) || !(cs < 3.0e38f)) cs = 1.f;          // all candidates coincide (or non-finite input)
+    hd.ox = red[0][0]; hd.oy = red[1][0]; hd.cs = cs; hd.inv_cs = 1.f / cs;
+    header[b] = hd;
+  }
+  __syncthreads();
+  const GridHeader g = hd;
+  // ---- histogram ----
+  for (int t = threadIdx.x; t < C; t += GRID_BUILD_THREADS) {
+    const float4 s = load_candidate(states, obstacles, b, t, N, M);
+    const int cell = cell_coord(s.y, g.oy, g.inv_cs, G) * G + cell_coord(s.x, g.ox, g.inv_cs, G);
+    atomicAdd(&cnt[cell], 1);
+  }
+  __syncthreads();
+  // ---- exclusive scan of cnt[0..cells) (each thread owns a contiguous chunk) ----
+  const int per = (cells + GRID_BUILD_THREADS - 1) / GRID_BUILD_THREADS;
+  const int c_begin = min(threadIdx.x * per, cells), c_end = min(c_begin + per, cells);
+  int local = 0;
+  for (int c = c_begin; c < c_end; ++c) local += cnt[c];
+  int incl = local;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    int v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  if (lane == 31) wsum[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    int v = wsum[lane], s = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      int u = __shfl_up_sync(0xffffffffu, s, o);
+      if (lane >= o) s += u;
+    }
+    wsum[lane] = s - v;   // exclusive prefix of the warp sums
+  }
+  __syncthreads();
+  int run = wsum[warp] + incl - local;
+  for (int c = c_begin; c < c_end; ++c) {
+    const int n = cnt[c];
+    cnt[c] = run;
+    cur[c] = run;
+    run += n;
+  }
+  if (threadIdx.x == GRID_BUILD_THREADS - 1) cnt[cells] = C;
+  __syncthreads();
+  for (int t = threadIdx.x; t <= cells; t += GRID_BUILD_THREADS) cell_start[(size_t)b * (GRID_GMAX * GRID_GMAX + 1) + t] = cnt[t];
+  // ---- scatter (order inside a cell is arbitrary: the query orders by (key, index) explicitly) ----
+  for (int t = threadIdx.x; t < C; t += GRID_BUILD_THREADS) {
+    const float4 s = load_candidate(states, obstacles, b, t, N, M);
+    const int cell = cell_coord(s.y, g.oy, g.inv_cs, G) * G + cell_coord(s.x, g.ox, g.inv_cs, G);
+    const int pos = atomicAdd(&cur[cell], 1);
+    sorted[(size_t)b * C + pos] = make_float4(s.x, s.y, __int_as_float(t), 0.f);
+  }
+}
+
+// ---- packed (key, index) entries: key bits in the high word (keys are positive floats, so the
+//      unsigned order of the bits is the numeric order), candidate index in the low word ----------
+typedef unsigned long long u64;
+constexpr u64 ENTRY_INF = 0x7f8000007fffffffull;
+
+__device__ __forceinline__ u64 shfl64(u64 v, int src) {
+  return ((u64)__shfl_sync(0xffffffffu, (unsigned)(v >> 32), src) << 32) | __shfl_sync(0xffffffffu, (unsigned)v, src);
+}
+__device__ __forceinline__ u64 shfl64_xor(u64 v, int m) {
+  return ((u64)__shfl_xor_sync(0xffffffffu, (unsigned)(v >> 32), m) << 32) | __shfl_xor_sync(0xffffffffu, (unsigned)v, m);
+}
+__device__ __forceinline__ u64 shfl64_up(u64 v, int d) {
+  return ((u64)__shfl_up_sync(0xffffffffu, (unsigned)(v >> 32), d) << 32) | __shfl_up_sync(0xffffffffu, (unsigned)v, d);
+}
+__device__ __forceinline__ u64 umin64(u64 a, u64 b) { return a < b ? a : b; }
+__device__ __forceinline__ u64 umax64(u64 a, u64 b) { return a < b ? b : a; }
+
+// ascending bitonic sort of one entry per lane
+__device__ __forceinline__ u64 warp_sort32(u64 x, int lane) {
+#pragma unroll
+  for (int k = 2; k <= 32; k <<= 1) {
+#pragma unroll
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      const u64 p = shfl64_xor(x, j);
+      const bool up = (lane & k) == 0 || k == 32;
+      const bool lower = (lane & j) == 0;
+      x = (lower == up) ? umin64(x, p) : umax64(x, p);
+    }
+  }
+  return x;
+}
+// list, fresh: ascending; returns the 32 smallest of the 64, ascending
+__device__ __forceinline__ u64 warp_merge32(u64 list, u64 fresh, int lane) {
+  u64 y = umin64(list, shfl64(fresh, 31 - lane));   // bitonic
+#pragma unroll
+  for (int j = 16; j > 0; j >>= 1) {
+    const u64 p = shfl64_xor(y, j);
+    y = ((lane & j) == 0) ? umin64(y, p) : umax64(y, p);
+  }
+  return y;
+}
+
+__global__ void __launch_bounds__(GRID_QUERY_THREADS)
+knn_grid_kernel(const float* __restrict__ states, const float4* __restrict__ sorted,
+                const int* __restrict__ cell_start, const GridHeader* __restrict__ header, int N, int C, int G,
+                int K, int32_t* __restrict__ idx_out) {
+  const int b = blockIdx.y;
+  const int lane = threadIdx.x & 31;
+  const int i = blockIdx.x * (GRID_QUERY_THREADS / 32) + (threadIdx.x >> 5);
+  if (i >= N) return;                                  // whole warp
+  const GridHeader g = header[b];
+  const int* cs = cell_start + (size_t)b * (GRID_GMAX * GRID_GMAX + 1);
+  const float4* pts = sorted + (size_t)b * C;
+  const float4 sq = __ldg(reinterpret_cast<const float4*>(states) + (size_t)b * N + i);
+  const float qx = sq.x, qy = sq.y;
+  const int cx = cell_coord(qx, g.ox, g.inv_cs, G), cy = cell_coord(qy, g.oy, g.inv_cs, G);
+
+  u64 list = ENTRY_INF;                                // entry e of the sorted best list lives in lane e
+  float vthr = __int_as_float(0x7f800000);             // a candidate with v >= vthr cannot enter the list
+
+  for (int r = 0; r < G; ++r) {
+    // ---- the cell ranges of ring r, one per lane (chunks of 32 ranges) ----
+    const int nranges = (r == 0) ? 1 : 4 * r;
+    for (int rb = 0; rb < nranges; rb += 32) {
+      const int t = rb + lane;
+      int start = 0, len = 0;
+      if (t < nranges) {
+        int y, x0, x1;
+        if (r == 0) { y = cy; x0 = cx; x1 = cx; }
+        else if (t == 0) { y = cy - r; x0 = cx - r; x1 = cx + r; }
+        else if (t == 1) { y = cy + r; x0 = cx - r; x1 = cx + r; }
+        else {
+          const int m = (t - 2) >> 1;
+          y = cy - r + 1 + m;
+          x0 = x1 = ((t - 2) & 1) ? cx + r : cx - r;
+        }
+        x0 = max(x0, 0); x1 = min(x1, G - 1);
+        if (y >= 0 && y < G && x0 <= x1 && (r == 0 || t < 2 || y < cy + r)) {
+          start = __ldg(cs + y * G + x0);
+          len = __ldg(cs + y * G + x1 + 1) - start;
+        }
+      }
+      int incl = len;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+      }
+      const int total = __shfl_sync(0xffffffffu, incl, 31);
+      const int excl = incl - len;
+      for (int t0 = 0; t0 < total; t0 += 32) {
+        // ---- load-balanced fetch: virtual candidate t0 + lane -> (range, offset) ----
+        const int tv = t0 + lane;
+        int lo = 0;
+#pragma unroll
+        for (int step = 16; step > 0; step >>= 1) {
+          const int v = __shfl_sync(0xffffffffu, incl, lo + step - 1);
+          if (v <= tv) lo += step;
+        }
+        lo = min(lo, 31);
+        const int rs = __shfl_sync(0xffffffffu, start, lo), re = __shfl_sync(0xffffffffu, excl, lo);
+        const bool valid = tv < total;
+        float v = __int_as_float(0x7f800000);
+        int cid = 0x7fffffff;
+        if (valid) {
+          const float4 p = __ldg(pts + rs + (tv - re));
+          cid = __float_as_int(p.z);
+          // core.py:238, op by op
+          const float dx = xsub(qx, p.x), dy = xsub(qy, p.y);
+          v = xadd(xadd(xmul(dx, dx), 1e-6f), xadd(xmul(dy, dy), 1e-6f));
+        }
+        const bool passf = valid && (v < vthr);
+        const unsigned pass = __ballot_sync(0xffffffffu, passf);
+        if (pass == 0u) continue;
+        const u64 cand = passf ? (((u64)__float_as_uint(__fsqrt_rn(v)) << 32) | (unsigned)cid) : ENTRY_INF;
+        if (__popc(pass) >= 6) {
+          list = warp_merge32(list, warp_sort32(cand, lane), lane);
+        } else {
+          unsigned rem = pass;
+          while (rem) {
+            const int src = __ffs(rem) - 1;
+            rem &= rem - 1;
+            const u64 c = shfl64(cand, src);
+            const u64 kth = shfl64(list, K - 1);
+            if (c < kth) {                              // exact lexicographic test (key, index)
+              const int pos = __popc(__ballot_sync(0xffffffffu, list < c));
+              const u64 up = shfl64_up(list, 1);
+              if (lane > pos) list = up;
+              else if (lane == pos) list = c;
+            }
+          }
+        }
+        // v >= RU(next(key_K)^2)  =>  sqrt_rn(v) > key_K: such a candidate can never enter
+        const float kK = __uint_as_float((unsigned)(shfl64(list, K - 1) >> 32));
+        const float kn = __uint_as_float(__float_as_uint(kK) + 1u);
+        vthr = (kK < __int_as_float(0x7f800000)) ? __fmul_ru(kn, kn) : kK;
+      }
+    }
+    // ---- stop test: everything not yet visited lies outside the square of rings 0..r ----
+    const float kK = __uint_as_float((unsigned)(shfl64(list, K - 1) >> 32));
+    float bound = __int_as_float(0x7f800000);
+    if (cx - r > 0) bound = fminf(bound, qx - (g.ox + (float)(cx - r) * g.cs));
+    if (cx + r < G - 1) bound = fminf(bound, (g.ox + (float)(cx + r + 1) * g.cs) - qx);
+    if (cy - r > 0) bound = fminf(bound, qy - (g.oy + (float)(cy - r) * g.cs));
+    if (cy + r < G - 1) bound = fminf(bound, (g.oy + (float)(cy + r + 1) * g.cs) - qy);
+    if (bound == __int_as_float(0x7f800000)) break;     // the square already covers the whole grid
+    // margin: cell assignment and the edge coordinates carry a few ulp of the coordinate range
+    if (kK < bound * 0.9999f - 1e-5f * g.cs) break;
+  }
+  if (lane < K) idx_out[((size_t)b * N + i) * K + lane] = (int32_t)(unsigned)list;
+}
+
+size_t neighbor_grid_workspace_bytes(int B, int N, int M) {
+  const size_t C = (size_t)N + M;
+  return (size_t)B * C * sizeof(float4) + (size_t)B * (GRID_GMAX * GRID_GMAX + 1) * sizeof(int) +
+         (size_t)B * sizeof(GridHeader) + 256;
+}
+
+// true when the grid path applies (the caller falls back to the brute-force kernel otherwise)
+bool neighbor_grid_applicable(int N, int M, int top_k) {
+  const int C = N + M;
+  return top_k <= 32 && C > top_k && C >= 256;
+}
+
+int neighbor_topk_grid(const float* states, const float* obstacles, int B, int N, int M, int K, int32_t* idx,
+                       void* workspace, size_t workspace_bytes, cudaStream_t st) {
+  const int C = N + M;
+  MACBF_CHECK_ARG(workspace_bytes >= neighbor_grid_workspace_bytes(B, N, M), "neighbor_topk: workspace too small (%zu < %zu)",
+                  workspace_bytes, neighbor_grid_workspace_bytes(B, N, M));
+  MACBF_CHECK_ARG((((uintptr_t)workspace) & 15) == 0, "neighbor_topk: workspace must be 16-byte aligned");
+  float4* sorted = (float4*)workspace;
+  int* cell_start = (int*)((char*)workspace + (size_t)B * C * sizeof(float4));
+  GridHeader* header = (GridHeader*)((char*)cell_start + (size_t)B * (GRID_GMAX * GRID_GMAX + 1) * sizeof(int));
+  int G = (int)floorf(sqrtf((float)C / 3.0f));           // ~3 candidates per cell
+  G = G < 1 ? 1 : (G > GRID_GMAX ? GRID_GMAX : G);
+  grid_build_kernel<<<B, GRID_BUILD_THREADS, 0, st>>>(states, obstacles, N, M, G, sorted, cell_start, header);
+  MACBF_CHECK_LAUNCH("grid_build_kernel");
+  dim3 grid((N + GRID_QUERY_THREADS / 32 - 1) / (GRID_QUERY_THREADS / 32), B);
+  knn_grid_kernel<<<grid, GRID_QUERY_THREADS, 0, st>>>(states, sorted, cell_start, header, N, C, G, K, idx);
+  MACBF_CHECK_LAUNCH("knn_grid_kernel");
+  return 0;
+}
+
+}  // namespace macbf

@@ -63,15 +63,23 @@ def neighbor_count(N: int, M: int, top_k: int) -> int:
     return min(top_k, N + M)
 
 
-def neighbor_topk(states: torch.Tensor, top_k: int = TOP_K, obstacles: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """core.py:234-250 -> idx [B,N,K_eff] int32."""
+def neighbor_topk(states: torch.Tensor, top_k: int = TOP_K, obstacles: Optional[torch.Tensor] = None,
+                  brute_force: bool = False) -> torch.Tensor:
+    """core.py:234-250 -> idx [B,N,K_eff] int32 (uniform-grid search when it applies, else brute force)."""
     _need_cuda(states, obstacles)
     states, obstacles = _c(states), _c(obstacles)
     B, N, M, obstacles = _dims(states, obstacles)
     K = neighbor_count(N, M, top_k)
     idx = torch.empty((B, N, K), dtype=torch.int32, device=states.device)
     L = _lib.load()
-    _lib.check(L.macbf_neighbor_topk(_p(states), _p(obstacles), B, N, M, top_k, _p(idx), _stream()), "macbf_neighbor_topk")
+    nbytes = L.macbf_neighbor_workspace_bytes(B, N, M, top_k)
+    if nbytes == 0 or brute_force:
+        _lib.check(L.macbf_neighbor_topk(_p(states), _p(obstacles), B, N, M, top_k, _p(idx), _stream()),
+                   "macbf_neighbor_topk")
+    else:
+        ws = torch.empty((nbytes,), dtype=torch.uint8, device=states.device)
+        _lib.check(L.macbf_neighbor_topk_ws(_p(states), _p(obstacles), B, N, M, top_k, _p(idx), _p(ws), nbytes,
+                                            _stream()), "macbf_neighbor_topk_ws")
     return idx
 
 

@@ -203,3 +203,50 @@ def test_c2_shape_against_oracle_sample(ops):
     assert (srt[:, :, 1:] != srt[:, :, :-1]).all()                 # no duplicate neighbours
     sc = buf.scalars.cpu().numpy()
     assert np.isfinite(sc).all() and (sc[:, 10] + sc[:, 11] == N * 12).all()
+
+
+def _grid_vs_brute(ops, s, k, obs=None):
+    sd = s.cuda().contiguous()
+    od = obs.cuda().contiguous() if obs is not None else None
+    a = ops.neighbor_topk(sd, k, od)                       # uniform-grid search
+    b = ops.neighbor_topk(sd, k, od, brute_force=True)     # tiled brute force
+    assert torch.equal(a, b)
+    return a
+
+
+@pytest.mark.parametrize("k", [1, 5, 12, 16, 32])
+def test_grid_search_equals_brute_force_uniform(ops, k):
+    from oracle import macbf_oracle as O
+    s, _ = O.synthetic_swarm(3, 2000, seed=300 + k)
+    idx = _grid_vs_brute(ops, s, k)
+    ref = O.neighbor_indices(s[1], k).numpy()
+    dec = O.decidable_rows(s[1], k).numpy()
+    assert np.array_equal(idx[1].cpu().numpy()[dec], ref[dec]) and dec.mean() > 0.99
+
+
+def test_grid_search_adversarial_layouts(ops):
+    """Exactness must not depend on the spatial distribution: tight clusters, a line, exact
+    duplicates, far outliers, obstacles - the grid search still returns the brute-force answer."""
+    from oracle import macbf_oracle as O
+    g = torch.Generator().manual_seed(9)
+    n = 1500
+    clustered = torch.zeros(1, n, 4)
+    centers = torch.rand(5, 2, generator=g) * 40
+    clustered[0, :, :2] = centers[torch.randint(0, 5, (n,), generator=g)] + torch.randn(n, 2, generator=g) * 0.05
+    line = torch.zeros(1, n, 4)
+    line[0, :, 0] = torch.rand(n, generator=g) * 100            # all on y = 0
+    dup = torch.zeros(1, n, 4)
+    dup[0, :, :2] = (torch.randint(0, 40, (n, 2), generator=g)).float() * 0.25   # lattice with many coincident agents
+    outl, _ = O.synthetic_swarm(1, n, seed=17)
+    outl[0, :7, :2] += 1e4                                          # a few agents very far away
+    for name, s in (("clustered", clustered), ("line", line), ("duplicates", dup), ("outliers", outl)):
+        idx = _grid_vs_brute(ops, s, 12)
+        ref = O.neighbor_indices(s[0], 12).numpy()
+        dec = O.decidable_rows(s[0], 12).numpy()
+        assert np.array_equal(idx[0].cpu().numpy()[dec], ref[dec]), name
+    s, _ = O.synthetic_swarm(2, 900, seed=23)
+    obs = O.synthetic_obstacles(2, 900, 4, 4, seed=23)
+    _grid_vs_brute(ops, s, 12, obs)
+    same = torch.zeros(1, 400, 4)                                    # every agent at the same point
+    idx = _grid_vs_brute(ops, same, 12)
+    assert np.array_equal(idx[0, :, :].cpu().numpy(), np.tile(np.arange(12), (400, 1)))
