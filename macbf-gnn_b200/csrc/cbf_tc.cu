@@ -28,6 +28,22 @@
 
 namespace macbf {
 
+// Optional phase timeline (build with -DMACBF_TRACE; tools/tc_trace.py reads it back): CTA 0 logs
+// (event, SM clock) pairs for worker warp 0 and for the MMA warp.
+#ifdef MACBF_TRACE
+__device__ unsigned long long g_tc_trace[2][4096];
+#define TC_TRACE(who, ev)                                                                          \
+  do {                                                                                             \
+    if (blockIdx.x == 0 && lane == 0 && trace_n < 4096)                                            \
+      g_tc_trace[who][trace_n++] = ((unsigned long long)(ev) << 56) | (clock64() & 0x00ffffffffffffffull); \
+  } while (0)
+extern "C" int macbf_debug_tc_trace(unsigned long long* host_out) {
+  return (int)cudaMemcpyFromSymbol(host_out, g_tc_trace, sizeof(g_tc_trace));
+}
+#else
+#define TC_TRACE(who, ev) do { } while (0)
+#endif
+
 namespace cbftc {
 constexpr int WORKERS = 512;
 constexpr int THREADS = WORKERS + 32;
@@ -101,9 +117,11 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
     constexpr uint32_t IDESC = idesc_tf32(128, 64);
     uint32_t par = 0;
     int it = 0;
+    int trace_n = 0; (void)trace_n;
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, par ^= 1, ++it) {
       mbar_wait(&a2_full, par);
       fence_after_sync();
+      TC_TRACE(1, 1);
       // layer 2, output columns [64c, 64c+64): B rows 64c.. of every 32-wide K block
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
@@ -119,11 +137,13 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
         }
         if (elect_one()) mma_commit(&d2_full[c]);
       }
+      TC_TRACE(1, 2);
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
         mbar_wait(&a3_full[c], par);
         if (c == 0 && it > 0) mbar_wait(&d3_free, par ^ 1);   // previous tile's D3/D3s have been read
         fence_after_sync();
+        TC_TRACE(1, 3 + c);
         // layer 3, K chunk [64c, 64c+64): cross terms -> D3s, hi*hi -> D3
 #pragma unroll
         for (int term = 0; term < 3; ++term) {
@@ -139,6 +159,7 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
         }
         if (c == 1 && elect_one()) mma_commit(&d3_full);
       }
+      TC_TRACE(1, 5);
     }
   } else {
     // ================================= worker warps =================================
@@ -205,6 +226,7 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
     prefetch_sj();
 
     uint32_t par = 0;
+    int trace_n = 0; (void)trace_n;
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, par ^= 1) {
       const long long a0 = tile * TA;
       const int rows = (int)min((long long)TA, agents_total - a0) * K;
@@ -214,6 +236,7 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
       for (int c = 0; c < 2; ++c) {
         mbar_wait(&d2_full[c], par);
         fence_after_sync();
+        if (warp == 0) TC_TRACE(0, 1 + 2 * c);
         const int c0 = c * 64 + cgrp * 16;
         float v[16];
         tmem_ld16(tlane + C_Y + c0, v);
@@ -234,15 +257,18 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
         }
         wait_st();
         warp_arrive_after_tmem(&a3_full[c]);
+        if (warp == 0) TC_TRACE(0, 2 + 2 * c);
       }
       // ---- layer 2 of this tile has completed (d2_full[1]): A2 is free -> next tile's layer 1 ----
       if (tile + gridDim.x < ntiles) {
         mk_next = layer1();
         prefetch_ij(tile + 2 * (long long)gridDim.x);
       }
+      if (warp == 0) TC_TRACE(0, 5);
       // ---- layer-3 epilogue: (D3 + D3s) bias + ReLU, 64 -> 1 over this thread's 16 channels ----
       mbar_wait(&d3_full, par);
       fence_after_sync();
+      if (warp == 0) TC_TRACE(0, 6);
       {
         const int c0 = cgrp * 16;
         float v[16], vs[16];
@@ -269,6 +295,7 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
         }
       }
       prefetch_sj();
+      if (warp == 0) TC_TRACE(0, 7);
     }
   }
   fence_before_sync();

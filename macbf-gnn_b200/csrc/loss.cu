@@ -10,7 +10,7 @@
 namespace macbf {
 
 constexpr int LOSS_THREADS = 256;
-constexpr int LOSS_ROWS_PER_CTA = 4096;
+constexpr int LOSS_ROWS_PER_CTA = 1024;
 constexpr int LOSS_NACC = 10;
 
 static inline int loss_chunks(int N, int K) {

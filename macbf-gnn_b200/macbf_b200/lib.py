@@ -7,7 +7,7 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "libmacbf_b200.so")
+LIB_PATH = os.environ.get("MACBF_B200_LIB", os.path.join(os.path.dirname(_HERE), "libmacbf_b200.so"))
 
 c_f32p = ctypes.c_void_p
 c_i32p = ctypes.c_void_p

@@ -50,7 +50,7 @@ def test_housekeeping_and_validation_without_gpu(lib):
     assert rc != 0 and b"NULL" in L.macbf_last_error()
     rc = L.macbf_cbf_forward(None, None, None, None, 1, 8, 0, 12, 1, 0.07, 1.0, None, None)
     assert rc != 0 and b"exceeds" in L.macbf_last_error()
-    assert L.macbf_loss_scratch_bytes(64, 1024, 12) == 64 * 3 * 10 * 4
+    assert L.macbf_loss_scratch_bytes(64, 1024, 12) == 64 * 12 * 10 * 4
     assert L.macbf_step_workspace_bytes(64, 1024, 0, 12) >= 64 * 1024 * 128 * 4
 
 

@@ -63,7 +63,7 @@ def test_noalloc_rejects_problems_beyond_the_fixed_array():
         pytest.skip("no CUDA device")
     from macbf_b200 import lib
     L = lib.load()
-    # 4096 envs x 4096 agents x 12 slots -> 4096 * 12 chunks * 10 sums = 491,520 floats > 65,536
+    # 4096 envs x 4096 agents x 12 slots -> 4096 * 48 chunks * 10 sums = 1,966,080 floats > 65,536
     assert L.macbf_loss_scratch_bytes(4096, 4096, 12) > 4 * 65536
     dummy = torch.zeros(16, device="cuda")
     p = dummy.data_ptr()
