@@ -54,7 +54,7 @@ constexpr int oW2HI = 0;
 constexpr int oW2LO = oW2HI + 128 * 64;
 constexpr int oW3HI = oW2LO + 128 * 64;
 constexpr int oW3LO = oW3HI + 64 * 128;
-constexpr int oW1 = oW3LO + 64 * 128;      // [64][8]: 6 weights, bias, 0
+constexpr int oW1 = oW3LO + 64 * 128;      // [8][64]: rows 0..5 = W1[:,k], row 6 = bias, row 7 = 0
 constexpr int oB2 = oW1 + 64 * 8;
 constexpr int oB3 = oB2 + 128;
 constexpr int oW4 = oB3 + 64;
@@ -92,7 +92,7 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
   fill_weight_sw128<128, 64>(params + CBF_W2, 64, W2hi, W2lo);
   fill_weight_sw128<64, 128>(params + CBF_W3, 128, W3hi, W3lo);
   for (int t = threadIdx.x; t < 64 * 8; t += THREADS) {
-    const int n = t >> 3, k = t & 7;
+    const int k = t >> 6, n = t & 63;
     W1[t] = (k < 6) ? __ldg(params + CBF_W1 + n * 6 + k) : (k == 6 ? __ldg(params + CBF_B1 + n) : 0.f);
   }
   for (int t = threadIdx.x; t < 128; t += THREADS) B2[t] = __ldg(params + CBF_B2 + t);
@@ -117,7 +117,7 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
     constexpr uint32_t IDESC = idesc_tf32(128, 64);
     uint32_t par = 0;
     int it = 0;
-    int trace_n = 0; (void)trace_n;
+    [[maybe_unused]] int trace_n = 0;
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, par ^= 1, ++it) {
       mbar_wait(&a2_full, par);
       fence_after_sync();
@@ -199,17 +199,28 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
       }
 #pragma unroll
       for (int half = 0; half < 2; ++half) {       // 8 channels at a time keeps the register count down
+        const float* wb = W1 + cgrp * 16 + half * 8;
+        float2 acc[4];
+        {
+          const float4 b0 = *reinterpret_cast<const float4*>(wb + 6 * 64), b1 = *reinterpret_cast<const float4*>(wb + 6 * 64 + 4);
+          acc[0] = make_float2(b0.x, b0.y); acc[1] = make_float2(b0.z, b0.w);
+          acc[2] = make_float2(b1.x, b1.y); acc[3] = make_float2(b1.z, b1.w);
+        }
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+          const float4 w0 = *reinterpret_cast<const float4*>(wb + k * 64), w1 = *reinterpret_cast<const float4*>(wb + k * 64 + 4);
+          const float2 fk = make_float2(f[k], f[k]);
+          acc[0] = __ffma2_rn(make_float2(w0.x, w0.y), fk, acc[0]);
+          acc[1] = __ffma2_rn(make_float2(w0.z, w0.w), fk, acc[1]);
+          acc[2] = __ffma2_rn(make_float2(w1.x, w1.y), fk, acc[2]);
+          acc[3] = __ffma2_rn(make_float2(w1.z, w1.w), fk, acc[3]);
+        }
         float hi[8], lo[8];
 #pragma unroll
-        for (int jn = 0; jn < 8; ++jn) {
-          const int n = cgrp * 16 + half * 8 + jn;
-          const float4 wa = *reinterpret_cast<const float4*>(W1 + n * 8);
-          const float4 wb = *reinterpret_cast<const float4*>(W1 + n * 8 + 4);
-          float v = wa.x * f[0];
-          v = fmaf(wa.y, f[1], v); v = fmaf(wa.z, f[2], v); v = fmaf(wa.w, f[3], v);
-          v = fmaf(wb.x, f[4], v); v = fmaf(wb.y, f[5], v);
-          v = fmaxf(v + wb.z, 0.f);
-          tf32_split_trunc(v, hi[jn], lo[jn]);
+        for (int p2 = 0; p2 < 4; ++p2) {
+          float2 h2, l2;
+          split2_trunc(relu2(acc[p2]), h2, l2);
+          hi[2 * p2] = h2.x; hi[2 * p2 + 1] = h2.y; lo[2 * p2] = l2.x; lo[2 * p2 + 1] = l2.y;
         }
         tmem_st8(tlane + C_A2HI + cgrp * 16 + half * 8, hi);
         tmem_st8(tlane + C_A2LO + cgrp * 16 + half * 8, lo);
@@ -226,7 +237,7 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
     prefetch_sj();
 
     uint32_t par = 0;
-    int trace_n = 0; (void)trace_n;
+    [[maybe_unused]] int trace_n = 0;
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, par ^= 1) {
       const long long a0 = tile * TA;
       const int rows = (int)min((long long)TA, agents_total - a0) * K;
@@ -247,10 +258,11 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
 #pragma unroll
           for (int j4 = 0; j4 < 2; ++j4) {
             const float4 bb = *reinterpret_cast<const float4*>(B2 + c0 + half * 8 + 4 * j4);
-            tf32_split_trunc(fmaxf(v[half * 8 + 4 * j4 + 0] + bb.x, 0.f), hi[4 * j4 + 0], lo[4 * j4 + 0]);
-            tf32_split_trunc(fmaxf(v[half * 8 + 4 * j4 + 1] + bb.y, 0.f), hi[4 * j4 + 1], lo[4 * j4 + 1]);
-            tf32_split_trunc(fmaxf(v[half * 8 + 4 * j4 + 2] + bb.z, 0.f), hi[4 * j4 + 2], lo[4 * j4 + 2]);
-            tf32_split_trunc(fmaxf(v[half * 8 + 4 * j4 + 3] + bb.w, 0.f), hi[4 * j4 + 3], lo[4 * j4 + 3]);
+            float2 h2, l2;
+            split2_trunc(relu2(__fadd2_rn(make_float2(v[half * 8 + 4 * j4 + 0], v[half * 8 + 4 * j4 + 1]), make_float2(bb.x, bb.y))), h2, l2);
+            hi[4 * j4 + 0] = h2.x; hi[4 * j4 + 1] = h2.y; lo[4 * j4 + 0] = l2.x; lo[4 * j4 + 1] = l2.y;
+            split2_trunc(relu2(__fadd2_rn(make_float2(v[half * 8 + 4 * j4 + 2], v[half * 8 + 4 * j4 + 3]), make_float2(bb.z, bb.w))), h2, l2);
+            hi[4 * j4 + 2] = h2.x; hi[4 * j4 + 3] = h2.y; lo[4 * j4 + 2] = l2.x; lo[4 * j4 + 3] = l2.y;
           }
           tmem_st8(tlane + C_Y + c0 + half * 8, hi);
           tmem_st8(tlane + C_A3LO + c0 + half * 8, lo);
@@ -276,16 +288,17 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
         tmem_ld16(tlane + C_D3S + c0, vs);
         wait_ld();
         warp_arrive_after_tmem(&d3_free);
-        float s = 0.f;
+        float2 s2 = make_float2(0.f, 0.f);
 #pragma unroll
         for (int j4 = 0; j4 < 4; ++j4) {
           const float4 bb = *reinterpret_cast<const float4*>(B3 + c0 + 4 * j4);
           const float4 ww = *reinterpret_cast<const float4*>(W4 + c0 + 4 * j4);
-          s = fmaf(ww.x, fmaxf((v[4 * j4 + 0] + vs[4 * j4 + 0]) + bb.x, 0.f), s);
-          s = fmaf(ww.y, fmaxf((v[4 * j4 + 1] + vs[4 * j4 + 1]) + bb.y, 0.f), s);
-          s = fmaf(ww.z, fmaxf((v[4 * j4 + 2] + vs[4 * j4 + 2]) + bb.z, 0.f), s);
-          s = fmaf(ww.w, fmaxf((v[4 * j4 + 3] + vs[4 * j4 + 3]) + bb.w, 0.f), s);
+          float2 x = __fadd2_rn(make_float2(v[4 * j4 + 0], v[4 * j4 + 1]), make_float2(vs[4 * j4 + 0], vs[4 * j4 + 1]));
+          s2 = __ffma2_rn(make_float2(ww.x, ww.y), relu2(__fadd2_rn(x, make_float2(bb.x, bb.y))), s2);
+          x = __fadd2_rn(make_float2(v[4 * j4 + 2], v[4 * j4 + 3]), make_float2(vs[4 * j4 + 2], vs[4 * j4 + 3]));
+          s2 = __ffma2_rn(make_float2(ww.z, ww.w), relu2(__fadd2_rn(x, make_float2(bb.z, bb.w))), s2);
         }
+        const float s = s2.x + s2.y;
         float* hp = hpart + (par * 4) * R;
         hp[cgrp * R + r] = s;
         named_bar_sync(1, WORKERS);

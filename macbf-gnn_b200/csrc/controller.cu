@@ -221,6 +221,8 @@ ctrl_node_kernel(const float* __restrict__ states, const float* __restrict__ goa
 
 int ctrl_edge_tc(const float* states, const float* obstacles, const int32_t* idx, const float* params, int B, int N,
                  int M, int K, double obs_radius, float* pool, cudaStream_t st);
+int ctrl_node_tc(const float* states, const float* goals, const float* pool, const float* params, long long agents,
+                 double dt, float* u, float* s_next, cudaStream_t st);
 
 // REPAIRED edge net runs on the tensor cores (ctrl_tc.cu); MACBF_CTRL_FFMA=1 forces the FP32-FFMA
 // kernel for A/B checks.  LITERAL always uses the FFMA kernel (row-crossing feature scramble).
@@ -272,7 +274,10 @@ int controller_forward(const float* states, const float* goals, const float* obs
     }
     MACBF_CHECK_LAUNCH("ctrl_edge_kernel");
   }
-  {
+  if (!ctrl_force_ffma()) {
+    // node net on the tensor cores (either semantics: LITERAL only changes what `pool` holds)
+    return ctrl_node_tc(states, goals, pool, params, agents, dt, u, s_next, st);
+  } else {
     const long long ntiles = (agents + cn_smem::R - 1) / cn_smem::R;
     const int grid = (int)(ntiles < NUM_SMS ? ntiles : (long long)NUM_SMS);
     const size_t smem = cn_smem::total * sizeof(float);

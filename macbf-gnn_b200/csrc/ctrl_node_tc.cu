@@ -1,0 +1,283 @@
+// K3b (tensor-core path) - controller node net, gains, action and Euler step
+// (controller.py:47-61, core.py:74-86, train.py:70) on tcgen05 / TMEM.
+//
+// A tile is 128 agents (TMEM lane = agent).  All three hidden layers run as 3xTF32 MMAs with the
+// activations in tensor memory and the hi/lo halves of the weights resident in shared memory:
+//
+//   A0 = [pool(128), p-g (2), v (2), 0-pad (4)]  -> tcgen05.st (hi, lo)         K = 136
+//   layer 1: D1[128x64]  = A0 * W1^T   (17 k-steps x 3 terms)
+//   bias + ReLU + split                            -> A1 (reuses the A0 columns)
+//   layer 2: D2[128x128] = A1 * W2^T;  bias + ReLU + split, hi in place -> A2
+//   layer 3: D3[128x64]  = A2 * W3^T
+//   bias + ReLU, 64 -> 4 (FFMA), gains 2*sigmoid+0.2, action, s' = s + [v,u] dt  -> u, s_next
+//
+// TMEM columns: A0_hi [0,136) A0_lo [136,272) D1 [272,336)   (layer 1)
+//               A1_hi [0,64)  A1_lo [64,128)  D2/A2_hi [128,256)  A2_lo [256,384)  D3 [384,448)
+// Each CTA handles only a few tiles (agents/128/148), so the phases of a tile run back to back
+// (block barriers) instead of the decoupled pipeline of the edge kernels.
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace macbf {
+
+namespace cntc {
+constexpr int THREADS = 512;
+constexpr int R = 128;
+constexpr int K1 = 136;                    // 132 inputs + 4 zero columns (k-step granularity 8)
+constexpr int K1P = 160;                   // shared-memory K extent of W1 (5 blocks of 32)
+constexpr uint32_t C_A0HI = 0, C_A0LO = 136, C_D1 = 272;
+constexpr uint32_t C_A1HI = 0, C_A1LO = 64, C_Y = 128, C_A2LO = 256, C_D3 = 384;
+constexpr int oW1HI = 0;
+constexpr int oW1LO = oW1HI + 64 * K1P;
+constexpr int oW2HI = oW1LO + 64 * K1P;
+constexpr int oW2LO = oW2HI + 128 * 64;
+constexpr int oW3HI = oW2LO + 128 * 64;
+constexpr int oW3LO = oW3HI + 64 * 128;
+constexpr int oB1 = oW3LO + 64 * 128;
+constexpr int oB2 = oB1 + 64;
+constexpr int oB3 = oB2 + 128;
+constexpr int oW4 = oB3 + 64;              // [4][64]
+constexpr int oB4 = oW4 + 256;
+constexpr int oPart = oB4 + 4;             // [4 cgrp][4 out][128]
+constexpr int total_floats = oPart + 16 * R;
+constexpr size_t smem_bytes = (size_t)total_floats * 4 + 1024;
+}  // namespace cntc
+
+__global__ void __launch_bounds__(cntc::THREADS, 1)
+ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ goals,
+                    const float* __restrict__ pool, const float* __restrict__ params, long long agents_total,
+                    float dt, float* __restrict__ u, float* __restrict__ s_next) {
+  using namespace cntc;
+  using namespace tc;
+  extern __shared__ unsigned char smem_raw[];
+  float* sm = reinterpret_cast<float*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
+  float* W1hi = sm + oW1HI; float* W1lo = sm + oW1LO;
+  float* W2hi = sm + oW2HI; float* W2lo = sm + oW2LO;
+  float* W3hi = sm + oW3HI; float* W3lo = sm + oW3LO;
+  float* B1 = sm + oB1; float* B2 = sm + oB2; float* B3 = sm + oB3; float* W4 = sm + oW4; float* B4 = sm + oB4;
+  float* part = sm + oPart;
+  __shared__ uint64_t bar[3];
+  __shared__ uint32_t tmem_base_s;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q = warp & 3, cgrp = warp >> 2;
+  const int r = q * 32 + lane;
+
+  if (warp == 0) tmem_alloc(&tmem_base_s, 512);
+  if (threadIdx.x == 32) {
+    mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_init(&bar[2], 1);
+    fence_mbar_init();
+  }
+  // W1 (64 x 132) zero-padded to K = 160 in the SWIZZLE_128B K-major layout
+  for (int t = threadIdx.x; t < 64 * (K1P / 4); t += THREADS) {
+    const int n = t / (K1P / 4), k4 = t % (K1P / 4);
+    const int kb = k4 >> 3, c = k4 & 7;
+    float h[4], l[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int k = 4 * k4 + e;
+      const float w = (k < 132) ? __ldg(params + CT_NW1 + n * 132 + k) : 0.f;
+      tf32_split(w, h[e], l[e]);
+    }
+    const int off = kb * (64 * 32) + n * 32 + ((c ^ (n & 7)) << 2);
+    *reinterpret_cast<float4*>(W1hi + off) = make_float4(h[0], h[1], h[2], h[3]);
+    *reinterpret_cast<float4*>(W1lo + off) = make_float4(l[0], l[1], l[2], l[3]);
+  }
+  fill_weight_sw128<128, 64>(params + CT_NW2, 64, W2hi, W2lo);
+  fill_weight_sw128<64, 128>(params + CT_NW3, 128, W3hi, W3lo);
+  for (int t = threadIdx.x; t < 64; t += THREADS) {
+    B1[t] = __ldg(params + CT_NB1 + t);
+    B3[t] = __ldg(params + CT_NB3 + t);
+  }
+  for (int t = threadIdx.x; t < 128; t += THREADS) B2[t] = __ldg(params + CT_NB2 + t);
+  for (int t = threadIdx.x; t < 256; t += THREADS) W4[t] = __ldg(params + CT_NW4 + t);
+  if (threadIdx.x < 4) B4[threadIdx.x] = __ldg(params + CT_NB4 + threadIdx.x);
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tbase = tmem_base_s;
+  const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16);
+  const uint32_t tb = __shfl_sync(0xffffffffu, tbase, 0);
+  const uint64_t d_w1hi = smem_desc_sw128(smem_u32(W1hi)), d_w1lo = smem_desc_sw128(smem_u32(W1lo));
+  const uint64_t d_w2hi = smem_desc_sw128(smem_u32(W2hi)), d_w2lo = smem_desc_sw128(smem_u32(W2lo));
+  const uint64_t d_w3hi = smem_desc_sw128(smem_u32(W3hi)), d_w3lo = smem_desc_sw128(smem_u32(W3lo));
+  constexpr uint32_t IDESC64 = idesc_tf32(128, 64), IDESC128 = idesc_tf32(128, 128);
+
+  const long long ntiles = (agents_total + R - 1) / R;
+  uint32_t par = 0;
+  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, par ^= 1) {
+    const long long a0 = tile * R;
+    const bool valid = a0 + r < agents_total;
+    // ---- A0 = [pool, p - g, v, 0]: this thread's 32 pooled channels (+ the 8 tail columns) ----
+    {
+      const float4* prow = reinterpret_cast<const float4*>(pool + (a0 + r) * 128 + cgrp * 32);
+#pragma unroll
+      for (int part8 = 0; part8 < 4; ++part8) {
+        float4 x0 = make_float4(0.f, 0.f, 0.f, 0.f), x1 = x0;
+        if (valid) { x0 = __ldg(prow + 2 * part8); x1 = __ldg(prow + 2 * part8 + 1); }
+        const float v[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+        float hi[8], lo[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) tf32_split_trunc(v[e], hi[e], lo[e]);
+        tmem_st8(tlane + C_A0HI + cgrp * 32 + part8 * 8, hi);
+        tmem_st8(tlane + C_A0LO + cgrp * 32 + part8 * 8, lo);
+      }
+      if (cgrp == 3) {
+        float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (valid) {
+          const float4 s = __ldg(reinterpret_cast<const float4*>(states) + a0 + r);
+          const float2 g = __ldg(reinterpret_cast<const float2*>(goals) + a0 + r);
+          v[0] = xsub(s.x, g.x); v[1] = xsub(s.y, g.y); v[2] = s.z; v[3] = s.w;   // controller.py:47
+        }
+        float hi[8], lo[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) tf32_split_trunc(v[e], hi[e], lo[e]);
+        tmem_st8(tlane + C_A0HI + 128, hi);
+        tmem_st8(tlane + C_A0LO + 128, lo);
+      }
+      wait_st();
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 0) {   // ---- layer 1 ----
+      fence_after_sync();
+#pragma unroll
+      for (int term = 0; term < 3; ++term) {           // lo*hi, hi*lo, hi*hi (small terms first)
+        const uint32_t a_col = tb + (term == 0 ? C_A0LO : C_A0HI);
+        const uint64_t b_desc = (term == 1) ? d_w1lo : d_w1hi;
+#pragma unroll
+        for (int ks = 0; ks < K1 / 8; ++ks) {
+          const uint64_t bd = desc_advance(b_desc, (ks >> 2) * (64 * 128) + (ks & 3) * 32);
+          if (elect_one()) mma_tf32_ts(tb + C_D1, a_col + ks * 8, bd, IDESC64, (term | ks) ? 1u : 0u);
+        }
+      }
+      if (elect_one()) mma_commit(&bar[0]);
+    }
+    mbar_wait(&bar[0], par);
+    fence_after_sync();
+    {  // bias + ReLU + split on this thread's 16 channels of D1 -> A1
+      const int c0 = cgrp * 16;
+      float v[16];
+      tmem_ld16(tlane + C_D1 + c0, v);
+      wait_ld();
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        float hi[8], lo[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) tf32_split_trunc(fmaxf(v[half * 8 + e] + B1[c0 + half * 8 + e], 0.f), hi[e], lo[e]);
+        tmem_st8(tlane + C_A1HI + c0 + half * 8, hi);
+        tmem_st8(tlane + C_A1LO + c0 + half * 8, lo);
+      }
+      wait_st();
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 0) {   // ---- layer 2 ----
+      fence_after_sync();
+#pragma unroll
+      for (int term = 0; term < 3; ++term) {
+        const uint32_t a_col = tb + (term == 0 ? C_A1LO : C_A1HI);
+        const uint64_t b_desc = (term == 1) ? d_w2lo : d_w2hi;
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {
+          const uint64_t bd = desc_advance(b_desc, (ks >> 2) * (128 * 128) + (ks & 3) * 32);
+          if (elect_one()) mma_tf32_ts(tb + C_Y, a_col + ks * 8, bd, IDESC128, (term | ks) ? 1u : 0u);
+        }
+      }
+      if (elect_one()) mma_commit(&bar[1]);
+    }
+    mbar_wait(&bar[1], par);
+    fence_after_sync();
+#pragma unroll
+    for (int half16 = 0; half16 < 2; ++half16) {   // bias + ReLU + split on 32 channels of D2: hi in place, lo aside
+      const int c0 = cgrp * 32 + half16 * 16;
+      float v[16];
+      tmem_ld16(tlane + C_Y + c0, v);
+      wait_ld();
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        float hi[8], lo[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) tf32_split_trunc(fmaxf(v[half * 8 + e] + B2[c0 + half * 8 + e], 0.f), hi[e], lo[e]);
+        tmem_st8(tlane + C_Y + c0 + half * 8, hi);
+        tmem_st8(tlane + C_A2LO + c0 + half * 8, lo);
+      }
+    }
+    wait_st();
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 0) {   // ---- layer 3 ----
+      fence_after_sync();
+#pragma unroll
+      for (int term = 0; term < 3; ++term) {
+        const uint32_t a_col = tb + (term == 0 ? C_A2LO : C_Y);
+        const uint64_t b_desc = (term == 1) ? d_w3lo : d_w3hi;
+#pragma unroll
+        for (int ks = 0; ks < 16; ++ks) {
+          const uint64_t bd = desc_advance(b_desc, (ks >> 2) * (64 * 128) + (ks & 3) * 32);
+          if (elect_one()) mma_tf32_ts(tb + C_D3, a_col + ks * 8, bd, IDESC64, (term | ks) ? 1u : 0u);
+        }
+      }
+      if (elect_one()) mma_commit(&bar[2]);
+    }
+    mbar_wait(&bar[2], par);
+    fence_after_sync();
+    {  // bias + ReLU and the 64 -> 4 layer over this thread's 16 channels
+      const int c0 = cgrp * 16;
+      float v[16];
+      tmem_ld16(tlane + C_D3 + c0, v);
+      wait_ld();
+      float o[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int e = 0; e < 16; ++e) {
+        const float a = fmaxf(v[e] + B3[c0 + e], 0.f);
+#pragma unroll
+        for (int qq = 0; qq < 4; ++qq) o[qq] = fmaf(W4[qq * 64 + c0 + e], a, o[qq]);
+      }
+#pragma unroll
+      for (int qq = 0; qq < 4; ++qq) part[(cgrp * 4 + qq) * R + r] = o[qq];
+    }
+    fence_before_sync();
+    __syncthreads();   // partial sums visible; every TMEM read of this tile is done
+    fence_after_sync();
+    if (cgrp == 0 && valid) {
+      float kk[4];
+#pragma unroll
+      for (int qq = 0; qq < 4; ++qq) {
+        const float o = B4[qq] + ((part[qq * R + r] + part[(4 + qq) * R + r]) + (part[(8 + qq) * R + r] + part[(12 + qq) * R + r]));
+        kk[qq] = 2.0f * (1.0f / (1.0f + expf(-o))) + 0.2f;          // controller.py:53
+      }
+      const float4 s = __ldg(reinterpret_cast<const float4*>(states) + a0 + r);
+      const float2 g = __ldg(reinterpret_cast<const float2*>(goals) + a0 + r);
+      const float ex = xsub(s.x, g.x), ey = xsub(s.y, g.y);
+      const float ax = xadd(xmul(ex, -kk[0]), xmul(s.z, -kk[1]));   // controller.py:54-61
+      const float ay = xadd(xmul(ey, -kk[2]), xmul(s.w, -kk[3]));
+      reinterpret_cast<float2*>(u)[a0 + r] = make_float2(ax, ay);
+      if (s_next != nullptr) {
+        float4 n;
+        n.x = xadd(s.x, xmul(s.z, dt)); n.y = xadd(s.y, xmul(s.w, dt));
+        n.z = xadd(s.z, xmul(ax, dt)); n.w = xadd(s.w, xmul(ay, dt));
+        reinterpret_cast<float4*>(s_next)[a0 + r] = n;
+      }
+    }
+    __syncthreads();   // `part` is rewritten by the next tile
+  }
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tbase, 512);
+}
+
+int ctrl_node_tc(const float* states, const float* goals, const float* pool, const float* params, long long agents,
+                 double dt, float* u, float* s_next, cudaStream_t st) {
+  const long long ntiles = (agents + cntc::R - 1) / cntc::R;
+  const int grid = (int)(ntiles < NUM_SMS ? ntiles : (long long)NUM_SMS);
+  MACBF_CHECK_CUDA(cudaFuncSetAttribute(ctrl_node_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)cntc::smem_bytes));
+  ctrl_node_tc_kernel<<<grid, cntc::THREADS, cntc::smem_bytes, st>>>(states, goals, pool, params, agents, (float)dt, u,
+                                                                    s_next);
+  MACBF_CHECK_LAUNCH("ctrl_node_tc_kernel");
+  return 0;
+}
+
+}  // namespace macbf

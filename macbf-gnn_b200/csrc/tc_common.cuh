@@ -167,6 +167,15 @@ __device__ __forceinline__ void tf32_split_trunc(float x, float& hi, float& lo) 
   hi = __uint_as_float(__float_as_uint(x) & 0xFFFFE000u);
   lo = x - hi;
 }
+// Packed fp32 pairs (Blackwell FFMA2/FADD2): one issue slot does two lanes of math; the epilogues
+// of the tensor-core kernels are issue-bound, so bias adds, the layer-1 FMAs and the lo = x - hi
+// subtraction (as hi * -1 + x, exact) go through these.
+__device__ __forceinline__ float2 relu2(float2 x) { return make_float2(fmaxf(x.x, 0.f), fmaxf(x.y, 0.f)); }
+__device__ __forceinline__ void split2_trunc(float2 x, float2& hi, float2& lo) {
+  hi.x = __uint_as_float(__float_as_uint(x.x) & 0xFFFFE000u);
+  hi.y = __uint_as_float(__float_as_uint(x.y) & 0xFFFFE000u);
+  lo = __ffma2_rn(hi, make_float2(-1.f, -1.f), x);
+}
 // split x into (hi, lo), both exactly representable in tf32
 __device__ __forceinline__ void tf32_split(float x, float& hi, float& lo) {
   hi = tf32_hi(x);
