@@ -165,7 +165,12 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
       for (int half = 0; half < 2; ++half) {
         float hi[8], lo[8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) tf32_split_trunc(fmaxf(v[half * 8 + e] + B1[c0 + half * 8 + e], 0.f), hi[e], lo[e]);
+        for (int e = 0; e < 8; e += 2) {
+          float2 h2, l2;
+          split2_trunc(relu2(__fadd2_rn(make_float2(v[half * 8 + e], v[half * 8 + e + 1]),
+                                        make_float2(B1[c0 + half * 8 + e], B1[c0 + half * 8 + e + 1]))), h2, l2);
+          hi[e] = h2.x; hi[e + 1] = h2.y; lo[e] = l2.x; lo[e + 1] = l2.y;
+        }
         tmem_st8(tlane + C_A1HI + c0 + half * 8, hi);
         tmem_st8(tlane + C_A1LO + c0 + half * 8, lo);
       }
@@ -199,7 +204,12 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
       for (int half = 0; half < 2; ++half) {
         float hi[8], lo[8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) tf32_split_trunc(fmaxf(v[half * 8 + e] + B2[c0 + half * 8 + e], 0.f), hi[e], lo[e]);
+        for (int e = 0; e < 8; e += 2) {
+          float2 h2, l2;
+          split2_trunc(relu2(__fadd2_rn(make_float2(v[half * 8 + e], v[half * 8 + e + 1]),
+                                        make_float2(B2[c0 + half * 8 + e], B2[c0 + half * 8 + e + 1]))), h2, l2);
+          hi[e] = h2.x; hi[e + 1] = h2.y; lo[e] = l2.x; lo[e + 1] = l2.y;
+        }
         tmem_st8(tlane + C_Y + c0 + half * 8, hi);
         tmem_st8(tlane + C_A2LO + c0 + half * 8, lo);
       }

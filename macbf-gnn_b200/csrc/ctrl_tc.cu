@@ -24,7 +24,7 @@ constexpr int RS = 132;   // stage row stride: 4 (mod 32) words -> conflict-free
 constexpr uint32_t C_A2HI = 0, C_A2LO = 64, C_D2 = 128, C_BUF = 256;
 constexpr int oW2HI = 0;
 constexpr int oW2LO = oW2HI + 128 * 64;
-constexpr int oW1 = oW2LO + 128 * 64;     // [64][8]: 5 weights, 0, bias, 0
+constexpr int oW1 = oW2LO + 128 * 64;     // [8][64]: rows 0..4 = W1[:,k], row 5 = 0, row 6 = bias, row 7 = 0
 constexpr int oB2 = oW1 + 64 * 8;
 constexpr int oStage = oB2 + 128;          // [2][128][RS]
 constexpr int total_floats = oStage + 2 * 128 * RS;
@@ -54,7 +54,7 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
   }
   fill_weight_sw128<128, 64>(params + CT_EW2, 64, W2hi, W2lo);
   for (int t = threadIdx.x; t < 64 * 8; t += THREADS) {
-    const int n = t >> 3, k = t & 7;
+    const int k = t >> 6, n = t & 63;
     W1[t] = (k < 5) ? __ldg(params + CT_EW1 + n * 5 + k) : (k == 6 ? __ldg(params + CT_EB1 + n) : 0.f);
   }
   for (int t = threadIdx.x; t < 128; t += THREADS) B2[t] = __ldg(params + CT_EB2 + t);
@@ -124,17 +124,28 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
       }
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
+        const float* wb = W1 + cgrp * 16 + half * 8;
+        float2 acc[4];
+        {
+          const float4 b0 = *reinterpret_cast<const float4*>(wb + 6 * 64), b1 = *reinterpret_cast<const float4*>(wb + 6 * 64 + 4);
+          acc[0] = make_float2(b0.x, b0.y); acc[1] = make_float2(b0.z, b0.w);
+          acc[2] = make_float2(b1.x, b1.y); acc[3] = make_float2(b1.z, b1.w);
+        }
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+          const float4 w0 = *reinterpret_cast<const float4*>(wb + k * 64), w1 = *reinterpret_cast<const float4*>(wb + k * 64 + 4);
+          const float2 fk = make_float2(f[k], f[k]);
+          acc[0] = __ffma2_rn(make_float2(w0.x, w0.y), fk, acc[0]);
+          acc[1] = __ffma2_rn(make_float2(w0.z, w0.w), fk, acc[1]);
+          acc[2] = __ffma2_rn(make_float2(w1.x, w1.y), fk, acc[2]);
+          acc[3] = __ffma2_rn(make_float2(w1.z, w1.w), fk, acc[3]);
+        }
         float hi[8], lo[8];
 #pragma unroll
-        for (int jn = 0; jn < 8; ++jn) {
-          const int n = cgrp * 16 + half * 8 + jn;
-          const float4 wa = *reinterpret_cast<const float4*>(W1 + n * 8);
-          const float4 wb = *reinterpret_cast<const float4*>(W1 + n * 8 + 4);
-          float v = wa.x * f[0];
-          v = fmaf(wa.y, f[1], v); v = fmaf(wa.z, f[2], v); v = fmaf(wa.w, f[3], v);
-          v = fmaf(wb.x, f[4], v);
-          v = fmaxf(v + wb.z, 0.f);
-          tf32_split_trunc(v, hi[jn], lo[jn]);
+        for (int p2 = 0; p2 < 4; ++p2) {
+          float2 h2, l2;
+          split2_trunc(relu2(acc[p2]), h2, l2);
+          hi[2 * p2] = h2.x; hi[2 * p2 + 1] = h2.y; lo[2 * p2] = l2.x; lo[2 * p2 + 1] = l2.y;
         }
         tmem_st8(tlane + b * C_BUF + C_A2HI + cgrp * 16 + half * 8, hi);
         tmem_st8(tlane + b * C_BUF + C_A2LO + cgrp * 16 + half * 8, lo);
@@ -169,13 +180,16 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
         float v[8];
         tmem_ld8(tlane + b * C_BUF + C_D2 + c0, v);
         wait_ld();
+        const float2 mk2 = make_float2(mk0, mk0);
 #pragma unroll
         for (int j4 = 0; j4 < 2; ++j4) {
           const float4 bb = *reinterpret_cast<const float4*>(B2 + c0 + 4 * j4);
-          stage[(c0 + 4 * j4 + 0) * RS + r] = fmaxf(v[4 * j4 + 0] + bb.x, 0.f) * mk0;
-          stage[(c0 + 4 * j4 + 1) * RS + r] = fmaxf(v[4 * j4 + 1] + bb.y, 0.f) * mk0;
-          stage[(c0 + 4 * j4 + 2) * RS + r] = fmaxf(v[4 * j4 + 2] + bb.z, 0.f) * mk0;
-          stage[(c0 + 4 * j4 + 3) * RS + r] = fmaxf(v[4 * j4 + 3] + bb.w, 0.f) * mk0;
+          const float2 y0 = __fmul2_rn(relu2(__fadd2_rn(make_float2(v[4 * j4 + 0], v[4 * j4 + 1]), make_float2(bb.x, bb.y))), mk2);
+          const float2 y1 = __fmul2_rn(relu2(__fadd2_rn(make_float2(v[4 * j4 + 2], v[4 * j4 + 3]), make_float2(bb.z, bb.w))), mk2);
+          stage[(c0 + 4 * j4 + 0) * RS + r] = y0.x;
+          stage[(c0 + 4 * j4 + 1) * RS + r] = y0.y;
+          stage[(c0 + 4 * j4 + 2) * RS + r] = y1.x;
+          stage[(c0 + 4 * j4 + 3) * RS + r] = y1.y;
         }
       }
       fence_before_sync();
