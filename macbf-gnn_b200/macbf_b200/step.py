@@ -75,10 +75,19 @@ class TrainStep:
                                                p(self.gs_next), B, N, M, K, ops.OBS_RADIUS, ops.TIME_STEP,
                                                p(self.grad_ctrl), None, None, p(self.scratch), self.scratch.numel(),
                                                st), "macbf_controller_backward")
-        if all_reduce and self.world_size > 1:
-            import torch.distributed as dist
-            dist.all_reduce(self.grad, op=dist.ReduceOp.SUM, group=self.group)
+        if all_reduce:
+            sync_gradients(self.grad, self.world_size, self.group)
         return b.scalars, self.grad
+
+
+def sync_gradients(flat_grad: torch.Tensor, world_size: int, group=None) -> torch.Tensor:
+    """The only collective of the path: all-reduce (sum) of the flat [cbf | ctrl] gradient buffer.
+    Every rank seeded its backward with 1/B_global, so the sum is the gradient of the global
+    env-mean objective.  NCCL on GPUs; the same call runs over gloo in the CPU tests."""
+    if world_size > 1:
+        import torch.distributed as dist
+        dist.all_reduce(flat_grad, op=dist.ReduceOp.SUM, group=group)
+    return flat_grad
 
 
 def shard_envs(n_envs: int, world_size: int, rank: int):

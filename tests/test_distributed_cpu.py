@@ -1,0 +1,69 @@
+"""CPU, world_size = 2 over gloo: the multi-GPU host logic without GPUs.
+
+Envs are independent, so the N>1 path is: contiguous env shards per rank, every rank's backward
+seeded with 1/B_global, ONE all-reduce(sum) of the flat 51,141-float gradient buffer
+(macbf_b200.step.sync_gradients - the call TrainStep makes over NCCL).  Here each rank computes its
+shard's gradient with the CPU oracle, goes through the same shard/seed/sync helpers over gloo, and
+the result must equal the un-sharded env-mean gradient.
+"""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, B, N, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.set_num_threads(2)
+        from macbf_b200 import step
+        from oracle import macbf_oracle as O
+        s, g = O.synthetic_swarm(B, N, seed=77)
+        p_cbf, p_ctrl = O.init_params(6)
+        lo, hi = step.shard_envs(B, world, rank)
+        seeds = step.env_mean_grad_scalars(hi - lo, B)
+        # weight of total (column 9) implied by the seeds: 20 on l_dang = 10 * 2 / B_global ...
+        assert abs(float(seeds[0, 0]) - 20.0 / B) < 1e-12 and seeds.shape == (hi - lo, 12)
+        flat = torch.zeros(17089 + 34052)
+        for b in range(lo, hi):
+            out = O.full_step(p_cbf, p_ctrl, s[b], g[b], with_grad=True)
+            flat += torch.cat([out["grad_cbf"], out["grad_ctrl"]]) / B
+        step.sync_gradients(flat, world)
+        np.save(os.path.join(out_dir, f"grad_rank{rank}.npy"), flat.numpy())
+    finally:
+        dist.destroy_process_group()
+
+
+def test_env_sharding_and_single_allreduce_gloo(tmp_path):
+    from macbf_b200 import step
+    from oracle import macbf_oracle as O
+    B, N, world = 5, 40, 2          # uneven shards: 3 + 2 envs
+    assert [step.shard_envs(B, world, r) for r in range(world)] == [(0, 3), (3, 5)]
+    assert [step.shard_envs(8, 4, r) for r in range(4)] == [(0, 2), (2, 4), (4, 6), (6, 8)]
+    port = _free_port()
+    mp.spawn(_worker, args=(world, port, B, N, str(tmp_path)), nprocs=world, join=True)
+    g0 = np.load(tmp_path / "grad_rank0.npy")
+    g1 = np.load(tmp_path / "grad_rank1.npy")
+    assert np.array_equal(g0, g1)   # every rank ends with the same gradient -> identical Adam steps
+    s, g = O.synthetic_swarm(B, N, seed=77)
+    p_cbf, p_ctrl = O.init_params(6)
+    ref = np.zeros_like(g0, dtype=np.float64)
+    for b in range(B):
+        out = O.full_step(p_cbf, p_ctrl, s[b], g[b], with_grad=True)
+        ref += torch.cat([out["grad_cbf"], out["grad_ctrl"]]).numpy().astype(np.float64) / B
+    scale = np.abs(ref).max()
+    assert np.abs(g0 - ref).max() <= 1e-5 * scale
