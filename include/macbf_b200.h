@@ -70,6 +70,11 @@ int macbf_neighbor_topk_ws(const float* states, const float* obstacles, int B, i
                            int top_k, int32_t* idx, void* workspace, size_t workspace_bytes,
                            void* stream);
 
+/* The reference's own call shape: core.remove_distant_agents(x[N,C,F], k) on an already
+ * materialised pair tensor (core.py:234-250); keys from x[i,j,0:2].  idx [N,k] int32 (column
+ * indices, ascending key, ties by index).  Requires k < C (core.py:236-237 returns x otherwise). */
+int macbf_dense_topk(const float* x, int N, int C, int F, int k, int32_t* idx, void* stream);
+
 /* ---- A2,A4,A5: CBF head  (cbf.py:21-45) ------------------------------------------------
  * h[b,i,k] = mask * MLP_cbf([dx,dy,dvx,dvy,eye, d - dist_min_thres]),
  * d = sqrt((dx^2+1e-4)+(dy^2+1e-4)), mask = d <= obs_radius.  h is [B,N,K] (the reference's

@@ -18,6 +18,7 @@ void count_launch(int n) { g_launches += n; }
 
 // implemented in the kernel translation units
 int neighbor_topk(const float*, const float*, int, int, int, int, int32_t*, cudaStream_t);
+int dense_topk(const float*, int, int, int, int, int32_t*, cudaStream_t);
 size_t neighbor_grid_workspace_bytes(int, int, int);
 bool neighbor_grid_applicable(int, int, int);
 int neighbor_topk_grid(const float*, const float*, int, int, int, int, int32_t*, void*, size_t, cudaStream_t);
@@ -80,6 +81,14 @@ int macbf_neighbor_topk(const float* states, const float* obstacles, int B, int 
   REQ_PTR(fn, states); REQ_PTR(fn, idx); REQ_A16(fn, states);
   MACBF_CHECK_ARG(M == 0 || obstacles != nullptr, "%s: obstacles is NULL but M=%d", fn, M);
   return neighbor_topk(states, obstacles, B, N, M, top_k, idx, (cudaStream_t)stream);
+}
+
+int macbf_dense_topk(const float* x, int N, int C, int F, int k, int32_t* idx, void* stream) {
+  const char* fn = "macbf_dense_topk";
+  MACBF_CHECK_ARG(N >= 1 && C >= 1 && F >= 2, "%s: bad extents N=%d C=%d F=%d (F >= 2: dx, dy lead)", fn, N, C, F);
+  MACBF_CHECK_ARG(k >= 1 && k <= MACBF_MAX_K && k < C, "%s: k=%d must be in [1,%d] and < C=%d", fn, k, MACBF_MAX_K, C);
+  REQ_PTR(fn, x); REQ_PTR(fn, idx);
+  return dense_topk(x, N, C, F, k, idx, (cudaStream_t)stream);
 }
 
 size_t macbf_neighbor_workspace_bytes(int B, int N, int M, int top_k) {

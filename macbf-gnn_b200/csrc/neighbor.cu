@@ -140,6 +140,55 @@ knn_kernel(const float* __restrict__ states, const float* __restrict__ obstacles
   }
 }
 
+// Dense variant for the reference's own call shape (core.py:234-250 takes the materialised
+// (N, C, F) pair tensor): keys come from x[i, j, 0:2], one warp per row, same list and order.
+template <int S>
+__global__ void __launch_bounds__(KNN_THREADS)
+knn_dense_kernel(const float* __restrict__ x, int N, int C, int F, int K, int32_t* __restrict__ idx_out) {
+  const int lane = threadIdx.x & 31;
+  const int i = blockIdx.x * KNN_WARPS + (threadIdx.x >> 5);
+  if (i >= N) return;
+  const float* row = x + (size_t)i * C * F;
+  TopList<S> top;
+  top.init();
+  float vthr = __int_as_float(0x7f800000);
+  for (int t0 = 0; t0 < C; t0 += 32) {
+    const int t = t0 + lane;
+    const bool valid = t < C;
+    float v = 0.f;
+    if (valid) {
+      const float dx = __ldg(row + (size_t)t * F), dy = __ldg(row + (size_t)t * F + 1);
+      v = xadd(xadd(xmul(dx, dx), 1e-6f), xadd(xmul(dy, dy), 1e-6f));   // core.py:238
+    }
+    unsigned pass = __ballot_sync(0xffffffffu, valid && (v < vthr));
+    while (pass) {
+      const int src = __ffs(pass) - 1;
+      pass &= pass - 1;
+      const float kc = __fsqrt_rn(__shfl_sync(0xffffffffu, v, src));
+      if (kc < top.key_at(K - 1)) {
+        top.insert(kc, t0 + src, lane);
+        const float nk = top.key_at(K - 1);
+        vthr = __fmul_ru(nk, nk);
+      }
+    }
+  }
+  int32_t* o = idx_out + (size_t)i * K;
+#pragma unroll
+  for (int s = 0; s < S; ++s) {
+    const int e = s * 32 + lane;
+    if (e < K) o[e] = top.idx[s];
+  }
+}
+
+int dense_topk(const float* x, int N, int C, int F, int K, int32_t* idx, cudaStream_t st) {
+  const int grid = (N + KNN_WARPS - 1) / KNN_WARPS;
+  if (K <= 32) knn_dense_kernel<1><<<grid, KNN_THREADS, 0, st>>>(x, N, C, F, K, idx);
+  else if (K <= 64) knn_dense_kernel<2><<<grid, KNN_THREADS, 0, st>>>(x, N, C, F, K, idx);
+  else knn_dense_kernel<4><<<grid, KNN_THREADS, 0, st>>>(x, N, C, F, K, idx);
+  MACBF_CHECK_LAUNCH("knn_dense_kernel");
+  return 0;
+}
+
 // N + M <= top_k: every candidate, in index order (core.py:236-237, repair F3).
 __global__ void knn_all_kernel(int total, int C, int32_t* __restrict__ idx_out) {
   int t = blockIdx.x * blockDim.x + threadIdx.x;

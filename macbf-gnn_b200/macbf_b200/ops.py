@@ -83,6 +83,17 @@ def neighbor_topk(states: torch.Tensor, top_k: int = TOP_K, obstacles: Optional[
     return idx
 
 
+def dense_topk(x: torch.Tensor, k: int) -> torch.Tensor:
+    """core.remove_distant_agents' selection on a materialised pair tensor x [N,C,F] -> idx [N,k] int32."""
+    _need_cuda(x)
+    x = _c(x)
+    n, c, f = x.shape
+    idx = torch.empty((n, k), dtype=torch.int32, device=x.device)
+    L = _lib.load()
+    _lib.check(L.macbf_dense_topk(_p(x), n, c, f, k, _p(idx), _stream()), "macbf_dense_topk")
+    return idx
+
+
 def cbf_forward(states, idx, cbf_params, obstacles=None, semantics=REPAIRED, dist_min_thres=DIST_MIN_THRES,
                 obs_radius=OBS_RADIUS) -> torch.Tensor:
     """cbf.py:21-45 -> h [B,N,K]."""

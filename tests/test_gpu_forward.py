@@ -250,3 +250,23 @@ def test_grid_search_adversarial_layouts(ops):
     same = torch.zeros(1, 400, 4)                                    # every agent at the same point
     idx = _grid_vs_brute(ops, same, 12)
     assert np.array_equal(idx[0, :, :].cpu().numpy(), np.tile(np.arange(12), (400, 1)))
+
+
+def test_remove_distant_agents_dense_api(ops):
+    """core.remove_distant_agents(x[N,N,C], k) - the reference's dense call shape (core.py:234-250) -
+    against the reference-made fixture: gathered rows and the (N*k, 2) index table."""
+    import core
+    z = load_npz("ref_n200_vel.npz")
+    s = dev(z["states"])
+    x = s.unsqueeze(1) - s.unsqueeze(0)
+    x = torch.cat([x, torch.eye(s.shape[0], device="cuda").unsqueeze(2)], dim=2)
+    xk, ind = core.remove_distant_agents(x, 12)
+    assert np.array_equal(ind.cpu().numpy(), z["idx"])
+    assert np.array_equal(xk.cpu().numpy(), z["xk"])
+    small, none = core.remove_distant_agents(x[:8, :8], 12)      # <= k candidates: unchanged (repair F3)
+    assert none is None and small.shape == (8, 8, 5)
+    # ttc_dangerous_mask / dynamics through the drop-in module
+    m = core.ttc_dangerous_mask(s)
+    assert m.shape == (200, 12, 1) and m.dtype == torch.bool
+    u = dev(z["u"])
+    assert np.array_equal(core.dynamics(s, u).cpu().numpy(), z["dsdt"])
