@@ -1,27 +1,29 @@
 // K2 (tensor-core path) - fused CBF head (cbf.py:21-45, REPAIRED) on tcgen05 / TMEM.
 //
 // One persistent CTA per SM: 16 worker warps + 1 MMA-issue warp, decoupled by mbarriers so the
-// tensor core never waits for the CUDA cores in steady state.  A tile is 128 edge rows
-// (floor(128/K) agents); row r is TMEM lane r.  Worker warp w owns lanes 32*(w%4).. (the lanes
-// tcgen05.ld/st lets it touch) and column group w/4 of whatever is being produced.
+// tensor core is never idle in steady state.  A tile is 128 edge rows (floor(128/K) agents);
+// row r is TMEM lane r.  Worker warp w owns lanes 32*(w%4).. (the lanes tcgen05.ld/st lets it
+// touch) and column group w/4 of whatever is being produced.  ALL dense layers of the MLP
+// except the final 64->1 dot run on the tensor core; the CUDA cores only build the 6 edge
+// features and run the epilogues:
 //
-//   workers   features + layer 1 (6->64, FFMA) -> tf32 hi/lo -> tcgen05.st        A2   (TMEM)
-//   MMA warp  layer 2: D2[128x128] = A2 * W2^T in two 64-column chunks, 3xTF32     D2   (TMEM)
-//   workers   per chunk: tcgen05.ld, bias + ReLU, hi/lo; hi overwrites D2 in place A3   (TMEM)
-//   MMA warp  layer 3: per 64-wide K chunk, cross terms -> D3s, hi*hi -> D3        D3   (TMEM)
-//   workers   (D3 + D3s) bias + ReLU, 64 -> 1 dot, * mask                          h    (global)
+//   workers(4 warps)  edge features (cbf.py:23-37) -> tf32 hi/lo -> shared memory A1 [128 x 8]
+//   MMA warp          layer 1: D1[128x64]  = A1 * W1^T      (A and B from smem, K = 8)
+//   workers           tcgen05.ld, bias + ReLU, hi/lo; hi overwrites D1 in place   -> A2   (TMEM)
+//   MMA warp          layer 2: D2[128x128] = A2 * W2^T in two 64-column chunks    -> D2   (TMEM)
+//   workers           per chunk: bias + ReLU, hi/lo; hi overwrites D2 in place    -> A3   (TMEM)
+//   MMA warp          layer 3: per 64-wide K chunk, cross terms -> D3s, hi*hi     -> D3   (TMEM)
+//   workers           (D3 + D3s) bias + ReLU, 64 -> 1 dot, * mask                 -> h    (global)
 //
-// While the tensor core runs layer 3 of tile i the workers already build A2 of tile i+1, and
-// layer 2 of tile i+1 runs while they finish tile i, so the MMA stream is back to back.
-// Hidden activations never leave the SM (registers -> TMEM -> tensor core -> TMEM -> registers);
-// shared memory holds the weights only: hi and lo tf32 halves of W2 and W3 in the canonical
-// SWIZZLE_128B K-major layout (128 KB) plus small vectors.
+// Issue order of the MMA warp: L2(i), L1(i+1), L3(i), L2(i+1), ... so the workers turn D1(i+1)
+// into A2(i+1) while the tensor core runs L3(i), and L2(i+1) starts the moment L3(i) retires.
+// Every GEMM is a 3xTF32 split (hi*hi + lo*hi + hi*lo) with fp32 accumulation in TMEM; the small
+// cross terms go first (layers 1, 2) or into their own accumulator D3s (K-chunked layer 3) because
+// the tensor core's accumulate is not round-to-nearest (tools/tc_probe.cu).
+// Hidden activations never leave the SM.  Shared memory: hi/lo halves of W1, W2, W3 in the
+// canonical SWIZZLE_128B K-major layout (144 KB), the A1 staging tiles (32 KB), small vectors.
 //
-// 3xTF32 ordering: the tensor core's fp32 accumulate is not round-to-nearest, so the small cross
-// terms (lo*hi, hi*lo) are accumulated where the running sum is small: first within a layer-2
-// chunk, and into their own accumulator D3s for the K-chunked layer 3 (tools/tc_probe.cu).
-//
-// TMEM columns: [0,64) A2_hi  [64,128) A2_lo  [128,256) D2 -> A3_hi (in place)
+// TMEM columns: [0,64) D1 -> A2_hi (in place)  [64,128) A2_lo  [128,256) D2 -> A3_hi (in place)
 //               [256,384) A3_lo  [384,448) D3  [448,512) D3s
 #include "common.cuh"
 #include "tc_common.cuh"
@@ -49,13 +51,17 @@ constexpr int WORKERS = 512;
 constexpr int THREADS = WORKERS + 32;
 constexpr int R = 128;
 constexpr uint32_t C_A2HI = 0, C_A2LO = 64, C_Y = 128, C_A3LO = 256, C_D3 = 384, C_D3S = 448;
-// dynamic shared memory (floats, after 1024-B alignment)
+// dynamic shared memory (floats, after 1024-B alignment); every MMA operand slab is 1024-B aligned
 constexpr int oW2HI = 0;
 constexpr int oW2LO = oW2HI + 128 * 64;
 constexpr int oW3HI = oW2LO + 128 * 64;
 constexpr int oW3LO = oW3HI + 64 * 128;
-constexpr int oW1 = oW3LO + 64 * 128;      // [8][64]: rows 0..5 = W1[:,k], row 6 = bias, row 7 = 0
-constexpr int oB2 = oW1 + 64 * 8;
+constexpr int oW1HI = oW3LO + 64 * 128;    // [64 rows][32]: k = 0..5 used (one 128-B swizzle row per channel)
+constexpr int oW1LO = oW1HI + 64 * 32;
+constexpr int oA1HI = oW1LO + 64 * 32;     // [128 rows][32]: the 6 edge features of the next tile
+constexpr int oA1LO = oA1HI + 128 * 32;
+constexpr int oB1 = oA1LO + 128 * 32;
+constexpr int oB2 = oB1 + 64;
 constexpr int oB3 = oB2 + 128;
 constexpr int oW4 = oB3 + 64;
 constexpr int oB4 = oW4 + 64;
@@ -74,50 +80,70 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
   float* sm = reinterpret_cast<float*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
   float* W2hi = sm + oW2HI; float* W2lo = sm + oW2LO;
   float* W3hi = sm + oW3HI; float* W3lo = sm + oW3LO;
-  float* W1 = sm + oW1; float* B2 = sm + oB2; float* B3 = sm + oB3; float* W4 = sm + oW4; float* B4 = sm + oB4;
+  float* W1hi = sm + oW1HI; float* W1lo = sm + oW1LO;
+  float* A1hi = sm + oA1HI; float* A1lo = sm + oA1LO;
+  float* B1 = sm + oB1; float* B2 = sm + oB2; float* B3 = sm + oB3; float* W4 = sm + oW4; float* B4 = sm + oB4;
   float* hpart = sm + oHpart;
-  // workers -> MMA: a2_full, a3_full[2], d3_free (16 arrivals: one per worker warp)
-  // MMA -> workers (tcgen05.commit): d2_full[2], d3_full
-  __shared__ uint64_t a2_full, a3_full[2], d3_free, d2_full[2], d3_full;
+  // workers -> MMA: a1_full (4 arrivals: the feature warps), a2_full, a3_full[2], d3_free (16: one per worker warp)
+  // MMA -> workers (tcgen05.commit): d1_full, d2_full[2], d3_full
+  __shared__ uint64_t a1_full, a2_full, a3_full[2], d3_free, d1_full, d2_full[2], d3_full;
   __shared__ uint32_t tmem_base_s;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (warp == 0) tmem_alloc(&tmem_base_s, 512);
   if (threadIdx.x == 32) {
-    mbar_init(&a2_full, 16); mbar_init(&a3_full[0], 16); mbar_init(&a3_full[1], 16); mbar_init(&d3_free, 16);
-    mbar_init(&d2_full[0], 1); mbar_init(&d2_full[1], 1); mbar_init(&d3_full, 1);
+    mbar_init(&a1_full, 4); mbar_init(&a2_full, 16); mbar_init(&a3_full[0], 16); mbar_init(&a3_full[1], 16);
+    mbar_init(&d3_free, 16);
+    mbar_init(&d1_full, 1); mbar_init(&d2_full[0], 1); mbar_init(&d2_full[1], 1); mbar_init(&d3_full, 1);
     fence_mbar_init();
   }
   fill_weight_sw128<128, 64>(params + CBF_W2, 64, W2hi, W2lo);
   fill_weight_sw128<64, 128>(params + CBF_W3, 128, W3hi, W3lo);
-  for (int t = threadIdx.x; t < 64 * 8; t += THREADS) {
-    const int k = t >> 6, n = t & 63;
-    W1[t] = (k < 6) ? __ldg(params + CBF_W1 + n * 6 + k) : (k == 6 ? __ldg(params + CBF_B1 + n) : 0.f);
+  // W1 (64 x 6): channel n is one 128-B row; 16-B chunk c sits at position c ^ (n & 7); A1 likewise
+  for (int t = threadIdx.x; t < 64 * 32; t += THREADS) {
+    const int n = t >> 5, pos = (t >> 2) & 7, e = t & 3;
+    const int k = ((pos ^ (n & 7)) << 2) + e;
+    float hi = 0.f, lo = 0.f;
+    if (k < 6) tf32_split(__ldg(params + CBF_W1 + n * 6 + k), hi, lo);
+    W1hi[t] = hi; W1lo[t] = lo;
   }
+  for (int t = threadIdx.x; t < 128 * 32; t += THREADS) { A1hi[t] = 0.f; A1lo[t] = 0.f; }
   for (int t = threadIdx.x; t < 128; t += THREADS) B2[t] = __ldg(params + CBF_B2 + t);
   for (int t = threadIdx.x; t < 64; t += THREADS) {
+    B1[t] = __ldg(params + CBF_B1 + t);
     B3[t] = __ldg(params + CBF_B3 + t);
     W4[t] = __ldg(params + CBF_W4 + t);
   }
   if (threadIdx.x == 0) B4[0] = __ldg(params + CBF_B4);
-  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // weights: generic proxy -> tensor-core proxy
+  fence_proxy_async_smem();   // weights and zeroed A1 tiles: generic proxy -> tensor-core proxy
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
   const uint32_t tbase = tmem_base_s;
   const long long ntiles = (agents_total + TA - 1) / TA;
+  [[maybe_unused]] int trace_n = 0;
 
   if (warp == WORKERS / 32) {
     // =============================== MMA-issue warp ===============================
     // Everything here is warp-uniform; only the tcgen05 instructions sit under elect_one().
+    const uint64_t d_w1hi = smem_desc_sw128(smem_u32(W1hi)), d_w1lo = smem_desc_sw128(smem_u32(W1lo));
+    const uint64_t d_a1hi = smem_desc_sw128(smem_u32(A1hi)), d_a1lo = smem_desc_sw128(smem_u32(A1lo));
     const uint64_t d_w2hi = smem_desc_sw128(smem_u32(W2hi)), d_w2lo = smem_desc_sw128(smem_u32(W2lo));
     const uint64_t d_w3hi = smem_desc_sw128(smem_u32(W3hi)), d_w3lo = smem_desc_sw128(smem_u32(W3lo));
     const uint32_t tb = __shfl_sync(0xffffffffu, tbase, 0);
     constexpr uint32_t IDESC = idesc_tf32(128, 64);
+    auto issue_layer1 = [&](uint32_t parity) {       // D1 = A1 * W1^T, one k-step of 8 per term
+      mbar_wait(&a1_full, parity);
+      fence_after_sync();
+      if (elect_one()) mma_tf32_ss(tb + C_A2HI, d_a1lo, d_w1hi, IDESC, 0u);
+      if (elect_one()) mma_tf32_ss(tb + C_A2HI, d_a1hi, d_w1lo, IDESC, 1u);
+      if (elect_one()) mma_tf32_ss(tb + C_A2HI, d_a1hi, d_w1hi, IDESC, 1u);
+      if (elect_one()) mma_commit(&d1_full);
+    };
+    issue_layer1(0);
     uint32_t par = 0;
     int it = 0;
-    [[maybe_unused]] int trace_n = 0;
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, par ^= 1, ++it) {
       mbar_wait(&a2_full, par);
       fence_after_sync();
@@ -138,6 +164,8 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
         if (elect_one()) mma_commit(&d2_full[c]);
       }
       TC_TRACE(1, 2);
+      // layer 1 of the next tile: its D1 lands in the A2 columns this tile's layer 2 has just finished reading
+      if (tile + gridDim.x < ntiles) issue_layer1(par ^ 1);
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
         mbar_wait(&a3_full[c], par);
@@ -166,15 +194,15 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
     const int q = warp & 3, cgrp = warp >> 2;
     const int r = q * 32 + lane;
     const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16);
+    const int a_loc = r / K;                       // agent of this row within a tile (tile-invariant)
 
-    // edge endpoints of upcoming tiles are fetched one phase ahead of their use
+    // Edge endpoints of upcoming tiles are fetched one phase ahead of their use (feature warps only).
     int pf_j = 0, pf_b = 0, pf_i = 0;
     bool pf_valid = false;
     float4 pf_si = make_float4(0.f, 0.f, 0.f, 0.f), pf_sj = pf_si;
-    const int a_loc = r / K;                       // agent of this row within a tile (tile-invariant)
     auto prefetch_ij = [&](long long t) {
       pf_valid = false;
-      if (t < ntiles) {
+      if (cgrp == 0 && t < ntiles) {
         const int ga = (int)(t * TA) + a_loc;      // B*N < 2^31 is checked by the host
         if (a_loc < TA && ga < (int)agents_total) {
           pf_b = ga / N; pf_i = ga - pf_b * N;
@@ -187,9 +215,9 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
     auto prefetch_sj = [&]() {
       if (pf_valid) pf_sj = load_candidate(states, obstacles, pf_b, pf_j, N, M);
     };
-    // features (cbf.py:23-37) + layer 1 for this thread's 16 channels -> A2; returns the radius mask
-    auto layer1 = [&]() -> float {
-      float f[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    // features (cbf.py:23-37) of this thread's row -> A1 (smem, swizzled row r); returns the radius mask
+    auto features = [&]() -> float {
+      float f[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
       float mk = 0.f;
       if (pf_valid) {
         const EdgeGeom g = edge_geom(pf_si, pf_sj, pf_i, pf_j);
@@ -197,51 +225,66 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
         f[0] = g.dx; f[1] = g.dy; f[2] = g.dvx; f[3] = g.dvy; f[4] = g.eye; f[5] = xsub(d, dist_min);
         mk = (d <= obs_radius) ? 1.f : 0.f;
       }
+      float hi[8], lo[8];
 #pragma unroll
-      for (int half = 0; half < 2; ++half) {       // 8 channels at a time keeps the register count down
-        const float* wb = W1 + cgrp * 16 + half * 8;
-        float2 acc[4];
-        {
-          const float4 b0 = *reinterpret_cast<const float4*>(wb + 6 * 64), b1 = *reinterpret_cast<const float4*>(wb + 6 * 64 + 4);
-          acc[0] = make_float2(b0.x, b0.y); acc[1] = make_float2(b0.z, b0.w);
-          acc[2] = make_float2(b1.x, b1.y); acc[3] = make_float2(b1.z, b1.w);
-        }
+      for (int e = 0; e < 8; ++e) tf32_split(f[e], hi[e], lo[e]);
+      const int p0 = (0 ^ (r & 7)) << 2, p1 = (1 ^ (r & 7)) << 2;      // swizzled positions of chunks 0 and 1
+      *reinterpret_cast<float4*>(A1hi + r * 32 + p0) = make_float4(hi[0], hi[1], hi[2], hi[3]);
+      *reinterpret_cast<float4*>(A1hi + r * 32 + p1) = make_float4(hi[4], hi[5], hi[6], hi[7]);
+      *reinterpret_cast<float4*>(A1lo + r * 32 + p0) = make_float4(lo[0], lo[1], lo[2], lo[3]);
+      *reinterpret_cast<float4*>(A1lo + r * 32 + p1) = make_float4(lo[4], lo[5], lo[6], lo[7]);
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&a1_full);
+      return mk;
+    };
+    // layer-1 epilogue: D1 -> bias + ReLU + split -> A2 (hi in place over D1, lo aside)
+    auto epilogue1 = [&](uint32_t parity) {
+      mbar_wait(&d1_full, parity);
+      fence_after_sync();
+      const int c0 = cgrp * 16;
+      float v[16];
+      tmem_ld16(tlane + C_A2HI + c0, v);
+      wait_ld();
 #pragma unroll
-        for (int k = 0; k < 6; ++k) {
-          const float4 w0 = *reinterpret_cast<const float4*>(wb + k * 64), w1 = *reinterpret_cast<const float4*>(wb + k * 64 + 4);
-          const float2 fk = make_float2(f[k], f[k]);
-          acc[0] = __ffma2_rn(make_float2(w0.x, w0.y), fk, acc[0]);
-          acc[1] = __ffma2_rn(make_float2(w0.z, w0.w), fk, acc[1]);
-          acc[2] = __ffma2_rn(make_float2(w1.x, w1.y), fk, acc[2]);
-          acc[3] = __ffma2_rn(make_float2(w1.z, w1.w), fk, acc[3]);
-        }
+      for (int half = 0; half < 2; ++half) {
         float hi[8], lo[8];
 #pragma unroll
-        for (int p2 = 0; p2 < 4; ++p2) {
+        for (int j4 = 0; j4 < 2; ++j4) {
+          const float4 bb = *reinterpret_cast<const float4*>(B1 + c0 + half * 8 + 4 * j4);
           float2 h2, l2;
-          split2_trunc(relu2(acc[p2]), h2, l2);
-          hi[2 * p2] = h2.x; hi[2 * p2 + 1] = h2.y; lo[2 * p2] = l2.x; lo[2 * p2 + 1] = l2.y;
+          split2_trunc(relu2(__fadd2_rn(make_float2(v[half * 8 + 4 * j4 + 0], v[half * 8 + 4 * j4 + 1]), make_float2(bb.x, bb.y))), h2, l2);
+          hi[4 * j4 + 0] = h2.x; hi[4 * j4 + 1] = h2.y; lo[4 * j4 + 0] = l2.x; lo[4 * j4 + 1] = l2.y;
+          split2_trunc(relu2(__fadd2_rn(make_float2(v[half * 8 + 4 * j4 + 2], v[half * 8 + 4 * j4 + 3]), make_float2(bb.z, bb.w))), h2, l2);
+          hi[4 * j4 + 2] = h2.x; hi[4 * j4 + 3] = h2.y; lo[4 * j4 + 2] = l2.x; lo[4 * j4 + 3] = l2.y;
         }
-        tmem_st8(tlane + C_A2HI + cgrp * 16 + half * 8, hi);
-        tmem_st8(tlane + C_A2LO + cgrp * 16 + half * 8, lo);
+        tmem_st8(tlane + C_A2HI + c0 + half * 8, hi);
+        tmem_st8(tlane + C_A2LO + c0 + half * 8, lo);
       }
       wait_st();
       warp_arrive_after_tmem(&a2_full);
-      return mk;
     };
 
+    // Software pipeline of the feature warps: the features of tile t+2 are built during tile t
+    // (in the slack before its layer-3 epilogue), so layer 1 of the next tile never waits for them.
+    const long long g = gridDim.x;
+    float m0 = 0.f, m1 = 0.f, m2 = 0.f;              // radius masks of tiles t, t+g, t+2g (feature warps)
     prefetch_ij(blockIdx.x);
     prefetch_sj();
-    float mk_next = layer1();
-    prefetch_ij((long long)blockIdx.x + gridDim.x);
+    if (cgrp == 0) m0 = features();
+    epilogue1(0);
+    prefetch_ij(blockIdx.x + g);
     prefetch_sj();
+    if (cgrp == 0 && blockIdx.x + g < ntiles) m1 = features();
+    prefetch_ij(blockIdx.x + 2 * g);
 
     uint32_t par = 0;
-    [[maybe_unused]] int trace_n = 0;
-    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, par ^= 1) {
+    for (long long tile = blockIdx.x; tile < ntiles; tile += g, par ^= 1) {
       const long long a0 = tile * TA;
       const int rows = (int)min((long long)TA, agents_total - a0) * K;
-      const float mk = mk_next;
+      const float mk = m0;
+      const bool has_next = tile + g < ntiles;
+      prefetch_sj();                                   // endpoints of tile + 2g (their idx arrived last iteration)
       // ---- layer-2 epilogue per 64-column chunk: bias + ReLU + split; hi in place, lo aside ----
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
@@ -271,10 +314,12 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
         warp_arrive_after_tmem(&a3_full[c]);
         if (warp == 0) TC_TRACE(0, 2 + 2 * c);
       }
-      // ---- layer 2 of this tile has completed (d2_full[1]): A2 is free -> next tile's layer 1 ----
-      if (tile + gridDim.x < ntiles) {
-        mk_next = layer1();
-        prefetch_ij(tile + 2 * (long long)gridDim.x);
+      // ---- layer-1 epilogue of the NEXT tile (overlaps this tile's layer 3 on the tensor core) ----
+      if (has_next) epilogue1(par ^ 1);
+      // ---- features of tile + 2g -> A1 (layer 1 of tile + g has retired: d1_full was just observed) ----
+      if (cgrp == 0 && tile + 2 * g < ntiles) {
+        m2 = features();
+        prefetch_ij(tile + 3 * g);
       }
       if (warp == 0) TC_TRACE(0, 5);
       // ---- layer-3 epilogue: (D3 + D3s) bias + ReLU, 64 -> 1 over this thread's 16 channels ----
@@ -307,8 +352,8 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
           h[a0 * K + r] = (t + B4[0]) * mk;          // cbf.py:43
         }
       }
-      prefetch_sj();
       if (warp == 0) TC_TRACE(0, 7);
+      m0 = m1; m1 = m2;
     }
   }
   fence_before_sync();
@@ -319,6 +364,7 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
 int cbf_forward_tc(const float* states, const float* obstacles, const int32_t* idx, const float* params, int B, int N,
                    int M, int K, double dist_min, double obs_radius, float* h, cudaStream_t st) {
   const long long agents = (long long)B * N;
+  MACBF_CHECK_ARG(agents < (1ll << 31), "cbf_forward: B*N must be < 2^31");
   const int TA = max(1, cbftc::R / K);
   const long long ntiles = (agents + TA - 1) / TA;
   const int grid = (int)(ntiles < NUM_SMS ? ntiles : (long long)NUM_SMS);

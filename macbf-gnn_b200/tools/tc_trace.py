@@ -25,7 +25,7 @@ buf = np.zeros((2, 4096), dtype=np.uint64)
 fn = L.macbf_debug_tc_trace
 fn.argtypes = [ctypes.c_void_p]
 assert fn(buf.ctypes.data) == 0
-names = {0: {1: "E2c0.start", 2: "E2c0.end", 3: "E2c1.start", 4: "E2c1.end", 5: "L1next.end", 6: "E3.start", 7: "E3.end"},
+names = {0: {1: "E2c0.start", 2: "E2c0.end", 3: "E2c1.start", 4: "E2c1.end", 5: "L1next.end", 6: "E3.start", 7: "E3.end", 8: "L1.features", 9: "L1.half0", 10: "L1.half1", 11: "L1.begin"},
          1: {1: "a2.ready", 2: "mma2.issued", 3: "a3[0].ready", 4: "a3[1].ready", 5: "mma3.issued"}}
 ev = []
 for who in (0, 1):
