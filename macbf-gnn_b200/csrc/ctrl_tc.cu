@@ -1,16 +1,21 @@
 // K3a (tensor-core path) - controller edge net + masked max pooling (controller.py:33-46,
 // REPAIRED) on tcgen05 / TMEM.
 //
-// One persistent CTA per SM: 16 worker warps + 1 MMA-issue warp, two tiles in flight (TMEM and
-// the pooling stage are double-buffered), so the tensor core computes tile i+1 while the CUDA
-// cores post-process tile i and prepare tile i+2.  A tile is 128 edge rows = floor(128/K) agents.
+// One persistent CTA per SM: 16 worker warps + 1 MMA-issue warp, two tiles in flight (the TMEM
+// tile is double-buffered), so the tensor core computes tile i+1 while the CUDA cores post-process
+// tile i and prepare tile i+2.  A tile is 128 edge rows = floor(128/K) agents.  Both dense layers
+// run on the tensor core as 3xTF32 MMAs (cross terms first); the CUDA cores build the 5 edge
+// features and run the epilogues:
 //
-//   workers   features + layer 1 (5->64, FFMA) -> tf32 hi/lo -> tcgen05.st   A2[b] (TMEM)
-//   MMA warp  layer 2: D2[b][128x128] = A2[b] * W2^T, 3xTF32 (cross terms first)
-//   workers   tcgen05.ld, bias + ReLU + * mask -> stage[b] (smem, [channel][row])
-//             max over the K slots of every agent -> pool [agents,128] (global)
+//   workers(4 warps)  edge features (controller.py:33-40) -> tf32 hi/lo -> smem A1 [128 x 8]
+//   MMA warp          layer 1: D1[b][128x64]  = A1 * W1^T    (A and B from smem, K = 8)
+//   workers           bias + ReLU, hi/lo; hi overwrites D1 in place              -> A2[b] (TMEM)
+//   MMA warp          layer 2: D2[b][128x128] = A2[b] * W2^T (A from TMEM)
+//   workers           bias + ReLU + * mask -> stage (smem, [channel][row])
+//                     max over the K slots of every agent                         -> pool (global)
 //
-// TMEM columns of buffer b: 256 b + [0,64) A2_hi, [64,128) A2_lo, [128,256) D2.
+// MMA issue order: L2(i), L1(i+2), L2(i+1), L1(i+3), ...
+// TMEM columns of buffer b: 256 b + [0,64) D1 -> A2_hi, [64,128) A2_lo, [128,256) D2.
 #include "common.cuh"
 #include "tc_common.cuh"
 
@@ -24,10 +29,15 @@ constexpr int RS = 132;   // stage row stride: 4 (mod 32) words -> conflict-free
 constexpr uint32_t C_A2HI = 0, C_A2LO = 64, C_D2 = 128, C_BUF = 256;
 constexpr int oW2HI = 0;
 constexpr int oW2LO = oW2HI + 128 * 64;
-constexpr int oW1 = oW2LO + 128 * 64;     // [8][64]: rows 0..4 = W1[:,k], row 5 = 0, row 6 = bias, row 7 = 0
-constexpr int oB2 = oW1 + 64 * 8;
-constexpr int oStage = oB2 + 128;          // [2][128][RS]
-constexpr int total_floats = oStage + 2 * 128 * RS;
+constexpr int oW1HI = oW2LO + 128 * 64;    // [64 rows][32]: k = 0..4 used
+constexpr int oW1LO = oW1HI + 64 * 32;
+constexpr int oA1HI = oW1LO + 64 * 32;     // [128 rows][32]
+constexpr int oA1LO = oA1HI + 128 * 32;
+constexpr int oB1 = oA1LO + 128 * 32;
+constexpr int oB2 = oB1 + 64;
+constexpr int oMask = oB2 + 128;           // [128] radius mask of the tile being pooled
+constexpr int oStage = oMask + 128;        // [128][RS]
+constexpr int total_floats = oStage + 128 * RS;
 constexpr size_t smem_bytes = (size_t)total_floats * 4 + 1024;
 }  // namespace cetc
 
@@ -40,38 +50,62 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
   extern __shared__ unsigned char smem_raw[];
   float* sm = reinterpret_cast<float*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
   float* W2hi = sm + oW2HI; float* W2lo = sm + oW2LO;
-  float* W1 = sm + oW1; float* B2 = sm + oB2; float* stage_all = sm + oStage;
-  __shared__ uint64_t a2_full[2], d2_full[2];   // workers -> MMA (16 arrivals) / MMA -> workers (commit)
+  float* W1hi = sm + oW1HI; float* W1lo = sm + oW1LO;
+  float* A1hi = sm + oA1HI; float* A1lo = sm + oA1LO;
+  float* B1 = sm + oB1; float* B2 = sm + oB2; float* mask = sm + oMask; float* stage = sm + oStage;
+  // workers -> MMA: a1_full (4 arrivals: feature warps), a2_full[2] (16);  MMA -> workers: d1_full[2], d2_full[2]
+  // (per-buffer barriers advance every second tile, so a lagging warp can never be lapped by two phases)
+  __shared__ uint64_t a1_full, a2_full[2], d1_full[2], d2_full[2];
   __shared__ uint32_t tmem_base_s;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (warp == 0) tmem_alloc(&tmem_base_s, 512);
   if (threadIdx.x == 32) {
-    mbar_init(&a2_full[0], 16); mbar_init(&a2_full[1], 16);
-    mbar_init(&d2_full[0], 1); mbar_init(&d2_full[1], 1);
+    mbar_init(&a1_full, 4); mbar_init(&a2_full[0], 16); mbar_init(&a2_full[1], 16);
+    mbar_init(&d1_full[0], 1); mbar_init(&d1_full[1], 1); mbar_init(&d2_full[0], 1); mbar_init(&d2_full[1], 1);
     fence_mbar_init();
   }
   fill_weight_sw128<128, 64>(params + CT_EW2, 64, W2hi, W2lo);
-  for (int t = threadIdx.x; t < 64 * 8; t += THREADS) {
-    const int k = t >> 6, n = t & 63;
-    W1[t] = (k < 5) ? __ldg(params + CT_EW1 + n * 5 + k) : (k == 6 ? __ldg(params + CT_EB1 + n) : 0.f);
+  for (int t = threadIdx.x; t < 64 * 32; t += THREADS) {   // W1 (64 x 5): chunk c of row n at position c ^ (n & 7)
+    const int n = t >> 5, pos = (t >> 2) & 7, e = t & 3;
+    const int k = ((pos ^ (n & 7)) << 2) + e;
+    float hi = 0.f, lo = 0.f;
+    if (k < 5) tf32_split(__ldg(params + CT_EW1 + n * 5 + k), hi, lo);
+    W1hi[t] = hi; W1lo[t] = lo;
   }
+  for (int t = threadIdx.x; t < 128 * 32; t += THREADS) { A1hi[t] = 0.f; A1lo[t] = 0.f; }
+  for (int t = threadIdx.x; t < 64; t += THREADS) B1[t] = __ldg(params + CT_EB1 + t);
   for (int t = threadIdx.x; t < 128; t += THREADS) B2[t] = __ldg(params + CT_EB2 + t);
-  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  fence_proxy_async_smem();
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
   const uint32_t tbase = tmem_base_s;
   const long long ntiles = (agents_total + TA - 1) / TA;
+  const long long g = gridDim.x;
 
   if (warp == WORKERS / 32) {
     // =============================== MMA-issue warp ===============================
+    const uint64_t d_w1hi = smem_desc_sw128(smem_u32(W1hi)), d_w1lo = smem_desc_sw128(smem_u32(W1lo));
+    const uint64_t d_a1hi = smem_desc_sw128(smem_u32(A1hi)), d_a1lo = smem_desc_sw128(smem_u32(A1lo));
     const uint64_t d_w2hi = smem_desc_sw128(smem_u32(W2hi)), d_w2lo = smem_desc_sw128(smem_u32(W2lo));
     const uint32_t tb = __shfl_sync(0xffffffffu, tbase, 0);
-    constexpr uint32_t IDESC = idesc_tf32(128, 128);
+    constexpr uint32_t IDESC1 = idesc_tf32(128, 64), IDESC2 = idesc_tf32(128, 128);
+    // layer 1 of local tile ordinal j (TMEM buffer j & 1); a1_full / d1_full complete once per tile
+    auto issue_layer1 = [&](int j) {
+      mbar_wait(&a1_full, j & 1);
+      fence_after_sync();
+      const uint32_t d1 = tb + (j & 1) * C_BUF + C_A2HI;
+      if (elect_one()) mma_tf32_ss(d1, d_a1lo, d_w1hi, IDESC1, 0u);
+      if (elect_one()) mma_tf32_ss(d1, d_a1hi, d_w1lo, IDESC1, 1u);
+      if (elect_one()) mma_tf32_ss(d1, d_a1hi, d_w1hi, IDESC1, 1u);
+      if (elect_one()) mma_commit(&d1_full[j & 1]);
+    };
+    issue_layer1(0);
+    if (blockIdx.x + g < ntiles) issue_layer1(1);
     int it = 0;
-    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+    for (long long tile = blockIdx.x; tile < ntiles; tile += g, ++it) {
       const int b = it & 1;
       mbar_wait(&a2_full[b], (it >> 1) & 1);
       fence_after_sync();
@@ -83,10 +117,12 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks) {
           const uint64_t bd = desc_advance(b_desc, (ks >> 2) * (128 * 128) + (ks & 3) * 32);
-          if (elect_one()) mma_tf32_ts(t0 + C_D2, a_col + ks * 8, bd, IDESC, (term | ks) ? 1u : 0u);
+          if (elect_one()) mma_tf32_ts(t0 + C_D2, a_col + ks * 8, bd, IDESC2, (term | ks) ? 1u : 0u);
         }
       }
       if (elect_one()) mma_commit(&d2_full[b]);
+      // layer 1 of tile + 2g goes into this buffer's A2 columns (layer 2 above has consumed them in order)
+      if (tile + 2 * g < ntiles) issue_layer1(it + 2);
     }
   } else {
     // ================================= worker warps =================================
@@ -100,7 +136,7 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
     float4 pf_si = make_float4(0.f, 0.f, 0.f, 0.f), pf_sj = pf_si;
     auto prefetch_ij = [&](long long t) {
       pf_valid = false;
-      if (t < ntiles) {
+      if (cgrp == 0 && t < ntiles) {
         const int ga = (int)(t * TA) + a_loc;      // B*N < 2^31 is checked by the host
         if (a_loc < TA && ga < (int)agents_total) {
           pf_b = ga / N; pf_i = ga - pf_b * N;
@@ -113,79 +149,95 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
     auto prefetch_sj = [&]() {
       if (pf_valid) pf_sj = load_candidate(states, obstacles, pf_b, pf_j, N, M);
     };
-    // features (controller.py:33-40) + layer 1 for this thread's 16 channels -> A2[b]; returns the mask
-    auto layer1 = [&](int b) -> float {
-      float f[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+    // features (controller.py:33-40) of this thread's row -> A1 (smem, swizzled); returns the radius mask
+    auto features = [&]() -> float {
+      float f[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
       float mk = 0.f;
       if (pf_valid) {
-        const EdgeGeom g = edge_geom(pf_si, pf_sj, pf_i, pf_j);
-        f[0] = g.dx; f[1] = g.dy; f[2] = g.dvx; f[3] = g.dvy; f[4] = g.eye;
-        mk = (ctrl_dist(g.dx, g.dy) < obs_radius) ? 1.f : 0.f;   // controller.py:38-39
+        const EdgeGeom e = edge_geom(pf_si, pf_sj, pf_i, pf_j);
+        f[0] = e.dx; f[1] = e.dy; f[2] = e.dvx; f[3] = e.dvy; f[4] = e.eye;
+        mk = (ctrl_dist(e.dx, e.dy) < obs_radius) ? 1.f : 0.f;   // controller.py:38-39
       }
+      float hi[8], lo[8];
 #pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        const float* wb = W1 + cgrp * 16 + half * 8;
-        float2 acc[4];
-        {
-          const float4 b0 = *reinterpret_cast<const float4*>(wb + 6 * 64), b1 = *reinterpret_cast<const float4*>(wb + 6 * 64 + 4);
-          acc[0] = make_float2(b0.x, b0.y); acc[1] = make_float2(b0.z, b0.w);
-          acc[2] = make_float2(b1.x, b1.y); acc[3] = make_float2(b1.z, b1.w);
-        }
-#pragma unroll
-        for (int k = 0; k < 5; ++k) {
-          const float4 w0 = *reinterpret_cast<const float4*>(wb + k * 64), w1 = *reinterpret_cast<const float4*>(wb + k * 64 + 4);
-          const float2 fk = make_float2(f[k], f[k]);
-          acc[0] = __ffma2_rn(make_float2(w0.x, w0.y), fk, acc[0]);
-          acc[1] = __ffma2_rn(make_float2(w0.z, w0.w), fk, acc[1]);
-          acc[2] = __ffma2_rn(make_float2(w1.x, w1.y), fk, acc[2]);
-          acc[3] = __ffma2_rn(make_float2(w1.z, w1.w), fk, acc[3]);
-        }
-        float hi[8], lo[8];
-#pragma unroll
-        for (int p2 = 0; p2 < 4; ++p2) {
-          float2 h2, l2;
-          split2_trunc(relu2(acc[p2]), h2, l2);
-          hi[2 * p2] = h2.x; hi[2 * p2 + 1] = h2.y; lo[2 * p2] = l2.x; lo[2 * p2 + 1] = l2.y;
-        }
-        tmem_st8(tlane + b * C_BUF + C_A2HI + cgrp * 16 + half * 8, hi);
-        tmem_st8(tlane + b * C_BUF + C_A2LO + cgrp * 16 + half * 8, lo);
-      }
-      wait_st();
-      warp_arrive_after_tmem(&a2_full[b]);
+      for (int e = 0; e < 8; ++e) tf32_split_trunc(f[e], hi[e], lo[e]);
+      const int p0 = (0 ^ (r & 7)) << 2, p1 = (1 ^ (r & 7)) << 2;
+      *reinterpret_cast<float4*>(A1hi + r * 32 + p0) = make_float4(hi[0], hi[1], hi[2], hi[3]);
+      *reinterpret_cast<float4*>(A1hi + r * 32 + p1) = make_float4(hi[4], hi[5], hi[6], hi[7]);
+      *reinterpret_cast<float4*>(A1lo + r * 32 + p0) = make_float4(lo[0], lo[1], lo[2], lo[3]);
+      *reinterpret_cast<float4*>(A1lo + r * 32 + p1) = make_float4(lo[4], lo[5], lo[6], lo[7]);
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&a1_full);
       return mk;
     };
+    // layer-1 epilogue of local tile ordinal j: D1 -> bias + ReLU + split -> A2[j & 1]
+    auto epilogue1 = [&](int j) {
+      mbar_wait(&d1_full[j & 1], (j >> 1) & 1);
+      fence_after_sync();
+      const uint32_t tl = tlane + (j & 1) * C_BUF;
+      const int c0 = cgrp * 16;
+      float v[16];
+      tmem_ld16(tl + C_A2HI + c0, v);
+      wait_ld();
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        float hi[8], lo[8];
+#pragma unroll
+        for (int j4 = 0; j4 < 2; ++j4) {
+          const float4 bb = *reinterpret_cast<const float4*>(B1 + c0 + half * 8 + 4 * j4);
+          float2 h2, l2;
+          split2_trunc(relu2(__fadd2_rn(make_float2(v[half * 8 + 4 * j4 + 0], v[half * 8 + 4 * j4 + 1]), make_float2(bb.x, bb.y))), h2, l2);
+          hi[4 * j4 + 0] = h2.x; hi[4 * j4 + 1] = h2.y; lo[4 * j4 + 0] = l2.x; lo[4 * j4 + 1] = l2.y;
+          split2_trunc(relu2(__fadd2_rn(make_float2(v[half * 8 + 4 * j4 + 2], v[half * 8 + 4 * j4 + 3]), make_float2(bb.z, bb.w))), h2, l2);
+          hi[4 * j4 + 2] = h2.x; hi[4 * j4 + 3] = h2.y; lo[4 * j4 + 2] = l2.x; lo[4 * j4 + 3] = l2.y;
+        }
+        tmem_st8(tl + C_A2HI + c0 + half * 8, hi);
+        tmem_st8(tl + C_A2LO + c0 + half * 8, lo);
+      }
+      wait_st();
+      warp_arrive_after_tmem(&a2_full[j & 1]);
+    };
 
-    const long long g = gridDim.x;
+    // prologue: tiles 0 and 1 through layer 1, features of tile 2 staged
+    float m0 = 0.f, m1 = 0.f, m2 = 0.f;              // radius masks of tiles t, t+g, t+2g (feature warps)
     prefetch_ij(blockIdx.x);
     prefetch_sj();
-    float mk0 = layer1(0), mk1 = 0.f;
+    if (cgrp == 0) m0 = features();
+    epilogue1(0);                                     // also proves layer 1 of tile 0 has read A1
     prefetch_ij(blockIdx.x + g);
     prefetch_sj();
-    if (blockIdx.x + g < ntiles) mk1 = layer1(1);
+    if (blockIdx.x + g < ntiles) {
+      if (cgrp == 0) m1 = features();
+      epilogue1(1);
+    }
     prefetch_ij(blockIdx.x + 2 * g);
+    prefetch_sj();
+    if (cgrp == 0 && blockIdx.x + 2 * g < ntiles) m2 = features();
+    prefetch_ij(blockIdx.x + 3 * g);
 
     int it = 0;
     for (long long tile = blockIdx.x; tile < ntiles; tile += g, ++it) {
       const int b = it & 1;
       const long long a0 = tile * TA;
       const int na = (int)min((long long)TA, agents_total - a0);
-      float* stage = stage_all + b * (128 * RS);
-      prefetch_sj();                                   // endpoints of tile + 2g (idx arrived last iteration)
+      prefetch_sj();                                   // endpoints of tile + 3g (idx arrived last iteration)
       mbar_wait(&d2_full[b], (it >> 1) & 1);
       fence_after_sync();
-      // ---- bias + ReLU + mask on this thread's 32 columns -> stage[c][r] ----
+      named_bar_sync(2, WORKERS);                      // previous tile's pooling has finished reading `stage`
+      if (cgrp == 0) mask[r] = m0;
+      // ---- bias + ReLU on this thread's 32 columns -> stage[c][r] (mask applied while pooling) ----
 #pragma unroll
       for (int part = 0; part < 4; ++part) {
         const int c0 = cgrp * 32 + part * 8;
         float v[8];
         tmem_ld8(tlane + b * C_BUF + C_D2 + c0, v);
         wait_ld();
-        const float2 mk2 = make_float2(mk0, mk0);
 #pragma unroll
         for (int j4 = 0; j4 < 2; ++j4) {
           const float4 bb = *reinterpret_cast<const float4*>(B2 + c0 + 4 * j4);
-          const float2 y0 = __fmul2_rn(relu2(__fadd2_rn(make_float2(v[4 * j4 + 0], v[4 * j4 + 1]), make_float2(bb.x, bb.y))), mk2);
-          const float2 y1 = __fmul2_rn(relu2(__fadd2_rn(make_float2(v[4 * j4 + 2], v[4 * j4 + 3]), make_float2(bb.z, bb.w))), mk2);
+          const float2 y0 = relu2(__fadd2_rn(make_float2(v[4 * j4 + 0], v[4 * j4 + 1]), make_float2(bb.x, bb.y)));
+          const float2 y1 = relu2(__fadd2_rn(make_float2(v[4 * j4 + 2], v[4 * j4 + 3]), make_float2(bb.z, bb.w)));
           stage[(c0 + 4 * j4 + 0) * RS + r] = y0.x;
           stage[(c0 + 4 * j4 + 1) * RS + r] = y0.y;
           stage[(c0 + 4 * j4 + 2) * RS + r] = y1.x;
@@ -193,26 +245,33 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
         }
       }
       fence_before_sync();
-      named_bar_sync(1, WORKERS);                      // stage[b] complete
-      // ---- max over the K slots (controller.py:46, repair F2: values) ----
-      for (int item = threadIdx.x; item < na * 128; item += WORKERS) {
-        const int c = item & 127, a = item >> 7;
-        const float* row = stage + c * RS + a * K;
-        float best = 0.f;                              // relu(.) * mask >= 0; slot 0 (self) is never masked
-        if ((K & 3) == 0) {
-          for (int k = 0; k < K; k += 4) {
-            const float4 x = *reinterpret_cast<const float4*>(row + k);
-            best = fmaxf(fmaxf(best, fmaxf(x.x, x.y)), fmaxf(x.z, x.w));
+      named_bar_sync(1, WORKERS);                      // stage complete; D2[b] fully read
+      // ---- layer-1 epilogue of tile + 2g into this buffer (its layer 1 was issued right after layer 2 above) ----
+      if (tile + 2 * g < ntiles) epilogue1(it + 2);
+      if (cgrp != 0) {
+        // ---- masked max over the K slots (controller.py:46, repair F2: values): 12 of the 16 warps ----
+        for (int item = threadIdx.x - 128; item < na * 128; item += WORKERS - 128) {
+          const int c = item & 127, a = item >> 7;
+          const float* row = stage + c * RS + a * K;
+          const float* mrow = mask + a * K;
+          float best = 0.f;                            // relu(.) * mask >= 0; slot 0 (self) is never masked
+          if ((K & 3) == 0) {
+            for (int k = 0; k < K; k += 4) {
+              const float4 x = *reinterpret_cast<const float4*>(row + k);
+              const float4 mm = *reinterpret_cast<const float4*>(mrow + k);
+              best = fmaxf(fmaxf(best, fmaxf(x.x * mm.x, x.y * mm.y)), fmaxf(x.z * mm.z, x.w * mm.w));
+            }
+          } else {
+            for (int k = 0; k < K; ++k) best = fmaxf(best, row[k] * mrow[k]);
           }
-        } else {
-          for (int k = 0; k < K; ++k) best = fmaxf(best, row[k]);
+          pool[(a0 + a) * 128 + c] = best;
         }
-        pool[(a0 + a) * 128 + c] = best;
       }
-      // ---- D2[b] and A2[b] are free: features + layer 1 of tile + 2g, then fetch idx of tile + 3g ----
-      mk0 = mk1;
-      if (tile + 2 * g < ntiles) mk1 = layer1(b);
-      prefetch_ij(tile + 3 * g);
+      // ---- ... while the 4 feature warps build A1 of tile + 3g (layer 1 of tile + 2g has retired:
+      //      d1_full was observed in epilogue1 above) ----
+      m0 = m1; m1 = m2;
+      if (cgrp == 0 && tile + 3 * g < ntiles) m2 = features();
+      prefetch_ij(tile + 4 * g);
     }
   }
   fence_before_sync();
