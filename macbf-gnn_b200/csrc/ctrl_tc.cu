@@ -21,6 +21,20 @@
 
 namespace macbf {
 
+#ifdef MACBF_TRACE
+__device__ unsigned long long g_ce_trace[3][4096];
+#define CE_TRACE(who, ev)                                                                          \
+  do {                                                                                             \
+    if (blockIdx.x == 0 && lane == 0 && trace_n < 4096)                                            \
+      g_ce_trace[who][trace_n++] = ((unsigned long long)(ev) << 56) | (clock64() & 0x00ffffffffffffffull); \
+  } while (0)
+extern "C" int macbf_debug_ce_trace(unsigned long long* host_out) {
+  return (int)cudaMemcpyFromSymbol(host_out, g_ce_trace, sizeof(g_ce_trace));
+}
+#else
+#define CE_TRACE(who, ev) do { } while (0)
+#endif
+
 namespace cetc {
 constexpr int WORKERS = 512;
 constexpr int THREADS = WORKERS + 32;
@@ -35,8 +49,8 @@ constexpr int oA1HI = oW1LO + 64 * 32;     // [128 rows][32]
 constexpr int oA1LO = oA1HI + 128 * 32;
 constexpr int oB1 = oA1LO + 128 * 32;
 constexpr int oB2 = oB1 + 64;
-constexpr int oMask = oB2 + 128;           // [128] radius mask of the tile being pooled
-constexpr int oStage = oMask + 128;        // [128][RS]
+constexpr int oMask = oB2 + 128;           // [4][128] radius masks of the tiles in flight (tile ordinal & 3)
+constexpr int oStage = oMask + 4 * 128;    // [128][RS]
 constexpr int total_floats = oStage + 128 * RS;
 constexpr size_t smem_bytes = (size_t)total_floats * 4 + 1024;
 }  // namespace cetc
@@ -84,6 +98,7 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
   const uint32_t tbase = tmem_base_s;
   const long long ntiles = (agents_total + TA - 1) / TA;
   const long long g = gridDim.x;
+  [[maybe_unused]] int trace_n = 0;
 
   if (warp == WORKERS / 32) {
     // =============================== MMA-issue warp ===============================
@@ -109,6 +124,7 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
       const int b = it & 1;
       mbar_wait(&a2_full[b], (it >> 1) & 1);
       fence_after_sync();
+      CE_TRACE(1, 1);
       const uint32_t t0 = tb + b * C_BUF;
 #pragma unroll
       for (int term = 0; term < 3; ++term) {           // lo*hi, hi*lo, hi*hi
@@ -121,8 +137,10 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
         }
       }
       if (elect_one()) mma_commit(&d2_full[b]);
+      CE_TRACE(1, 2);
       // layer 1 of tile + 2g goes into this buffer's A2 columns (layer 2 above has consumed them in order)
       if (tile + 2 * g < ntiles) issue_layer1(it + 2);
+      CE_TRACE(1, 3);
     }
   } else {
     // ================================= worker warps =================================
@@ -150,7 +168,7 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
       if (pf_valid) pf_sj = load_candidate(states, obstacles, pf_b, pf_j, N, M);
     };
     // features (controller.py:33-40) of this thread's row -> A1 (smem, swizzled); returns the radius mask
-    auto features = [&]() -> float {
+    auto features = [&](int j) {
       float f[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
       float mk = 0.f;
       if (pf_valid) {
@@ -166,10 +184,10 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
       *reinterpret_cast<float4*>(A1hi + r * 32 + p1) = make_float4(hi[4], hi[5], hi[6], hi[7]);
       *reinterpret_cast<float4*>(A1lo + r * 32 + p0) = make_float4(lo[0], lo[1], lo[2], lo[3]);
       *reinterpret_cast<float4*>(A1lo + r * 32 + p1) = make_float4(lo[4], lo[5], lo[6], lo[7]);
+      mask[(j & 3) * 128 + r] = mk;                     // read by every warp's layer-2 epilogue of tile j
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(&a1_full);
-      return mk;
     };
     // layer-1 epilogue of local tile ordinal j: D1 -> bias + ReLU + split -> A2[j & 1]
     auto epilogue1 = [&](int j) {
@@ -200,20 +218,19 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
     };
 
     // prologue: tiles 0 and 1 through layer 1, features of tile 2 staged
-    float m0 = 0.f, m1 = 0.f, m2 = 0.f;              // radius masks of tiles t, t+g, t+2g (feature warps)
     prefetch_ij(blockIdx.x);
     prefetch_sj();
-    if (cgrp == 0) m0 = features();
+    if (cgrp == 0) features(0);
     epilogue1(0);                                     // also proves layer 1 of tile 0 has read A1
     prefetch_ij(blockIdx.x + g);
     prefetch_sj();
     if (blockIdx.x + g < ntiles) {
-      if (cgrp == 0) m1 = features();
+      if (cgrp == 0) features(1);
       epilogue1(1);
     }
     prefetch_ij(blockIdx.x + 2 * g);
     prefetch_sj();
-    if (cgrp == 0 && blockIdx.x + 2 * g < ntiles) m2 = features();
+    if (cgrp == 0 && blockIdx.x + 2 * g < ntiles) features(2);
     prefetch_ij(blockIdx.x + 3 * g);
 
     int it = 0;
@@ -224,54 +241,63 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
       prefetch_sj();                                   // endpoints of tile + 3g (idx arrived last iteration)
       mbar_wait(&d2_full[b], (it >> 1) & 1);
       fence_after_sync();
-      named_bar_sync(2, WORKERS);                      // previous tile's pooling has finished reading `stage`
-      if (cgrp == 0) mask[r] = m0;
-      // ---- bias + ReLU on this thread's 32 columns -> stage[c][r] (mask applied while pooling) ----
+      if (warp == 0) CE_TRACE(0, 1); else if (warp == 15) CE_TRACE(2, 1);
+      named_bar_sync(2, WORKERS);
+      if (warp == 0) CE_TRACE(0, 2); else if (warp == 15) CE_TRACE(2, 2);                      // previous tile's pooling has finished reading `stage`
+      // ---- bias + ReLU + mask on this thread's 32 columns -> stage[c][r] ----
+      {
+        const float mk = mask[(it & 3) * 128 + r];
+        const float2 mk2 = make_float2(mk, mk);
+        float v[32];
 #pragma unroll
-      for (int part = 0; part < 4; ++part) {
-        const int c0 = cgrp * 32 + part * 8;
-        float v[8];
-        tmem_ld8(tlane + b * C_BUF + C_D2 + c0, v);
+        for (int part = 0; part < 4; ++part) tmem_ld8(tlane + b * C_BUF + C_D2 + cgrp * 32 + part * 8, v + part * 8);
         wait_ld();
 #pragma unroll
-        for (int j4 = 0; j4 < 2; ++j4) {
-          const float4 bb = *reinterpret_cast<const float4*>(B2 + c0 + 4 * j4);
-          const float2 y0 = relu2(__fadd2_rn(make_float2(v[4 * j4 + 0], v[4 * j4 + 1]), make_float2(bb.x, bb.y)));
-          const float2 y1 = relu2(__fadd2_rn(make_float2(v[4 * j4 + 2], v[4 * j4 + 3]), make_float2(bb.z, bb.w)));
-          stage[(c0 + 4 * j4 + 0) * RS + r] = y0.x;
-          stage[(c0 + 4 * j4 + 1) * RS + r] = y0.y;
-          stage[(c0 + 4 * j4 + 2) * RS + r] = y1.x;
-          stage[(c0 + 4 * j4 + 3) * RS + r] = y1.y;
+        for (int j4 = 0; j4 < 8; ++j4) {
+          const int c0 = cgrp * 32 + 4 * j4;
+          const float4 bb = *reinterpret_cast<const float4*>(B2 + c0);
+          const float2 y0 = __fmul2_rn(relu2(__fadd2_rn(make_float2(v[4 * j4 + 0], v[4 * j4 + 1]), make_float2(bb.x, bb.y))), mk2);
+          const float2 y1 = __fmul2_rn(relu2(__fadd2_rn(make_float2(v[4 * j4 + 2], v[4 * j4 + 3]), make_float2(bb.z, bb.w))), mk2);
+          stage[(c0 + 0) * RS + r] = y0.x;
+          stage[(c0 + 1) * RS + r] = y0.y;
+          stage[(c0 + 2) * RS + r] = y1.x;
+          stage[(c0 + 3) * RS + r] = y1.y;
         }
       }
       fence_before_sync();
+      if (warp == 0) CE_TRACE(0, 3); else if (warp == 15) CE_TRACE(2, 3);
       named_bar_sync(1, WORKERS);                      // stage complete; D2[b] fully read
+      if (warp == 0) CE_TRACE(0, 4); else if (warp == 15) CE_TRACE(2, 4);
       // ---- layer-1 epilogue of tile + 2g into this buffer (its layer 1 was issued right after layer 2 above) ----
       if (tile + 2 * g < ntiles) epilogue1(it + 2);
+      if (warp == 0) CE_TRACE(0, 5); else if (warp == 15) CE_TRACE(2, 5);
       if (cgrp != 0) {
         // ---- masked max over the K slots (controller.py:46, repair F2: values): 12 of the 16 warps ----
         for (int item = threadIdx.x - 128; item < na * 128; item += WORKERS - 128) {
           const int c = item & 127, a = item >> 7;
           const float* row = stage + c * RS + a * K;
-          const float* mrow = mask + a * K;
           float best = 0.f;                            // relu(.) * mask >= 0; slot 0 (self) is never masked
-          if ((K & 3) == 0) {
+          if (K == 12) {                               // the reference's TOP_K: three independent 16-byte loads
+            const float4 x0 = *reinterpret_cast<const float4*>(row), x1 = *reinterpret_cast<const float4*>(row + 4),
+                         x2 = *reinterpret_cast<const float4*>(row + 8);
+            best = fmaxf(fmaxf(fmaxf(x0.x, x0.y), fmaxf(x0.z, x0.w)),
+                         fmaxf(fmaxf(fmaxf(x1.x, x1.y), fmaxf(x1.z, x1.w)), fmaxf(fmaxf(x2.x, x2.y), fmaxf(x2.z, x2.w))));
+          } else if ((K & 3) == 0) {
             for (int k = 0; k < K; k += 4) {
               const float4 x = *reinterpret_cast<const float4*>(row + k);
-              const float4 mm = *reinterpret_cast<const float4*>(mrow + k);
-              best = fmaxf(fmaxf(best, fmaxf(x.x * mm.x, x.y * mm.y)), fmaxf(x.z * mm.z, x.w * mm.w));
+              best = fmaxf(fmaxf(best, fmaxf(x.x, x.y)), fmaxf(x.z, x.w));
             }
           } else {
-            for (int k = 0; k < K; ++k) best = fmaxf(best, row[k] * mrow[k]);
+            for (int k = 0; k < K; ++k) best = fmaxf(best, row[k]);
           }
           pool[(a0 + a) * 128 + c] = best;
         }
       }
       // ---- ... while the 4 feature warps build A1 of tile + 3g (layer 1 of tile + 2g has retired:
       //      d1_full was observed in epilogue1 above) ----
-      m0 = m1; m1 = m2;
-      if (cgrp == 0 && tile + 3 * g < ntiles) m2 = features();
+      if (cgrp == 0 && tile + 3 * g < ntiles) features(it + 3);
       prefetch_ij(tile + 4 * g);
+      if (warp == 0) CE_TRACE(0, 6); else if (warp == 15) CE_TRACE(2, 6);
     }
   }
   fence_before_sync();
