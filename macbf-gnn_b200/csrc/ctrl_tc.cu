@@ -22,6 +22,20 @@
 
 namespace macbf {
 
+#ifdef MACBF_TRACE
+__device__ unsigned long long g_ce_trace[3][4096];
+#define CE_TRACE(who, ev)                                                                          \
+  do {                                                                                             \
+    if (blockIdx.x == 0 && lane == 0 && trace_n < 4096)                                            \
+      g_ce_trace[who][trace_n++] = ((unsigned long long)(ev) << 56) | (clock64() & 0x00ffffffffffffffull); \
+  } while (0)
+extern "C" int macbf_debug_ce_trace(unsigned long long* host_out) {
+  return (int)cudaMemcpyFromSymbol(host_out, g_ce_trace, sizeof(g_ce_trace));
+}
+#else
+#define CE_TRACE(who, ev) do { } while (0)
+#endif
+
 namespace cetc {
 constexpr int GROUP_THREADS = 256;           // 8 worker warps per group
 constexpr int WORKERS = 2 * GROUP_THREADS;
@@ -85,6 +99,7 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
   const uint32_t tbase = tmem_base_s;
   const long long ntiles = (agents_total + TA - 1) / TA;
   const long long gdim = gridDim.x;
+  [[maybe_unused]] int trace_n = 0;
 
   if (warp >= WORKERS / 32) {
     // ========================= MMA-issue warp of group gi =========================
@@ -110,6 +125,7 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
     for (long long tile = first; tile < ntiles; tile += 2 * gdim, ++j) {
       mbar_wait(&a2_full[gi], j & 1);
       fence_after_sync();
+      if (gi == 0) CE_TRACE(1, 1);
 #pragma unroll
       for (int term = 0; term < 3; ++term) {           // lo*hi, hi*lo, hi*hi
         const uint32_t a_col = tg + (term == 0 ? C_A2LO : C_A2HI);
@@ -121,8 +137,10 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
         }
       }
       if (elect_one()) mma_commit(&d2_full[gi]);
+      if (gi == 0) CE_TRACE(1, 2);
       // layer 1 of the group's next tile: D1 lands in the A2 columns layer 2 above has consumed (in order)
       if (tile + 2 * gdim < ntiles) issue_layer1(j + 1);
+      if (gi == 0) CE_TRACE(1, 3);
     }
   } else {
     // ============================ worker warps of group gi ============================
@@ -229,6 +247,7 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
       prefetch_sj();                                   // endpoints of the tile after next (idx arrived last iteration)
       mbar_wait(&d2_full[gi], j & 1);
       fence_after_sync();
+      if (warp == 0) CE_TRACE(0, 1); else if (warp == 4) CE_TRACE(2, 1);
       const float mk = mask[(j & 3) * 128 + r];
       const float2 mk2 = make_float2(mk, mk);
 #pragma unroll 1
@@ -236,13 +255,16 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
         named_bar_sync(bar_id, GROUP_THREADS);         // the previous pooling pass has finished reading `stage`
         {
           float v[32];
+          float4 bias[8];                              // issued before the TMEM wait so their latency is hidden
+#pragma unroll
+          for (int j4 = 0; j4 < 8; ++j4) bias[j4] = *reinterpret_cast<const float4*>(B2 + hf * 64 + cg * 32 + 4 * j4);
 #pragma unroll
           for (int part = 0; part < 4; ++part) tmem_ld8(tlane + C_D2 + hf * 64 + cg * 32 + part * 8, v + part * 8);
           wait_ld();
 #pragma unroll
           for (int j4 = 0; j4 < 8; ++j4) {
             const int cl = cg * 32 + 4 * j4;           // channel within this half
-            const float4 bb = *reinterpret_cast<const float4*>(B2 + hf * 64 + cl);
+            const float4 bb = bias[j4];
             const float2 y0 = __fmul2_rn(relu2(__fadd2_rn(make_float2(v[4 * j4 + 0], v[4 * j4 + 1]), make_float2(bb.x, bb.y))), mk2);
             const float2 y1 = __fmul2_rn(relu2(__fadd2_rn(make_float2(v[4 * j4 + 2], v[4 * j4 + 3]), make_float2(bb.z, bb.w))), mk2);
             stage[(cl + 0) * RS + r] = y0.x;
@@ -252,11 +274,20 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
           }
         }
         fence_before_sync();
+        if (warp == 0) CE_TRACE(0, 2 + 4 * hf); else if (warp == 4) CE_TRACE(2, 2 + 4 * hf);
         named_bar_sync(bar_id, GROUP_THREADS);         // stage complete (and, for hf = 1, D2 fully read)
+        if (warp == 0) CE_TRACE(0, 3 + 4 * hf); else if (warp == 4) CE_TRACE(2, 3 + 4 * hf);
         // layer-1 epilogue of the next tile first, so its layer 2 can start while we pool
         if (hf == 1 && has_next) epilogue1(j + 1);
-        // ---- masked max over the K slots (controller.py:46, repair F2: values) ----
-        for (int item = gtid; item < na * 64; item += GROUP_THREADS) {
+        if (warp == 0) CE_TRACE(0, 4 + 4 * hf); else if (warp == 4) CE_TRACE(2, 4 + 4 * hf);
+        // ---- masked max over the K slots (controller.py:46, repair F2: values).  First half: all 8
+        //      warps.  Second half: the 4 non-feature warps, while the feature warps build the A1 tile
+        //      of the tile after next (layer 1 of the next tile has retired: d1_full observed above) ----
+        const bool feat_now = (hf == 1) && (tile + 2 * step < ntiles);
+        if (feat_now && cg == 0) features(j + 2);
+        const int p_first = feat_now ? gtid - GROUP_THREADS / 2 : gtid;
+        const int p_step = feat_now ? GROUP_THREADS / 2 : GROUP_THREADS;
+        for (int item = p_first; item < na * 64 && item >= 0; item += p_step) {
           const int c = item & 63, a = item >> 6;
           const float* row = stage + c * RS + a * K;
           float best = 0.f;                            // relu(.) * mask >= 0; slot 0 (self) is never masked
@@ -275,10 +306,10 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
           }
           pool[(a0 + a) * 128 + hf * 64 + c] = best;
         }
+        if (warp == 0) CE_TRACE(0, 5 + 4 * hf); else if (warp == 4) CE_TRACE(2, 5 + 4 * hf);
       }
-      // ---- features of the tile after next -> A1 (layer 1 of the next tile has retired: d1_full observed) ----
-      if (cg == 0 && tile + 2 * step < ntiles) features(j + 2);
       prefetch_ij(tile + 3 * step);
+      if (warp == 0) CE_TRACE(0, 10);
     }
   }
   fence_before_sync();

@@ -23,8 +23,8 @@ buf = np.zeros((3, 4096), dtype=np.uint64)
 fn = L.macbf_debug_ce_trace
 fn.argtypes = [ctypes.c_void_p]
 assert fn(buf.ctypes.data) == 0
-names = {0: {1: "w0 d2.ready", 2: "w0 bar2.out", 3: "w0 E2.end", 4: "w0 bar1.out", 5: "w0 E1.end", 6: "w0 feat.end"},
-         2: {1: "      w15 d2.ready", 2: "      w15 bar2.out", 3: "      w15 E2.end", 4: "      w15 bar1.out", 5: "      w15 E1.end", 6: "      w15 pool.end"},
+wn = {1: "d2.ready", 2: "E2h0.end", 3: "bar.out", 4: "(h0)", 5: "pool0.end", 6: "E2h1.end", 7: "bar.out", 8: "E1next.end", 9: "pool1.end", 10: "feat.end"}
+names = {0: {k: "w0 " + v for k, v in wn.items()}, 2: {k: "        w4 " + v for k, v in wn.items()},
          1: {1: "MMA a2.ready", 2: "MMA mma2.issued", 3: "MMA mma1.issued"}}
 ev = []
 for who in (0, 1, 2):
