@@ -12,19 +12,19 @@
 //   workers           tcgen05.ld, bias + ReLU, hi/lo; hi overwrites D1 in place   -> A2   (TMEM)
 //   MMA warp          layer 2: D2[128x128] = A2 * W2^T in two 64-column chunks    -> D2   (TMEM)
 //   workers           per chunk: bias + ReLU, hi/lo; hi overwrites D2 in place    -> A3   (TMEM)
-//   MMA warp          layer 3: per 64-wide K chunk, cross terms -> D3s, hi*hi     -> D3   (TMEM)
-//   workers           (D3 + D3s) bias + ReLU, 64 -> 1 dot, * mask                 -> h    (global)
+//   MMA warp          layer 3: cross terms per 64-wide K chunk, then hi*hi        -> D3   (TMEM)
+//   workers           bias + ReLU, 64 -> 1 dot, * mask                            -> h    (global)
 //
 // Issue order of the MMA warp: L2(i), L1(i+1), L3(i), L2(i+1), ... so the workers turn D1(i+1)
 // into A2(i+1) while the tensor core runs L3(i), and L2(i+1) starts the moment L3(i) retires.
 // Every GEMM is a 3xTF32 split (hi*hi + lo*hi + hi*lo) with fp32 accumulation in TMEM; the small
-// cross terms go first (layers 1, 2) or into their own accumulator D3s (K-chunked layer 3) because
-// the tensor core's accumulate is not round-to-nearest (tools/tc_probe.cu).
+// cross terms always go first because the tensor core's accumulate is not round-to-nearest
+// (tools/tc_probe.cu).
 // Hidden activations never leave the SM.  Shared memory: hi/lo halves of W1, W2, W3 in the
 // canonical SWIZZLE_128B K-major layout (144 KB), the A1 staging tiles (32 KB), small vectors.
 //
 // TMEM columns: [0,64) D1 -> A2_hi (in place)  [64,128) A2_lo  [128,256) D2 -> A3_hi (in place)
-//               [256,384) A3_lo  [384,448) D3  [448,512) D3s
+//               [256,384) A3_lo  [384,448) D3
 #include "common.cuh"
 #include "tc_common.cuh"
 
@@ -50,7 +50,7 @@ namespace cbftc {
 constexpr int WORKERS = 512;
 constexpr int THREADS = WORKERS + 32;
 constexpr int R = 128;
-constexpr uint32_t C_A2HI = 0, C_A2LO = 64, C_Y = 128, C_A3LO = 256, C_D3 = 384, C_D3S = 448;
+constexpr uint32_t C_A2HI = 0, C_A2LO = 64, C_Y = 128, C_A3LO = 256, C_D3 = 384;
 // dynamic shared memory (floats, after 1024-B alignment); every MMA operand slab is 1024-B aligned
 constexpr int oW2HI = 0;
 constexpr int oW2LO = oW2HI + 128 * 64;
@@ -166,27 +166,33 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
       TC_TRACE(1, 2);
       // layer 1 of the next tile: its D1 lands in the A2 columns this tile's layer 2 has just finished reading
       if (tile + gridDim.x < ntiles) issue_layer1(par ^ 1);
+      // layer 3 accumulates into ONE tile D3: the cross terms of both 64-wide K chunks first (each as
+      // soon as its A3 chunk exists), the two hi*hi passes last - small terms still meet a small sum,
+      // and the epilogue reads 64 TMEM columns instead of 128 (tcgen05.ld bandwidth, 64 B/clk/SM, is
+      // what bounds the epilogues).
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
         mbar_wait(&a3_full[c], par);
-        if (c == 0 && it > 0) mbar_wait(&d3_free, par ^ 1);   // previous tile's D3/D3s have been read
+        if (c == 0 && it > 0) mbar_wait(&d3_free, par ^ 1);   // previous tile's D3 has been read
         fence_after_sync();
         TC_TRACE(1, 3 + c);
-        // layer 3, K chunk [64c, 64c+64): cross terms -> D3s, hi*hi -> D3
 #pragma unroll
-        for (int term = 0; term < 3; ++term) {
+        for (int term = 0; term < 2; ++term) {         // lo*hi, hi*lo of K chunk [64c, 64c+64)
           const uint32_t a_col = tb + (term == 0 ? C_A3LO : C_Y) + c * 64;
           const uint64_t b_desc = desc_advance((term == 1) ? d_w3lo : d_w3hi, (2 * c) * (64 * 128));
-          const uint32_t d = tb + (term == 2 ? C_D3 : C_D3S);
 #pragma unroll
           for (int ks = 0; ks < 8; ++ks) {
             const uint64_t bd = desc_advance(b_desc, (ks >> 2) * (64 * 128) + (ks & 3) * 32);
-            const uint32_t acc = (c > 0 || ks > 0 || term == 1) ? 1u : 0u;
-            if (elect_one()) mma_tf32_ts(d, a_col + ks * 8, bd, IDESC, acc);
+            if (elect_one()) mma_tf32_ts(tb + C_D3, a_col + ks * 8, bd, IDESC, (c | term | ks) ? 1u : 0u);
           }
         }
-        if (c == 1 && elect_one()) mma_commit(&d3_full);
       }
+#pragma unroll
+      for (int ks = 0; ks < 16; ++ks) {                // hi*hi over the whole K = 128
+        const uint64_t bd = desc_advance(d_w3hi, (ks >> 2) * (64 * 128) + (ks & 3) * 32);
+        if (elect_one()) mma_tf32_ts(tb + C_D3, tb + C_Y + ks * 8, bd, IDESC, 1u);
+      }
+      if (elect_one()) mma_commit(&d3_full);
       TC_TRACE(1, 5);
     }
   } else {
@@ -322,15 +328,14 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
         prefetch_ij(tile + 3 * g);
       }
       if (warp == 0) TC_TRACE(0, 5);
-      // ---- layer-3 epilogue: (D3 + D3s) bias + ReLU, 64 -> 1 over this thread's 16 channels ----
+      // ---- layer-3 epilogue: bias + ReLU, 64 -> 1 over this thread's 16 channels ----
       mbar_wait(&d3_full, par);
       fence_after_sync();
       if (warp == 0) TC_TRACE(0, 6);
       {
         const int c0 = cgrp * 16;
-        float v[16], vs[16];
+        float v[16];
         tmem_ld16(tlane + C_D3 + c0, v);
-        tmem_ld16(tlane + C_D3S + c0, vs);
         wait_ld();
         warp_arrive_after_tmem(&d3_free);
         float2 s2 = make_float2(0.f, 0.f);
@@ -338,10 +343,8 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
         for (int j4 = 0; j4 < 4; ++j4) {
           const float4 bb = *reinterpret_cast<const float4*>(B3 + c0 + 4 * j4);
           const float4 ww = *reinterpret_cast<const float4*>(W4 + c0 + 4 * j4);
-          float2 x = __fadd2_rn(make_float2(v[4 * j4 + 0], v[4 * j4 + 1]), make_float2(vs[4 * j4 + 0], vs[4 * j4 + 1]));
-          s2 = __ffma2_rn(make_float2(ww.x, ww.y), relu2(__fadd2_rn(x, make_float2(bb.x, bb.y))), s2);
-          x = __fadd2_rn(make_float2(v[4 * j4 + 2], v[4 * j4 + 3]), make_float2(vs[4 * j4 + 2], vs[4 * j4 + 3]));
-          s2 = __ffma2_rn(make_float2(ww.z, ww.w), relu2(__fadd2_rn(x, make_float2(bb.z, bb.w))), s2);
+          s2 = __ffma2_rn(make_float2(ww.x, ww.y), relu2(__fadd2_rn(make_float2(v[4 * j4 + 0], v[4 * j4 + 1]), make_float2(bb.x, bb.y))), s2);
+          s2 = __ffma2_rn(make_float2(ww.z, ww.w), relu2(__fadd2_rn(make_float2(v[4 * j4 + 2], v[4 * j4 + 3]), make_float2(bb.z, bb.w))), s2);
         }
         const float s = s2.x + s2.y;
         float* hp = hpart + (par * 4) * R;
