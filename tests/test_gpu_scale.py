@@ -1,0 +1,123 @@
+"""GPU: BASELINE.json's larger configurations through size-independent properties and sampled oracle checks.
+
+C3  4096 agents + 384 obstacle points (16 circles + 16 rectangles), full training step: one env is
+    small enough for the dense CPU oracle (a few seconds), so it is compared directly.
+C4  16384-agent envs: neighbour sets of sampled rows against the row-chunked oracle, structure checks.
+C5  65536 agents, K in {8, 32, 64, 128} with the sensing radius scaled to the neighbour count.
+"""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import RTOL, assert_close, dev, rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ops():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from macbf_b200 import ops as _ops
+    return _ops
+
+
+def _params():
+    from oracle import macbf_oracle as O
+    p_cbf, p_ctrl = O.init_params(21)
+    return p_cbf, p_ctrl, dev(O.flatten_params(p_cbf, O.CBF_KEYS).numpy()), dev(O.flatten_params(p_ctrl, O.CTRL_KEYS).numpy())
+
+
+def test_c3_training_step_with_obstacles(ops):
+    from macbf_b200 import step
+    from oracle import macbf_oracle as O
+    N = 4096
+    s, g = O.synthetic_swarm(1, N, seed=1234 + 3000)
+    obs = O.synthetic_obstacles(1, N, 16, 16, seed=1234 + 3000)
+    assert obs.shape == (1, 384, 2)
+    p_cbf, p_ctrl, cf, tf = _params()
+    ts = step.TrainStep(1, N, 384, 12, "cuda")
+    scal, grad = ts.forward_backward(s.cuda(), g.cuda(), cf, tf, obs.cuda())
+    torch.cuda.synchronize()
+    ref = O.full_step(p_cbf, p_ctrl, s[0], g[0], obs[0], 12, O.REPAIRED, with_grad=True)
+    idx_ref = O.neighbor_indices(s[0], 12, obs[0], row_chunk=512).numpy()
+    dec = O.decidable_rows(s[0], 12, obs[0]).numpy()
+    assert np.array_equal(ts.buf.idx[0].cpu().numpy()[dec], idx_ref[dec]) and dec.mean() > 0.999
+    assert (ts.buf.idx[0].cpu().numpy() >= N).any()                 # some neighbours are obstacle points
+    assert_close(ts.buf.u[0].cpu().numpy(), ref["u"].numpy(), RTOL, "u")
+    assert_close(ts.buf.h[0].cpu().numpy(), ref["h"][:, 0, :].numpy(), RTOL, "h")
+    assert np.array_equal(ts.buf.ttc_mask[0].cpu().numpy().astype(bool), ref["ttc_mask"][:, :, 0].numpy())
+    same = (ts.buf.idx_next[0].cpu().numpy() == O.neighbor_indices(ref["s_next"], 12, obs[0], row_chunk=512).numpy()).all(axis=1)
+    assert same.mean() > 0.995
+    if same.all():
+        sc = scal[0].cpu().numpy()
+        for q in range(9):
+            r = float(ref["scalars"][q])
+            assert abs(float(sc[q]) - r) <= 2 * RTOL * max(abs(r), 1e-3), (q, sc[q], r)
+        g_ref = np.concatenate([ref["grad_cbf"].numpy(), ref["grad_ctrl"].numpy()])
+        assert rel_err(grad.cpu().numpy(), g_ref) <= 1e-4
+
+
+def _structure_checks(idx, N, C, K):
+    assert idx.min() >= 0 and idx.max() < C
+    assert (idx[:, 0] == np.arange(N)).all()                         # slot 0 is the agent itself
+    srt = np.sort(idx, axis=1)
+    assert (srt[:, 1:] != srt[:, :-1]).all()                          # no duplicates
+
+
+def test_c4_large_envs_sampled_rows(ops):
+    from oracle import macbf_oracle as O
+    B, N = 3, 16384
+    s, g = O.synthetic_swarm(B, N, seed=1234 + 4000)
+    idx = ops.neighbor_topk(s.cuda(), 12).cpu().numpy()
+    rows = np.random.RandomState(0).choice(N, 512, replace=False)
+    for b in range(B):
+        _structure_checks(idx[b], N, N, 12)
+        d = s[b, rows, None, :2] - s[b, None, :, :2]
+        ref = torch.topk(-O.knn_keys(d), 12)[1].numpy()
+        assert np.array_equal(idx[b][rows], ref)
+    _, _, cf, tf = _params()
+    buf = ops.StepBuffers(B, N, 0, 12, "cuda")
+    ops.step_forward(s.cuda(), g.cuda(), cf, tf, buf)
+    torch.cuda.synchronize()
+    sc = buf.scalars.cpu().numpy()
+    assert np.isfinite(sc).all() and (sc[:, 10] + sc[:, 11] == N * 12).all()
+    # h is exactly zero where (and only where) the sensing-radius mask is off: check against geometry
+    sd = s[0]
+    j = torch.from_numpy(idx[0].astype(np.int64))
+    dxy = sd[:, None, :2] - sd[j][:, :, :2]
+    dist = torch.sqrt((dxy[..., 0] ** 2 + 1e-4) + (dxy[..., 1] ** 2 + 1e-4))
+    masked = (dist > 1.0).numpy()
+    h0 = buf.h[0].cpu().numpy()
+    assert (h0[masked] == 0).all()
+
+
+@pytest.mark.parametrize("k", [8, 32, 64, 128])
+def test_c5_density_sweep_65536(ops, k):
+    from oracle import macbf_oracle as O
+    N = 65536
+    s, g = O.synthetic_swarm(1, N, seed=1234 + 5000 + k)
+    idx = ops.neighbor_topk(s.cuda(), k)[0].cpu().numpy()
+    _structure_checks(idx, N, N, k)
+    rows = np.random.RandomState(k).choice(N, 256, replace=False)
+    d = s[0, rows, None, :2] - s[0, None, :, :2]
+    keys = O.knn_keys(d)
+    vals, ref = torch.topk(-keys, k + 1)
+    vals = -vals
+    gap_ok = ((vals[:, 1:].view(torch.int32) - vals[:, :-1].view(torch.int32)) >= 2).all(dim=1).numpy()
+    assert np.array_equal(idx[rows][gap_ok], ref[:, :k].numpy()[gap_ok]) and gap_ok.mean() > 0.95
+    # keys along every row are non-decreasing (sortedness)
+    jj = torch.from_numpy(idx[rows].astype(np.int64))
+    kk = torch.gather(keys, 1, jj)
+    assert (kk[:, 1:] >= kk[:, :-1]).all()
+    # radius scaled to the neighbour count: R = sqrt(K / (8 pi)); CBF + controller run at that K
+    R = math.sqrt(k / (8 * math.pi))
+    _, _, cf, tf = _params()
+    idx_d = torch.from_numpy(idx).cuda().unsqueeze(0)
+    h = ops.cbf_forward(s.cuda(), idx_d, cf, obs_radius=R)
+    u, sn, pool = ops.controller_forward(s.cuda(), g.cuda(), idx_d, tf, obs_radius=R)
+    assert torch.isfinite(h).all() and torch.isfinite(u).all() and torch.isfinite(sn).all()
+    frac_in_range = float((h != 0).float().mean())
+    assert 0.2 < frac_in_range < 0.995                                # R holds K agents on average: most, not all, of the K nearest are inside
