@@ -169,6 +169,23 @@ int macbf_step_forward(const float* states, const float* goals, const float* obs
                        float* s_next, float* h, float* h_next, uint8_t* ttc_mask, float* scalars,
                        void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- closed-loop rollout (train.py:59-81) with the stop test on the device ------------------
+ * For t = 0 .. max_steps-1: record s_t; u_t = Controller(s_t, goals); s_{t+1} = s_t + [v,u_t] dt; record
+ * u_t; an env stops after the first t with mean_i |p_{t+1} - g| < dist_stop (train.py:78-81).
+ * traj_states [max_steps+1, B,N,4] (slot 0 = states0), traj_actions [max_steps, B,N,2],
+ * steps_run [B] = number of recorded steps per env (slots beyond it hold the continued simulation of
+ * that env while others were still running, or are untouched once every env has stopped).
+ * noise: NULL, or [max_steps, B,N,2] added to u_t before the Euler step (train.py:66-68; the host draws
+ * it, all-zero rows = no noise at that step).
+ * No host synchronisation: once all envs have stopped the remaining kernels return at once. */
+size_t macbf_rollout_workspace_bytes(int B, int N, int M, int top_k);
+int macbf_rollout_forward(const float* states0, const float* goals, const float* obstacles,
+                          const float* ctrl_params, const float* noise, int B, int N, int M, int top_k,
+                          int max_steps,
+                          int semantics, double obs_radius, double dt, double dist_stop,
+                          float* traj_states, float* traj_actions, int32_t* steps_run, void* workspace,
+                          size_t workspace_bytes, void* stream);
+
 /* Kernel launches issued by this library on the calling thread since load (bench.py reports
  * the per-step delta as gpu_launches). */
 long long macbf_launch_count(void);

@@ -7,6 +7,7 @@ namespace macbf {
 
 static thread_local char g_err[512] = "";
 static thread_local long long g_launches = 0;
+thread_local const int* tl_skip_flag = nullptr;
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -19,6 +20,9 @@ void count_launch(int n) { g_launches += n; }
 // implemented in the kernel translation units
 int neighbor_topk(const float*, const float*, int, int, int, int, int32_t*, cudaStream_t);
 int dense_topk(const float*, int, int, int, int, int32_t*, cudaStream_t);
+size_t rollout_workspace_bytes(int, int, int, int);
+int rollout_forward(const float*, const float*, const float*, const float*, const float*, int, int, int, int, int, int, double, double,
+                    double, float*, float*, int32_t*, void*, size_t, cudaStream_t);
 size_t neighbor_grid_workspace_bytes(int, int, int);
 bool neighbor_grid_applicable(int, int, int);
 int neighbor_topk_grid(const float*, const float*, int, int, int, int, int32_t*, void*, size_t, cudaStream_t);
@@ -241,6 +245,24 @@ int macbf_step_forward(const float* states, const float* goals, const float* obs
                         h_next, st))) return rc;
   return loss_forward(states, goals, obstacles, idx, h, h_next, u, B, N, M, K, dist_min_thres, ttc, dt, alpha,
                       ttc_mask_out, scalars, lscratch, loss_scratch_bytes(B, N, K), st);
+}
+
+size_t macbf_rollout_workspace_bytes(int B, int N, int M, int top_k) { return rollout_workspace_bytes(B, N, M, top_k); }
+
+int macbf_rollout_forward(const float* states0, const float* goals, const float* obstacles, const float* ctrl_params,
+                          const float* noise, int B, int N, int M, int top_k, int max_steps, int semantics, double obs_radius, double dt,
+                          double dist_stop, float* traj_states, float* traj_actions, int32_t* steps_run,
+                          void* workspace, size_t workspace_bytes, void* stream) {
+  const char* fn = "macbf_rollout_forward";
+  MACBF_CHECK_ARG(top_k >= 1 && top_k <= MACBF_MAX_K, "%s: top_k=%d out of range [1,%d]", fn, top_k, MACBF_MAX_K);
+  if (check_dims(fn, B, N, M, macbf_neighbor_count(N, M, top_k))) return 1;
+  MACBF_CHECK_ARG(max_steps >= 1, "%s: max_steps=%d must be >= 1", fn, max_steps);
+  REQ_PTR(fn, states0); REQ_PTR(fn, goals); REQ_PTR(fn, ctrl_params); REQ_PTR(fn, traj_states); REQ_PTR(fn, traj_actions);
+  REQ_PTR(fn, steps_run); REQ_PTR(fn, workspace); REQ_A16(fn, states0); REQ_A16(fn, traj_states); REQ_A16(fn, workspace);
+  MACBF_CHECK_ARG(M == 0 || obstacles != nullptr, "%s: obstacles is NULL but M=%d", fn, M);
+  MACBF_CHECK_ARG(semantics == MACBF_LITERAL || semantics == MACBF_REPAIRED, "%s: bad semantics %d", fn, semantics);
+  return rollout_forward(states0, goals, obstacles, ctrl_params, noise, B, N, M, top_k, max_steps, semantics, obs_radius, dt,
+                         dist_stop, traj_states, traj_actions, steps_run, workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -24,6 +24,11 @@ constexpr int NUM_SMS = 148;
 
 // ---- error plumbing ------------------------------------------------------------------------
 void set_error(const char* fmt, ...);
+// Device flag consulted by the rollout kernels (neighbour search, controller): when it points to a
+// non-zero int the kernel returns at once.  macbf_rollout_forward sets it around its launches so that
+// the steps after every env has reached its goal cost (almost) nothing and no host sync is needed.
+extern thread_local const int* tl_skip_flag;
+#define MACBF_SKIP_IF_SET(skip) do { if ((skip) != nullptr && *(skip) != 0) return; } while (0)
 void count_launch(int n = 1);
 #define MACBF_CHECK_ARG(cond, ...)      \
   do {                                  \

@@ -46,7 +46,8 @@ constexpr size_t smem_bytes = (size_t)total_floats * 4 + 1024;
 __global__ void __launch_bounds__(cntc::THREADS, 1)
 ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ goals,
                     const float* __restrict__ pool, const float* __restrict__ params, long long agents_total,
-                    float dt, float* __restrict__ u, float* __restrict__ s_next) {
+                    float dt, float* __restrict__ u, float* __restrict__ s_next, const int* __restrict__ skip) {
+  MACBF_SKIP_IF_SET(skip);
   using namespace cntc;
   using namespace tc;
   extern __shared__ unsigned char smem_raw[];
@@ -285,7 +286,7 @@ int ctrl_node_tc(const float* states, const float* goals, const float* pool, con
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(ctrl_node_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)cntc::smem_bytes));
   ctrl_node_tc_kernel<<<grid, cntc::THREADS, cntc::smem_bytes, st>>>(states, goals, pool, params, agents, (float)dt, u,
-                                                                    s_next);
+                                                                    s_next, tl_skip_flag);
   MACBF_CHECK_LAUNCH("ctrl_node_tc_kernel");
   return 0;
 }

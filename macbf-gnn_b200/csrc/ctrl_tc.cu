@@ -59,7 +59,9 @@ constexpr size_t smem_bytes = (size_t)total_floats * 4 + 1024;
 __global__ void __launch_bounds__(cetc::THREADS, 1)
 ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ obstacles,
                     const int32_t* __restrict__ idx, const float* __restrict__ params, int N, int M, int K,
-                    long long agents_total, int TA, float obs_radius, float* __restrict__ pool) {
+                    long long agents_total, int TA, float obs_radius, float* __restrict__ pool,
+                    const int* __restrict__ skip) {
+  MACBF_SKIP_IF_SET(skip);
   using namespace cetc;
   using namespace tc;
   extern __shared__ unsigned char smem_raw[];
@@ -327,7 +329,7 @@ int ctrl_edge_tc(const float* states, const float* obstacles, const int32_t* idx
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(ctrl_edge_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)cetc::smem_bytes));
   ctrl_edge_tc_kernel<<<grid, cetc::THREADS, cetc::smem_bytes, st>>>(states, obstacles, idx, params, N, M, K, agents, TA,
-                                                                    (float)obs_radius, pool);
+                                                                    (float)obs_radius, pool, tl_skip_flag);
   MACBF_CHECK_LAUNCH("ctrl_edge_tc_kernel");
   return 0;
 }

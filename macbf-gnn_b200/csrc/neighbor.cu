@@ -73,7 +73,8 @@ struct TopList {
 template <int S, int Q>
 __global__ void __launch_bounds__(KNN_THREADS)
 knn_kernel(const float* __restrict__ states, const float* __restrict__ obstacles, int N, int M, int K,
-           int32_t* __restrict__ idx_out) {
+           int32_t* __restrict__ idx_out, const int* __restrict__ skip) {
+  MACBF_SKIP_IF_SET(skip);
   __shared__ float2 tile[KNN_TILE];
   const int b = blockIdx.y;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -199,7 +200,7 @@ template <int S, int Q>
 static int launch_knn(const float* states, const float* obstacles, int B, int N, int M, int K,
                       int32_t* idx, cudaStream_t st) {
   dim3 grid((N + KNN_WARPS * Q - 1) / (KNN_WARPS * Q), B);
-  knn_kernel<S, Q><<<grid, KNN_THREADS, 0, st>>>(states, obstacles, N, M, K, idx);
+  knn_kernel<S, Q><<<grid, KNN_THREADS, 0, st>>>(states, obstacles, N, M, K, idx, tl_skip_flag);
   MACBF_CHECK_LAUNCH("knn_kernel");
   return 0;
 }

@@ -38,7 +38,9 @@ __device__ __forceinline__ int cell_coord(float x, float o, float inv_cs, int G)
 
 __global__ void __launch_bounds__(GRID_BUILD_THREADS)
 grid_build_kernel(const float* __restrict__ states, const float* __restrict__ obstacles, int N, int M, int G,
-                  float4* __restrict__ sorted, int* __restrict__ cell_start, GridHeader* __restrict__ header) {
+                  float4* __restrict__ sorted, int* __restrict__ cell_start, GridHeader* __restrict__ header,
+                  const int* __restrict__ skip) {
+  MACBF_SKIP_IF_SET(skip);
   __shared__ int cnt[GRID_GMAX * GRID_GMAX + 1];
   __shared__ int cur[GRID_GMAX * GRID_GMAX];
   __shared__ float red[4][32];
@@ -170,7 +172,8 @@ __device__ __forceinline__ u64 warp_merge32(u64 list, u64 fresh, int lane) {
 __global__ void __launch_bounds__(GRID_QUERY_THREADS)
 knn_grid_kernel(const float* __restrict__ states, const float4* __restrict__ sorted,
                 const int* __restrict__ cell_start, const GridHeader* __restrict__ header, int N, int C, int G,
-                int K, int32_t* __restrict__ idx_out) {
+                int K, int32_t* __restrict__ idx_out, const int* __restrict__ skip) {
+  MACBF_SKIP_IF_SET(skip);
   const int b = blockIdx.y;
   const int lane = threadIdx.x & 31;
   const int i = blockIdx.x * (GRID_QUERY_THREADS / 32) + (threadIdx.x >> 5);
@@ -286,7 +289,9 @@ knn_grid_kernel(const float* __restrict__ states, const float4* __restrict__ sor
 template <int K>
 __global__ void __launch_bounds__(128)
 knn_grid_tpq_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start,
-                    const GridHeader* __restrict__ header, int N, int C, int G, int32_t* __restrict__ idx_out) {
+                    const GridHeader* __restrict__ header, int N, int C, int G, int32_t* __restrict__ idx_out,
+                    const int* __restrict__ skip) {
+  MACBF_SKIP_IF_SET(skip);
   const int b = blockIdx.y;
   const int p0 = blockIdx.x * blockDim.x + threadIdx.x;
   if (p0 >= C) return;
@@ -360,7 +365,7 @@ template <int K>
 static int launch_tpq(const float4* sorted, const int* cell_start, const GridHeader* header, int B, int N, int C, int G,
                       int32_t* idx, cudaStream_t st) {
   dim3 grid((C + 127) / 128, B);
-  knn_grid_tpq_kernel<K><<<grid, 128, 0, st>>>(sorted, cell_start, header, N, C, G, idx);
+  knn_grid_tpq_kernel<K><<<grid, 128, 0, st>>>(sorted, cell_start, header, N, C, G, idx, tl_skip_flag);
   MACBF_CHECK_LAUNCH("knn_grid_tpq_kernel");
   return 0;
 }
@@ -396,7 +401,7 @@ int neighbor_topk_grid(const float* states, const float* obstacles, int B, int N
   const float per_cell = cell_override > 0.f ? cell_override : fmaxf(3.0f, 0.25f * (float)K);
   int G = (int)floorf(sqrtf((float)C / per_cell));
   G = G < 1 ? 1 : (G > GRID_GMAX ? GRID_GMAX : G);
-  grid_build_kernel<<<B, GRID_BUILD_THREADS, 0, st>>>(states, obstacles, N, M, G, sorted, cell_start, header);
+  grid_build_kernel<<<B, GRID_BUILD_THREADS, 0, st>>>(states, obstacles, N, M, G, sorted, cell_start, header, tl_skip_flag);
   MACBF_CHECK_LAUNCH("grid_build_kernel");
   static const bool force_warp = [] {
     const char* e = getenv("MACBF_KNN_WARP");
@@ -414,7 +419,7 @@ int neighbor_topk_grid(const float* states, const float* obstacles, int B, int N
     }
   }
   dim3 grid((N + GRID_QUERY_THREADS / 32 - 1) / (GRID_QUERY_THREADS / 32), B);
-  knn_grid_kernel<<<grid, GRID_QUERY_THREADS, 0, st>>>(states, sorted, cell_start, header, N, C, G, K, idx);
+  knn_grid_kernel<<<grid, GRID_QUERY_THREADS, 0, st>>>(states, sorted, cell_start, header, N, C, G, K, idx, tl_skip_flag);
   MACBF_CHECK_LAUNCH("knn_grid_kernel");
   return 0;
 }

@@ -259,5 +259,27 @@ def step_forward(states, goals, cbf_params, ctrl_params, buf: StepBuffers, obsta
     return buf
 
 
+def rollout_forward(states, goals, ctrl_params, max_steps, obstacles=None, noise=None, top_k=TOP_K, semantics=REPAIRED,
+                    obs_radius=OBS_RADIUS, dt=TIME_STEP, dist_stop=0.07):
+    """train.py:59-81 in one call, stop test on the device (no per-step host sync).
+    -> (traj_states [T+1,B,N,4], traj_actions [T,B,N,2], steps_run [B] int32)."""
+    _need_cuda(states, goals, ctrl_params, obstacles, noise)
+    states, goals, ctrl_params, obstacles, noise = map(_c, (states, goals, ctrl_params, obstacles, noise))
+    B, N, M, obstacles = _dims(states, obstacles)
+    if noise is not None and tuple(noise.shape) != (max_steps, B, N, 2):
+        raise ValueError(f"noise must be [{max_steps}, {B}, {N}, 2], got {tuple(noise.shape)}")
+    dev = states.device
+    L = _lib.load()
+    ts = torch.zeros((max_steps + 1, B, N, 4), dtype=torch.float32, device=dev)
+    ta = torch.zeros((max_steps, B, N, 2), dtype=torch.float32, device=dev)
+    steps = torch.empty((B,), dtype=torch.int32, device=dev)
+    nbytes = L.macbf_rollout_workspace_bytes(B, N, M, top_k)
+    ws = torch.empty((nbytes,), dtype=torch.uint8, device=dev)
+    _lib.check(L.macbf_rollout_forward(_p(states), _p(goals), _p(obstacles), _p(ctrl_params), _p(noise), B, N, M, top_k, max_steps,
+                                       semantics, obs_radius, dt, dist_stop, _p(ts), _p(ta), _p(steps), _p(ws), nbytes,
+                                       _stream()), "macbf_rollout_forward")
+    return ts, ta, steps
+
+
 def launch_count() -> int:
     return int(_lib.load().macbf_launch_count())
