@@ -7,6 +7,8 @@
 // does not depend on scheduling.  d/dstates goes through the edge features
 // [dx,dy,dvx,dvy,.,d-r] (indices and the radius mask are constants of the backward pass, as in
 // eager autograd): +grad to agent i, -grad to neighbour j (fp32 atomics; obstacles get none).
+#include <stdlib.h>
+
 #include "mlp_tile.cuh"
 
 namespace macbf {
@@ -192,8 +194,19 @@ static inline int cbf_bwd_grid(int B, int N, int K) {
   return (int)(ntiles < NUM_SMS ? ntiles : (long long)NUM_SMS);
 }
 
+size_t cbf_backward_tc_scratch_bytes(int B, int N, int K);
+int cbf_backward_tc(const float*, const float*, const int32_t*, const float*, const float*, int, int, int, int, double,
+                    double, float*, float*, void*, size_t, cudaStream_t);
+// MACBF_CBF_BWD_FFMA=1 keeps this FP32-FFMA kernel (A/B reference of the tensor-core path in cbf_bwd_tc.cu)
+static bool cbf_bwd_force_ffma() {
+  static const bool v = [] { const char* e = getenv("MACBF_CBF_BWD_FFMA"); return e != nullptr && e[0] == '1'; }();
+  return v;
+}
+
 size_t cbf_backward_scratch_bytes(int B, int N, int K) {
-  return (size_t)cbf_bwd_grid(B, N, K) * MACBF_CBF_PARAMS * sizeof(float);
+  const size_t ffma = (size_t)cbf_bwd_grid(B, N, K) * MACBF_CBF_PARAMS * sizeof(float);
+  const size_t tc = cbf_backward_tc_scratch_bytes(B, N, K);
+  return ffma > tc ? ffma : tc;
 }
 
 int cbf_backward(const float* states, const float* obstacles, const int32_t* idx, const float* params,
@@ -201,8 +214,11 @@ int cbf_backward(const float* states, const float* obstacles, const int32_t* idx
                  float* grad_params, float* grad_states, void* scratch, size_t scratch_bytes, cudaStream_t st) {
   const long long agents = (long long)B * N;
   MACBF_CHECK_ARG(agents < (1ll << 31), "cbf_backward: B*N must be < 2^31");
+  if (!cbf_bwd_force_ffma())
+    return cbf_backward_tc(states, obstacles, idx, params, grad_h, B, N, M, K, dist_min, obs_radius, grad_params,
+                           grad_states, scratch, scratch_bytes, st);
   const int grid = cbf_bwd_grid(B, N, K);
-  const size_t need = cbf_backward_scratch_bytes(B, N, K);
+  const size_t need = (size_t)grid * MACBF_CBF_PARAMS * sizeof(float);
   MACBF_CHECK_ARG(scratch_bytes >= need, "cbf_backward: scratch too small (%zu < %zu)", scratch_bytes, need);
   const int TA = max(1, cbfb_smem::R / K);
   const size_t smem = cbfb_smem::total * sizeof(float);

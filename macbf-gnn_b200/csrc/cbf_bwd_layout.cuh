@@ -1,0 +1,27 @@
+// Per-tile record shared by the three kernels of the tensor-core CBF backward (cbf_bwd_tc.cu):
+//   K2b-1  cbf_forward_tc_kernel<true>   recompute + dump activations         (writes A1, A2, masks, xrec, gm)
+//   K2b-2  cbf_dgrad_tc_kernel           delta chain on the tensor core       (writes dZ3, dZ2)
+//   K2b-3  cbf_wgrad_tc_kernel           dW3, dW2, db3, db2 = GEMMs over edges (reads the four images)
+// A tile is 128 edge rows.  Activations / deltas are stored as bf16 (hi, lo) operand images in exactly
+// the shared-memory layout the wgrad MMAs read (MN-major SWIZZLE_128B: per 64-channel block 128 rows x
+// 128 B, 16-byte chunk c of row e at position c ^ (e & 7)), so K2b-3 stages them with plain bulk copies.
+#pragma once
+#include <stdint.h>
+
+namespace macbf {
+namespace cbfrec {
+constexpr uint32_t BLK = 128 * 128;            // one 64-channel block of one image half: 16 KB
+// stage G3 (dW3^T = A2^T dZ3): 96 KB
+constexpr uint32_t A2_HI = 0, A2_LO = 2 * BLK, Z3_HI = 4 * BLK, Z3_LO = 5 * BLK;
+// stage G2 (dW2 = dZ2^T A1): 96 KB
+constexpr uint32_t G2 = 6 * BLK;
+constexpr uint32_t Z2_HI = G2 + 0, Z2_LO = G2 + 2 * BLK, A1_HI = G2 + 4 * BLK, A1_LO = G2 + 5 * BLK;
+constexpr uint32_t STAGE_BYTES = 6 * BLK;      // 98,304
+// per-thread ReLU masks (bit q = channel c0 + q was active), [which][cgrp][row] uint32
+constexpr uint32_t MASKS = 12 * BLK;           // which: 0 = layer 1, 1/2 = layer 2 chunk 0/1, 3 = layer 3
+constexpr uint32_t XREC = MASKS + 4 * 4 * 128 * 4;    // float[128][8]: the 6 edge features, d, unused
+constexpr uint32_t GM = XREC + 128 * 8 * 4;           // float[128]: dL/dh * radius mask (0 for padding rows)
+constexpr uint32_t BYTES = GM + 128 * 4 + 512;        // 209,920 = 205 * 1024
+static_assert(BYTES % 1024 == 0, "tile records must keep 1024-B alignment");
+}  // namespace cbfrec
+}  // namespace macbf

@@ -1,0 +1,453 @@
+// K2b (tensor-core path) - backward of the fused CBF head (autograd of cbf.py:21-45, REPAIRED).
+//
+// Three kernels per chunk of tiles (a tile = 128 edge rows; records in cbf_bwd_layout.cuh):
+//
+//   1. cbf_forward_tc_kernel<true> (cbf_tc.cu)  recompute the forward on the tensor core; dump the
+//      layer-1/2 activations as bf16 hi/lo operand images, the ReLU bit masks, the edge features and
+//      gm = dL/dh * radius mask; accumulate dW4, db4.
+//   2. cbf_dgrad_tc_kernel   delta chain  dZ3 = gm w4 [z3>0] -> dA2 = dZ3 W3 -> dZ2 = dA2 [z2>0] -> dA1 = dZ2 W2
+//      -> dZ1 = dA1 [z1>0]: the two GEMMs are 3xTF32 tcgen05.mma with A (deltas) in tensor memory and
+//      B = the TRANSPOSED weights resident in shared memory (same machinery as the forward's layers 2, 3).
+//      dZ3, dZ2 are dumped as bf16 hi/lo images; dW1, db1 and d/dstates (6 features, fp32 atomics) are
+//      finished here on the CUDA cores.
+//   3. cbf_wgrad_tc_kernel   dW3^T = A2^T dZ3, dW2 = dZ2^T A1, db3, db2: GEMMs whose contraction index is the
+//      EDGE, so both operands come from shared memory as MN-major bf16 images, staged by bulk copies
+//      (cp.async.bulk + mbarrier, two 96-KB stages), 3 products (hi*hi, lo*hi, hi*lo) per GEMM with fp32
+//      accumulation in tensor memory across all tiles of the CTA; bias gradients ride along as GEMMs against
+//      a constant block of ones.  HBM-bound (1.5 KB per edge).
+//
+// Every kernel adds into its CTA's private slice of the gradient partial buffer (flat state_dict layout);
+// reduce_partials_kernel adds the slices in order, so parameter gradients are run-to-run deterministic.
+// Precision: dgrad chain 3xTF32 (~5e-7); wgrad operands carry 16 mantissa bits (~7e-6 scale-relative on dW2,
+// dW3, measured against an fp64 reference on the fixtures) - inside the 5e-5 gradient tolerance of the tests.
+#include "common.cuh"
+#include "tc_common.cuh"
+#include "cbf_bwd_layout.cuh"
+
+namespace macbf {
+
+__global__ void reduce_partials_kernel(const float* __restrict__ partial, int nslices, int P, float* __restrict__ out);
+int cbf_forward_tc_dump(const float* states, const float* obstacles, const int32_t* idx, const float* params, int N, int M,
+                        int K, long long agents, double dist_min, double obs_radius, long long tile_begin,
+                        long long tile_end, const float* grad_h, unsigned char* rec, float* slices, cudaStream_t st);
+
+// ================================ kernel 2: delta chain ================================
+namespace cbfdg {
+constexpr int WORKERS = 512;
+constexpr int THREADS = WORKERS + 32;
+constexpr int R = 128;
+// TMEM columns: [0,64) dZ3_hi  [64,128) dZ3_lo  [128,256) dA2 -> dZ2_hi (in place)  [256,384) dZ2_lo  [384,448) dA1
+constexpr uint32_t C_Z3HI = 0, C_Z3LO = 64, C_DA2 = 128, C_Z2LO = 256, C_DA1 = 384;
+constexpr int DZS = 129;                       // row stride of the transposed dZ1 stage: conflict-free both ways
+constexpr int oW3THI = 0;                      // B[n = in (128)][k = out (64)] = W3[k][n]
+constexpr int oW3TLO = oW3THI + 128 * 64;
+constexpr int oW2THI = oW3TLO + 128 * 64;      // B[n = in (64)][k = out (128)] = W2[k][n]
+constexpr int oW2TLO = oW2THI + 64 * 128;
+constexpr int oW1 = oW2TLO + 64 * 128;         // [64][8] plain
+constexpr int oW4 = oW1 + 64 * 8;
+constexpr int oDz1 = oW4 + 64;                 // [64][129]
+constexpr int oXs = oDz1 + 64 * DZS;           // [128][8]: features, xs[e][6] = 1 (bias column)
+constexpr int oXpart = oXs + 128 * 8;          // [4][6][128]
+constexpr int total_floats = oXpart + 4 * 6 * 128;
+constexpr size_t smem_bytes = (size_t)total_floats * 4 + 1024;
+}  // namespace cbfdg
+
+__global__ void __launch_bounds__(cbfdg::THREADS, 1)
+cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ params, int N, int K,
+                    long long agents_total, int TA, long long tile_begin, long long tile_end,
+                    unsigned char* __restrict__ rec, float* __restrict__ slices, float* __restrict__ grad_states) {
+  using namespace cbfdg;
+  using namespace tc;
+  extern __shared__ unsigned char smem_raw[];
+  float* sm = reinterpret_cast<float*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
+  float* W3Thi = sm + oW3THI; float* W3Tlo = sm + oW3TLO;
+  float* W2Thi = sm + oW2THI; float* W2Tlo = sm + oW2TLO;
+  float* W1 = sm + oW1; float* W4 = sm + oW4;
+  float* dz1s = sm + oDz1; float* xs = sm + oXs; float* xpart = sm + oXpart;
+  // workers -> MMA: z3_full, z2_full[2] (16 arrivals each); MMA -> workers: da2_full[2], da1_full
+  __shared__ uint64_t z3_full, z2_full[2], da2_full[2], da1_full;
+  __shared__ uint32_t tmem_base_s;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0) tmem_alloc(&tmem_base_s, 512);
+  if (threadIdx.x == 32) {
+    mbar_init(&z3_full, 16); mbar_init(&z2_full[0], 16); mbar_init(&z2_full[1], 16);
+    mbar_init(&da2_full[0], 1); mbar_init(&da2_full[1], 1); mbar_init(&da1_full, 1);
+    fence_mbar_init();
+  }
+  fill_weight_sw128_strided<128, 64>(params + CBF_W3, 1, 128, W3Thi, W3Tlo);
+  fill_weight_sw128_strided<64, 128>(params + CBF_W2, 1, 64, W2Thi, W2Tlo);
+  for (int t = threadIdx.x; t < 64 * 8; t += THREADS) W1[t] = ((t & 7) < 6) ? __ldg(params + CBF_W1 + (t >> 3) * 6 + (t & 7)) : 0.f;
+  for (int t = threadIdx.x; t < 64; t += THREADS) W4[t] = __ldg(params + CBF_W4 + t);
+  fence_proxy_async_smem();
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tbase = tmem_base_s;
+  const long long first = tile_begin + blockIdx.x;
+
+  if (warp == WORKERS / 32) {
+    // =============================== MMA-issue warp ===============================
+    const uint64_t d_w3hi = smem_desc_sw128(smem_u32(W3Thi)), d_w3lo = smem_desc_sw128(smem_u32(W3Tlo));
+    const uint64_t d_w2hi = smem_desc_sw128(smem_u32(W2Thi)), d_w2lo = smem_desc_sw128(smem_u32(W2Tlo));
+    const uint32_t tb = __shfl_sync(0xffffffffu, tbase, 0);
+    constexpr uint32_t IDESC = idesc_tf32(128, 64);
+    uint32_t par = 0;
+    for (long long tile = first; tile < tile_end; tile += gridDim.x, par ^= 1) {
+      mbar_wait(&z3_full, par);
+      fence_after_sync();
+      // dA2[128 x 128] = dZ3[128 x 64] * W3 in two 64-column chunks (B rows 64c.. of each 32-wide K block)
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+#pragma unroll
+        for (int term = 0; term < 3; ++term) {         // lo*hi, hi*lo, hi*hi (small terms first)
+          const uint32_t a_col = tb + (term == 0 ? C_Z3LO : C_Z3HI);
+          const uint64_t b_desc = desc_advance((term == 1) ? d_w3lo : d_w3hi, c * (64 * 128));
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks) {
+            const uint64_t bd = desc_advance(b_desc, (ks >> 2) * (128 * 128) + (ks & 3) * 32);
+            if (elect_one()) mma_tf32_ts(tb + C_DA2 + c * 64, a_col + ks * 8, bd, IDESC, (term | ks) ? 1u : 0u);
+          }
+        }
+        if (elect_one()) mma_commit(&da2_full[c]);
+      }
+      // dA1[128 x 64] = dZ2[128 x 128] * W2: cross terms per 64-wide K chunk as it arrives, hi*hi last
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        mbar_wait(&z2_full[c], par);
+        fence_after_sync();
+#pragma unroll
+        for (int term = 0; term < 2; ++term) {
+          const uint32_t a_col = tb + (term == 0 ? C_Z2LO : C_DA2) + c * 64;
+          const uint64_t b_desc = desc_advance((term == 1) ? d_w2lo : d_w2hi, (2 * c) * (64 * 128));
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks) {
+            const uint64_t bd = desc_advance(b_desc, (ks >> 2) * (64 * 128) + (ks & 3) * 32);
+            if (elect_one()) mma_tf32_ts(tb + C_DA1, a_col + ks * 8, bd, IDESC, (c | term | ks) ? 1u : 0u);
+          }
+        }
+      }
+#pragma unroll
+      for (int ks = 0; ks < 16; ++ks) {
+        const uint64_t bd = desc_advance(d_w2hi, (ks >> 2) * (64 * 128) + (ks & 3) * 32);
+        if (elect_one()) mma_tf32_ts(tb + C_DA1, tb + C_DA2 + ks * 8, bd, IDESC, 1u);
+      }
+      if (elect_one()) mma_commit(&da1_full);
+    }
+  } else {
+    // ================================= worker warps =================================
+    const int q = warp & 3, cgrp = warp >> 2;
+    const int r = q * 32 + lane;
+    const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16);
+    const int c0 = cgrp * 16;
+    const int wc = threadIdx.x & 63, wf = threadIdx.x >> 6;     // dW1 / db1 output of this thread: channel wc, column wf (6 = bias)
+    float accw1 = 0.f;
+    auto dump8 = [&](unsigned char* img_hi, unsigned char* img_lo, int chunk, const float* x) {
+      uint4 bh, bl;
+      bf16_split8(x, bh, bl);
+      const uint32_t off = img_off(r, chunk);
+      *reinterpret_cast<uint4*>(img_hi + off) = bh;
+      *reinterpret_cast<uint4*>(img_lo + off) = bl;
+    };
+    uint32_t par = 0;
+    for (long long tile = first; tile < tile_end; tile += gridDim.x, par ^= 1) {
+      unsigned char* tr = rec + (size_t)(tile - tile_begin) * cbfrec::BYTES;
+      const uint32_t* masks = reinterpret_cast<const uint32_t*>(tr + cbfrec::MASKS);
+      const uint32_t mb1 = masks[(0 * 4 + cgrp) * R + r];
+      const uint32_t mb2[2] = {masks[(1 * 4 + cgrp) * R + r], masks[(2 * 4 + cgrp) * R + r]};
+      const uint32_t mb3 = masks[(3 * 4 + cgrp) * R + r];
+      const float gm = reinterpret_cast<const float*>(tr + cbfrec::GM)[r];
+      float4 x0 = make_float4(0.f, 0.f, 0.f, 0.f), x1 = x0;
+      if (cgrp == 0) {
+        const float4* xr = reinterpret_cast<const float4*>(tr + cbfrec::XREC) + 2 * r;
+        x0 = xr[0]; x1 = xr[1];
+        *reinterpret_cast<float4*>(xs + r * 8) = x0;
+        *reinterpret_cast<float4*>(xs + r * 8 + 4) = make_float4(x1.x, x1.y, 1.f, 0.f);
+      }
+      // ---- dZ3 = gm * w4 * [z3 > 0]  (this thread: row r, channels c0 .. c0+15) ----
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        float x[8], hi[8], lo[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          x[e] = ((mb3 >> (half * 8 + e)) & 1u) ? gm * W4[c0 + half * 8 + e] : 0.f;
+          tf32_split(x[e], hi[e], lo[e]);
+        }
+        tmem_st8(tlane + C_Z3HI + c0 + half * 8, hi);
+        tmem_st8(tlane + C_Z3LO + c0 + half * 8, lo);
+        dump8(tr + cbfrec::Z3_HI, tr + cbfrec::Z3_LO, 2 * cgrp + half, x);
+      }
+      wait_st();
+      warp_arrive_after_tmem(&z3_full);
+      // ---- dZ2 = dA2 * [z2 > 0] per 64-column chunk: hi in place, lo aside, image dumped ----
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        mbar_wait(&da2_full[c], par);
+        fence_after_sync();
+        float v[16];
+        tmem_ld16(tlane + C_DA2 + c * 64 + c0, v);
+        wait_ld();
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          float x[8], hi[8], lo[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            x[e] = ((mb2[c] >> (half * 8 + e)) & 1u) ? v[half * 8 + e] : 0.f;
+            tf32_split(x[e], hi[e], lo[e]);
+          }
+          tmem_st8(tlane + C_DA2 + c * 64 + c0 + half * 8, hi);
+          tmem_st8(tlane + C_Z2LO + c * 64 + c0 + half * 8, lo);
+          dump8(tr + cbfrec::Z2_HI + c * cbfrec::BLK, tr + cbfrec::Z2_LO + c * cbfrec::BLK, 2 * cgrp + half, x);
+        }
+        wait_st();
+        warp_arrive_after_tmem(&z2_full[c]);
+      }
+      // ---- dZ1 = dA1 * [z1 > 0]; d/dfeatures partials; stage dZ1^T for dW1 ----
+      mbar_wait(&da1_full, par);
+      fence_after_sync();
+      {
+        float v[16];
+        tmem_ld16(tlane + C_DA1 + c0, v);
+        wait_ld();
+        float px[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+          const float dz = ((mb1 >> e) & 1u) ? v[e] : 0.f;
+          dz1s[(c0 + e) * DZS + r] = dz;
+          const float4 wa = *reinterpret_cast<const float4*>(W1 + (c0 + e) * 8);
+          const float4 wb = *reinterpret_cast<const float4*>(W1 + (c0 + e) * 8 + 4);
+          px[0] = fmaf(dz, wa.x, px[0]); px[1] = fmaf(dz, wa.y, px[1]); px[2] = fmaf(dz, wa.z, px[2]);
+          px[3] = fmaf(dz, wa.w, px[3]); px[4] = fmaf(dz, wb.x, px[4]); px[5] = fmaf(dz, wb.y, px[5]);
+        }
+#pragma unroll
+        for (int f = 0; f < 6; ++f) xpart[(cgrp * 6 + f) * R + r] = px[f];
+      }
+      fence_before_sync();
+      named_bar_sync(1, WORKERS);
+      // ---- dW1[c][f], db1[c] += sum over the tile's rows (rows without an edge have dZ1 = 0) ----
+      if (wf < 7) {
+        const float* dzr = dz1s + wc * DZS;
+        float s = 0.f;
+#pragma unroll 8
+        for (int e = 0; e < R; ++e) s = fmaf(dzr[e], xs[e * 8 + wf], s);
+        accw1 += s;
+      }
+      // ---- features -> states (cbf.py:23-30): +grad to agent i, -grad to neighbour j ----
+      if (grad_states != nullptr && cgrp == 0) {
+        const long long a0 = tile * TA;
+        const int rows = (int)min((long long)TA, agents_total - a0) * K;
+        if (r < rows) {
+          float d0[6];
+#pragma unroll
+          for (int f = 0; f < 6; ++f)
+            d0[f] = (xpart[(0 * 6 + f) * R + r] + xpart[(1 * 6 + f) * R + r]) + (xpart[(2 * 6 + f) * R + r] + xpart[(3 * 6 + f) * R + r]);
+          const float inv_d = 1.f / x1.z;
+          const float gx = d0[0] + d0[5] * x0.x * inv_d;
+          const float gy = d0[1] + d0[5] * x0.y * inv_d;
+          const long long ga = a0 + r / K;
+          const int b = (int)(ga / N);
+          const int j = __ldg(idx + a0 * K + r);
+          const long long gj = (j < N) ? (long long)b * N + j : -1;
+          if (gj != ga) {   // the self edge contributes +g - g = 0
+            float* pi = grad_states + (size_t)ga * 4;
+            atomicAdd(pi + 0, gx); atomicAdd(pi + 1, gy); atomicAdd(pi + 2, d0[2]); atomicAdd(pi + 3, d0[3]);
+            if (gj >= 0) {
+              float* pj = grad_states + (size_t)gj * 4;
+              atomicAdd(pj + 0, -gx); atomicAdd(pj + 1, -gy); atomicAdd(pj + 2, -d0[2]); atomicAdd(pj + 3, -d0[3]);
+            }
+          }
+        }
+      }
+      named_bar_sync(1, WORKERS);                      // dz1s / xs / xpart are rewritten by the next tile
+    }
+    float* gp = slices + (size_t)blockIdx.x * MACBF_CBF_PARAMS;
+    if (wf < 6) gp[CBF_W1 + wc * 6 + wf] += accw1;
+    else if (wf == 6) gp[CBF_B1 + wc] += accw1;
+  }
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tbase, 512);
+}
+
+// ================================ kernel 3: weight gradients ================================
+namespace cbfwg {
+constexpr int THREADS = 192;                   // warp 0: bulk-copy producer, warp 1: MMA issue, warps 2..5: final epilogue
+constexpr uint32_t STAGE = cbfrec::STAGE_BYTES;
+constexpr uint32_t ONES = 2 * STAGE;           // bf16 ones: 2 blocks x 16 rows x 128 B = 4 KB (A operand M = 128, K = 16)
+constexpr size_t smem_bytes = 2 * (size_t)STAGE + 4096 + 1024;
+// TMEM columns: [0,64) dW3^T[in][out]  [64,128) dW2[out][in]  [128,192) db3 (every lane)  [192,208) db2 (column 0)
+constexpr uint32_t C_W3 = 0, C_W2 = 64, C_B3 = 128, C_B2 = 192;
+}  // namespace cbfwg
+
+__global__ void __launch_bounds__(cbfwg::THREADS, 1)
+cbf_wgrad_tc_kernel(const unsigned char* __restrict__ rec, long long ntiles, float* __restrict__ slices) {
+  using namespace cbfwg;
+  using namespace tc;
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* sm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  __shared__ uint64_t full[2], empty[2], done;
+  __shared__ uint32_t tmem_base_s;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp == 0) tmem_alloc(&tmem_base_s, 256);
+  if (threadIdx.x == 32) {
+    mbar_init(&full[0], 1); mbar_init(&full[1], 1); mbar_init(&empty[0], 1); mbar_init(&empty[1], 1); mbar_init(&done, 1);
+    fence_mbar_init();
+  }
+  for (int t = threadIdx.x; t < 1024; t += THREADS) reinterpret_cast<uint32_t*>(sm + ONES)[t] = 0x3f803f80u;   // bf16 1.0 pairs
+  fence_proxy_async_smem();
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tbase = tmem_base_s;
+  // this CTA's tiles: blockIdx.x, blockIdx.x + grid, ...; two stages (G3, G2) per tile through a 2-deep ring
+  if (warp == 0) {
+    uint32_t n = 0;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      for (int s = 0; s < 2; ++s, ++n) {
+        const uint32_t buf = n & 1;
+        if (n >= 2) mbar_wait(&empty[buf], ((n >> 1) - 1) & 1);
+        if (elect_one()) {
+          const unsigned char* src = rec + (size_t)tile * cbfrec::BYTES + (size_t)s * STAGE;
+          mbar_expect_tx(&full[buf], STAGE);
+#pragma unroll
+          for (int p = 0; p < 3; ++p) bulk_g2s(sm + buf * STAGE + p * (STAGE / 3), src + p * (STAGE / 3), STAGE / 3, &full[buf]);
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp == 1) {
+    const uint32_t tb = __shfl_sync(0xffffffffu, tbase, 0);
+    constexpr uint32_t ID64 = idesc_bf16_mn(128, 64), ID16 = idesc_bf16_mn(128, 16);   // M = 128 needs N % 16 == 0
+    const uint64_t d_ones_a = smem_desc_mn_sw128(smem_u32(sm + ONES), 2048);     // M = 128: two 64-wide blocks 2 KB apart
+    const uint64_t d_ones_b = smem_desc_mn_sw128(smem_u32(sm + ONES), 2048);
+    uint32_t n = 0;
+    bool first_tile = true;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, first_tile = false) {
+      for (int s = 0; s < 2; ++s, ++n) {
+        const uint32_t buf = n & 1;
+        mbar_wait(&full[buf], (n >> 1) & 1);
+        fence_after_sync();
+        const uint32_t base = smem_u32(sm + buf * STAGE);
+        // A: 128 channels (two 64-wide blocks, 16 KB apart), B: 64 channels; hi at +0 / +4 BLK, lo at +2 / +5 BLK
+        const uint64_t a_hi = smem_desc_mn_sw128(base, cbfrec::BLK), a_lo = smem_desc_mn_sw128(base + 2 * cbfrec::BLK, cbfrec::BLK);
+        const uint64_t b_hi = smem_desc_mn_sw128(base + 4 * cbfrec::BLK, cbfrec::BLK), b_lo = smem_desc_mn_sw128(base + 5 * cbfrec::BLK, cbfrec::BLK);
+        const uint32_t dcol = tb + (s == 0 ? C_W3 : C_W2);
+        const uint32_t acc0 = first_tile ? 0u : 1u;
+#pragma unroll
+        for (int term = 0; term < 3; ++term) {          // lo*hi, hi*lo, hi*hi
+          const uint64_t ad = (term == 0) ? a_lo : a_hi, bd = (term == 1) ? b_lo : b_hi;
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)                // 16 edges per MMA: two 8-row groups = 2048 B
+            if (elect_one()) mma_f16_ss(dcol, desc_advance(ad, ks * 2048), desc_advance(bd, ks * 2048), ID64, (term | ks) ? 1u : acc0);
+        }
+        if (s == 0) {
+          // db3[n] = sum_e dZ3[e][n]: ones (A, M = 128) x dZ3 (B)
+#pragma unroll
+          for (int term = 0; term < 2; ++term)
+#pragma unroll
+            for (int ks = 0; ks < 8; ++ks)
+              if (elect_one()) mma_f16_ss(tb + C_B3, d_ones_a, desc_advance(term == 0 ? b_lo : b_hi, ks * 2048), ID64, (term | ks) ? 1u : acc0);
+        } else {
+          // db2[m] = sum_e dZ2[e][m]: dZ2 (A) x ones (B, N = 16)
+#pragma unroll
+          for (int term = 0; term < 2; ++term)
+#pragma unroll
+            for (int ks = 0; ks < 8; ++ks)
+              if (elect_one()) mma_f16_ss(tb + C_B2, desc_advance(term == 0 ? a_lo : a_hi, ks * 2048), d_ones_b, ID16, (term | ks) ? 1u : acc0);
+        }
+        if (elect_one()) mma_commit(&empty[buf]);       // the stage may be overwritten once these MMAs have read it
+      }
+    }
+    if (elect_one()) mma_commit(&done);
+  } else {
+    // final epilogue: accumulators -> this CTA's gradient slice
+    mbar_wait(&done, 0);
+    fence_after_sync();
+    const int q = warp & 3;                             // TMEM lane quadrant this warp may read
+    const int m = q * 32 + lane;
+    const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16);
+    float* gp = slices + (size_t)blockIdx.x * MACBF_CBF_PARAMS;
+    for (int c0 = 0; c0 < 64; c0 += 16) {
+      float v[16];
+      tmem_ld16(tlane + C_W3 + c0, v);                  // dW3^T[m = in][n = out]
+      wait_ld();
+#pragma unroll
+      for (int e = 0; e < 16; ++e) gp[CBF_W3 + (c0 + e) * 128 + m] += v[e];
+      tmem_ld16(tlane + C_W2 + c0, v);                  // dW2[m = out][n = in]
+      wait_ld();
+#pragma unroll
+      for (int e = 0; e < 16; ++e) gp[CBF_W2 + m * 64 + c0 + e] += v[e];
+    }
+    {
+      float v[8];
+      tmem_ld8(tlane + C_B2, v);
+      wait_ld();
+      gp[CBF_B2 + m] += v[0];
+    }
+    if (q == 0) {                                       // every lane holds the same db3 row; lane m < 32 writes channels 2m, 2m+1
+      for (int c0 = 0; c0 < 64; c0 += 16) {
+        float v[16];
+        tmem_ld16(tlane + C_B3 + c0, v);
+        wait_ld();
+        if (lane == 0) {
+#pragma unroll
+          for (int e = 0; e < 16; ++e) gp[CBF_B3 + c0 + e] += v[e];
+        }
+      }
+    }
+  }
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tbase, 256);
+}
+
+// ================================ host side ================================
+namespace {
+constexpr long long CHUNK_TILES = 8192;        // records of one chunk: 8192 x 205 KB = 1.6 GB
+inline long long cbf_bwd_tiles(long long agents, int K) {
+  const int TA = max(1, 128 / K);
+  return (agents + TA - 1) / TA;
+}
+}  // namespace
+
+size_t cbf_backward_tc_scratch_bytes(int B, int N, int K) {
+  const long long nt = cbf_bwd_tiles((long long)B * N, K);
+  const long long ct = nt < CHUNK_TILES ? nt : CHUNK_TILES;
+  return (size_t)NUM_SMS * MACBF_CBF_PARAMS * sizeof(float) + 1024 + (size_t)ct * cbfrec::BYTES;
+}
+
+int cbf_backward_tc(const float* states, const float* obstacles, const int32_t* idx, const float* params,
+                    const float* grad_h, int B, int N, int M, int K, double dist_min, double obs_radius,
+                    float* grad_params, float* grad_states, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+  const long long agents = (long long)B * N;
+  MACBF_CHECK_ARG(agents < (1ll << 31), "cbf_backward: B*N must be < 2^31");
+  MACBF_CHECK_ARG(K <= 128, "cbf_backward: tensor-core path needs K <= 128");
+  const size_t need = cbf_backward_tc_scratch_bytes(B, N, K);
+  MACBF_CHECK_ARG(scratch_bytes >= need, "cbf_backward: scratch too small (%zu < %zu)", scratch_bytes, need);
+  const size_t slice_bytes = (size_t)NUM_SMS * MACBF_CBF_PARAMS * sizeof(float);
+  float* slices = (float*)scratch;
+  unsigned char* rec = (unsigned char*)(((uintptr_t)scratch + slice_bytes + 1023) & ~(uintptr_t)1023);
+  const int TA = max(1, 128 / K);
+  const long long nt = cbf_bwd_tiles(agents, K);
+  MACBF_CHECK_CUDA(cudaMemsetAsync(slices, 0, slice_bytes, st));
+  MACBF_CHECK_CUDA(cudaFuncSetAttribute(cbf_dgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfdg::smem_bytes));
+  MACBF_CHECK_CUDA(cudaFuncSetAttribute(cbf_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfwg::smem_bytes));
+  for (long long t0 = 0; t0 < nt; t0 += CHUNK_TILES) {
+    const long long t1 = (t0 + CHUNK_TILES < nt) ? t0 + CHUNK_TILES : nt;
+    const long long ct = t1 - t0;
+    const int grid = (int)(ct < NUM_SMS ? ct : (long long)NUM_SMS);
+    if (int rc = cbf_forward_tc_dump(states, obstacles, idx, params, N, M, K, agents, dist_min, obs_radius, t0, t1, grad_h, rec,
+                                     slices, st))
+      return rc;
+    cbf_dgrad_tc_kernel<<<grid, cbfdg::THREADS, cbfdg::smem_bytes, st>>>(idx, params, N, K, agents, TA, t0, t1, rec, slices,
+                                                                        grad_states);
+    MACBF_CHECK_LAUNCH("cbf_dgrad_tc_kernel");
+    cbf_wgrad_tc_kernel<<<grid, cbfwg::THREADS, cbfwg::smem_bytes, st>>>(rec, ct, slices);
+    MACBF_CHECK_LAUNCH("cbf_wgrad_tc_kernel");
+  }
+  reduce_partials_kernel<<<(MACBF_CBF_PARAMS + 255) / 256, 256, 0, st>>>(slices, NUM_SMS, MACBF_CBF_PARAMS, grad_params);
+  MACBF_CHECK_LAUNCH("reduce_partials_kernel");
+  return 0;
+}
+
+}  // namespace macbf

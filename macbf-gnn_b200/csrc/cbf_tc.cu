@@ -27,6 +27,7 @@
 //               [256,384) A3_lo  [384,448) D3
 #include "common.cuh"
 #include "tc_common.cuh"
+#include "cbf_bwd_layout.cuh"
 
 namespace macbf {
 
@@ -66,14 +67,22 @@ constexpr int oB3 = oB2 + 128;
 constexpr int oW4 = oB3 + 64;
 constexpr int oB4 = oW4 + 64;
 constexpr int oHpart = oB4 + 4;            // [2][4][128]
-constexpr int total_floats = oHpart + 2 * 4 * R;
+constexpr int oGms = oHpart + 2 * 4 * R;    // [4][128] ring: dL/dh * mask of the tiles in flight (DUMP mode)
+constexpr int total_floats = oGms + 4 * R;
 constexpr size_t smem_bytes = (size_t)total_floats * 4 + 1024;
 }  // namespace cbftc
 
+// DUMP = true is the first kernel of the tensor-core backward (cbf_bwd_tc.cu): the same forward, over
+// tiles [tile_begin, tile_end), that also writes per tile (record `tile - tile_begin`, cbf_bwd_layout.cuh)
+// the bf16 hi/lo images of the layer-1/2 activations, the ReLU bit masks of all three layers, the edge
+// features and gm = dL/dh * radius mask, and accumulates dW4 / db4 into this CTA's gradient slice.
+template <bool DUMP>
 __global__ void __launch_bounds__(cbftc::THREADS, 1)
 cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict__ obstacles,
                       const int32_t* __restrict__ idx, const float* __restrict__ params, int N, int M, int K,
-                      long long agents_total, int TA, float dist_min, float obs_radius, float* __restrict__ h) {
+                      long long agents_total, int TA, float dist_min, float obs_radius, float* __restrict__ h,
+                      long long tile_begin, long long tile_end, const float* __restrict__ grad_h,
+                      unsigned char* __restrict__ rec, float* __restrict__ slices) {
   using namespace cbftc;
   using namespace tc;
   extern __shared__ unsigned char smem_raw[];
@@ -84,6 +93,7 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
   float* A1hi = sm + oA1HI; float* A1lo = sm + oA1LO;
   float* B1 = sm + oB1; float* B2 = sm + oB2; float* B3 = sm + oB3; float* W4 = sm + oW4; float* B4 = sm + oB4;
   float* hpart = sm + oHpart;
+  [[maybe_unused]] float* gms = sm + oGms;
   // workers -> MMA: a1_full (4 arrivals: the feature warps), a2_full, a3_full[2], d3_free (16: one per worker warp)
   // MMA -> workers (tcgen05.commit): d1_full, d2_full[2], d3_full
   __shared__ uint64_t a1_full, a2_full, a3_full[2], d3_free, d1_full, d2_full[2], d3_full;
@@ -121,7 +131,8 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
   __syncthreads();
   fence_after_sync();
   const uint32_t tbase = tmem_base_s;
-  const long long ntiles = (agents_total + TA - 1) / TA;
+  const long long ntiles = tile_end;
+  const long long first = tile_begin + blockIdx.x;
   [[maybe_unused]] int trace_n = 0;
 
   if (warp == WORKERS / 32) {
@@ -144,7 +155,7 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
     issue_layer1(0);
     uint32_t par = 0;
     int it = 0;
-    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, par ^= 1, ++it) {
+    for (long long tile = first; tile < ntiles; tile += gridDim.x, par ^= 1, ++it) {
       mbar_wait(&a2_full, par);
       fence_after_sync();
       TC_TRACE(1, 1);
@@ -204,10 +215,13 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
 
     // Edge endpoints of upcoming tiles are fetched one phase ahead of their use (feature warps only).
     int pf_j = 0, pf_b = 0, pf_i = 0;
+    [[maybe_unused]] long long pf_tile = 0;
+    [[maybe_unused]] int pf_slot = 0;
     bool pf_valid = false;
     float4 pf_si = make_float4(0.f, 0.f, 0.f, 0.f), pf_sj = pf_si;
     auto prefetch_ij = [&](long long t) {
       pf_valid = false;
+      pf_tile = t;
       if (cgrp == 0 && t < ntiles) {
         const int ga = (int)(t * TA) + a_loc;      // B*N < 2^31 is checked by the host
         if (a_loc < TA && ga < (int)agents_total) {
@@ -231,6 +245,20 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
         f[0] = g.dx; f[1] = g.dy; f[2] = g.dvx; f[3] = g.dvy; f[4] = g.eye; f[5] = xsub(d, dist_min);
         mk = (d <= obs_radius) ? 1.f : 0.f;
       }
+      if constexpr (DUMP) {
+        unsigned char* tr = rec + (size_t)(pf_tile - tile_begin) * cbfrec::BYTES;
+        float gm = 0.f, dd = 1.f;
+        if (pf_valid) {
+          gm = __ldg(grad_h + (size_t)(pf_tile * TA) * K + r) * mk;      // d h / d y4 = mask (cbf.py:43)
+          dd = xadd(f[5], dist_min);
+        }
+        float4* xr = reinterpret_cast<float4*>(tr + cbfrec::XREC) + 2 * r;
+        xr[0] = make_float4(f[0], f[1], f[2], f[3]);
+        xr[1] = make_float4(f[4], f[5], dd, 0.f);
+        reinterpret_cast<float*>(tr + cbfrec::GM)[r] = gm;
+        gms[pf_slot * R + r] = gm;
+        pf_slot = (pf_slot + 1) & 3;
+      }
       float hi[8], lo[8];
 #pragma unroll
       for (int e = 0; e < 8; ++e) tf32_split(f[e], hi[e], lo[e]);
@@ -245,28 +273,48 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
       return mk;
     };
     // layer-1 epilogue: D1 -> bias + ReLU + split -> A2 (hi in place over D1, lo aside)
-    auto epilogue1 = [&](uint32_t parity) {
+    // DUMP: post-ReLU values x[8] of channels [8*chunk, 8*chunk+8) of a 64-channel block -> bf16 hi/lo image
+    auto dump8 = [&](unsigned char* img_hi, unsigned char* img_lo, int chunk, const float* x) {
+      uint4 bh, bl;
+      bf16_split8(x, bh, bl);
+      const uint32_t off = img_off(r, chunk);
+      *reinterpret_cast<uint4*>(img_hi + off) = bh;
+      *reinterpret_cast<uint4*>(img_lo + off) = bl;
+    };
+    auto epilogue1 = [&](uint32_t parity, [[maybe_unused]] long long tile_e) {
       mbar_wait(&d1_full, parity);
       fence_after_sync();
       const int c0 = cgrp * 16;
       float v[16];
       tmem_ld16(tlane + C_A2HI + c0, v);
       wait_ld();
+      [[maybe_unused]] uint32_t bits = 0;
+      [[maybe_unused]] unsigned char* tr = DUMP ? rec + (size_t)(tile_e - tile_begin) * cbfrec::BYTES : nullptr;
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
         float hi[8], lo[8];
+        [[maybe_unused]] float x[8];
 #pragma unroll
         for (int j4 = 0; j4 < 2; ++j4) {
           const float4 bb = *reinterpret_cast<const float4*>(B1 + c0 + half * 8 + 4 * j4);
           float2 h2, l2;
-          split2_trunc(relu2(__fadd2_rn(make_float2(v[half * 8 + 4 * j4 + 0], v[half * 8 + 4 * j4 + 1]), make_float2(bb.x, bb.y))), h2, l2);
+          const float2 xa = relu2(__fadd2_rn(make_float2(v[half * 8 + 4 * j4 + 0], v[half * 8 + 4 * j4 + 1]), make_float2(bb.x, bb.y)));
+          split2_trunc(xa, h2, l2);
           hi[4 * j4 + 0] = h2.x; hi[4 * j4 + 1] = h2.y; lo[4 * j4 + 0] = l2.x; lo[4 * j4 + 1] = l2.y;
-          split2_trunc(relu2(__fadd2_rn(make_float2(v[half * 8 + 4 * j4 + 2], v[half * 8 + 4 * j4 + 3]), make_float2(bb.z, bb.w))), h2, l2);
+          const float2 xb = relu2(__fadd2_rn(make_float2(v[half * 8 + 4 * j4 + 2], v[half * 8 + 4 * j4 + 3]), make_float2(bb.z, bb.w)));
+          split2_trunc(xb, h2, l2);
           hi[4 * j4 + 2] = h2.x; hi[4 * j4 + 3] = h2.y; lo[4 * j4 + 2] = l2.x; lo[4 * j4 + 3] = l2.y;
+          if constexpr (DUMP) { x[4 * j4 + 0] = xa.x; x[4 * j4 + 1] = xa.y; x[4 * j4 + 2] = xb.x; x[4 * j4 + 3] = xb.y; }
         }
         tmem_st8(tlane + C_A2HI + c0 + half * 8, hi);
         tmem_st8(tlane + C_A2LO + c0 + half * 8, lo);
+        if constexpr (DUMP) {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) bits |= (x[e] > 0.f ? 1u : 0u) << (half * 8 + e);
+          dump8(tr + cbfrec::A1_HI, tr + cbfrec::A1_LO, 2 * cgrp + half, x);
+        }
       }
+      if constexpr (DUMP) reinterpret_cast<uint32_t*>(tr + cbfrec::MASKS)[(0 * 4 + cgrp) * R + r] = bits;
       wait_st();
       warp_arrive_after_tmem(&a2_full);
     };
@@ -275,17 +323,25 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
     // (in the slack before its layer-3 epilogue), so layer 1 of the next tile never waits for them.
     const long long g = gridDim.x;
     float m0 = 0.f, m1 = 0.f, m2 = 0.f;              // radius masks of tiles t, t+g, t+2g (feature warps)
-    prefetch_ij(blockIdx.x);
+    prefetch_ij(first);
     prefetch_sj();
     if (cgrp == 0) m0 = features();
-    epilogue1(0);
-    prefetch_ij(blockIdx.x + g);
+    epilogue1(0, first);
+    prefetch_ij(first + g);
     prefetch_sj();
-    if (cgrp == 0 && blockIdx.x + g < ntiles) m1 = features();
-    prefetch_ij(blockIdx.x + 2 * g);
+    if (cgrp == 0 && first + g < ntiles) m1 = features();
+    prefetch_ij(first + 2 * g);
+    [[maybe_unused]] float acc4[16];
+    [[maybe_unused]] float accb4 = 0.f;
+    [[maybe_unused]] int gslot = 0;
+    if constexpr (DUMP) {
+#pragma unroll
+      for (int q = 0; q < 16; ++q) acc4[q] = 0.f;
+    }
 
     uint32_t par = 0;
-    for (long long tile = blockIdx.x; tile < ntiles; tile += g, par ^= 1) {
+    for (long long tile = first; tile < ntiles; tile += g, par ^= 1) {
+      [[maybe_unused]] unsigned char* tr = DUMP ? rec + (size_t)(tile - tile_begin) * cbfrec::BYTES : nullptr;
       const long long a0 = tile * TA;
       const int rows = (int)min((long long)TA, agents_total - a0) * K;
       const float mk = m0;
@@ -301,27 +357,38 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
         float v[16];
         tmem_ld16(tlane + C_Y + c0, v);
         wait_ld();
+        [[maybe_unused]] uint32_t bits = 0;
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
           float hi[8], lo[8];
+          [[maybe_unused]] float x[8];
 #pragma unroll
           for (int j4 = 0; j4 < 2; ++j4) {
             const float4 bb = *reinterpret_cast<const float4*>(B2 + c0 + half * 8 + 4 * j4);
             float2 h2, l2;
-            split2_trunc(relu2(__fadd2_rn(make_float2(v[half * 8 + 4 * j4 + 0], v[half * 8 + 4 * j4 + 1]), make_float2(bb.x, bb.y))), h2, l2);
+            const float2 xa = relu2(__fadd2_rn(make_float2(v[half * 8 + 4 * j4 + 0], v[half * 8 + 4 * j4 + 1]), make_float2(bb.x, bb.y)));
+            split2_trunc(xa, h2, l2);
             hi[4 * j4 + 0] = h2.x; hi[4 * j4 + 1] = h2.y; lo[4 * j4 + 0] = l2.x; lo[4 * j4 + 1] = l2.y;
-            split2_trunc(relu2(__fadd2_rn(make_float2(v[half * 8 + 4 * j4 + 2], v[half * 8 + 4 * j4 + 3]), make_float2(bb.z, bb.w))), h2, l2);
+            const float2 xb = relu2(__fadd2_rn(make_float2(v[half * 8 + 4 * j4 + 2], v[half * 8 + 4 * j4 + 3]), make_float2(bb.z, bb.w)));
+            split2_trunc(xb, h2, l2);
             hi[4 * j4 + 2] = h2.x; hi[4 * j4 + 3] = h2.y; lo[4 * j4 + 2] = l2.x; lo[4 * j4 + 3] = l2.y;
+            if constexpr (DUMP) { x[4 * j4 + 0] = xa.x; x[4 * j4 + 1] = xa.y; x[4 * j4 + 2] = xb.x; x[4 * j4 + 3] = xb.y; }
           }
           tmem_st8(tlane + C_Y + c0 + half * 8, hi);
           tmem_st8(tlane + C_A3LO + c0 + half * 8, lo);
+          if constexpr (DUMP) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) bits |= (x[e] > 0.f ? 1u : 0u) << (half * 8 + e);
+            dump8(tr + cbfrec::A2_HI + c * cbfrec::BLK, tr + cbfrec::A2_LO + c * cbfrec::BLK, 2 * cgrp + half, x);
+          }
         }
+        if constexpr (DUMP) reinterpret_cast<uint32_t*>(tr + cbfrec::MASKS)[((1 + c) * 4 + cgrp) * R + r] = bits;
         wait_st();
         warp_arrive_after_tmem(&a3_full[c]);
         if (warp == 0) TC_TRACE(0, 2 + 2 * c);
       }
       // ---- layer-1 epilogue of the NEXT tile (overlaps this tile's layer 3 on the tensor core) ----
-      if (has_next) epilogue1(par ^ 1);
+      if (has_next) epilogue1(par ^ 1, tile + g);
       // ---- features of tile + 2g -> A1 (layer 1 of tile + g has retired: d1_full was just observed) ----
       if (cgrp == 0 && tile + 2 * g < ntiles) {
         m2 = features();
@@ -338,6 +405,20 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
         tmem_ld16(tlane + C_D3 + c0, v);
         wait_ld();
         warp_arrive_after_tmem(&d3_free);
+        if constexpr (DUMP) {
+          named_bar_sync(1, WORKERS);                    // gms[gslot] (written >= 1 tile ago by the feature warps) is visible
+          const float gm = gms[gslot * R + r];
+          gslot = (gslot + 1) & 3;
+          uint32_t bits = 0;
+#pragma unroll
+          for (int q = 0; q < 16; ++q) {
+            const float z = fmaxf(v[q] + B3[c0 + q], 0.f);
+            bits |= (z > 0.f ? 1u : 0u) << q;
+            acc4[q] = fmaf(gm, z, acc4[q]);              // dW4 (cbf.py:19)
+          }
+          if (cgrp == 0) accb4 += gm;
+          reinterpret_cast<uint32_t*>(tr + cbfrec::MASKS)[(3 * 4 + cgrp) * R + r] = bits;
+        }
         float2 s2 = make_float2(0.f, 0.f);
 #pragma unroll
         for (int j4 = 0; j4 < 4; ++j4) {
@@ -346,17 +427,39 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
           s2 = __ffma2_rn(make_float2(ww.x, ww.y), relu2(__fadd2_rn(make_float2(v[4 * j4 + 0], v[4 * j4 + 1]), make_float2(bb.x, bb.y))), s2);
           s2 = __ffma2_rn(make_float2(ww.z, ww.w), relu2(__fadd2_rn(make_float2(v[4 * j4 + 2], v[4 * j4 + 3]), make_float2(bb.z, bb.w))), s2);
         }
-        const float s = s2.x + s2.y;
-        float* hp = hpart + (par * 4) * R;
-        hp[cgrp * R + r] = s;
-        named_bar_sync(1, WORKERS);
-        if (cgrp == 0 && r < rows) {
-          const float t = (hp[r] + hp[R + r]) + (hp[2 * R + r] + hp[3 * R + r]);
-          h[a0 * K + r] = (t + B4[0]) * mk;          // cbf.py:43
+        if (h != nullptr) {
+          const float s = s2.x + s2.y;
+          float* hp = hpart + (par * 4) * R;
+          hp[cgrp * R + r] = s;
+          named_bar_sync(1, WORKERS);
+          if (cgrp == 0 && r < rows) {
+            const float t = (hp[r] + hp[R + r]) + (hp[2 * R + r] + hp[3 * R + r]);
+            h[a0 * K + r] = (t + B4[0]) * mk;          // cbf.py:43
+          }
         }
       }
       if (warp == 0) TC_TRACE(0, 7);
       m0 = m1; m1 = m2;
+    }
+    if constexpr (DUMP) {
+      // dW4 / db4 of this CTA: lanes, then the 4 lane-quadrant warps of each column group
+      named_bar_sync(1, WORKERS);
+#pragma unroll
+      for (int q = 0; q < 16; ++q) {
+        const float s = warp_sum(acc4[q]);
+        if (lane == 0) hpart[warp * 16 + q] = s;
+      }
+      const float sb = warp_sum(accb4);
+      if (lane == 0) hpart[256 + warp] = sb;
+      named_bar_sync(1, WORKERS);
+      float* gp = slices + (size_t)blockIdx.x * MACBF_CBF_PARAMS;
+      if (threadIdx.x < 64) {
+        const int cg = threadIdx.x >> 4, q = threadIdx.x & 15;
+        gp[CBF_W4 + threadIdx.x] += (hpart[(cg * 4 + 0) * 16 + q] + hpart[(cg * 4 + 1) * 16 + q]) +
+                                    (hpart[(cg * 4 + 2) * 16 + q] + hpart[(cg * 4 + 3) * 16 + q]);
+      } else if (threadIdx.x == 64) {
+        gp[CBF_B4] += (hpart[256 + 0] + hpart[256 + 1]) + (hpart[256 + 2] + hpart[256 + 3]);
+      }
     }
   }
   fence_before_sync();
@@ -371,11 +474,28 @@ int cbf_forward_tc(const float* states, const float* obstacles, const int32_t* i
   const int TA = max(1, cbftc::R / K);
   const long long ntiles = (agents + TA - 1) / TA;
   const int grid = (int)(ntiles < NUM_SMS ? ntiles : (long long)NUM_SMS);
-  MACBF_CHECK_CUDA(cudaFuncSetAttribute(cbf_forward_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  MACBF_CHECK_CUDA(cudaFuncSetAttribute(cbf_forward_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)cbftc::smem_bytes));
-  cbf_forward_tc_kernel<<<grid, cbftc::THREADS, cbftc::smem_bytes, st>>>(states, obstacles, idx, params, N, M, K, agents,
-                                                                        TA, (float)dist_min, (float)obs_radius, h);
+  cbf_forward_tc_kernel<false><<<grid, cbftc::THREADS, cbftc::smem_bytes, st>>>(
+      states, obstacles, idx, params, N, M, K, agents, TA, (float)dist_min, (float)obs_radius, h, 0, ntiles, nullptr,
+      nullptr, nullptr);
   MACBF_CHECK_LAUNCH("cbf_forward_tc_kernel");
+  return 0;
+}
+
+// First kernel of the tensor-core backward: tiles [tile_begin, tile_end) -> records + dW4/db4 slices.
+int cbf_forward_tc_dump(const float* states, const float* obstacles, const int32_t* idx, const float* params, int N, int M,
+                        int K, long long agents, double dist_min, double obs_radius, long long tile_begin,
+                        long long tile_end, const float* grad_h, unsigned char* rec, float* slices, cudaStream_t st) {
+  const int TA = max(1, cbftc::R / K);
+  const long long nt = tile_end - tile_begin;
+  const int grid = (int)(nt < NUM_SMS ? nt : (long long)NUM_SMS);
+  MACBF_CHECK_CUDA(cudaFuncSetAttribute(cbf_forward_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)cbftc::smem_bytes));
+  cbf_forward_tc_kernel<true><<<grid, cbftc::THREADS, cbftc::smem_bytes, st>>>(
+      states, obstacles, idx, params, N, M, K, agents, TA, (float)dist_min, (float)obs_radius, nullptr, tile_begin, tile_end,
+      grad_h, rec, slices);
+  MACBF_CHECK_LAUNCH("cbf_forward_tc_kernel<dump>");
   return 0;
 }
 

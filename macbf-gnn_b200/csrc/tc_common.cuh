@@ -217,5 +217,84 @@ __device__ __forceinline__ void fill_weight_sw128(const float* __restrict__ W, i
   }
 }
 
+// Same, for a strided view: element (n, k) = W[n * stride_n + k * stride_k]  (a transposed weight for dgrad).
+template <int N, int K>
+__device__ __forceinline__ void fill_weight_sw128_strided(const float* __restrict__ W, int stride_n, int stride_k,
+                                                          float* __restrict__ hi, float* __restrict__ lo) {
+  constexpr int CHUNKS = N * (K / 4);
+  for (int t = threadIdx.x; t < CHUNKS; t += blockDim.x) {
+    const int n = t % N, k4 = t / N;                 // consecutive threads -> consecutive n (coalesced when stride_n == 1)
+    const int kb = k4 >> 3, c = k4 & 7;
+    float h[4], l[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) tf32_split(__ldg(W + (size_t)n * stride_n + (size_t)(4 * k4 + q) * stride_k), h[q], l[q]);
+    const int off = kb * (N * 32) + n * 32 + ((c ^ (n & 7)) << 2);
+    *reinterpret_cast<float4*>(hi + off) = make_float4(h[0], h[1], h[2], h[3]);
+    *reinterpret_cast<float4*>(lo + off) = make_float4(l[0], l[1], l[2], l[3]);
+  }
+}
+
+// ---- bf16 hi/lo images for the weight-gradient GEMMs (K = edges) ------------------------------
+// x ~= hi + lo with hi = bf16_rn(x), lo = bf16_rn(x - hi): 16 mantissa bits, 2^-17 relative.  Eight
+// consecutive channels of one edge row are one 16-byte chunk of an MN-major SWIZZLE_128B operand
+// image: block (64 channels) -> 128 rows (edges) x 128 B, chunk c of row e at position c ^ (e & 7).
+__device__ __forceinline__ uint32_t bf16x2_rn(float lo_elem, float hi_elem) {
+  uint32_t d;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi_elem), "f"(lo_elem));   // d = {hi16: first src, lo16: second src}
+  return d;
+}
+__device__ __forceinline__ void bf16_split8(const float* x, uint4& hi, uint4& lo) {
+  uint32_t h[4], l[4];
+#pragma unroll
+  for (int p = 0; p < 4; ++p) {
+    h[p] = bf16x2_rn(x[2 * p], x[2 * p + 1]);
+    const float r0 = x[2 * p] - __uint_as_float(h[p] << 16);
+    const float r1 = x[2 * p + 1] - __uint_as_float(h[p] & 0xffff0000u);
+    l[p] = bf16x2_rn(r0, r1);
+  }
+  hi = make_uint4(h[0], h[1], h[2], h[3]);
+  lo = make_uint4(l[0], l[1], l[2], l[3]);
+}
+// byte offset of 16-byte chunk `chunk` (8 channels) of edge row `row` inside a 64-channel block
+__device__ __forceinline__ uint32_t img_off(int row, int chunk) { return (uint32_t)row * 128u + (uint32_t)((chunk ^ (row & 7)) << 4); }
+
+// MN-major SWIZZLE_128B shared-memory operand: 64 elements (bf16) contiguous along M/N per 128-B row, rows = K,
+// 8-row groups 1024 B apart (SBO), 64-element blocks `lbo_bytes` apart (LBO).
+__device__ __forceinline__ uint64_t smem_desc_mn_sw128(uint32_t addr, uint32_t lbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((addr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// kind::f16 with bf16 operands, fp32 accumulate, A and B MN-major
+__host__ __device__ constexpr uint32_t idesc_bf16_mn(int M, int N) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(N >> 3) << 17) |
+         ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void mma_f16_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                           uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}\n" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+// ---- bulk global -> shared copies completing on an mbarrier (no tensor map needed) -------------
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst_smem)),
+               "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
 }  // namespace tc
 }  // namespace macbf

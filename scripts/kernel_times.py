@@ -38,3 +38,14 @@ u, sn, _ = ops.controller_forward(s, g, idx, tf)
 timeit("loss_forward", lambda: ops.loss_forward(s, idx, h, h, u, g))
 buf = ops.StepBuffers(B, N, 0, k, "cuda")
 timeit("step_forward", lambda: ops.step_forward(s, g, cf, tf, buf))
+
+if os.environ.get("BWD", "1") == "1":
+    gh = torch.randn_like(h) * 1e-3
+    gu = torch.randn_like(u) * 1e-3
+    gs = torch.randn_like(sn) * 1e-3
+    timeit("cbf_backward (params)", lambda: ops.cbf_backward(s, idx, cf, gh))
+    timeit("cbf_backward (+d states)", lambda: ops.cbf_backward(s, idx, cf, gh, want_grad_states=True))
+    timeit("controller_backward", lambda: ops.controller_backward(s, g, idx, tf, gu, gs))
+    from macbf_b200.step import TrainStep
+    ts = TrainStep(B, N, 0, k, "cuda")
+    timeit("train forward_backward", lambda: ts.forward_backward(s, g, cf, tf))
