@@ -92,11 +92,10 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
     const uint64_t d_w2hi = smem_desc_sw128(smem_u32(W2Thi)), d_w2lo = smem_desc_sw128(smem_u32(W2Tlo));
     const uint32_t tb = __shfl_sync(0xffffffffu, tbase, 0);
     constexpr uint32_t IDESC = idesc_tf32(128, 64);
-    uint32_t par = 0;
-    for (long long tile = first; tile < tile_end; tile += gridDim.x, par ^= 1) {
-      mbar_wait(&z3_full, par);
+    // dA2[128 x 128] = dZ3[128 x 64] * W3 in two 64-column chunks (B rows 64c.. of each 32-wide K block)
+    auto issue_da2 = [&](uint32_t parity) {
+      mbar_wait(&z3_full, parity);
       fence_after_sync();
-      // dA2[128 x 128] = dZ3[128 x 64] * W3 in two 64-column chunks (B rows 64c.. of each 32-wide K block)
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
 #pragma unroll
@@ -111,6 +110,10 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
         }
         if (elect_one()) mma_commit(&da2_full[c]);
       }
+    };
+    issue_da2(0);
+    uint32_t par = 0;
+    for (long long tile = first; tile < tile_end; tile += gridDim.x, par ^= 1) {
       // dA1[128 x 64] = dZ2[128 x 128] * W2: cross terms per 64-wide K chunk as it arrives, hi*hi last
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
@@ -133,6 +136,9 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
         if (elect_one()) mma_tf32_ts(tb + C_DA1, tb + C_DA2 + ks * 8, bd, IDESC, 1u);
       }
       if (elect_one()) mma_commit(&da1_full);
+      // dA2 of the NEXT tile runs while the workers finish this one (dZ1, dW1, d/dstates); the tensor core executes
+      // in order, so its writes to the dA2 columns follow this tile's reads of dZ2_hi from the same columns.
+      if (tile + gridDim.x < tile_end) issue_da2(par ^ 1);
     }
   } else {
     // ================================= worker warps =================================
@@ -142,29 +148,40 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
     const int c0 = cgrp * 16;
     const int wc = threadIdx.x & 63, wf = threadIdx.x >> 6;     // dW1 / db1 output of this thread: channel wc, column wf (6 = bias)
     float accw1 = 0.f;
-    auto dump8 = [&](unsigned char* img_hi, unsigned char* img_lo, int chunk, const float* x) {
-      uint4 bh, bl;
-      bf16_split8(x, bh, bl);
-      const uint32_t off = img_off(r, chunk);
-      *reinterpret_cast<uint4*>(img_hi + off) = bh;
-      *reinterpret_cast<uint4*>(img_lo + off) = bl;
-    };
-    uint32_t par = 0;
-    for (long long tile = first; tile < tile_end; tile += gridDim.x, par ^= 1) {
-      unsigned char* tr = rec + (size_t)(tile - tile_begin) * cbfrec::BYTES;
-      const uint32_t* masks = reinterpret_cast<const uint32_t*>(tr + cbfrec::MASKS);
-      const uint32_t mb1 = masks[(0 * 4 + cgrp) * R + r];
-      const uint32_t mb2[2] = {masks[(1 * 4 + cgrp) * R + r], masks[(2 * 4 + cgrp) * R + r]};
-      const uint32_t mb3 = masks[(3 * 4 + cgrp) * R + r];
-      const float gm = reinterpret_cast<const float*>(tr + cbfrec::GM)[r];
-      float4 x0 = make_float4(0.f, 0.f, 0.f, 0.f), x1 = x0;
-      if (cgrp == 0) {
-        const float4* xr = reinterpret_cast<const float4*>(tr + cbfrec::XREC) + 2 * r;
-        x0 = xr[0]; x1 = xr[1];
-        *reinterpret_cast<float4*>(xs + r * 8) = x0;
-        *reinterpret_cast<float4*>(xs + r * 8 + 4) = make_float4(x1.x, x1.y, 1.f, 0.f);
+    // dZ3 = gm * w4 * [z3 > 0] of tile t (this thread: row r, channels c0 .. c0+15) -> TMEM hi/lo + image
+    // Record words are fetched one tile ahead of their use (they come from HBM: ~1 us of latency otherwise
+    // sits at the head of every tile).
+    struct RecA { uint32_t mb1, mb2a, mb2b; float4 x0, x1; };
+    struct RecZ { uint32_t mb3; float gm; };
+    auto load_a = [&](long long t) {
+      RecA a;
+      a.mb1 = a.mb2a = a.mb2b = 0u; a.x0 = make_float4(0.f, 0.f, 0.f, 0.f); a.x1 = a.x0;
+      if (t < tile_end) {
+        const unsigned char* tr = rec + (size_t)(t - tile_begin) * cbfrec::BYTES;
+        const uint32_t* masks = reinterpret_cast<const uint32_t*>(tr + cbfrec::MASKS);
+        a.mb1 = masks[(0 * 4 + cgrp) * R + r]; a.mb2a = masks[(1 * 4 + cgrp) * R + r]; a.mb2b = masks[(2 * 4 + cgrp) * R + r];
+        if (cgrp == 0) {
+          const float4* xr = reinterpret_cast<const float4*>(tr + cbfrec::XREC) + 2 * r;
+          a.x0 = xr[0]; a.x1 = xr[1];
+        }
       }
-      // ---- dZ3 = gm * w4 * [z3 > 0]  (this thread: row r, channels c0 .. c0+15) ----
+      return a;
+    };
+    auto load_z = [&](long long t) {
+      RecZ z;
+      z.mb3 = 0u; z.gm = 0.f;
+      if (t < tile_end) {
+        const unsigned char* tr = rec + (size_t)(t - tile_begin) * cbfrec::BYTES;
+        z.mb3 = reinterpret_cast<const uint32_t*>(tr + cbfrec::MASKS)[(3 * 4 + cgrp) * R + r];
+        z.gm = reinterpret_cast<const float*>(tr + cbfrec::GM)[r];
+      }
+      return z;
+    };
+    auto build_z3 = [&](long long t, const RecZ& z) {
+      unsigned char* tr = rec + (size_t)(t - tile_begin) * cbfrec::BYTES;
+      const uint32_t mb3 = z.mb3;
+      const float gm = z.gm;
+      uint4 bh[2], bl[2];
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
         float x[8], hi[8], lo[8];
@@ -175,10 +192,29 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
         }
         tmem_st8(tlane + C_Z3HI + c0 + half * 8, hi);
         tmem_st8(tlane + C_Z3LO + c0 + half * 8, lo);
-        dump8(tr + cbfrec::Z3_HI, tr + cbfrec::Z3_LO, 2 * cgrp + half, x);
+        bf16_split8(x, bh[half], bl[half]);
       }
+      img_store16(tr + cbfrec::Z3_HI, r, cgrp, bh[0], bh[1]);
+      img_store16(tr + cbfrec::Z3_LO, r, cgrp, bl[0], bl[1]);
       wait_st();
       warp_arrive_after_tmem(&z3_full);
+    };
+    build_z3(first, load_z(first));
+    RecA ra = load_a(first);
+    RecZ rz = load_z(first + gridDim.x);
+    uint32_t par = 0;
+    for (long long tile = first; tile < tile_end; tile += gridDim.x, par ^= 1) {
+      unsigned char* tr = rec + (size_t)(tile - tile_begin) * cbfrec::BYTES;
+      const uint32_t mb1 = ra.mb1;
+      const uint32_t mb2[2] = {ra.mb2a, ra.mb2b};
+      const float4 x0 = ra.x0, x1 = ra.x1;
+      if (cgrp == 0) {
+        *reinterpret_cast<float4*>(xs + r * 8) = x0;
+        *reinterpret_cast<float4*>(xs + r * 8 + 4) = make_float4(x1.x, x1.y, 1.f, 0.f);
+      }
+      ra = load_a(tile + gridDim.x);                    // consumed next iteration
+      const RecZ rz_next = load_z(tile + 2 * gridDim.x);
+      uint4 bh[2], bl[2];
       // ---- dZ2 = dA2 * [z2 > 0] per 64-column chunk: hi in place, lo aside, image dumped ----
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
@@ -197,11 +233,16 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
           }
           tmem_st8(tlane + C_DA2 + c * 64 + c0 + half * 8, hi);
           tmem_st8(tlane + C_Z2LO + c * 64 + c0 + half * 8, lo);
-          dump8(tr + cbfrec::Z2_HI + c * cbfrec::BLK, tr + cbfrec::Z2_LO + c * cbfrec::BLK, 2 * cgrp + half, x);
+          bf16_split8(x, bh[half], bl[half]);
         }
+        img_store16(tr + cbfrec::Z2_HI + c * cbfrec::BLK, r, cgrp, bh[0], bh[1]);
+        img_store16(tr + cbfrec::Z2_LO + c * cbfrec::BLK, r, cgrp, bl[0], bl[1]);
         wait_st();
         warp_arrive_after_tmem(&z2_full[c]);
       }
+      // ---- dZ3 of the next tile (the dZ3 columns are free: both dA2 chunks of this tile have been observed) ----
+      if (tile + gridDim.x < tile_end) build_z3(tile + gridDim.x, rz);
+      rz = rz_next;
       // ---- dZ1 = dA1 * [z1 > 0]; d/dfeatures partials; stage dZ1^T for dW1 ----
       mbar_wait(&da1_full, par);
       fence_after_sync();
@@ -227,10 +268,15 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
       // ---- dW1[c][f], db1[c] += sum over the tile's rows (rows without an edge have dZ1 = 0) ----
       if (wf < 7) {
         const float* dzr = dz1s + wc * DZS;
-        float s = 0.f;
-#pragma unroll 8
-        for (int e = 0; e < R; ++e) s = fmaf(dzr[e], xs[e * 8 + wf], s);
-        accw1 += s;
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll 4
+        for (int e = 0; e < R; e += 4) {
+          s0 = fmaf(dzr[e + 0], xs[(e + 0) * 8 + wf], s0);
+          s1 = fmaf(dzr[e + 1], xs[(e + 1) * 8 + wf], s1);
+          s2 = fmaf(dzr[e + 2], xs[(e + 2) * 8 + wf], s2);
+          s3 = fmaf(dzr[e + 3], xs[(e + 3) * 8 + wf], s3);
+        }
+        accw1 += (s0 + s1) + (s2 + s3);
       }
       // ---- features -> states (cbf.py:23-30): +grad to agent i, -grad to neighbour j ----
       if (grad_states != nullptr && cgrp == 0) {

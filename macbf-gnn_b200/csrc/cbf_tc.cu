@@ -273,14 +273,6 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
       return mk;
     };
     // layer-1 epilogue: D1 -> bias + ReLU + split -> A2 (hi in place over D1, lo aside)
-    // DUMP: post-ReLU values x[8] of channels [8*chunk, 8*chunk+8) of a 64-channel block -> bf16 hi/lo image
-    auto dump8 = [&](unsigned char* img_hi, unsigned char* img_lo, int chunk, const float* x) {
-      uint4 bh, bl;
-      bf16_split8(x, bh, bl);
-      const uint32_t off = img_off(r, chunk);
-      *reinterpret_cast<uint4*>(img_hi + off) = bh;
-      *reinterpret_cast<uint4*>(img_lo + off) = bl;
-    };
     auto epilogue1 = [&](uint32_t parity, [[maybe_unused]] long long tile_e) {
       mbar_wait(&d1_full, parity);
       fence_after_sync();
@@ -290,6 +282,7 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
       wait_ld();
       [[maybe_unused]] uint32_t bits = 0;
       [[maybe_unused]] unsigned char* tr = DUMP ? rec + (size_t)(tile_e - tile_begin) * cbfrec::BYTES : nullptr;
+      [[maybe_unused]] uint4 bh[2], bl[2];
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
         float hi[8], lo[8];
@@ -311,10 +304,14 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
         if constexpr (DUMP) {
 #pragma unroll
           for (int e = 0; e < 8; ++e) bits |= (x[e] > 0.f ? 1u : 0u) << (half * 8 + e);
-          dump8(tr + cbfrec::A1_HI, tr + cbfrec::A1_LO, 2 * cgrp + half, x);
+          bf16_split8(x, bh[half], bl[half]);
         }
       }
-      if constexpr (DUMP) reinterpret_cast<uint32_t*>(tr + cbfrec::MASKS)[(0 * 4 + cgrp) * R + r] = bits;
+      if constexpr (DUMP) {
+        img_store16(tr + cbfrec::A1_HI, r, cgrp, bh[0], bh[1]);
+        img_store16(tr + cbfrec::A1_LO, r, cgrp, bl[0], bl[1]);
+        reinterpret_cast<uint32_t*>(tr + cbfrec::MASKS)[(0 * 4 + cgrp) * R + r] = bits;
+      }
       wait_st();
       warp_arrive_after_tmem(&a2_full);
     };
@@ -358,6 +355,7 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
         tmem_ld16(tlane + C_Y + c0, v);
         wait_ld();
         [[maybe_unused]] uint32_t bits = 0;
+        [[maybe_unused]] uint4 bh[2], bl[2];
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
           float hi[8], lo[8];
@@ -379,10 +377,14 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
           if constexpr (DUMP) {
 #pragma unroll
             for (int e = 0; e < 8; ++e) bits |= (x[e] > 0.f ? 1u : 0u) << (half * 8 + e);
-            dump8(tr + cbfrec::A2_HI + c * cbfrec::BLK, tr + cbfrec::A2_LO + c * cbfrec::BLK, 2 * cgrp + half, x);
+            bf16_split8(x, bh[half], bl[half]);
           }
         }
-        if constexpr (DUMP) reinterpret_cast<uint32_t*>(tr + cbfrec::MASKS)[((1 + c) * 4 + cgrp) * R + r] = bits;
+        if constexpr (DUMP) {
+          img_store16(tr + cbfrec::A2_HI + c * cbfrec::BLK, r, cgrp, bh[0], bh[1]);
+          img_store16(tr + cbfrec::A2_LO + c * cbfrec::BLK, r, cgrp, bl[0], bl[1]);
+          reinterpret_cast<uint32_t*>(tr + cbfrec::MASKS)[((1 + c) * 4 + cgrp) * R + r] = bits;
+        }
         wait_st();
         warp_arrive_after_tmem(&a3_full[c]);
         if (warp == 0) TC_TRACE(0, 2 + 2 * c);

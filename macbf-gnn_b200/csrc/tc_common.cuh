@@ -258,6 +258,19 @@ __device__ __forceinline__ void bf16_split8(const float* x, uint4& hi, uint4& lo
 // byte offset of 16-byte chunk `chunk` (8 channels) of edge row `row` inside a 64-channel block
 __device__ __forceinline__ uint32_t img_off(int row, int chunk) { return (uint32_t)row * 128u + (uint32_t)((chunk ^ (row & 7)) << 4); }
 
+// Sixteen consecutive channels (chunks 2*pair, 2*pair+1) of row `row`: one aligned 32-byte sector of the image,
+// written with a single 256-bit store (the swizzle only swaps the two 16-byte halves on odd rows).
+__device__ __forceinline__ void st_global_v8(void* p, uint4 a, uint4 b) {
+  asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(a.x), "r"(a.y), "r"(a.z), "r"(a.w), "r"(b.x),
+               "r"(b.y), "r"(b.z), "r"(b.w)
+               : "memory");
+}
+__device__ __forceinline__ void img_store16(unsigned char* img, int row, int pair, uint4 c0, uint4 c1) {
+  const uint32_t off = (uint32_t)row * 128u + (uint32_t)((((2 * pair) ^ (row & 7)) & ~1) << 4);
+  if (row & 1) st_global_v8(img + off, c1, c0);
+  else st_global_v8(img + off, c0, c1);
+}
+
 // MN-major SWIZZLE_128B shared-memory operand: 64 elements (bf16) contiguous along M/N per 128-B row, rows = K,
 // 8-row groups 1024 B apart (SBO), 64-element blocks `lbo_bytes` apart (LBO).
 __device__ __forceinline__ uint64_t smem_desc_mn_sw128(uint32_t addr, uint32_t lbo_bytes) {
