@@ -10,7 +10,7 @@
 //      B = the TRANSPOSED weights resident in shared memory (same machinery as the forward's layers 2, 3).
 //      dZ3, dZ2 are dumped as bf16 hi/lo images; dW1, db1 and d/dstates (6 features, fp32 atomics) are
 //      finished here on the CUDA cores.
-//   3. cbf_wgrad_tc_kernel   dW3^T = A2^T dZ3, dW2 = dZ2^T A1, db3, db2: GEMMs whose contraction index is the
+//   3. wgrad_tc_kernel   dW3^T = A2^T dZ3, dW2 = dZ2^T A1, db3, db2: GEMMs whose contraction index is the
 //      EDGE, so both operands come from shared memory as MN-major bf16 images, staged by bulk copies
 //      (cp.async.bulk + mbarrier, two 96-KB stages), 3 products (hi*hi, lo*hi, hi*lo) per GEMM with fp32
 //      accumulation in tensor memory across all tiles of the CTA; bias gradients ride along as GEMMs against
@@ -325,8 +325,13 @@ constexpr size_t smem_bytes = 2 * (size_t)STAGE + 4096 + 1024;
 constexpr uint32_t C_W3 = 0, C_W2 = 64, C_B3 = 128, C_B2 = 192;
 }  // namespace cbfwg
 
+// NST = 2: CBF (stage 0 = G3: dW3^T, db3; stage 1 = G2: dW2, db2).  NST = 1: controller edge net (one G2-type stage
+// per tile: A = dZ2 (128 channels), B = A1 (64 channels) -> dW2[out][in], db2); `rec_stride` bytes between tile records,
+// P floats per gradient slice, off* = offsets of the parameter tensors inside a slice.
+template <int NST>
 __global__ void __launch_bounds__(cbfwg::THREADS, 1)
-cbf_wgrad_tc_kernel(const unsigned char* __restrict__ rec, long long ntiles, float* __restrict__ slices) {
+wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long long ntiles, float* __restrict__ slices, int P,
+                int offW3, int offB3, int offW2, int offB2) {
   using namespace cbfwg;
   using namespace tc;
   extern __shared__ unsigned char smem_raw[];
@@ -349,11 +354,11 @@ cbf_wgrad_tc_kernel(const unsigned char* __restrict__ rec, long long ntiles, flo
   if (warp == 0) {
     uint32_t n = 0;
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-      for (int s = 0; s < 2; ++s, ++n) {
+      for (int s = 0; s < NST; ++s, ++n) {
         const uint32_t buf = n & 1;
         if (n >= 2) mbar_wait(&empty[buf], ((n >> 1) - 1) & 1);
         if (elect_one()) {
-          const unsigned char* src = rec + (size_t)tile * cbfrec::BYTES + (size_t)s * STAGE;
+          const unsigned char* src = rec + (size_t)tile * rec_stride + (size_t)s * STAGE;
           mbar_expect_tx(&full[buf], STAGE);
 #pragma unroll
           for (int p = 0; p < 3; ++p) bulk_g2s(sm + buf * STAGE + p * (STAGE / 3), src + p * (STAGE / 3), STAGE / 3, &full[buf]);
@@ -369,7 +374,8 @@ cbf_wgrad_tc_kernel(const unsigned char* __restrict__ rec, long long ntiles, flo
     uint32_t n = 0;
     bool first_tile = true;
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, first_tile = false) {
-      for (int s = 0; s < 2; ++s, ++n) {
+      for (int s0 = 0; s0 < NST; ++s0, ++n) {
+        const int s = (NST == 2) ? s0 : 1;
         const uint32_t buf = n & 1;
         mbar_wait(&full[buf], (n >> 1) & 1);
         fence_after_sync();
@@ -412,32 +418,34 @@ cbf_wgrad_tc_kernel(const unsigned char* __restrict__ rec, long long ntiles, flo
     const int q = warp & 3;                             // TMEM lane quadrant this warp may read
     const int m = q * 32 + lane;
     const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16);
-    float* gp = slices + (size_t)blockIdx.x * MACBF_CBF_PARAMS;
+    float* gp = slices + (size_t)blockIdx.x * P;
     for (int c0 = 0; c0 < 64; c0 += 16) {
       float v[16];
-      tmem_ld16(tlane + C_W3 + c0, v);                  // dW3^T[m = in][n = out]
-      wait_ld();
+      if (NST == 2) {
+        tmem_ld16(tlane + C_W3 + c0, v);                // dW3^T[m = in][n = out]
+        wait_ld();
 #pragma unroll
-      for (int e = 0; e < 16; ++e) gp[CBF_W3 + (c0 + e) * 128 + m] += v[e];
+        for (int e = 0; e < 16; ++e) gp[offW3 + (c0 + e) * 128 + m] += v[e];
+      }
       tmem_ld16(tlane + C_W2 + c0, v);                  // dW2[m = out][n = in]
       wait_ld();
 #pragma unroll
-      for (int e = 0; e < 16; ++e) gp[CBF_W2 + m * 64 + c0 + e] += v[e];
+      for (int e = 0; e < 16; ++e) gp[offW2 + m * 64 + c0 + e] += v[e];
     }
     {
       float v[8];
       tmem_ld8(tlane + C_B2, v);
       wait_ld();
-      gp[CBF_B2 + m] += v[0];
+      gp[offB2 + m] += v[0];
     }
-    if (q == 0) {                                       // every lane holds the same db3 row; lane m < 32 writes channels 2m, 2m+1
+    if (NST == 2 && q == 0) {                                       // every lane holds the same db3 row; lane m < 32 writes channels 2m, 2m+1
       for (int c0 = 0; c0 < 64; c0 += 16) {
         float v[16];
         tmem_ld16(tlane + C_B3 + c0, v);
         wait_ld();
         if (lane == 0) {
 #pragma unroll
-          for (int e = 0; e < 16; ++e) gp[CBF_B3 + c0 + e] += v[e];
+          for (int e = 0; e < 16; ++e) gp[offB3 + c0 + e] += v[e];
         }
       }
     }
@@ -445,6 +453,15 @@ cbf_wgrad_tc_kernel(const unsigned char* __restrict__ rec, long long ntiles, flo
   fence_before_sync();
   __syncthreads();
   if (warp == 0) tmem_dealloc(tbase, 256);
+}
+
+// controller edge net (ctrl_edge_bwd_tc.cu): one 96-KB stage per tile record
+int wgrad_tc_ctrl(const unsigned char* rec, size_t rec_stride, long long ntiles, float* slices, int grid, cudaStream_t st) {
+  MACBF_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfwg::smem_bytes));
+  wgrad_tc_kernel<1><<<grid, cbfwg::THREADS, cbfwg::smem_bytes, st>>>(rec, rec_stride, ntiles, slices, MACBF_CTRL_PARAMS, 0, 0,
+                                                                     CT_EW2, CT_EB2);
+  MACBF_CHECK_LAUNCH("wgrad_tc_kernel<ctrl>");
+  return 0;
 }
 
 // ================================ host side ================================
@@ -477,7 +494,7 @@ int cbf_backward_tc(const float* states, const float* obstacles, const int32_t* 
   const long long nt = cbf_bwd_tiles(agents, K);
   MACBF_CHECK_CUDA(cudaMemsetAsync(slices, 0, slice_bytes, st));
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(cbf_dgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfdg::smem_bytes));
-  MACBF_CHECK_CUDA(cudaFuncSetAttribute(cbf_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfwg::smem_bytes));
+  MACBF_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfwg::smem_bytes));
   for (long long t0 = 0; t0 < nt; t0 += CHUNK_TILES) {
     const long long t1 = (t0 + CHUNK_TILES < nt) ? t0 + CHUNK_TILES : nt;
     const long long ct = t1 - t0;
@@ -488,8 +505,9 @@ int cbf_backward_tc(const float* states, const float* obstacles, const int32_t* 
     cbf_dgrad_tc_kernel<<<grid, cbfdg::THREADS, cbfdg::smem_bytes, st>>>(idx, params, N, K, agents, TA, t0, t1, rec, slices,
                                                                         grad_states);
     MACBF_CHECK_LAUNCH("cbf_dgrad_tc_kernel");
-    cbf_wgrad_tc_kernel<<<grid, cbfwg::THREADS, cbfwg::smem_bytes, st>>>(rec, ct, slices);
-    MACBF_CHECK_LAUNCH("cbf_wgrad_tc_kernel");
+    wgrad_tc_kernel<2><<<grid, cbfwg::THREADS, cbfwg::smem_bytes, st>>>(rec, cbfrec::BYTES, ct, slices, MACBF_CBF_PARAMS, CBF_W3,
+                                                                       CBF_B3, CBF_W2, CBF_B2);
+    MACBF_CHECK_LAUNCH("wgrad_tc_kernel<cbf>");
   }
   reduce_partials_kernel<<<(MACBF_CBF_PARAMS + 255) / 256, 256, 0, st>>>(slices, NUM_SMS, MACBF_CBF_PARAMS, grad_params);
   MACBF_CHECK_LAUNCH("reduce_partials_kernel");

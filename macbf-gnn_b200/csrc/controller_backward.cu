@@ -6,6 +6,8 @@
 //   3. ctrl_edge_backward_kernel: edge MLP forward, routes d/dpool to the arg-max slot of every
 //      (agent, channel) (torch.max backward; first maximum), backward through 5->64->128,
 //   4. reduce_partials_kernel: per-CTA weight-gradient slices -> grad_params, in CTA order.
+#include <stdlib.h>
+
 #include "mlp_tile.cuh"
 
 namespace macbf {
@@ -348,10 +350,20 @@ static inline int grid_for(long long ntiles) { return (int)(ntiles < NUM_SMS ? n
 
 static inline size_t a256(size_t x) { return (x + 255) & ~(size_t)255; }
 
-// scratch: [pool / dz : B*N*128 f32][partial : NUM_SMS * 34052 f32]
+bool ctrl_edge_bwd_tc_applicable(int K);
+size_t ctrl_edge_bwd_tc_scratch_bytes(int B, int N, int K);
+int ctrl_edge_bwd_tc(const float*, const float*, const int32_t*, const float*, const float*, int, int, int, int, double,
+                     float*, float*, void*, cudaStream_t);
+// MACBF_CTRL_BWD_FFMA=1 keeps the FP32-FFMA edge backward (A/B reference of ctrl_edge_bwd_tc.cu)
+static bool ctrl_bwd_force_ffma() {
+  static const bool v = [] { const char* e = getenv("MACBF_CTRL_BWD_FFMA"); return e != nullptr && e[0] == '1'; }();
+  return v;
+}
+
+// scratch: [pool / dz : B*N*128 f32][partial : NUM_SMS * 34052 f32][tile records of the tensor-core edge backward]
 size_t controller_backward_scratch_bytes(int B, int N, int K) {
-  (void)K;
-  return a256((size_t)B * N * MACBF_POOL_DIM * sizeof(float)) + (size_t)NUM_SMS * MACBF_CTRL_PARAMS * sizeof(float);
+  return a256((size_t)B * N * MACBF_POOL_DIM * sizeof(float)) + a256((size_t)NUM_SMS * MACBF_CTRL_PARAMS * sizeof(float)) +
+         (ctrl_edge_bwd_tc_applicable(K) ? ctrl_edge_bwd_tc_scratch_bytes(B, N, K) : 0);
 }
 
 int controller_backward(const float* states, const float* goals, const float* obstacles, const int32_t* idx,
@@ -375,7 +387,11 @@ int controller_backward(const float* states, const float* goals, const float* ob
         states, goals, params, grad_u, grad_s_next, agents, (float)dt, pool, partial, grad_states, grad_goals);
     MACBF_CHECK_LAUNCH("ctrl_node_backward_kernel");
   }
-  {
+  if (ctrl_edge_bwd_tc_applicable(K) && !ctrl_bwd_force_ffma()) {
+    void* recs = (char*)partial + a256((size_t)NUM_SMS * MACBF_CTRL_PARAMS * sizeof(float));
+    rc = ctrl_edge_bwd_tc(states, obstacles, idx, params, pool, B, N, M, K, obs_radius, partial, grad_states, recs, st);
+    if (rc) return rc;
+  } else {
     const int TA = max(1, ceb_smem::R / K);
     const long long ntiles = (agents + TA - 1) / TA;
     const size_t smem = ceb_smem::total * sizeof(float);
