@@ -220,7 +220,7 @@ ctrl_node_kernel(const float* __restrict__ states, const float* __restrict__ goa
 }
 
 int ctrl_edge_tc(const float* states, const float* obstacles, const int32_t* idx, const float* params, int B, int N,
-                 int M, int K, double obs_radius, float* pool, cudaStream_t st);
+                 int M, int K, double obs_radius, float* pool, cudaStream_t st, uint8_t* argk = nullptr);
 int ctrl_node_tc(const float* states, const float* goals, const float* pool, const float* params, long long agents,
                  double dt, float* u, float* s_next, cudaStream_t st);
 

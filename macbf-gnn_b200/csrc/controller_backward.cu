@@ -351,18 +351,23 @@ static inline int grid_for(long long ntiles) { return (int)(ntiles < NUM_SMS ? n
 static inline size_t a256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 bool ctrl_edge_bwd_tc_applicable(int K);
+int ctrl_edge_bwd_tc_slices();
 size_t ctrl_edge_bwd_tc_scratch_bytes(int B, int N, int K);
-int ctrl_edge_bwd_tc(const float*, const float*, const int32_t*, const float*, const float*, int, int, int, int, double,
-                     float*, float*, void*, cudaStream_t);
+uint8_t* ctrl_edge_bwd_tc_argk(void* scratch);
+int ctrl_edge_bwd_tc(const float*, const float*, const int32_t*, const float*, const float*, int, int, int, int, float*,
+                     float*, void*, cudaStream_t);
+int ctrl_edge_tc(const float* states, const float* obstacles, const int32_t* idx, const float* params, int B, int N,
+                 int M, int K, double obs_radius, float* pool, cudaStream_t st, uint8_t* argk);
+constexpr int CTRL_SLICES = 2 * NUM_SMS;   // the tensor-core edge backward runs two CTAs per SM
 // MACBF_CTRL_BWD_FFMA=1 keeps the FP32-FFMA edge backward (A/B reference of ctrl_edge_bwd_tc.cu)
 static bool ctrl_bwd_force_ffma() {
   static const bool v = [] { const char* e = getenv("MACBF_CTRL_BWD_FFMA"); return e != nullptr && e[0] == '1'; }();
   return v;
 }
 
-// scratch: [pool / dz : B*N*128 f32][partial : NUM_SMS * 34052 f32][tile records of the tensor-core edge backward]
+// scratch: [pool / dz : B*N*128 f32][partial : CTRL_SLICES * 34052 f32][winners + tile records of the tensor-core edge backward]
 size_t controller_backward_scratch_bytes(int B, int N, int K) {
-  return a256((size_t)B * N * MACBF_POOL_DIM * sizeof(float)) + a256((size_t)NUM_SMS * MACBF_CTRL_PARAMS * sizeof(float)) +
+  return a256((size_t)B * N * MACBF_POOL_DIM * sizeof(float)) + a256((size_t)CTRL_SLICES * MACBF_CTRL_PARAMS * sizeof(float)) +
          (ctrl_edge_bwd_tc_applicable(K) ? ctrl_edge_bwd_tc_scratch_bytes(B, N, K) : 0);
 }
 
@@ -376,8 +381,11 @@ int controller_backward(const float* states, const float* goals, const float* ob
   MACBF_CHECK_ARG(scratch_bytes >= need, "controller_backward: scratch too small (%zu < %zu)", scratch_bytes, need);
   float* pool = (float*)scratch;
   float* partial = (float*)((char*)scratch + a256((size_t)B * N * MACBF_POOL_DIM * sizeof(float)));
-  MACBF_CHECK_CUDA(cudaMemsetAsync(partial, 0, (size_t)NUM_SMS * MACBF_CTRL_PARAMS * sizeof(float), st));
-  int rc = controller_forward_pool_only(states, obstacles, idx, params, B, N, M, K, obs_radius, pool, st);
+  MACBF_CHECK_CUDA(cudaMemsetAsync(partial, 0, (size_t)CTRL_SLICES * MACBF_CTRL_PARAMS * sizeof(float), st));
+  const bool edge_tc = ctrl_edge_bwd_tc_applicable(K) && !ctrl_bwd_force_ffma();
+  void* edge_scratch = (char*)partial + a256((size_t)CTRL_SLICES * MACBF_CTRL_PARAMS * sizeof(float));
+  int rc = edge_tc ? ctrl_edge_tc(states, obstacles, idx, params, B, N, M, K, obs_radius, pool, st, ctrl_edge_bwd_tc_argk(edge_scratch))
+                   : controller_forward_pool_only(states, obstacles, idx, params, B, N, M, K, obs_radius, pool, st);
   if (rc) return rc;
   {
     const long long ntiles = (agents + cnb_smem::R - 1) / cnb_smem::R;
@@ -387,9 +395,8 @@ int controller_backward(const float* states, const float* goals, const float* ob
         states, goals, params, grad_u, grad_s_next, agents, (float)dt, pool, partial, grad_states, grad_goals);
     MACBF_CHECK_LAUNCH("ctrl_node_backward_kernel");
   }
-  if (ctrl_edge_bwd_tc_applicable(K) && !ctrl_bwd_force_ffma()) {
-    void* recs = (char*)partial + a256((size_t)NUM_SMS * MACBF_CTRL_PARAMS * sizeof(float));
-    rc = ctrl_edge_bwd_tc(states, obstacles, idx, params, pool, B, N, M, K, obs_radius, partial, grad_states, recs, st);
+  if (edge_tc) {
+    rc = ctrl_edge_bwd_tc(states, obstacles, idx, params, pool, B, N, M, K, partial, grad_states, edge_scratch, st);
     if (rc) return rc;
   } else {
     const int TA = max(1, ceb_smem::R / K);
@@ -400,7 +407,7 @@ int controller_backward(const float* states, const float* goals, const float* ob
         states, obstacles, idx, params, pool, N, M, K, agents, TA, (float)obs_radius, partial, grad_states);
     MACBF_CHECK_LAUNCH("ctrl_edge_backward_kernel");
   }
-  reduce_partials_kernel<<<(MACBF_CTRL_PARAMS + 255) / 256, 256, 0, st>>>(partial, NUM_SMS, MACBF_CTRL_PARAMS,
+  reduce_partials_kernel<<<(MACBF_CTRL_PARAMS + 255) / 256, 256, 0, st>>>(partial, CTRL_SLICES, MACBF_CTRL_PARAMS,
                                                                           grad_params);
   MACBF_CHECK_LAUNCH("reduce_partials_kernel");
   return 0;

@@ -56,11 +56,13 @@ constexpr int total_floats = oStage + 2 * 64 * RS;
 constexpr size_t smem_bytes = (size_t)total_floats * 4 + 1024;
 }  // namespace cetc
 
+// WIN = true (backward pass): also writes the first arg-max slot of every (agent, channel) to `argk`.
+template <bool WIN>
 __global__ void __launch_bounds__(cetc::THREADS, 1)
 ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ obstacles,
                     const int32_t* __restrict__ idx, const float* __restrict__ params, int N, int M, int K,
                     long long agents_total, int TA, float obs_radius, float* __restrict__ pool,
-                    const int* __restrict__ skip) {
+                    const int* __restrict__ skip, uint8_t* __restrict__ argk) {
   MACBF_SKIP_IF_SET(skip);
   using namespace cetc;
   using namespace tc;
@@ -293,7 +295,14 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
           const int c = item & 63, a = item >> 6;
           const float* row = stage + c * RS + a * K;
           float best = 0.f;                            // relu(.) * mask >= 0; slot 0 (self) is never masked
-          if (K == 12) {                               // the reference's TOP_K: three independent 16-byte loads
+          if constexpr (WIN) {
+            // backward pass: also the FIRST arg-max slot (torch.max backward); 255 = no gradient (winner is 0)
+            int bi = 0;
+            best = row[0];
+            for (int k = 1; k < K; ++k)
+              if (row[k] > best) { best = row[k]; bi = k; }
+            argk[(a0 + a) * 128 + hf * 64 + c] = (best > 0.f) ? (uint8_t)bi : (uint8_t)255;
+          } else if (K == 12) {                        // the reference's TOP_K: three independent 16-byte loads
             const float4 x0 = *reinterpret_cast<const float4*>(row), x1 = *reinterpret_cast<const float4*>(row + 4),
                          x2 = *reinterpret_cast<const float4*>(row + 8);
             best = fmaxf(fmaxf(fmaxf(x0.x, x0.y), fmaxf(x0.z, x0.w)),
@@ -320,16 +329,23 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
 }
 
 int ctrl_edge_tc(const float* states, const float* obstacles, const int32_t* idx, const float* params, int B, int N,
-                 int M, int K, double obs_radius, float* pool, cudaStream_t st) {
+                 int M, int K, double obs_radius, float* pool, cudaStream_t st, uint8_t* argk) {
   const long long agents = (long long)B * N;
   MACBF_CHECK_ARG(agents < (1ll << 31), "controller_forward: B*N must be < 2^31");
   const int TA = max(1, cetc::R / K);
   const long long ntiles = (agents + TA - 1) / TA;
   const int grid = (int)(ntiles < NUM_SMS ? ntiles : (long long)NUM_SMS);
-  MACBF_CHECK_CUDA(cudaFuncSetAttribute(ctrl_edge_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        (int)cetc::smem_bytes));
-  ctrl_edge_tc_kernel<<<grid, cetc::THREADS, cetc::smem_bytes, st>>>(states, obstacles, idx, params, N, M, K, agents, TA,
-                                                                    (float)obs_radius, pool, tl_skip_flag);
+  if (argk != nullptr) {
+    MACBF_CHECK_CUDA(cudaFuncSetAttribute(ctrl_edge_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)cetc::smem_bytes));
+    ctrl_edge_tc_kernel<true><<<grid, cetc::THREADS, cetc::smem_bytes, st>>>(states, obstacles, idx, params, N, M, K, agents,
+                                                                            TA, (float)obs_radius, pool, tl_skip_flag, argk);
+  } else {
+    MACBF_CHECK_CUDA(cudaFuncSetAttribute(ctrl_edge_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)cetc::smem_bytes));
+    ctrl_edge_tc_kernel<false><<<grid, cetc::THREADS, cetc::smem_bytes, st>>>(states, obstacles, idx, params, N, M, K, agents,
+                                                                             TA, (float)obs_radius, pool, tl_skip_flag, argk);
+  }
   MACBF_CHECK_LAUNCH("ctrl_edge_tc_kernel");
   return 0;
 }
