@@ -198,9 +198,9 @@ size_t cbf_backward_tc_scratch_bytes(int B, int N, int K);
 int cbf_backward_tc(const float*, const float*, const int32_t*, const float*, const float*, int, int, int, int, double,
                     double, float*, float*, void*, size_t, cudaStream_t);
 // MACBF_CBF_BWD_FFMA=1 keeps this FP32-FFMA kernel (A/B reference of the tensor-core path in cbf_bwd_tc.cu)
-static bool cbf_bwd_force_ffma() {
-  static const bool v = [] { const char* e = getenv("MACBF_CBF_BWD_FFMA"); return e != nullptr && e[0] == '1'; }();
-  return v;
+static bool cbf_bwd_force_ffma() {      // read per call, so a test can switch paths inside one process
+  const char* e = getenv("MACBF_CBF_BWD_FFMA");
+  return e != nullptr && e[0] == '1';
 }
 
 size_t cbf_backward_scratch_bytes(int B, int N, int K) {

@@ -20,6 +20,8 @@
 // reduce_partials_kernel adds the slices in order, so parameter gradients are run-to-run deterministic.
 // Precision: dgrad chain 3xTF32 (~5e-7); wgrad operands carry 16 mantissa bits (~7e-6 scale-relative on dW2,
 // dW3, measured against an fp64 reference on the fixtures) - inside the 5e-5 gradient tolerance of the tests.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "tc_common.cuh"
 #include "cbf_bwd_layout.cuh"
@@ -467,6 +469,12 @@ int wgrad_tc_ctrl(const unsigned char* rec, size_t rec_stride, long long ntiles,
 // ================================ host side ================================
 namespace {
 constexpr long long CHUNK_TILES = 8192;        // records of one chunk: 8192 x 205 KB = 1.6 GB
+// MACBF_BWD_CHUNK_TILES=<n> shrinks the chunk (tests exercise the multi-chunk path on small problems)
+inline long long chunk_tiles() {
+  const char* e = getenv("MACBF_BWD_CHUNK_TILES");
+  const long long v = e ? atoll(e) : 0;
+  return (v > 0 && v < CHUNK_TILES) ? v : CHUNK_TILES;
+}
 inline long long cbf_bwd_tiles(long long agents, int K) {
   const int TA = max(1, 128 / K);
   return (agents + TA - 1) / TA;
@@ -495,8 +503,9 @@ int cbf_backward_tc(const float* states, const float* obstacles, const int32_t* 
   MACBF_CHECK_CUDA(cudaMemsetAsync(slices, 0, slice_bytes, st));
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(cbf_dgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfdg::smem_bytes));
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfwg::smem_bytes));
-  for (long long t0 = 0; t0 < nt; t0 += CHUNK_TILES) {
-    const long long t1 = (t0 + CHUNK_TILES < nt) ? t0 + CHUNK_TILES : nt;
+  const long long CH = chunk_tiles();
+  for (long long t0 = 0; t0 < nt; t0 += CH) {
+    const long long t1 = (t0 + CH < nt) ? t0 + CH : nt;
     const long long ct = t1 - t0;
     const int grid = (int)(ct < NUM_SMS ? ct : (long long)NUM_SMS);
     if (int rc = cbf_forward_tc_dump(states, obstacles, idx, params, N, M, K, agents, dist_min, obs_radius, t0, t1, grad_h, rec,

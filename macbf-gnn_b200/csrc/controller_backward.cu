@@ -360,9 +360,9 @@ int ctrl_edge_tc(const float* states, const float* obstacles, const int32_t* idx
                  int M, int K, double obs_radius, float* pool, cudaStream_t st, uint8_t* argk);
 constexpr int CTRL_SLICES = 2 * NUM_SMS;   // the tensor-core edge backward runs two CTAs per SM
 // MACBF_CTRL_BWD_FFMA=1 keeps the FP32-FFMA edge backward (A/B reference of ctrl_edge_bwd_tc.cu)
-static bool ctrl_bwd_force_ffma() {
-  static const bool v = [] { const char* e = getenv("MACBF_CTRL_BWD_FFMA"); return e != nullptr && e[0] == '1'; }();
-  return v;
+static bool ctrl_bwd_force_ffma() {     // read per call, so a test can switch paths inside one process
+  const char* e = getenv("MACBF_CTRL_BWD_FFMA");
+  return e != nullptr && e[0] == '1';
 }
 
 // scratch: [pool / dz : B*N*128 f32][partial : CTRL_SLICES * 34052 f32][winners + tile records of the tensor-core edge backward]

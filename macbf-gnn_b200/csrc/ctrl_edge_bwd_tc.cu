@@ -13,6 +13,8 @@
 //   workers   dZ1 = dA1 [z1 > 0]; dW1, db1; d/dstates through [dx, dy, dvx, dvy] (fp32 atomics)
 // dW2 = dZ2^T a1 and db2 are GEMMs over the EDGES: wgrad_tc_kernel<1> (cbf_bwd_tc.cu) reads the two images
 // with bulk copies (bf16x3, fp32 accumulation in TMEM).
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "tc_common.cuh"
 
@@ -265,6 +267,11 @@ namespace {
 constexpr long long CE_CHUNK_TILES = 16384;    // 16384 x 96 KB = 1.5 GB of records per chunk
 constexpr int CE_GRID = 2 * NUM_SMS;           // two co-resident CTAs per SM
 static inline size_t a1k(size_t x) { return (x + 1023) & ~(size_t)1023; }
+inline long long chunk_tiles() {               // MACBF_BWD_CHUNK_TILES=<n>: see cbf_bwd_tc.cu
+  const char* e = getenv("MACBF_BWD_CHUNK_TILES");
+  const long long v = e ? atoll(e) : 0;
+  return (v > 0 && v < CE_CHUNK_TILES) ? v : CE_CHUNK_TILES;
+}
 }
 bool ctrl_edge_bwd_tc_applicable(int K) { return K >= 1 && K <= 128; }
 int ctrl_edge_bwd_tc_slices() { return CE_GRID; }
@@ -287,8 +294,9 @@ int ctrl_edge_bwd_tc(const float* states, const float* obstacles, const int32_t*
   const uint8_t* argk = ctrl_edge_bwd_tc_argk(scratch);
   unsigned char* rec = (unsigned char*)argk + a1k((size_t)agents * 128);
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(ctrl_edge_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cebtc::smem_bytes));
-  for (long long t0 = 0; t0 < nt; t0 += CE_CHUNK_TILES) {
-    const long long t1 = (t0 + CE_CHUNK_TILES < nt) ? t0 + CE_CHUNK_TILES : nt;
+  const long long CH = chunk_tiles();
+  for (long long t0 = 0; t0 < nt; t0 += CH) {
+    const long long t1 = (t0 + CH < nt) ? t0 + CH : nt;
     const long long ct = t1 - t0;
     const int grid = (int)(ct < CE_GRID ? ct : (long long)CE_GRID);
     ctrl_edge_bwd_tc_kernel<<<grid, cebtc::THREADS, cebtc::smem_bytes, st>>>(states, obstacles, idx, params, dpool, argk, N, M, K,

@@ -1,0 +1,89 @@
+"""GPU: the tensor-core backward kernels (cbf_bwd_tc.cu, ctrl_edge_bwd_tc.cu) against the FP32-FFMA backward
+kernels they replace (which tests/test_gpu_backward.py pins to torch autograd of the oracle), over tile
+geometries the golden fixtures do not reach: K from 1 to 128, ragged last tiles, obstacles, multi-chunk records."""
+import os
+
+import pytest
+import torch
+
+from helpers import dev
+
+pytestmark = pytest.mark.gpu
+GTOL = 5e-5   # scale-relative, as in test_gpu_backward.py
+
+
+@pytest.fixture(scope="module")
+def ops():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from macbf_b200 import ops as _ops
+    return _ops
+
+
+def _rel(a, b):
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+def _run(ops, s, g, obs, idx, cf, tf, gh, gu, gs):
+    gp, gst = ops.cbf_backward(s, idx, cf, gh, obstacles=obs, want_grad_states=True)
+    cp, cst, cg = ops.controller_backward(s, g, idx, tf, gu, gs, obstacles=obs, want_grad_states=True, want_grad_goals=True)
+    torch.cuda.synchronize()
+    return [x.clone() for x in (gp, gst, cp, cst, cg)]
+
+
+def _case(ops, B, N, K, n_obs, seed):
+    import oracle.macbf_oracle as O
+    s, g = O.synthetic_swarm(B, N, seed)
+    obs = dev(O.synthetic_obstacles(B, N, n_obs, 0, seed + 1)) if n_obs else None
+    p_cbf, p_ctrl = O.init_params(seed)
+    cf, tf = dev(O.flatten_params(p_cbf, O.CBF_KEYS)), dev(O.flatten_params(p_ctrl, O.CTRL_KEYS))
+    s, g = dev(s), dev(g)
+    idx = ops.neighbor_topk(s, K, obs)
+    Ke = idx.shape[2]
+    gen = torch.Generator(device="cuda").manual_seed(seed)
+    gh = torch.randn(B, N, Ke, device="cuda", generator=gen) * (torch.rand(B, N, Ke, device="cuda", generator=gen) < 0.4)
+    gu = torch.randn(B, N, 2, device="cuda", generator=gen)
+    gs = torch.randn(B, N, 4, device="cuda", generator=gen)
+    return s, g, obs, idx, cf, tf, gh, gu, gs
+
+
+def _with_env(env, fn):
+    old = {k: os.environ.get(k) for k in env}
+    os.environ.update(env)
+    try:
+        return fn()
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+
+
+NAMES = ["cbf params", "cbf grad_states", "ctrl params", "ctrl grad_states", "ctrl grad_goals"]
+
+
+@pytest.mark.parametrize("K,N,n_obs", [(1, 150, 0), (3, 150, 0), (5, 333, 2), (12, 150, 0), (20, 150, 3), (64, 150, 0), (128, 200, 0)])
+def test_tensor_core_backward_matches_ffma(ops, K, N, n_obs):
+    args = _case(ops, 3, N, K, n_obs, 10 + K)
+    tc = _run(ops, *args)
+    ff = _with_env({"MACBF_CBF_BWD_FFMA": "1", "MACBF_CTRL_BWD_FFMA": "1"}, lambda: _run(ops, *args))
+    for name, a, b in zip(NAMES, tc, ff):
+        assert _rel(a, b) < GTOL, f"K={K}: {name} differs by {_rel(a, b):.2e}"
+    assert float(tc[0].abs().max()) > 0 and float(tc[2].abs().max()) > 0
+
+
+def test_multi_chunk_records_match_single_chunk(ops):
+    args = _case(ops, 4, 257, 12, 0, 5)          # 1028 agents / 10 per tile = 103 tiles
+    one = _run(ops, *args)
+    many = _with_env({"MACBF_BWD_CHUNK_TILES": "7"}, lambda: _run(ops, *args))
+    for name, a, b in zip(NAMES, many, one):
+        # same kernels, different partition of the tiles over CTAs: only the fp32 summation order changes
+        assert _rel(a, b) < 2e-6, f"{name} differs by {_rel(a, b):.2e}"
+
+
+def test_backward_is_run_to_run_deterministic_for_parameters(ops):
+    args = _case(ops, 2, 300, 12, 0, 9)
+    a = _run(ops, *args)
+    b = _run(ops, *args)
+    assert torch.equal(a[0], b[0]) and torch.equal(a[2], b[2])   # parameter gradients: fixed reduction order
