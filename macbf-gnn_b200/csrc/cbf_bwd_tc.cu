@@ -47,10 +47,11 @@ constexpr int oW2THI = oW3TLO + 128 * 64;      // B[n = in (64)][k = out (128)] 
 constexpr int oW2TLO = oW2THI + 64 * 128;
 constexpr int oW1 = oW2TLO + 64 * 128;         // [64][8] plain
 constexpr int oW4 = oW1 + 64 * 8;
-constexpr int oDz1 = oW4 + 64;                 // [64][129]
-constexpr int oXs = oDz1 + 64 * DZS;           // [128][8]: features, xs[e][6] = 1 (bias column)
-constexpr int oXpart = oXs + 128 * 8;          // [4][6][128]
-constexpr int total_floats = oXpart + 4 * 6 * 128;
+// double-buffered hand-off of a tile's dZ1 to the (deferred) dW1 / d-states pass:
+constexpr int oDz1 = oW4 + 64;                 // [2][64][129]  dZ1^T
+constexpr int oXs = oDz1 + 2 * 64 * DZS;       // [2][128][8]   features f0..f5, 1 (bias column), d
+constexpr int oXpart = oXs + 2 * 128 * 8;      // [2][4][5][128] d/d(f0,f1,f2,f3,f5) partials of the 4 column groups
+constexpr int total_floats = oXpart + 2 * 4 * 5 * 128;
 constexpr size_t smem_bytes = (size_t)total_floats * 4 + 1024;
 }  // namespace cbfdg
 
@@ -67,7 +68,8 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
   float* W1 = sm + oW1; float* W4 = sm + oW4;
   float* dz1s = sm + oDz1; float* xs = sm + oXs; float* xpart = sm + oXpart;
   // workers -> MMA: z3_full, z2_full[2] (16 arrivals each); MMA -> workers: da2_full[2], da1_full
-  __shared__ uint64_t z3_full, z2_full[2], da2_full[2], da1_full;
+  // workers -> workers: dz_full[b] (16 arrivals): buffer b of dz1s / xs / xpart is complete
+  __shared__ uint64_t z3_full, z2_full[2], da2_full[2], da1_full, dz_full[2];
   __shared__ uint32_t tmem_base_s;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -75,6 +77,7 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
   if (threadIdx.x == 32) {
     mbar_init(&z3_full, 16); mbar_init(&z2_full[0], 16); mbar_init(&z2_full[1], 16);
     mbar_init(&da2_full[0], 1); mbar_init(&da2_full[1], 1); mbar_init(&da1_full, 1);
+    mbar_init(&dz_full[0], 16); mbar_init(&dz_full[1], 16);
     fence_mbar_init();
   }
   fill_weight_sw128_strided<128, 64>(params + CBF_W3, 1, 128, W3Thi, W3Tlo);
@@ -201,19 +204,68 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
       wait_st();
       warp_arrive_after_tmem(&z3_full);
     };
+    // Deferred tail of tile ordinal `ord` (buffer ord & 1): dW1 / db1 partial sums and d/dstates.  It runs one tile
+    // later, in the shadow of the tensor core's dA1 GEMM, after an ACQUIRE of dz_full (complete long before) - no
+    // CTA-wide barrier.  The buffer is rewritten at ordinal ord + 2, whose dA1 needs every warp's z2 arrival of that
+    // tile, which each warp issues after this call: write-after-read is ordered by the MMA barriers.
+    auto finish = [&](long long t, int ord) {
+      const int b = ord & 1;
+      mbar_wait(&dz_full[b], (ord >> 1) & 1);
+      const float* dzb = dz1s + b * (64 * DZS);
+      const float* xsb = xs + b * (128 * 8);
+      const float* xpb = xpart + b * (4 * 5 * 128);
+      if (wf < 7) {     // dW1[c][f], db1[c] += sum over the tile's rows (rows without an edge have dZ1 = 0)
+        const float* dzr = dzb + wc * DZS;
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll 4
+        for (int e = 0; e < R; e += 4) {
+          s0 = fmaf(dzr[e + 0], xsb[(e + 0) * 8 + wf], s0);
+          s1 = fmaf(dzr[e + 1], xsb[(e + 1) * 8 + wf], s1);
+          s2 = fmaf(dzr[e + 2], xsb[(e + 2) * 8 + wf], s2);
+          s3 = fmaf(dzr[e + 3], xsb[(e + 3) * 8 + wf], s3);
+        }
+        accw1 += (s0 + s1) + (s2 + s3);
+      }
+      // features -> states (cbf.py:23-30): +grad to agent i, -grad to neighbour j
+      if (grad_states != nullptr && cgrp == 0) {
+        const long long a0 = t * TA;
+        const int rows = (int)min((long long)TA, agents_total - a0) * K;
+        if (r < rows) {
+          float d0[5];
+#pragma unroll
+          for (int f = 0; f < 5; ++f)
+            d0[f] = (xpb[(0 * 5 + f) * R + r] + xpb[(1 * 5 + f) * R + r]) + (xpb[(2 * 5 + f) * R + r] + xpb[(3 * 5 + f) * R + r]);
+          const float4 xa = *reinterpret_cast<const float4*>(xsb + r * 8);
+          const float inv_d = 1.f / xsb[r * 8 + 7];
+          const float gx = d0[0] + d0[4] * xa.x * inv_d;
+          const float gy = d0[1] + d0[4] * xa.y * inv_d;
+          const long long ga = a0 + r / K;
+          const int b_env = (int)(ga / N);
+          const int j = __ldg(idx + a0 * K + r);
+          const long long gj = (j < N) ? (long long)b_env * N + j : -1;
+          if (gj != ga) {   // the self edge contributes +g - g = 0
+            float* pi = grad_states + (size_t)ga * 4;
+            atomicAdd(pi + 0, gx); atomicAdd(pi + 1, gy); atomicAdd(pi + 2, d0[2]); atomicAdd(pi + 3, d0[3]);
+            if (gj >= 0) {
+              float* pj = grad_states + (size_t)gj * 4;
+              atomicAdd(pj + 0, -gx); atomicAdd(pj + 1, -gy); atomicAdd(pj + 2, -d0[2]); atomicAdd(pj + 3, -d0[3]);
+            }
+          }
+        }
+      }
+    };
     build_z3(first, load_z(first));
     RecA ra = load_a(first);
     RecZ rz = load_z(first + gridDim.x);
     uint32_t par = 0;
-    for (long long tile = first; tile < tile_end; tile += gridDim.x, par ^= 1) {
+    int it = 0;
+    long long tile = first;
+    for (; tile < tile_end; tile += gridDim.x, par ^= 1, ++it) {
       unsigned char* tr = rec + (size_t)(tile - tile_begin) * cbfrec::BYTES;
       const uint32_t mb1 = ra.mb1;
       const uint32_t mb2[2] = {ra.mb2a, ra.mb2b};
       const float4 x0 = ra.x0, x1 = ra.x1;
-      if (cgrp == 0) {
-        *reinterpret_cast<float4*>(xs + r * 8) = x0;
-        *reinterpret_cast<float4*>(xs + r * 8 + 4) = make_float4(x1.x, x1.y, 1.f, 0.f);
-      }
+      const int buf = it & 1;
       ra = load_a(tile + gridDim.x);                    // consumed next iteration
       const RecZ rz_next = load_z(tile + 2 * gridDim.x);
       uint4 bh[2], bl[2];
@@ -245,6 +297,8 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
       // ---- dZ3 of the next tile (the dZ3 columns are free: both dA2 chunks of this tile have been observed) ----
       if (tile + gridDim.x < tile_end) build_z3(tile + gridDim.x, rz);
       rz = rz_next;
+      // ---- deferred tail of the previous tile, while the tensor core finishes this tile's dA1 ----
+      if (it > 0) finish(tile - gridDim.x, it - 1);
       // ---- dZ1 = dA1 * [z1 > 0]; d/dfeatures partials; stage dZ1^T for dW1 ----
       mbar_wait(&da1_full, par);
       fence_after_sync();
@@ -252,62 +306,30 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
         float v[16];
         tmem_ld16(tlane + C_DA1 + c0, v);
         wait_ld();
-        float px[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        float px[5] = {0.f, 0.f, 0.f, 0.f, 0.f};       // d/d(f0, f1, f2, f3, f5); the identity indicator f4 has no gradient
+        float* dzb = dz1s + buf * (64 * DZS);
 #pragma unroll
         for (int e = 0; e < 16; ++e) {
           const float dz = ((mb1 >> e) & 1u) ? v[e] : 0.f;
-          dz1s[(c0 + e) * DZS + r] = dz;
+          dzb[(c0 + e) * DZS + r] = dz;
           const float4 wa = *reinterpret_cast<const float4*>(W1 + (c0 + e) * 8);
-          const float4 wb = *reinterpret_cast<const float4*>(W1 + (c0 + e) * 8 + 4);
           px[0] = fmaf(dz, wa.x, px[0]); px[1] = fmaf(dz, wa.y, px[1]); px[2] = fmaf(dz, wa.z, px[2]);
-          px[3] = fmaf(dz, wa.w, px[3]); px[4] = fmaf(dz, wb.x, px[4]); px[5] = fmaf(dz, wb.y, px[5]);
+          px[3] = fmaf(dz, wa.w, px[3]); px[4] = fmaf(dz, W1[(c0 + e) * 8 + 5], px[4]);
         }
+        float* xpb = xpart + buf * (4 * 5 * 128);
 #pragma unroll
-        for (int f = 0; f < 6; ++f) xpart[(cgrp * 6 + f) * R + r] = px[f];
+        for (int f = 0; f < 5; ++f) xpb[(cgrp * 5 + f) * R + r] = px[f];
+        if (cgrp == 0) {
+          float* xsb = xs + buf * (128 * 8);
+          *reinterpret_cast<float4*>(xsb + r * 8) = x0;
+          *reinterpret_cast<float4*>(xsb + r * 8 + 4) = make_float4(x1.x, x1.y, 1.f, x1.z);
+        }
       }
       fence_before_sync();
-      named_bar_sync(1, WORKERS);
-      // ---- dW1[c][f], db1[c] += sum over the tile's rows (rows without an edge have dZ1 = 0) ----
-      if (wf < 7) {
-        const float* dzr = dz1s + wc * DZS;
-        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-#pragma unroll 4
-        for (int e = 0; e < R; e += 4) {
-          s0 = fmaf(dzr[e + 0], xs[(e + 0) * 8 + wf], s0);
-          s1 = fmaf(dzr[e + 1], xs[(e + 1) * 8 + wf], s1);
-          s2 = fmaf(dzr[e + 2], xs[(e + 2) * 8 + wf], s2);
-          s3 = fmaf(dzr[e + 3], xs[(e + 3) * 8 + wf], s3);
-        }
-        accw1 += (s0 + s1) + (s2 + s3);
-      }
-      // ---- features -> states (cbf.py:23-30): +grad to agent i, -grad to neighbour j ----
-      if (grad_states != nullptr && cgrp == 0) {
-        const long long a0 = tile * TA;
-        const int rows = (int)min((long long)TA, agents_total - a0) * K;
-        if (r < rows) {
-          float d0[6];
-#pragma unroll
-          for (int f = 0; f < 6; ++f)
-            d0[f] = (xpart[(0 * 6 + f) * R + r] + xpart[(1 * 6 + f) * R + r]) + (xpart[(2 * 6 + f) * R + r] + xpart[(3 * 6 + f) * R + r]);
-          const float inv_d = 1.f / x1.z;
-          const float gx = d0[0] + d0[5] * x0.x * inv_d;
-          const float gy = d0[1] + d0[5] * x0.y * inv_d;
-          const long long ga = a0 + r / K;
-          const int b = (int)(ga / N);
-          const int j = __ldg(idx + a0 * K + r);
-          const long long gj = (j < N) ? (long long)b * N + j : -1;
-          if (gj != ga) {   // the self edge contributes +g - g = 0
-            float* pi = grad_states + (size_t)ga * 4;
-            atomicAdd(pi + 0, gx); atomicAdd(pi + 1, gy); atomicAdd(pi + 2, d0[2]); atomicAdd(pi + 3, d0[3]);
-            if (gj >= 0) {
-              float* pj = grad_states + (size_t)gj * 4;
-              atomicAdd(pj + 0, -gx); atomicAdd(pj + 1, -gy); atomicAdd(pj + 2, -d0[2]); atomicAdd(pj + 3, -d0[3]);
-            }
-          }
-        }
-      }
-      named_bar_sync(1, WORKERS);                      // dz1s / xs / xpart are rewritten by the next tile
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&dz_full[buf]);
     }
+    if (it > 0) finish(tile - gridDim.x, it - 1);
     float* gp = slices + (size_t)blockIdx.x * MACBF_CBF_PARAMS;
     if (wf < 6) gp[CBF_W1 + wc * 6 + wf] += accw1;
     else if (wf == 6) gp[CBF_B1 + wc] += accw1;

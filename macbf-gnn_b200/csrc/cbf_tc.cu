@@ -97,6 +97,10 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
   // workers -> MMA: a1_full (4 arrivals: the feature warps), a2_full, a3_full[2], d3_free (16: one per worker warp)
   // MMA -> workers (tcgen05.commit): d1_full, d2_full[2], d3_full
   __shared__ uint64_t a1_full, a2_full, a3_full[2], d3_free, d1_full, d2_full[2], d3_full;
+  // DUMP: the feature warps publish gm of tile ordinal j on gm_full[j & 3] (4 arrivals); every worker acquires it in
+  // its layer-3 epilogue.  The producers run 2 ordinals ahead of the consumers, so with one barrier per slot of the
+  // 4-deep gm ring a barrier is never more than one phase ahead of a waiter (a parity wait would alias otherwise).
+  __shared__ uint64_t gm_full[4];
   __shared__ uint32_t tmem_base_s;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -106,6 +110,7 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
     mbar_init(&a1_full, 4); mbar_init(&a2_full, 16); mbar_init(&a3_full[0], 16); mbar_init(&a3_full[1], 16);
     mbar_init(&d3_free, 16);
     mbar_init(&d1_full, 1); mbar_init(&d2_full[0], 1); mbar_init(&d2_full[1], 1); mbar_init(&d3_full, 1);
+    for (int i = 0; i < 4; ++i) mbar_init(&gm_full[i], 4);
     fence_mbar_init();
   }
   fill_weight_sw128<128, 64>(params + CBF_W2, 64, W2hi, W2lo);
@@ -256,8 +261,10 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
         xr[0] = make_float4(f[0], f[1], f[2], f[3]);
         xr[1] = make_float4(f[4], f[5], dd, 0.f);
         reinterpret_cast<float*>(tr + cbfrec::GM)[r] = gm;
-        gms[pf_slot * R + r] = gm;
-        pf_slot = (pf_slot + 1) & 3;
+        gms[(pf_slot & 3) * R + r] = gm;
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&gm_full[pf_slot & 3]);
+        ++pf_slot;
       }
       float hi[8], lo[8];
 #pragma unroll
@@ -408,9 +415,9 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
         wait_ld();
         warp_arrive_after_tmem(&d3_free);
         if constexpr (DUMP) {
-          named_bar_sync(1, WORKERS);                    // gms[gslot] (written >= 1 tile ago by the feature warps) is visible
-          const float gm = gms[gslot * R + r];
-          gslot = (gslot + 1) & 3;
+          mbar_wait(&gm_full[gslot & 3], (gslot >> 2) & 1);   // published >= 1 tile ago: an acquire, not a wait
+          const float gm = gms[(gslot & 3) * R + r];
+          ++gslot;
           uint32_t bits = 0;
 #pragma unroll
           for (int q = 0; q < 16; ++q) {
