@@ -233,12 +233,15 @@ class StepBuffers:
         f32, dev = torch.float32, device
         self.idx = torch.empty((B, N, K), dtype=torch.int32, device=dev)
         self.idx_next = torch.empty((B, N, K), dtype=torch.int32, device=dev)
-        self.u = torch.empty((B, N, 2), dtype=f32, device=dev)
+        # `result` = [scalars | u] in ONE block, so a host that wants the losses and the actions of a step reads
+        # them back with a single device-to-host copy
+        self.result = torch.empty((B * NUM_SCALARS + B * N * 2,), dtype=f32, device=dev)
+        self.scalars = self.result[:B * NUM_SCALARS].view(B, NUM_SCALARS)
+        self.u = self.result[B * NUM_SCALARS:].view(B, N, 2)
         self.s_next = torch.empty((B, N, 4), dtype=f32, device=dev)
         self.h = torch.empty((B, N, K), dtype=f32, device=dev)
         self.h_next = torch.empty((B, N, K), dtype=f32, device=dev)
         self.ttc_mask = torch.empty((B, N, K), dtype=torch.uint8, device=dev)
-        self.scalars = torch.empty((B, NUM_SCALARS), dtype=f32, device=dev)
         self.workspace = torch.empty((L.macbf_step_workspace_bytes(B, N, M, top_k),), dtype=torch.uint8, device=dev)
 
 
