@@ -304,11 +304,11 @@ def main():
         peak = peaks["bf16_tflops"]
         roofline = {
             "kernel": "cbf_forward_tc_kernel (fused CBF edge MLP 6-64-128-64-1 on tcgen05/TMEM, 3xTF32; 2 launches "
-                      "per step, 48% of the step's GPU time in profiles/r1_launches_forward_c2.txt)",
+                      "per step, 47% of the step's GPU time in profiles/r1_launches_forward_c2.txt)",
             "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-            # dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full (profiles/r1_ncu_full_summary.txt);
+            # dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full (profiles/r1_ncu_full_forward.txt);
             # algorithmic bytes per launch = edges * 8 (idx in, h out) + states: the 3 MB of h stay in L2
-            "traffic": 4307968,
+            "traffic": 4311808,
             "peak_source": f"MEASURED_PEAKS.json bf16 burst ({peaks['source']})",
             "ms_per_launch": kms, "edges_per_launch": edges, "flop_per_edge": 33664,
             "note": "fp32 results within 1e-5 are required, so every MMA runs as a 3xTF32 split: the tensor pipe "
@@ -316,7 +316,7 @@ def main():
                     "can therefore reach at most 1/6 of the bf16 peak used as the denominator",
             "tf32_mma_tflops_executed": 3 * achieved * (2 * (64 * 128 + 128 * 64)) / 33664.0,
             "frac_of_3xtf32_ceiling": achieved / (peak / 6.0),
-            "tensor_pipe_active_pct_ncu_r1": 67.8,
+            "tensor_pipe_active_pct_ncu_r1": 75.4,
             "hbm_gbs_achieved": edges * (4 + 4) / (kms * 1e-3) / 1e9, "hbm_peak_gbs": peaks["hbm_gbs"],
             "step_hbm_frac": (value / world) * bytes_per_agent(K, args.mode) / (peaks["hbm_gbs"] * 1e9),
             "step_tflops": (value / world) * flops_per_agent(K, args.mode) / 1e12,
