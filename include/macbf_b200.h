@@ -140,7 +140,10 @@ int macbf_loss_backward(const float* states, const float* goals, const float* h,
 /* ---- backward of A5 (autograd of cbf.py:21-45) ------------------------------------------
  * grad_params [17089] is ACCUMULATED into (caller zeroes it); grad_states [B,N,4] is
  * accumulated into when non-NULL (caller zeroes it).  Activations are recomputed from
- * states + idx; nothing from the forward needs to be kept.  REPAIRED semantics only. */
+ * states + idx; nothing from the forward needs to be kept.  REPAIRED semantics only.
+ * Scratch holds the per-CTA gradient slices and the tile records the tensor-core kernels hand to each
+ * other (bf16 operand images, 205 KB per 128 edges, at most 8192 tiles = 1.6 GB at a time; larger
+ * problems are processed in chunks), so ask for its size - it is not small. */
 size_t macbf_cbf_backward_scratch_bytes(int B, int N, int K);
 int macbf_cbf_backward(const float* states, const float* obstacles, const int32_t* idx,
                        const float* cbf_params, const float* grad_h, int B, int N, int M, int K,
@@ -149,7 +152,9 @@ int macbf_cbf_backward(const float* states, const float* obstacles, const int32_
 
 /* ---- backward of A6-A8 (autograd of controller.py:31-63 + Euler step) --------------------
  * grad_u [B,N,2] and (optional) grad_s_next [B,N,4] are the incoming gradients; grad_params
- * [34052] and (optional) grad_states [B,N,4], grad_goals [B,N,2] are accumulated into. */
+ * [34052] and (optional) grad_states [B,N,4], grad_goals [B,N,2] are accumulated into.
+ * Scratch: pooled features / d-pool (512 B per agent), gradient slices, arg-max slots (128 B per agent)
+ * and tile records of the edge backward (96 KB per 128 edges, at most 16384 tiles at a time). */
 size_t macbf_controller_backward_scratch_bytes(int B, int N, int K);
 int macbf_controller_backward(const float* states, const float* goals, const float* obstacles,
                               const int32_t* idx, const float* ctrl_params, const float* grad_u,
