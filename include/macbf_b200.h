@@ -96,6 +96,14 @@ int macbf_controller_forward(const float* states, const float* goals, const floa
 int macbf_ttc_mask(const float* states, const float* obstacles, const int32_t* idx, int B, int N,
                    int M, int K, double dist_min_thres, double ttc, uint8_t* mask, void* stream);
 
+/* ---- evaluation-time dense check  (core.py:212-231 ttc_dangerous_mask_np; train.py:74-75) ----
+ * For every ordered pair (i, j) of an env: within sqrt(dist_min_sq) or colliding within ttc, in the
+ * reference's numpy mixed float32/float64 arithmetic (bit-exact mask).  dist_min_sq is the host's
+ * DIST_MIN_CHECK ** 2 (a double).  counts [B,N] = number of dangerous j per row (safety rate of
+ * train.py:74 = 1 - counts/N); mask [B,N,N] in {0,1}; either may be NULL, not both. */
+int macbf_ttc_dense(const float* states, int B, int N, double dist_min_sq, double ttc,
+                    int32_t* counts, uint8_t* mask, void* stream);
+
 /* ---- A10,A11,A12,A13: losses  (core.py:89-184, train.py:93-98) --------------------------
  * scalars [B,12] per env: 0 loss_dang, 1 loss_safe, 2 acc_dang, 3 acc_safe,
  *   4 loss_dang_deriv, 5 loss_safe_deriv, 6 acc_dang_deriv, 7 acc_safe_deriv, 8 loss_action,

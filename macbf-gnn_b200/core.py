@@ -110,7 +110,14 @@ def ttc_dangerous_mask(s):
 
 
 def ttc_dangerous_mask_np(s):
-    """Dense (N,N,1) evaluation-time check with the *_CHECK constants (core.py:212-231); host numpy."""
+    """Dense (N,N,1) evaluation-time check with the *_CHECK constants (core.py:212-231).  A numpy array is
+    evaluated on the host exactly as the reference does; a CUDA tensor (N,4) / (B,N,4) goes through
+    macbf_ttc_dense (same bits) and returns a bool tensor (N,N,1) / (B,N,N,1)."""
+    if isinstance(s, torch.Tensor):
+        sb, squeeze = _F._batched(s.detach(), 4)
+        _, m = _ops.ttc_dense(sb, _cfg.DIST_MIN_CHECK, _cfg.TIME_TO_COLLISION_CHECK, want_counts=False)
+        m = m.bool().unsqueeze(-1)
+        return m[0] if squeeze else m
     d = s[:, None, :] - s[None, :, :]
     eye = np.eye(s.shape[0])[:, :, None]
     x, y, vx, vy = d[:, :, 0:1] + eye, d[:, :, 1:2] + eye, d[:, :, 2:3], d[:, :, 3:4]

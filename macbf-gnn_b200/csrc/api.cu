@@ -39,6 +39,7 @@ int cbf_forward(const float*, const float*, const int32_t*, const float*, int, i
 int controller_forward(const float*, const float*, const float*, const int32_t*, const float*, int, int, int, int,
                        int, double, double, float*, float*, float*, cudaStream_t);
 int ttc_mask(const float*, const float*, const int32_t*, int, int, int, int, double, double, uint8_t*, cudaStream_t);
+int ttc_dense(const float*, int, int, double, double, int32_t*, uint8_t*, cudaStream_t);
 size_t loss_scratch_bytes(int, int, int);
 int loss_forward(const float*, const float*, const float*, const int32_t*, const float*, const float*, const float*,
                  int, int, int, int, double, double, double, double, uint8_t*, float*, void*, size_t, cudaStream_t);
@@ -245,6 +246,16 @@ int macbf_step_forward(const float* states, const float* goals, const float* obs
                         h_next, st))) return rc;
   return loss_forward(states, goals, obstacles, idx, h, h_next, u, B, N, M, K, dist_min_thres, ttc, dt, alpha,
                       ttc_mask_out, scalars, lscratch, loss_scratch_bytes(B, N, K), st);
+}
+
+int macbf_ttc_dense(const float* states, int B, int N, double dist_min_sq, double ttc, int32_t* counts, uint8_t* mask,
+                    void* stream) {
+  const char* fn = "macbf_ttc_dense";
+  MACBF_CHECK_ARG(B >= 1 && N >= 1, "%s: B=%d, N=%d must be >= 1", fn, B, N);
+  MACBF_CHECK_ARG(B <= 65535, "%s: B=%d exceeds 65535", fn, B);
+  REQ_PTR(fn, states); REQ_A16(fn, states);
+  MACBF_CHECK_ARG(counts != nullptr || mask != nullptr, "%s: counts and mask are both NULL", fn);
+  return ttc_dense(states, B, N, dist_min_sq, ttc, counts, mask, (cudaStream_t)stream);
 }
 
 size_t macbf_rollout_workspace_bytes(int B, int N, int M, int top_k) { return rollout_workspace_bytes(B, N, M, top_k); }

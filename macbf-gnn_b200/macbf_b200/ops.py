@@ -262,6 +262,20 @@ def step_forward(states, goals, cbf_params, ctrl_params, buf: StepBuffers, obsta
     return buf
 
 
+def ttc_dense(states, dist_min_check=0.07, ttc_check=0.1, want_mask=True, want_counts=True):
+    """core.py:212-231 on the device: (counts [B,N] int32 | None, mask [B,N,N] uint8 | None), bit-exact."""
+    _need_cuda(states)
+    states = _c(states)
+    B, N, _ = states.shape
+    dev = states.device
+    counts = torch.empty((B, N), dtype=torch.int32, device=dev) if want_counts else None
+    mask = torch.empty((B, N, N), dtype=torch.uint8, device=dev) if want_mask else None
+    L = _lib.load()
+    _lib.check(L.macbf_ttc_dense(_p(states), B, N, dist_min_check ** 2, ttc_check, _p(counts), _p(mask), _stream()),
+               "macbf_ttc_dense")
+    return counts, mask
+
+
 def rollout_forward(states, goals, ctrl_params, max_steps, obstacles=None, noise=None, top_k=TOP_K, semantics=REPAIRED,
                     obs_radius=OBS_RADIUS, dt=TIME_STEP, dist_stop=0.07):
     """train.py:59-81 in one call, stop test on the device (no per-step host sync).

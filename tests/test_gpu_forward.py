@@ -270,3 +270,32 @@ def test_remove_distant_agents_dense_api(ops):
     assert m.shape == (200, 12, 1) and m.dtype == torch.bool
     u = dev(z["u"])
     assert np.array_equal(core.dynamics(s, u).cpu().numpy(), z["dsdt"])
+
+
+@pytest.mark.parametrize("case", ref_cases())
+def test_dense_ttc_check_bit_exact_vs_reference_vectors(ops, case):
+    """macbf_ttc_dense against the UNMODIFIED reference's ttc_dangerous_mask_np output (core.py:212-231)."""
+    z = load_npz(case)
+    counts, mask = ops.ttc_dense(dev(z["states"]).unsqueeze(0))
+    want = z["ttc_np"][:, :, 0]
+    assert np.array_equal(mask[0].cpu().numpy().astype(bool), want)
+    assert np.array_equal(counts[0].cpu().numpy(), want.sum(axis=1))
+
+
+def test_dense_ttc_check_batched_vs_oracle_and_dropin(ops):
+    import oracle.macbf_oracle as O
+    import core
+    s, _ = O.synthetic_swarm(3, 777, 21, vel_std=0.6)        # fast agents: the collision-course branch fires
+    s[1, :40, :2] = s[1, 40:80, :2] + 0.03                  # pairs inside DIST_MIN_CHECK
+    counts, mask = ops.ttc_dense(dev(s))
+    got = mask.cpu().numpy().astype(bool)
+    for b in range(3):
+        want = O.ttc_dangerous_mask_dense_np(s[b].numpy())[:, :, 0]
+        assert np.array_equal(got[b], want)
+        assert np.array_equal(counts[b].cpu().numpy(), want.sum(axis=1))
+        assert want.sum() > want.shape[0] * 0       # non-trivial
+    assert got[1].sum() > got[0].sum()
+    m1 = core.ttc_dangerous_mask_np(dev(s[2]))               # drop-in: CUDA tensor in, bool (N,N,1) out
+    assert m1.shape == (777, 777, 1) and np.array_equal(m1[:, :, 0].cpu().numpy(), got[2])
+    c_only, none = ops.ttc_dense(dev(s), want_mask=False)
+    assert none is None and torch.equal(c_only, counts)
