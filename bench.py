@@ -154,6 +154,8 @@ def workload_config(args, envs_timed=None):
                         "(graph+controller+Euler+graph'+CBF(S)+CBF(S')+TTC+losses)",
             "agents": args.agents, "envs_per_gpu": args.envs, "top_k": args.top_k, "obstacles": args.obstacles,
             "mode": args.mode, "semantics": "REPAIRED", "l2": "flushed between timed steps (256 MiB write)",
+            **({"variant": "reuse_indices (h' on S's graph; NOT the reference's default path)"}
+               if getattr(args, "reuse_indices", False) else {}),
             **({"envs_timed_on_cpu": envs_timed} if envs_timed is not None else {})}
 
 
@@ -170,6 +172,8 @@ def main():
     ap.add_argument("--obstacles", type=int, default=0, help="obstacle points per env (multiple of 24)")
     ap.add_argument("--cpu-envs", type=int, default=4, help="envs per CPU-arm step (bounded sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--reuse-indices", action="store_true",
+                    help="opt-in variant (not the reference's default): h' on S's neighbour sets, one graph search per step")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -208,9 +212,9 @@ def main():
 
     def one_step(s, g):
         if trainer is None:
-            ops.step_forward(s, g, cf, tf, buf, obs_d)
+            ops.step_forward(s, g, cf, tf, buf, obs_d, reuse_indices=args.reuse_indices)
         else:
-            trainer.forward_backward(s, g, cf, tf, obs_d)
+            trainer.forward_backward(s, g, cf, tf, obs_d, reuse_indices=args.reuse_indices)
 
     def barrier():
         if world > 1:

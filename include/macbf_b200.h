@@ -175,10 +175,21 @@ int macbf_controller_backward(const float* states, const float* goals, const flo
  * private; size it with macbf_step_workspace_bytes.  Outputs u, s_next, h, h_next, idx,
  * idx_next, ttc_mask, scalars as documented above (idx_next/h_next/ttc_mask may not be NULL). */
 size_t macbf_step_workspace_bytes(int B, int N, int M, int top_k);
+/* flags for macbf_step_forward_ex.  MACBF_STEP_REUSE_INDICES: h' = CBF(S') is evaluated on the neighbour
+ * sets of S instead of a fresh top-k on S' (the `indices=` argument of the code the reference derives
+ * from; the reference itself recomputes, core.py:137, which stays the default): slot k of h and h' then
+ * refer to the same neighbour and one of the two graph searches is saved.  idx_next receives a copy of idx. */
+#define MACBF_STEP_REUSE_INDICES 1
 int macbf_step_forward(const float* states, const float* goals, const float* obstacles,
                        const float* cbf_params, const float* ctrl_params, int B, int N, int M,
                        int top_k, int semantics, double dist_min_thres, double obs_radius, double ttc,
                        double dt, double alpha, int32_t* idx, int32_t* idx_next, float* u,
+                       float* s_next, float* h, float* h_next, uint8_t* ttc_mask, float* scalars,
+                       void* workspace, size_t workspace_bytes, void* stream);
+int macbf_step_forward_ex(const float* states, const float* goals, const float* obstacles,
+                       const float* cbf_params, const float* ctrl_params, int B, int N, int M,
+                       int top_k, int semantics, double dist_min_thres, double obs_radius, double ttc,
+                       double dt, double alpha, int flags, int32_t* idx, int32_t* idx_next, float* u,
                        float* s_next, float* h, float* h_next, uint8_t* ttc_mask, float* scalars,
                        void* workspace, size_t workspace_bytes, void* stream);
 

@@ -219,7 +219,18 @@ int macbf_step_forward(const float* states, const float* goals, const float* obs
                        double obs_radius, double ttc, double dt, double alpha, int32_t* idx, int32_t* idx_next,
                        float* u, float* s_next, float* h, float* h_next, uint8_t* ttc_mask_out, float* scalars,
                        void* workspace, size_t workspace_bytes, void* stream) {
+  return macbf_step_forward_ex(states, goals, obstacles, cbf_params, ctrl_params, B, N, M, top_k, semantics, dist_min_thres,
+                               obs_radius, ttc, dt, alpha, 0, idx, idx_next, u, s_next, h, h_next, ttc_mask_out, scalars,
+                               workspace, workspace_bytes, stream);
+}
+
+int macbf_step_forward_ex(const float* states, const float* goals, const float* obstacles, const float* cbf_params,
+                          const float* ctrl_params, int B, int N, int M, int top_k, int semantics, double dist_min_thres,
+                          double obs_radius, double ttc, double dt, double alpha, int flags, int32_t* idx,
+                          int32_t* idx_next, float* u, float* s_next, float* h, float* h_next, uint8_t* ttc_mask_out,
+                          float* scalars, void* workspace, size_t workspace_bytes, void* stream) {
   const char* fn = "macbf_step_forward";
+  MACBF_CHECK_ARG((flags & ~MACBF_STEP_REUSE_INDICES) == 0, "%s: unknown flags 0x%x", fn, flags);
   MACBF_CHECK_ARG(top_k >= 1 && top_k <= MACBF_MAX_K, "%s: top_k=%d out of range [1,%d]", fn, top_k, MACBF_MAX_K);
   const int K = macbf_neighbor_count(N, M, top_k);
   if (check_dims(fn, B, N, M, K)) return 1;
@@ -239,7 +250,11 @@ int macbf_step_forward(const float* states, const float* goals, const float* obs
   if ((rc = neighbor_any(states, obstacles, B, N, M, top_k, idx, gscratch, gbytes, st))) return rc;
   if ((rc = controller_forward(states, goals, obstacles, idx, ctrl_params, B, N, M, K, semantics, obs_radius, dt, pool,
                                u, s_next, st))) return rc;
-  if ((rc = neighbor_any(s_next, obstacles, B, N, M, top_k, idx_next, gscratch, gbytes, st))) return rc;   // core.py:137
+  if (flags & MACBF_STEP_REUSE_INDICES) {   // h' on S's graph (the upstream `indices=` argument the reference dropped)
+    MACBF_CHECK_CUDA(cudaMemcpyAsync(idx_next, idx, (size_t)B * N * K * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+  } else if ((rc = neighbor_any(s_next, obstacles, B, N, M, top_k, idx_next, gscratch, gbytes, st))) {   // core.py:137
+    return rc;
+  }
   if ((rc = cbf_forward(states, obstacles, idx, cbf_params, B, N, M, K, semantics, dist_min_thres, obs_radius, h, st)))
     return rc;
   if ((rc = cbf_forward(s_next, obstacles, idx_next, cbf_params, B, N, M, K, semantics, dist_min_thres, obs_radius,

@@ -223,6 +223,9 @@ def controller_backward(states, goals, idx, ctrl_params, grad_u, grad_s_next=Non
     return grad_params, gs, gg
 
 
+STEP_REUSE_INDICES = 1   # include/macbf_b200.h: MACBF_STEP_REUSE_INDICES
+
+
 class StepBuffers:
     """Pre-allocated outputs + workspace for macbf_step_forward: the timed loop allocates nothing."""
 
@@ -247,18 +250,20 @@ class StepBuffers:
 
 def step_forward(states, goals, cbf_params, ctrl_params, buf: StepBuffers, obstacles=None, semantics=REPAIRED,
                  dist_min_thres=DIST_MIN_THRES, obs_radius=OBS_RADIUS, ttc=TIME_TO_COLLISION, dt=TIME_STEP,
-                 alpha=ALPHA_CBF):
-    """The whole per-step path (graph -> u, S' -> graph' -> h, h' -> TTC mask -> scalars) in one C call."""
+                 alpha=ALPHA_CBF, reuse_indices=False):
+    """The whole per-step path (graph -> u, S' -> graph' -> h, h' -> TTC mask -> scalars) in one C call.
+    reuse_indices=True evaluates h' on S's neighbour sets (MACBF_STEP_REUSE_INDICES; not the reference's default)."""
     _need_cuda(states, goals, cbf_params, ctrl_params, obstacles)
     B, N, M, obstacles = _dims(states, obstacles)
     assert (B, N, M) == (buf.B, buf.N, buf.M), "StepBuffers were sized for another problem"
     assert states.is_contiguous() and goals.is_contiguous() and cbf_params.is_contiguous() and ctrl_params.is_contiguous()
     L = _lib.load()
-    _lib.check(L.macbf_step_forward(_p(states), _p(goals), _p(obstacles), _p(cbf_params), _p(ctrl_params), B, N, M,
-                                    buf.top_k, semantics, dist_min_thres, obs_radius, ttc, dt, alpha, _p(buf.idx),
-                                    _p(buf.idx_next), _p(buf.u), _p(buf.s_next), _p(buf.h), _p(buf.h_next),
-                                    _p(buf.ttc_mask), _p(buf.scalars), _p(buf.workspace), buf.workspace.numel(),
-                                    _stream()), "macbf_step_forward")
+    _lib.check(L.macbf_step_forward_ex(_p(states), _p(goals), _p(obstacles), _p(cbf_params), _p(ctrl_params), B, N, M,
+                                       buf.top_k, semantics, dist_min_thres, obs_radius, ttc, dt, alpha,
+                                       STEP_REUSE_INDICES if reuse_indices else 0, _p(buf.idx), _p(buf.idx_next),
+                                       _p(buf.u), _p(buf.s_next), _p(buf.h), _p(buf.h_next), _p(buf.ttc_mask),
+                                       _p(buf.scalars), _p(buf.workspace), buf.workspace.numel(), _stream()),
+               "macbf_step_forward")
     return buf
 
 

@@ -48,12 +48,13 @@ class TrainStep:
         self.scratch = torch.empty((nb,), dtype=torch.uint8, device=dev)
 
     def forward_backward(self, states, goals, cbf_params, ctrl_params, obstacles: Optional[torch.Tensor] = None,
-                         all_reduce: bool = True):
-        """Returns (scalars [B,12], grad [51141] = [grad_cbf | grad_ctrl] of the env-mean objective)."""
+                         all_reduce: bool = True, reuse_indices: bool = False):
+        """Returns (scalars [B,12], grad [51141] = [grad_cbf | grad_ctrl] of the env-mean objective).
+        reuse_indices: h' on S's neighbour sets (ops.step_forward); the backward needs no change, idx_next = idx."""
         L = _lib.load()
         b = self.buf
         B, N, M, K = self.B, self.N, self.M, b.K
-        ops.step_forward(states, goals, cbf_params, ctrl_params, b, obstacles)
+        ops.step_forward(states, goals, cbf_params, ctrl_params, b, obstacles, reuse_indices=reuse_indices)
         st = torch.cuda.current_stream().cuda_stream
         p = ops._p
         obs = obstacles if (obstacles is not None and M > 0) else None

@@ -172,13 +172,18 @@ def decidable_rows(states: torch.Tensor, k: int, obstacles: Optional[torch.Tenso
 # ----------------------------------------------------------------------------------------
 # edge features shared by CBF / controller / TTC
 # ----------------------------------------------------------------------------------------
-def _gather_edges(states, obstacles, k, extra_cbf_feature: bool):
+def _gather_edges(states, obstacles, k, extra_cbf_feature: bool, indices: Optional[torch.Tensor] = None):
+    """indices (N, K) int64: gather these candidate columns instead of a fresh top-k (the `indices=` argument of the
+    code the reference derives from; the reference recomputes, core.py:137) - an opt-in extension."""
     diff, eye = pair_tensor(states, obstacles)
     feats = [diff, eye.unsqueeze(2)]
     if extra_cbf_feature:
         d = torch.sqrt(torch.sum(torch.square(diff[:, :, :2]) + 1e-4, dim=2))   # cbf.py:24-25
         feats.append((d - DIST_MIN_THRES).unsqueeze(2))                         # cbf.py:29
     x = torch.cat(feats, dim=2)
+    if indices is not None:
+        rows = torch.arange(x.shape[0]).unsqueeze(1).expand_as(indices)
+        return x[rows, indices], indices
     return remove_distant_agents(x, k)
 
 
@@ -194,9 +199,9 @@ def _to_channels_first(x: torch.Tensor, semantics: int) -> torch.Tensor:
 # ----------------------------------------------------------------------------------------
 def cbf_forward(p: Dict[str, torch.Tensor], states: torch.Tensor, semantics: int = REPAIRED,
                 obstacles: Optional[torch.Tensor] = None, k: int = TOP_K,
-                obs_radius: float = OBS_RADIUS) -> torch.Tensor:
+                obs_radius: float = OBS_RADIUS, indices: Optional[torch.Tensor] = None) -> torch.Tensor:
     """h (N, 1, K_eff)."""
-    x, _ = _gather_edges(states, obstacles, k, True)
+    x, _ = _gather_edges(states, obstacles, k, True, indices)
     dist = torch.sqrt(torch.sum(torch.square(x[:, :, :2]) + 1e-4, dim=2, keepdim=True))  # cbf.py:34-35
     mask = torch.less_equal(dist, obs_radius).type_as(x)
     mask = mask.reshape(-1, mask.shape[2], mask.shape[1])                                # cbf.py:37
@@ -321,10 +326,11 @@ def loss_barrier(h, states, obstacles=None, k=TOP_K, r=DIST_MIN_THRES, ttc=TIME_
 
 def loss_derivatives(p_cbf, states, actions, h, semantics=REPAIRED, obstacles=None, k=TOP_K,
                      r=DIST_MIN_THRES, ttc=TIME_TO_COLLISION, dt=TIME_STEP, alpha=ALPHA_CBF,
-                     obs_radius=OBS_RADIUS):
-    """core.py:132-171 (repair L8: the CBF is evaluated on states_next)."""
+                     obs_radius=OBS_RADIUS, reuse_indices=False):
+    """core.py:132-171 (repair L8: the CBF is evaluated on states_next).  reuse_indices: h' on S's neighbour sets."""
     states_next = euler_step(states, actions, dt)
-    h_next = cbf_forward(p_cbf, states_next, semantics, obstacles, k, obs_radius)
+    ind = neighbor_indices(states.detach(), k, obstacles).long() if reuse_indices else None
+    h_next = cbf_forward(p_cbf, states_next, semantics, obstacles, k, obs_radius, ind)
     deriv = h_next - h + dt * alpha * h
     dang = ttc_dangerous_mask(states, obstacles, k, r, ttc)
     out = _hinge_pair(deriv, dang,
@@ -351,7 +357,7 @@ def total_loss(l_dang, l_safe, l_dang_d, l_safe_d, l_act):
 # ----------------------------------------------------------------------------------------
 def full_step(p_cbf, p_ctrl, states, goals, obstacles=None, k=TOP_K, semantics=REPAIRED,
               with_grad=False, r=DIST_MIN_THRES, ttc=TIME_TO_COLLISION, dt=TIME_STEP,
-              alpha=ALPHA_CBF, obs_radius=OBS_RADIUS):
+              alpha=ALPHA_CBF, obs_radius=OBS_RADIUS, reuse_indices=False):
     """graph(S) -> u -> S' -> graph(S') -> h, h' -> TTC mask -> 9 scalars [-> gradients].
     Returns a dict of tensors.  The action fed to the derivative loss keeps its autograd
     link to the controller (train.py:60-70 is not detached)."""
@@ -364,7 +370,7 @@ def full_step(p_cbf, p_ctrl, states, goals, obstacles=None, k=TOP_K, semantics=R
         h = cbf_forward(p_cbf, states, semantics, obstacles, k, obs_radius)
         lb = loss_barrier(h, states, obstacles, k, r, ttc)
         ld, h_next = loss_derivatives(p_cbf, states, u, h, semantics, obstacles, k, r, ttc, dt, alpha,
-                                      obs_radius)
+                                      obs_radius, reuse_indices)
         la = loss_actions(states, goals, u)
         total = total_loss(lb[0], lb[1], ld[0], ld[1], la)
         out = {
