@@ -255,9 +255,6 @@ __device__ __forceinline__ void bf16_split8(const float* x, uint4& hi, uint4& lo
   hi = make_uint4(h[0], h[1], h[2], h[3]);
   lo = make_uint4(l[0], l[1], l[2], l[3]);
 }
-// byte offset of 16-byte chunk `chunk` (8 channels) of edge row `row` inside a 64-channel block
-__device__ __forceinline__ uint32_t img_off(int row, int chunk) { return (uint32_t)row * 128u + (uint32_t)((chunk ^ (row & 7)) << 4); }
-
 // Sixteen consecutive channels (chunks 2*pair, 2*pair+1) of row `row`: one aligned 32-byte sector of the image,
 // written with a single 256-bit store (the swizzle only swaps the two 16-byte halves on odd rows).
 __device__ __forceinline__ void st_global_v8(void* p, uint4 a, uint4 b) {
