@@ -96,6 +96,18 @@ int macbf_controller_forward(const float* states, const float* goals, const floa
 int macbf_ttc_mask(const float* states, const float* obstacles, const int32_t* idx, int B, int N,
                    int M, int K, double dist_min_thres, double ttc, uint8_t* mask, void* stream);
 
+/* ---- A0: scenario generation on the device  (core.py:45-71 generate_data) -------------------
+ * The reference's sequential dart throwing (starts in a square of side sqrt(max(1,N/8)), goals within
+ * +-0.5 of the starts, all pairs farther apart than dist_min_thres, unplaced rows repelling from the
+ * origin) resolved in parallel on a counter-based random stream (seed, env, index); one CTA per env.
+ * n_candidates >= N start candidates are drawn per env (2N + 256 is ample at the reference's density);
+ * accepted [B] receives how many were accepted: if accepted[b] < N, env b is incomplete - call again with
+ * more candidates.  states [B,N,4] (zero velocity), goals [B,N,2].  The stream is NOT numpy's MT19937. */
+size_t macbf_scenario_workspace_bytes(int B, int N, int n_candidates);
+int macbf_generate_scenario(unsigned long long seed, int B, int N, int n_candidates,
+                            double dist_min_thres, float* states, float* goals, int32_t* accepted,
+                            void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- evaluation-time dense check  (core.py:212-231 ttc_dangerous_mask_np; train.py:74-75) ----
  * For every ordered pair (i, j) of an env: within sqrt(dist_min_sq) or colliding within ttc, in the
  * reference's numpy mixed float32/float64 arithmetic (bit-exact mask).  dist_min_sq is the host's

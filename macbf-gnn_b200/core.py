@@ -66,6 +66,14 @@ def generate_data(num_agents, dist_min_thres):
     return np.concatenate([pos, np.zeros_like(pos)], axis=1), goals
 
 
+def generate_data_cuda(num_agents, dist_min_thres, seed=0, num_envs=None, device="cuda"):
+    """generate_data on the device (macbf_generate_scenario): the same dart-throwing process on a counter-based
+    stream keyed by (seed, env) instead of np.random.  -> CUDA tensors (states (N,4), goals (N,2)), or batched
+    (B,N,4), (B,N,2) when num_envs is given."""
+    s, g = _ops.generate_scenario(seed, 1 if num_envs is None else int(num_envs), int(num_agents), dist_min_thres, device)
+    return (s[0], g[0]) if num_envs is None else (s, g)
+
+
 # ------------------------------------------------------------------ hot path
 def _obstacles_for(states_b):
     if OBSTACLES is None:

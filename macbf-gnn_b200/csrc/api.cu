@@ -40,6 +40,8 @@ int controller_forward(const float*, const float*, const float*, const int32_t*,
                        int, double, double, float*, float*, float*, cudaStream_t);
 int ttc_mask(const float*, const float*, const int32_t*, int, int, int, int, double, double, uint8_t*, cudaStream_t);
 int ttc_dense(const float*, int, int, double, double, int32_t*, uint8_t*, cudaStream_t);
+size_t scenario_workspace_bytes(int, int, int);
+int scenario_generate(unsigned long long, int, int, int, double, float*, float*, int32_t*, void*, size_t, cudaStream_t);
 size_t loss_scratch_bytes(int, int, int);
 int loss_forward(const float*, const float*, const float*, const int32_t*, const float*, const float*, const float*,
                  int, int, int, int, double, double, double, double, uint8_t*, float*, void*, size_t, cudaStream_t);
@@ -271,6 +273,18 @@ int macbf_ttc_dense(const float* states, int B, int N, double dist_min_sq, doubl
   REQ_PTR(fn, states); REQ_A16(fn, states);
   MACBF_CHECK_ARG(counts != nullptr || mask != nullptr, "%s: counts and mask are both NULL", fn);
   return ttc_dense(states, B, N, dist_min_sq, ttc, counts, mask, (cudaStream_t)stream);
+}
+
+size_t macbf_scenario_workspace_bytes(int B, int N, int n_candidates) { return scenario_workspace_bytes(B, N, n_candidates); }
+
+int macbf_generate_scenario(unsigned long long seed, int B, int N, int n_candidates, double dist_min_thres, float* states,
+                            float* goals, int32_t* accepted, void* workspace, size_t workspace_bytes, void* stream) {
+  const char* fn = "macbf_generate_scenario";
+  MACBF_CHECK_ARG(B >= 1 && N >= 1, "%s: B=%d, N=%d must be >= 1", fn, B, N);
+  REQ_PTR(fn, states); REQ_PTR(fn, goals); REQ_PTR(fn, accepted); REQ_PTR(fn, workspace);
+  REQ_A16(fn, states); REQ_A16(fn, workspace);
+  return scenario_generate(seed, B, N, n_candidates, dist_min_thres, states, goals, accepted, workspace, workspace_bytes,
+                           (cudaStream_t)stream);
 }
 
 size_t macbf_rollout_workspace_bytes(int B, int N, int M, int top_k) { return rollout_workspace_bytes(B, N, M, top_k); }

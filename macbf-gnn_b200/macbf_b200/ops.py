@@ -267,6 +267,29 @@ def step_forward(states, goals, cbf_params, ctrl_params, buf: StepBuffers, obsta
     return buf
 
 
+def generate_scenario(seed, B, N, dist_min_thres=DIST_MIN_THRES, device="cuda", n_candidates=None):
+    """core.py:45-71 on the device -> (states [B,N,4] with zero velocity, goals [B,N,2]); deterministic in
+    (seed, env).  Retries with more candidates in the (unlikely) case an env ran short."""
+    dev = torch.device(device)
+    if dev.type != "cuda":
+        raise _lib.MacbfError("macbf_b200 has no CPU path: scenarios are generated on a CUDA device")
+    L = _lib.load()
+    T = int(n_candidates) if n_candidates else 2 * N + 256
+    states = torch.empty((B, N, 4), dtype=torch.float32, device=dev)
+    goals = torch.empty((B, N, 2), dtype=torch.float32, device=dev)
+    accepted = torch.empty((B,), dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        for _ in range(6):
+            nbytes = L.macbf_scenario_workspace_bytes(B, N, T)
+            ws = torch.empty((nbytes,), dtype=torch.uint8, device=dev)
+            _lib.check(L.macbf_generate_scenario(int(seed) & 0xFFFFFFFFFFFFFFFF, B, N, T, dist_min_thres, _p(states), _p(goals),
+                                                 _p(accepted), _p(ws), nbytes, _stream()), "macbf_generate_scenario")
+            if int(accepted.min()) >= N:
+                return states, goals
+            T *= 2
+    raise _lib.MacbfError(f"generate_scenario: could not place {N} agents (threshold {dist_min_thres})")
+
+
 def ttc_dense(states, dist_min_check=0.07, ttc_check=0.1, want_mask=True, want_counts=True):
     """core.py:212-231 on the device: (counts [B,N] int32 | None, mask [B,N,N] uint8 | None), bit-exact."""
     _need_cuda(states)

@@ -424,3 +424,74 @@ def synthetic_obstacles(n_envs: int, n_agents: int, n_circles: int, n_rects: int
             pts.append(np.concatenate([top, right, bottom, left], 0) + c)
         envs.append(np.concatenate(pts, 0) if pts else np.zeros((0, 2)))
     return torch.from_numpy(np.stack(envs, 0).astype(np.float32))
+
+
+# ----------------------------------------------------------------------------------------
+# scenario generation (core.py:45-71) on a counter-based stream - the sequential restatement of what
+# csrc/scenario.cu resolves in parallel (same stream, same fp32 decisions, identical bits)
+# ----------------------------------------------------------------------------------------
+_M64 = (1 << 64) - 1
+
+
+def _mix64(z: int) -> int:
+    z &= _M64
+    z ^= z >> 30
+    z = (z * 0xBF58476D1CE4E5B9) & _M64
+    z ^= z >> 27
+    z = (z * 0x94D049BB133111EB) & _M64
+    z ^= z >> 31
+    return z
+
+
+def stream_uniform2(seed: int, env: int, stream: int, index: int):
+    """Two fp32 uniforms in [0,1) with 24 random bits each (scenario.cu: rng2)."""
+    h = _mix64((seed & _M64) ^ _mix64(env + 1))
+    h = _mix64(h ^ _mix64(stream + 0x1234567))
+    h = _mix64(h + index * 0x9E3779B97F4A7C15)
+    scale = np.float32(2.0 ** -24)
+    return np.float32(h >> 40) * scale, np.float32((h >> 8) & 0xFFFFFF) * scale
+
+
+def _dist32(ax, ay, bx, by):
+    dx = np.float32(ax) - np.float32(bx)
+    dy = np.float32(ay) - np.float32(by)
+    return np.sqrt(dx * dx + dy * dy)
+
+
+def generate_data_stream(seed: int, env: int, n_agents: int, dist_min_thres: float = DIST_MIN_THRES,
+                         n_candidates: Optional[int] = None):
+    """core.py:45-71 step by step (dart throwing with the unplaced rows at the origin), drawing from the
+    counter-based stream: -> (states (N,4) float32, goals (N,2) float32), or None if the candidates run out."""
+    thres = np.float32(dist_min_thres)
+    side = np.float32(math.sqrt(max(1.0, n_agents / 8.0)))
+    T = n_candidates if n_candidates else 2 * n_agents + 256
+    pos = np.zeros((n_agents, 2), dtype=np.float32)
+    i = 0
+    for t in range(T):
+        if i == n_agents:
+            break
+        u0, u1 = stream_uniform2(seed, env, 0, t)
+        c = np.array([u0 * side, u1 * side], dtype=np.float32)
+        if _dist32(c[0], c[1], 0, 0) <= thres:                        # rows i.. are still (0,0): core.py:47,54
+            continue
+        if i and np.min(_dist32(pos[:i, 0], pos[:i, 1], c[0], c[1])) <= thres:
+            continue
+        pos[i] = c
+        i += 1
+    if i < n_agents:
+        return None
+    goals = np.zeros((n_agents, 2), dtype=np.float32)
+    half = np.float32(0.5)
+    for i in range(n_agents):
+        a = 0
+        while True:
+            u0, u1 = stream_uniform2(seed, env, 1, (i << 20) | a)
+            g = np.array([(u0 - half) + pos[i, 0], (u1 - half) + pos[i, 1]], dtype=np.float32)   # core.py:59
+            ok = _dist32(g[0], g[1], 0, 0) > thres
+            if ok and i:
+                ok = np.min(_dist32(goals[:i, 0], goals[:i, 1], g[0], g[1])) > thres
+            if ok:
+                break
+            a += 1
+        goals[i] = g
+    return np.concatenate([pos, np.zeros_like(pos)], axis=1), goals
