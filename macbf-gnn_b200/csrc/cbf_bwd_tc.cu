@@ -25,6 +25,7 @@
 #include "common.cuh"
 #include "tc_common.cuh"
 #include "cbf_bwd_layout.cuh"
+#include "ctrl_node_bwd_layout.cuh"
 
 namespace macbf {
 
@@ -346,16 +347,18 @@ constexpr uint32_t STAGE = cbfrec::STAGE_BYTES;
 constexpr uint32_t ONES = 2 * STAGE;           // bf16 ones: 2 blocks x 16 rows x 128 B = 4 KB (A operand M = 128, K = 16)
 constexpr size_t smem_bytes = 2 * (size_t)STAGE + 4096 + 1024;
 // TMEM columns: [0,64) dW3^T[in][out]  [64,128) dW2[out][in]  [128,192) db3 (every lane)  [192,208) db2 (column 0)
-constexpr uint32_t C_W3 = 0, C_W2 = 64, C_B3 = 128, C_B2 = 192;
+//               [256,320) dW1^T[in][out] (NST = 3)
+constexpr uint32_t C_W3 = 0, C_W2 = 64, C_B3 = 128, C_B2 = 192, C_W1 = 256;
 }  // namespace cbfwg
 
 // NST = 2: CBF (stage 0 = G3: dW3^T, db3; stage 1 = G2: dW2, db2).  NST = 1: controller edge net (one G2-type stage
-// per tile: A = dZ2 (128 channels), B = A1 (64 channels) -> dW2[out][in], db2); `rec_stride` bytes between tile records,
-// P floats per gradient slice, off* = offsets of the parameter tensors inside a slice.
+// per tile: A = dZ2 (128 channels), B = A1 (64 channels) -> dW2[out][in], db2).  NST = 3: controller node net (G3, G2 and
+// a third stage A = pool (128 channels), B = dZ1 (64 channels) -> dW1[:, :128]^T, rows of W1 being `ldW1` floats long).
+// `rec_stride` bytes between tile records, P floats per gradient slice, off* = offsets of the parameter tensors in a slice.
 template <int NST>
 __global__ void __launch_bounds__(cbfwg::THREADS, 1)
 wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long long ntiles, float* __restrict__ slices, int P,
-                int offW3, int offB3, int offW2, int offB2) {
+                int offW3, int offB3, int offW2, int offB2, int offW1, int ldW1) {
   using namespace cbfwg;
   using namespace tc;
   extern __shared__ unsigned char smem_raw[];
@@ -363,7 +366,8 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
   __shared__ uint64_t full[2], empty[2], done;
   __shared__ uint32_t tmem_base_s;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (warp == 0) tmem_alloc(&tmem_base_s, 256);
+  constexpr uint32_t TMEM_COLS = (NST == 3) ? 512 : 256;
+  if (warp == 0) tmem_alloc(&tmem_base_s, TMEM_COLS);
   if (threadIdx.x == 32) {
     mbar_init(&full[0], 1); mbar_init(&full[1], 1); mbar_init(&empty[0], 1); mbar_init(&empty[1], 1); mbar_init(&done, 1);
     fence_mbar_init();
@@ -399,7 +403,7 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
     bool first_tile = true;
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, first_tile = false) {
       for (int s0 = 0; s0 < NST; ++s0, ++n) {
-        const int s = (NST == 2) ? s0 : 1;
+        const int s = (NST == 1) ? 1 : s0;                // 0: G3-type, 1: G2-type, 2: pool x dZ1 (G3-shaped, no bias)
         const uint32_t buf = n & 1;
         mbar_wait(&full[buf], (n >> 1) & 1);
         fence_after_sync();
@@ -407,7 +411,7 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
         // A: 128 channels (two 64-wide blocks, 16 KB apart), B: 64 channels; hi at +0 / +4 BLK, lo at +2 / +5 BLK
         const uint64_t a_hi = smem_desc_mn_sw128(base, cbfrec::BLK), a_lo = smem_desc_mn_sw128(base + 2 * cbfrec::BLK, cbfrec::BLK);
         const uint64_t b_hi = smem_desc_mn_sw128(base + 4 * cbfrec::BLK, cbfrec::BLK), b_lo = smem_desc_mn_sw128(base + 5 * cbfrec::BLK, cbfrec::BLK);
-        const uint32_t dcol = tb + (s == 0 ? C_W3 : C_W2);
+        const uint32_t dcol = tb + (s == 0 ? C_W3 : (s == 1 ? C_W2 : C_W1));
         const uint32_t acc0 = first_tile ? 0u : 1u;
 #pragma unroll
         for (int term = 0; term < 3; ++term) {          // lo*hi, hi*lo, hi*hi
@@ -423,7 +427,7 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
 #pragma unroll
             for (int ks = 0; ks < 8; ++ks)
               if (elect_one()) mma_f16_ss(tb + C_B3, d_ones_a, desc_advance(term == 0 ? b_lo : b_hi, ks * 2048), ID64, (term | ks) ? 1u : acc0);
-        } else {
+        } else if (s == 1) {
           // db2[m] = sum_e dZ2[e][m]: dZ2 (A) x ones (B, N = 16)
 #pragma unroll
           for (int term = 0; term < 2; ++term)
@@ -445,7 +449,7 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
     float* gp = slices + (size_t)blockIdx.x * P;
     for (int c0 = 0; c0 < 64; c0 += 16) {
       float v[16];
-      if (NST == 2) {
+      if (NST >= 2) {
         tmem_ld16(tlane + C_W3 + c0, v);                // dW3^T[m = in][n = out]
         wait_ld();
 #pragma unroll
@@ -462,7 +466,16 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
       wait_ld();
       gp[offB2 + m] += v[0];
     }
-    if (NST == 2 && q == 0) {                                       // every lane holds the same db3 row; lane m < 32 writes channels 2m, 2m+1
+    if (NST == 3) {
+      for (int c0 = 0; c0 < 64; c0 += 16) {
+        float v[16];
+        tmem_ld16(tlane + C_W1 + c0, v);                // dW1^T[m = pool channel][n = out]
+        wait_ld();
+#pragma unroll
+        for (int e = 0; e < 16; ++e) gp[offW1 + (c0 + e) * ldW1 + m] += v[e];
+      }
+    }
+    if (NST >= 2 && q == 0) {                                       // every lane holds the same db3 row; lane m < 32 writes channels 2m, 2m+1
       for (int c0 = 0; c0 < 64; c0 += 16) {
         float v[16];
         tmem_ld16(tlane + C_B3 + c0, v);
@@ -476,14 +489,23 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
   }
   fence_before_sync();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tbase, 256);
+  if (warp == 0) tmem_dealloc(tbase, TMEM_COLS);
+}
+
+// controller node net (ctrl_node_bwd_tc.cu): three 96-KB stages per tile record
+int wgrad_tc_node(const unsigned char* rec, long long ntiles, float* slices, int grid, cudaStream_t st) {
+  MACBF_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfwg::smem_bytes));
+  wgrad_tc_kernel<3><<<grid, cbfwg::THREADS, cbfwg::smem_bytes, st>>>(rec, cnrec::BYTES, ntiles, slices, MACBF_CTRL_PARAMS, CT_NW3,
+                                                                     CT_NB3, CT_NW2, CT_NB2, CT_NW1, 132);
+  MACBF_CHECK_LAUNCH("wgrad_tc_kernel<node>");
+  return 0;
 }
 
 // controller edge net (ctrl_edge_bwd_tc.cu): one 96-KB stage per tile record
 int wgrad_tc_ctrl(const unsigned char* rec, size_t rec_stride, long long ntiles, float* slices, int grid, cudaStream_t st) {
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfwg::smem_bytes));
   wgrad_tc_kernel<1><<<grid, cbfwg::THREADS, cbfwg::smem_bytes, st>>>(rec, rec_stride, ntiles, slices, MACBF_CTRL_PARAMS, 0, 0,
-                                                                     CT_EW2, CT_EB2);
+                                                                     CT_EW2, CT_EB2, 0, 0);
   MACBF_CHECK_LAUNCH("wgrad_tc_kernel<ctrl>");
   return 0;
 }
@@ -537,7 +559,7 @@ int cbf_backward_tc(const float* states, const float* obstacles, const int32_t* 
                                                                         grad_states);
     MACBF_CHECK_LAUNCH("cbf_dgrad_tc_kernel");
     wgrad_tc_kernel<2><<<grid, cbfwg::THREADS, cbfwg::smem_bytes, st>>>(rec, cbfrec::BYTES, ct, slices, MACBF_CBF_PARAMS, CBF_W3,
-                                                                       CBF_B3, CBF_W2, CBF_B2);
+                                                                       CBF_B3, CBF_W2, CBF_B2, 0, 0);
     MACBF_CHECK_LAUNCH("wgrad_tc_kernel<cbf>");
   }
   reduce_partials_kernel<<<(MACBF_CBF_PARAMS + 255) / 256, 256, 0, st>>>(slices, NUM_SMS, MACBF_CBF_PARAMS, grad_params);

@@ -358,17 +358,22 @@ int ctrl_edge_bwd_tc(const float*, const float*, const int32_t*, const float*, c
                      float*, void*, cudaStream_t);
 int ctrl_edge_tc(const float* states, const float* obstacles, const int32_t* idx, const float* params, int B, int N,
                  int M, int K, double obs_radius, float* pool, cudaStream_t st, uint8_t* argk);
+size_t ctrl_node_bwd_tc_scratch_bytes(int B, int N);
+int ctrl_node_bwd_tc(const float*, const float*, const float*, const float*, const float*, int, int, double, float*, float*,
+                     float*, float*, void*, cudaStream_t);
 constexpr int CTRL_SLICES = 2 * NUM_SMS;   // the tensor-core edge backward runs two CTAs per SM
 // MACBF_CTRL_BWD_FFMA=1 keeps the FP32-FFMA edge backward (A/B reference of ctrl_edge_bwd_tc.cu)
 static bool ctrl_bwd_force_ffma() {     // read per call, so a test can switch paths inside one process
   const char* e = getenv("MACBF_CTRL_BWD_FFMA");
   return e != nullptr && e[0] == '1';
 }
+static inline size_t max_sz(size_t a, size_t b) { return a > b ? a : b; }
 
 // scratch: [pool / dz : B*N*128 f32][partial : CTRL_SLICES * 34052 f32][winners + tile records of the tensor-core edge backward]
 size_t controller_backward_scratch_bytes(int B, int N, int K) {
   return a256((size_t)B * N * MACBF_POOL_DIM * sizeof(float)) + a256((size_t)CTRL_SLICES * MACBF_CTRL_PARAMS * sizeof(float)) +
-         (ctrl_edge_bwd_tc_applicable(K) ? ctrl_edge_bwd_tc_scratch_bytes(B, N, K) : 0);
+         max_sz(ctrl_edge_bwd_tc_applicable(K) ? ctrl_edge_bwd_tc_scratch_bytes(B, N, K) : 0,
+                ((size_t)B * N * 128 + 4096) + ctrl_node_bwd_tc_scratch_bytes(B, N));   // node records sit behind the winners
 }
 
 int controller_backward(const float* states, const float* goals, const float* obstacles, const int32_t* idx,
@@ -387,7 +392,14 @@ int controller_backward(const float* states, const float* goals, const float* ob
   int rc = edge_tc ? ctrl_edge_tc(states, obstacles, idx, params, B, N, M, K, obs_radius, pool, st, ctrl_edge_bwd_tc_argk(edge_scratch))
                    : controller_forward_pool_only(states, obstacles, idx, params, B, N, M, K, obs_radius, pool, st);
   if (rc) return rc;
-  {
+  if (!ctrl_bwd_force_ffma()) {
+    // the node records live where the edge backward's winners / records go afterwards - except the winners, which the
+    // recomputed forward has already written: keep them (first B*N*128 bytes of edge_scratch, 1024-aligned)
+    char* node_scratch = (char*)edge_scratch + (edge_tc ? (((size_t)agents * 128 + 2047) & ~(size_t)1023) : 0);
+    rc = ctrl_node_bwd_tc(states, goals, params, grad_u, grad_s_next, B, N, dt, pool, partial, grad_states, grad_goals,
+                          node_scratch, st);
+    if (rc) return rc;
+  } else {
     const long long ntiles = (agents + cnb_smem::R - 1) / cnb_smem::R;
     const size_t smem = cnb_smem::total * sizeof(float);
     MACBF_CHECK_CUDA(cudaFuncSetAttribute(ctrl_node_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

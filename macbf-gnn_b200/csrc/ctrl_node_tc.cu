@@ -17,6 +17,7 @@
 // (block barriers) instead of the decoupled pipeline of the edge kernels.
 #include "common.cuh"
 #include "tc_common.cuh"
+#include "ctrl_node_bwd_layout.cuh"
 
 namespace macbf {
 
@@ -38,15 +39,23 @@ constexpr int oB2 = oB1 + 64;
 constexpr int oB3 = oB2 + 128;
 constexpr int oW4 = oB3 + 64;              // [4][64]
 constexpr int oB4 = oW4 + 256;
-constexpr int oPart = oB4 + 4;             // [4 cgrp][4 out][128]
-constexpr int total_floats = oPart + 16 * R;
+constexpr int oPart = oB4 + 4;             // [4 cgrp][4 out][128]; DUMP: then [16 warps][64] partial dW4 sums
+constexpr int oD4 = oPart + 16 * R;        // DUMP: d/d(pre-sigmoid) [4][128]
+constexpr int total_floats = oD4 + 4 * R;
 constexpr size_t smem_bytes = (size_t)total_floats * 4 + 1024;
 }  // namespace cntc
 
+// DUMP = true is the first kernel of the tensor-core node backward (ctrl_node_bwd_tc.cu): the same forward, additionally
+// writing per tile (ctrl_node_bwd_layout.cuh) the bf16 hi/lo images of pool, a1, a2, the ReLU masks, and per agent
+// d/d(pre-sigmoid outputs) from the incoming gradients (controller.py:50-61 backwards) and the direct d/d(e, v) through
+// the action; accumulates dW4, db4 into this CTA's gradient slice.  u / s_next are not written.
+template <bool DUMP>
 __global__ void __launch_bounds__(cntc::THREADS, 1)
 ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ goals,
                     const float* __restrict__ pool, const float* __restrict__ params, long long agents_total,
-                    float dt, float* __restrict__ u, float* __restrict__ s_next, const int* __restrict__ skip) {
+                    float dt, float* __restrict__ u, float* __restrict__ s_next, const int* __restrict__ skip,
+                    const float* __restrict__ grad_u, const float* __restrict__ grad_s_next,
+                    unsigned char* __restrict__ rec, float* __restrict__ slices) {
   MACBF_SKIP_IF_SET(skip);
   using namespace cntc;
   using namespace tc;
@@ -57,6 +66,8 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
   float* W3hi = sm + oW3HI; float* W3lo = sm + oW3LO;
   float* B1 = sm + oB1; float* B2 = sm + oB2; float* B3 = sm + oB3; float* W4 = sm + oW4; float* B4 = sm + oB4;
   float* part = sm + oPart;
+  [[maybe_unused]] float* d4s = sm + oD4;
+  [[maybe_unused]] float acc4 = 0.f;         // DUMP: thread t < 256 owns dW4[t >> 6][t & 63]; 256..259 own db4
   __shared__ uint64_t bar[3];
   __shared__ uint32_t tmem_base_s;
 
@@ -110,9 +121,11 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, par ^= 1) {
     const long long a0 = tile * R;
     const bool valid = a0 + r < agents_total;
+    [[maybe_unused]] unsigned char* tr = DUMP ? rec + (size_t)tile * cnrec::BYTES : nullptr;
     // ---- A0 = [pool, p - g, v, 0]: this thread's 32 pooled channels (+ the 8 tail columns) ----
     {
       const float4* prow = reinterpret_cast<const float4*>(pool + (a0 + r) * 128 + cgrp * 32);
+      [[maybe_unused]] uint4 pbh[2], pbl[2];
 #pragma unroll
       for (int part8 = 0; part8 < 4; ++part8) {
         float4 x0 = make_float4(0.f, 0.f, 0.f, 0.f), x1 = x0;
@@ -123,6 +136,13 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
         for (int e = 0; e < 8; ++e) tf32_split_trunc(v[e], hi[e], lo[e]);
         tmem_st8(tlane + C_A0HI + cgrp * 32 + part8 * 8, hi);
         tmem_st8(tlane + C_A0LO + cgrp * 32 + part8 * 8, lo);
+        if constexpr (DUMP) {      // this thread's 32 channels = pairs (cgrp & 1) * 2 + {0, 1} of 64-channel block cgrp >> 1
+          bf16_split8(v, pbh[part8 & 1], pbl[part8 & 1]);
+          if (part8 & 1) {
+            img_store16(tr + cnrec::P_HI + (cgrp >> 1) * cnrec::BLK, r, (cgrp & 1) * 2 + (part8 >> 1), pbh[0], pbh[1]);
+            img_store16(tr + cnrec::P_LO + (cgrp >> 1) * cnrec::BLK, r, (cgrp & 1) * 2 + (part8 >> 1), pbl[0], pbl[1]);
+          }
+        }
       }
       if (cgrp == 3) {
         float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -162,18 +182,33 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
       float v[16];
       tmem_ld16(tlane + C_D1 + c0, v);
       wait_ld();
+      [[maybe_unused]] uint32_t bits = 0;
+      [[maybe_unused]] uint4 bh[2], bl[2];
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
         float hi[8], lo[8];
+        [[maybe_unused]] float x[8];
 #pragma unroll
         for (int e = 0; e < 8; e += 2) {
           float2 h2, l2;
-          split2_trunc(relu2(__fadd2_rn(make_float2(v[half * 8 + e], v[half * 8 + e + 1]),
-                                        make_float2(B1[c0 + half * 8 + e], B1[c0 + half * 8 + e + 1]))), h2, l2);
+          const float2 xa = relu2(__fadd2_rn(make_float2(v[half * 8 + e], v[half * 8 + e + 1]),
+                                             make_float2(B1[c0 + half * 8 + e], B1[c0 + half * 8 + e + 1])));
+          split2_trunc(xa, h2, l2);
           hi[e] = h2.x; hi[e + 1] = h2.y; lo[e] = l2.x; lo[e + 1] = l2.y;
+          if constexpr (DUMP) { x[e] = xa.x; x[e + 1] = xa.y; }
         }
         tmem_st8(tlane + C_A1HI + c0 + half * 8, hi);
         tmem_st8(tlane + C_A1LO + c0 + half * 8, lo);
+        if constexpr (DUMP) {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) bits |= (x[e] > 0.f ? 1u : 0u) << (half * 8 + e);
+          bf16_split8(x, bh[half], bl[half]);
+        }
+      }
+      if constexpr (DUMP) {
+        img_store16(tr + cnrec::A1_HI, r, cgrp, bh[0], bh[1]);
+        img_store16(tr + cnrec::A1_LO, r, cgrp, bl[0], bl[1]);
+        reinterpret_cast<uint32_t*>(tr + cnrec::MASKS)[(0 * 4 + cgrp) * R + r] = bits;
       }
       wait_st();
     }
@@ -196,25 +231,41 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
     mbar_wait(&bar[1], par);
     fence_after_sync();
 #pragma unroll
+    [[maybe_unused]] uint32_t bits2 = 0;
+#pragma unroll
     for (int half16 = 0; half16 < 2; ++half16) {   // bias + ReLU + split on 32 channels of D2: hi in place, lo aside
       const int c0 = cgrp * 32 + half16 * 16;
       float v[16];
       tmem_ld16(tlane + C_Y + c0, v);
       wait_ld();
+      [[maybe_unused]] uint4 bh[2], bl[2];
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
         float hi[8], lo[8];
+        [[maybe_unused]] float x[8];
 #pragma unroll
         for (int e = 0; e < 8; e += 2) {
           float2 h2, l2;
-          split2_trunc(relu2(__fadd2_rn(make_float2(v[half * 8 + e], v[half * 8 + e + 1]),
-                                        make_float2(B2[c0 + half * 8 + e], B2[c0 + half * 8 + e + 1]))), h2, l2);
+          const float2 xa = relu2(__fadd2_rn(make_float2(v[half * 8 + e], v[half * 8 + e + 1]),
+                                             make_float2(B2[c0 + half * 8 + e], B2[c0 + half * 8 + e + 1])));
+          split2_trunc(xa, h2, l2);
           hi[e] = h2.x; hi[e + 1] = h2.y; lo[e] = l2.x; lo[e + 1] = l2.y;
+          if constexpr (DUMP) { x[e] = xa.x; x[e + 1] = xa.y; }
         }
         tmem_st8(tlane + C_Y + c0 + half * 8, hi);
         tmem_st8(tlane + C_A2LO + c0 + half * 8, lo);
+        if constexpr (DUMP) {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) bits2 |= (x[e] > 0.f ? 1u : 0u) << (half16 * 16 + half * 8 + e);
+          bf16_split8(x, bh[half], bl[half]);
+        }
+      }
+      if constexpr (DUMP) {
+        img_store16(tr + cnrec::A2_HI + (cgrp >> 1) * cnrec::BLK, r, (cgrp & 1) * 2 + half16, bh[0], bh[1]);
+        img_store16(tr + cnrec::A2_LO + (cgrp >> 1) * cnrec::BLK, r, (cgrp & 1) * 2 + half16, bl[0], bl[1]);
       }
     }
+    if constexpr (DUMP) reinterpret_cast<uint32_t*>(tr + cnrec::MASKS)[(1 * 4 + cgrp) * R + r] = bits2;
     wait_st();
     fence_before_sync();
     __syncthreads();
@@ -240,19 +291,87 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
       tmem_ld16(tlane + C_D3 + c0, v);
       wait_ld();
       float o[4] = {0.f, 0.f, 0.f, 0.f};
+      [[maybe_unused]] uint32_t bits = 0;
 #pragma unroll
       for (int e = 0; e < 16; ++e) {
         const float a = fmaxf(v[e] + B3[c0 + e], 0.f);
+        if constexpr (DUMP) bits |= (a > 0.f ? 1u : 0u) << e;
 #pragma unroll
         for (int qq = 0; qq < 4; ++qq) o[qq] = fmaf(W4[qq * 64 + c0 + e], a, o[qq]);
       }
 #pragma unroll
       for (int qq = 0; qq < 4; ++qq) part[(cgrp * 4 + qq) * R + r] = o[qq];
+      if constexpr (DUMP) reinterpret_cast<uint32_t*>(tr + cnrec::MASKS)[(2 * 4 + cgrp) * R + r] = bits;
     }
     fence_before_sync();
     __syncthreads();   // partial sums visible; every TMEM read of this tile is done
     fence_after_sync();
-    if (cgrp == 0 && valid) {
+    if constexpr (DUMP) {
+      // ---- head backward (controller.py:50-61): d/d(pre-sigmoid), direct d/d(e, v); then dW4, db4 ----
+      if (cgrp == 0) {
+        float d_o[4] = {0.f, 0.f, 0.f, 0.f}, dir[4] = {0.f, 0.f, 0.f, 0.f}, ev[4] = {0.f, 0.f, 0.f, 0.f};
+        if (valid) {
+          float kk[4], sg[4];
+#pragma unroll
+          for (int qq = 0; qq < 4; ++qq) {
+            const float o = B4[qq] + ((part[qq * R + r] + part[(4 + qq) * R + r]) + (part[(8 + qq) * R + r] + part[(12 + qq) * R + r]));
+            sg[qq] = 1.0f / (1.0f + expf(-o));
+            kk[qq] = 2.0f * sg[qq] + 0.2f;
+          }
+          const float4 s = __ldg(reinterpret_cast<const float4*>(states) + a0 + r);
+          const float2 g = __ldg(reinterpret_cast<const float2*>(goals) + a0 + r);
+          ev[0] = xsub(s.x, g.x); ev[1] = xsub(s.y, g.y); ev[2] = s.z; ev[3] = s.w;
+          float gux = 0.f, guy = 0.f;
+          if (grad_u != nullptr) {
+            const float2 gu = __ldg(reinterpret_cast<const float2*>(grad_u) + a0 + r);
+            gux = gu.x; guy = gu.y;
+          }
+          if (grad_s_next != nullptr) {   // s' = s + [v, u] * dt
+            const float4 gsn = __ldg(reinterpret_cast<const float4*>(grad_s_next) + a0 + r);
+            gux = fmaf(dt, gsn.z, gux); guy = fmaf(dt, gsn.w, guy);
+          }
+          // a_x = -(k1 e_x + k2 v_x), a_y = -(k3 e_y + k4 v_y)
+          const float dk[4] = {-ev[0] * gux, -ev[2] * gux, -ev[1] * guy, -ev[3] * guy};
+          dir[0] = -kk[0] * gux; dir[2] = -kk[1] * gux; dir[1] = -kk[2] * guy; dir[3] = -kk[3] * guy;
+#pragma unroll
+          for (int qq = 0; qq < 4; ++qq) d_o[qq] = dk[qq] * 2.0f * sg[qq] * (1.0f - sg[qq]);
+        }
+        float4* aux = reinterpret_cast<float4*>(tr + cnrec::AUX) + 3 * r;
+        aux[0] = make_float4(d_o[0], d_o[1], d_o[2], d_o[3]);
+        aux[1] = make_float4(dir[0], dir[1], dir[2], dir[3]);
+        aux[2] = make_float4(ev[0], ev[1], ev[2], ev[3]);
+#pragma unroll
+        for (int qq = 0; qq < 4; ++qq) d4s[qq * R + r] = d_o[qq];
+      }
+      __syncthreads();
+      {  // per-warp sums over its 32 agents of d_o[q] * a3[c] for this thread's 16 channels (D3 is still in TMEM)
+        const int c0 = cgrp * 16;
+        float v[16];
+        tmem_ld16(tlane + C_D3 + c0, v);
+        wait_ld();
+        const float dq[4] = {d4s[r], d4s[R + r], d4s[2 * R + r], d4s[3 * R + r]};
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+          const float a = fmaxf(v[e] + B3[c0 + e], 0.f);
+#pragma unroll
+          for (int qq = 0; qq < 4; ++qq) {
+            const float sw = warp_sum(dq[qq] * a);
+            if (lane == 0) part[warp * 64 + qq * 16 + e] = sw;
+          }
+        }
+      }
+      fence_before_sync();
+      __syncthreads();
+      if (threadIdx.x < 256) {
+        const int qq = threadIdx.x >> 6, c = threadIdx.x & 63, cg = c >> 4, e = c & 15;
+        acc4 += (part[(cg * 4 + 0) * 64 + qq * 16 + e] + part[(cg * 4 + 1) * 64 + qq * 16 + e]) +
+                (part[(cg * 4 + 2) * 64 + qq * 16 + e] + part[(cg * 4 + 3) * 64 + qq * 16 + e]);
+      } else if (threadIdx.x < 260) {
+        float sb = 0.f;
+        for (int rr = 0; rr < R; ++rr) sb += d4s[(threadIdx.x - 256) * R + rr];
+        acc4 += sb;
+      }
+    } else if (cgrp == 0 && valid) {
       float kk[4];
 #pragma unroll
       for (int qq = 0; qq < 4; ++qq) {
@@ -274,6 +393,11 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
     }
     __syncthreads();   // `part` is rewritten by the next tile
   }
+  if constexpr (DUMP) {
+    float* gp = slices + (size_t)blockIdx.x * MACBF_CTRL_PARAMS;
+    if (threadIdx.x < 256) gp[CT_NW4 + threadIdx.x] += acc4;          // dW4 [4][64] is contiguous
+    else if (threadIdx.x < 260) gp[CT_NB4 + threadIdx.x - 256] += acc4;
+  }
   fence_before_sync();
   __syncthreads();
   if (warp == 0) tmem_dealloc(tbase, 512);
@@ -283,11 +407,27 @@ int ctrl_node_tc(const float* states, const float* goals, const float* pool, con
                  double dt, float* u, float* s_next, cudaStream_t st) {
   const long long ntiles = (agents + cntc::R - 1) / cntc::R;
   const int grid = (int)(ntiles < NUM_SMS ? ntiles : (long long)NUM_SMS);
-  MACBF_CHECK_CUDA(cudaFuncSetAttribute(ctrl_node_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  MACBF_CHECK_CUDA(cudaFuncSetAttribute(ctrl_node_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)cntc::smem_bytes));
-  ctrl_node_tc_kernel<<<grid, cntc::THREADS, cntc::smem_bytes, st>>>(states, goals, pool, params, agents, (float)dt, u,
-                                                                    s_next, tl_skip_flag);
+  ctrl_node_tc_kernel<false><<<grid, cntc::THREADS, cntc::smem_bytes, st>>>(states, goals, pool, params, agents, (float)dt, u,
+                                                                           s_next, tl_skip_flag, nullptr, nullptr, nullptr,
+                                                                           nullptr);
   MACBF_CHECK_LAUNCH("ctrl_node_tc_kernel");
+  return 0;
+}
+
+// first kernel of the tensor-core node backward: records for tiles 0 .. ceil(agents/128) and dW4/db4 slices
+int ctrl_node_tc_dump(const float* states, const float* goals, const float* pool, const float* params, long long agents,
+                      double dt, const float* grad_u, const float* grad_s_next, unsigned char* rec, float* slices,
+                      cudaStream_t st) {
+  const long long ntiles = (agents + cntc::R - 1) / cntc::R;
+  const int grid = (int)(ntiles < NUM_SMS ? ntiles : (long long)NUM_SMS);
+  MACBF_CHECK_CUDA(cudaFuncSetAttribute(ctrl_node_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)cntc::smem_bytes));
+  ctrl_node_tc_kernel<true><<<grid, cntc::THREADS, cntc::smem_bytes, st>>>(states, goals, pool, params, agents, (float)dt,
+                                                                          nullptr, nullptr, nullptr, grad_u, grad_s_next, rec,
+                                                                          slices);
+  MACBF_CHECK_LAUNCH("ctrl_node_tc_kernel<dump>");
   return 0;
 }
 
