@@ -9,6 +9,8 @@
 //      that are not a GEMM against pool are reduced with warp shuffles (a CTA sees only a few tiles).
 //   3. wgrad_tc_kernel<3> (cbf_bwd_tc.cu)  dW3, dW2, dW1[:, :128], db3, db2 as bf16x3 GEMMs over the agents.
 // A CTA handles agents/128/148 tiles, so the phases of a tile run back to back with block barriers, as in the forward.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "tc_common.cuh"
 #include "ctrl_node_bwd_layout.cuh"
@@ -286,6 +288,11 @@ ctrl_node_dgrad_tc_kernel(const float* __restrict__ params, const float* __restr
 // ---- host side ----
 namespace {
 constexpr long long CN_CHUNK_TILES = 4096;     // 4096 x 300 KB = 1.2 GB of records at a time
+inline long long chunk_tiles() {               // MACBF_BWD_CHUNK_TILES=<n>: see cbf_bwd_tc.cu
+  const char* e = getenv("MACBF_BWD_CHUNK_TILES");
+  const long long v = e ? atoll(e) : 0;
+  return (v > 0 && v < CN_CHUNK_TILES) ? v : CN_CHUNK_TILES;
+}
 }
 size_t ctrl_node_bwd_tc_scratch_bytes(int B, int N) {
   const long long nt = ((long long)B * N + 127) / 128;
@@ -300,8 +307,9 @@ int ctrl_node_bwd_tc(const float* states, const float* goals, const float* param
   unsigned char* rec = (unsigned char*)(((uintptr_t)scratch + 1023) & ~(uintptr_t)1023);
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(ctrl_node_dgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cnbtc::smem_bytes));
   // every per-agent array is contiguous, so a chunk of tiles is just an offset into each of them
-  for (long long a0 = 0; a0 < agents; a0 += CN_CHUNK_TILES * 128) {
-    const long long na = (agents - a0 < CN_CHUNK_TILES * 128) ? agents - a0 : CN_CHUNK_TILES * 128;
+  const long long CH = chunk_tiles() * 128;
+  for (long long a0 = 0; a0 < agents; a0 += CH) {
+    const long long na = (agents - a0 < CH) ? agents - a0 : CH;
     const long long nt = (na + 127) / 128;
     const float* gu = grad_u ? grad_u + a0 * 2 : nullptr;
     const float* gsn = grad_s_next ? grad_s_next + a0 * 4 : nullptr;
