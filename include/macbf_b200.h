@@ -69,6 +69,13 @@ size_t macbf_neighbor_workspace_bytes(int B, int N, int M, int top_k);
 int macbf_neighbor_topk_ws(const float* states, const float* obstacles, int B, int N, int M,
                            int top_k, int32_t* idx, void* workspace, size_t workspace_bytes,
                            void* stream);
+/* Row-sharded graph of ONE large env over several GPUs: part `part` of `nparts` computes a contiguous
+ * share of the queries (of the cell-sorted order on the grid path, so the shares are spatially compact; of the agent
+ * index otherwise) and leaves every other row of idx untouched.  Start from a zeroed idx on every rank and sum the
+ * arrays (one all-reduce of B*N*K int32) to obtain the full graph everywhere; positions are replicated. */
+int macbf_neighbor_topk_part(const float* states, const float* obstacles, int B, int N, int M, int top_k,
+                             int part, int nparts, int32_t* idx, void* workspace, size_t workspace_bytes,
+                             void* stream);
 
 /* The reference's own call shape: core.remove_distant_agents(x[N,C,F], k) on an already
  * materialised pair tensor (core.py:234-250); keys from x[i,j,0:2].  idx [N,k] int32 (column

@@ -8,6 +8,7 @@ namespace macbf {
 static thread_local char g_err[512] = "";
 static thread_local long long g_launches = 0;
 thread_local const int* tl_skip_flag = nullptr;
+thread_local QueryPart tl_query_part = {0, 1};
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -112,6 +113,16 @@ int macbf_neighbor_topk_ws(const float* states, const float* obstacles, int B, i
   MACBF_CHECK_ARG(workspace != nullptr || macbf_neighbor_workspace_bytes(B, N, M, top_k) == 0,
                   "%s: workspace is NULL but %zu bytes are needed", fn, macbf_neighbor_workspace_bytes(B, N, M, top_k));
   return neighbor_any(states, obstacles, B, N, M, top_k, idx, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int macbf_neighbor_topk_part(const float* states, const float* obstacles, int B, int N, int M, int top_k, int part,
+                             int nparts, int32_t* idx, void* workspace, size_t workspace_bytes, void* stream) {
+  const char* fn = "macbf_neighbor_topk_part";
+  MACBF_CHECK_ARG(nparts >= 1 && part >= 0 && part < nparts, "%s: part %d of %d", fn, part, nparts);
+  tl_query_part = QueryPart{part, nparts};
+  const int rc = macbf_neighbor_topk_ws(states, obstacles, B, N, M, top_k, idx, workspace, workspace_bytes, stream);
+  tl_query_part = QueryPart{0, 1};
+  return rc;
 }
 
 int macbf_cbf_forward(const float* states, const float* obstacles, const int32_t* idx, const float* cbf_params, int B,

@@ -28,6 +28,15 @@ void set_error(const char* fmt, ...);
 // non-zero int the kernel returns at once.  macbf_rollout_forward sets it around its launches so that
 // the steps after every env has reached its goal cost (almost) nothing and no host sync is needed.
 extern thread_local const int* tl_skip_flag;
+// Query partition consulted by the neighbour-search launchers: part p of n handles a contiguous n-th of the queries
+// (of the cell-sorted order on the grid path, of the agent index otherwise) and leaves the other rows of idx
+// untouched.  macbf_neighbor_topk_part sets it around its launch (row-sharding one large env over several GPUs).
+struct QueryPart { int part, nparts; };
+extern thread_local QueryPart tl_query_part;
+inline void query_range(int total, int* begin, int* end) {
+  *begin = (int)((long long)total * tl_query_part.part / tl_query_part.nparts);
+  *end = (int)((long long)total * (tl_query_part.part + 1) / tl_query_part.nparts);
+}
 #define MACBF_SKIP_IF_SET(skip) do { if ((skip) != nullptr && *(skip) != 0) return; } while (0)
 void count_launch(int n = 1);
 #define MACBF_CHECK_ARG(cond, ...)      \

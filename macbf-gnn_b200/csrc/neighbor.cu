@@ -73,12 +73,12 @@ struct TopList {
 template <int S, int Q>
 __global__ void __launch_bounds__(KNN_THREADS)
 knn_kernel(const float* __restrict__ states, const float* __restrict__ obstacles, int N, int M, int K,
-           int32_t* __restrict__ idx_out, const int* __restrict__ skip) {
+           int32_t* __restrict__ idx_out, const int* __restrict__ skip, int q_begin, int q_end) {
   MACBF_SKIP_IF_SET(skip);
   __shared__ float2 tile[KNN_TILE];
   const int b = blockIdx.y;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int q0 = (blockIdx.x * KNN_WARPS + warp) * Q;
+  const int q0 = q_begin + (blockIdx.x * KNN_WARPS + warp) * Q;
   const int C = N + M;
 
   float qx[Q], qy[Q], vthr[Q];
@@ -130,7 +130,7 @@ knn_kernel(const float* __restrict__ states, const float* __restrict__ obstacles
 #pragma unroll
   for (int q = 0; q < Q; ++q) {
     const int i = q0 + q;
-    if (i < N) {
+    if (i < q_end) {
       int32_t* o = idx_out + ((size_t)b * N + i) * K;
 #pragma unroll
       for (int s = 0; s < S; ++s) {
@@ -199,8 +199,11 @@ __global__ void knn_all_kernel(int total, int C, int32_t* __restrict__ idx_out) 
 template <int S, int Q>
 static int launch_knn(const float* states, const float* obstacles, int B, int N, int M, int K,
                       int32_t* idx, cudaStream_t st) {
-  dim3 grid((N + KNN_WARPS * Q - 1) / (KNN_WARPS * Q), B);
-  knn_kernel<S, Q><<<grid, KNN_THREADS, 0, st>>>(states, obstacles, N, M, K, idx, tl_skip_flag);
+  int q_begin, q_end;
+  query_range(N, &q_begin, &q_end);
+  if (q_end <= q_begin) return 0;
+  dim3 grid((q_end - q_begin + KNN_WARPS * Q - 1) / (KNN_WARPS * Q), B);
+  knn_kernel<S, Q><<<grid, KNN_THREADS, 0, st>>>(states, obstacles, N, M, K, idx, tl_skip_flag, q_begin, q_end);
   MACBF_CHECK_LAUNCH("knn_kernel");
   return 0;
 }
@@ -209,7 +212,7 @@ int neighbor_topk(const float* states, const float* obstacles, int B, int N, int
                   int32_t* idx, cudaStream_t st) {
   const int C = N + M;
   if (C <= top_k) {
-    int total = B * N * C;
+    int total = B * N * C;                         // tiny problem: every part writes every row (identical values)
     knn_all_kernel<<<(total + 255) / 256, 256, 0, st>>>(total, C, idx);
     MACBF_CHECK_LAUNCH("knn_all_kernel");
     return 0;

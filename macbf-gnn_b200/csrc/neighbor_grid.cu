@@ -172,12 +172,12 @@ __device__ __forceinline__ u64 warp_merge32(u64 list, u64 fresh, int lane) {
 __global__ void __launch_bounds__(GRID_QUERY_THREADS)
 knn_grid_kernel(const float* __restrict__ states, const float4* __restrict__ sorted,
                 const int* __restrict__ cell_start, const GridHeader* __restrict__ header, int N, int C, int G,
-                int K, int32_t* __restrict__ idx_out, const int* __restrict__ skip) {
+                int K, int32_t* __restrict__ idx_out, const int* __restrict__ skip, int q_begin, int q_end) {
   MACBF_SKIP_IF_SET(skip);
   const int b = blockIdx.y;
   const int lane = threadIdx.x & 31;
-  const int i = blockIdx.x * (GRID_QUERY_THREADS / 32) + (threadIdx.x >> 5);
-  if (i >= N) return;                                  // whole warp
+  const int i = q_begin + blockIdx.x * (GRID_QUERY_THREADS / 32) + (threadIdx.x >> 5);
+  if (i >= q_end) return;                              // whole warp
   const GridHeader g = header[b];
   const int* cs = cell_start + (size_t)b * (GRID_GMAX * GRID_GMAX + 1);
   const float4* pts = sorted + (size_t)b * C;
@@ -290,7 +290,7 @@ template <int K>
 __global__ void __launch_bounds__(128)
 knn_grid_tpq_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start,
                     const GridHeader* __restrict__ header, int N, int C, int G, int32_t* __restrict__ idx_out,
-                    const int* __restrict__ skip) {
+                    const int* __restrict__ skip, int part, int nparts) {
   MACBF_SKIP_IF_SET(skip);
   const int b = blockIdx.y;
   const int p0 = blockIdx.x * blockDim.x + threadIdx.x;
@@ -303,6 +303,9 @@ knn_grid_tpq_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
   if (i >= N) return;                                  // obstacle points are candidates, not queries
   const float qx = me.x, qy = me.y;
   const int cx = cell_coord(qx, g.ox, g.inv_cs, G), cy = cell_coord(qy, g.oy, g.inv_cs, G);
+  // row sharding: a query belongs to the part that owns its CELL (by the cell's start in the sorted order) - the order
+  // of the candidates inside a cell is not reproducible between two builds of the grid, cell membership is
+  if (nparts > 1 && (int)((long long)cs[cy * G + cx] * nparts / C) != part) return;
 
   u64 list[K];
 #pragma unroll
@@ -365,7 +368,8 @@ template <int K>
 static int launch_tpq(const float4* sorted, const int* cell_start, const GridHeader* header, int B, int N, int C, int G,
                       int32_t* idx, cudaStream_t st) {
   dim3 grid((C + 127) / 128, B);
-  knn_grid_tpq_kernel<K><<<grid, 128, 0, st>>>(sorted, cell_start, header, N, C, G, idx, tl_skip_flag);
+  knn_grid_tpq_kernel<K><<<grid, 128, 0, st>>>(sorted, cell_start, header, N, C, G, idx, tl_skip_flag, tl_query_part.part,
+                                               tl_query_part.nparts);
   MACBF_CHECK_LAUNCH("knn_grid_tpq_kernel");
   return 0;
 }
@@ -418,8 +422,12 @@ int neighbor_topk_grid(const float* states, const float* obstacles, int B, int N
       default: break;
     }
   }
-  dim3 grid((N + GRID_QUERY_THREADS / 32 - 1) / (GRID_QUERY_THREADS / 32), B);
-  knn_grid_kernel<<<grid, GRID_QUERY_THREADS, 0, st>>>(states, sorted, cell_start, header, N, C, G, K, idx, tl_skip_flag);
+  int q_begin, q_end;
+  query_range(N, &q_begin, &q_end);
+  if (q_end <= q_begin) return 0;
+  dim3 grid((q_end - q_begin + GRID_QUERY_THREADS / 32 - 1) / (GRID_QUERY_THREADS / 32), B);
+  knn_grid_kernel<<<grid, GRID_QUERY_THREADS, 0, st>>>(states, sorted, cell_start, header, N, C, G, K, idx, tl_skip_flag,
+                                                       q_begin, q_end);
   MACBF_CHECK_LAUNCH("knn_grid_kernel");
   return 0;
 }

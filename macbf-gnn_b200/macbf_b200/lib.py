@@ -24,6 +24,7 @@ SIGNATURES = {
     "macbf_neighbor_topk": (I, [c_f32p, c_f32p, I, I, I, I, c_i32p, c_void]),
     "macbf_neighbor_workspace_bytes": (SZ, [I, I, I, I]),
     "macbf_neighbor_topk_ws": (I, [c_f32p, c_f32p, I, I, I, I, c_i32p, c_void, SZ, c_void]),
+    "macbf_neighbor_topk_part": (I, [c_f32p, c_f32p, I, I, I, I, I, I, c_i32p, c_void, SZ, c_void]),
     "macbf_dense_topk": (I, [c_f32p, I, I, I, I, c_i32p, c_void]),
     "macbf_cbf_forward": (I, [c_f32p, c_f32p, c_i32p, c_f32p, I, I, I, I, I, D, D, c_f32p, c_void]),
     "macbf_controller_forward": (I, [c_f32p, c_f32p, c_f32p, c_i32p, c_f32p, I, I, I, I, I, D, D, c_f32p, c_f32p,

@@ -83,6 +83,35 @@ def neighbor_topk(states: torch.Tensor, top_k: int = TOP_K, obstacles: Optional[
     return idx
 
 
+def neighbor_topk_part(states, top_k, part, nparts, obstacles=None, out=None):
+    """Rows of the neighbour graph owned by part `part` of `nparts` (macbf_neighbor_topk_part); the other rows of
+    `out` (default: zeros) are left as they are.  Summing the results of all parts gives neighbor_topk."""
+    _need_cuda(states, obstacles)
+    states, obstacles = _c(states), _c(obstacles)
+    B, N, M, obstacles = _dims(states, obstacles)
+    K = neighbor_count(N, M, top_k)
+    if out is None:
+        out = torch.zeros((B, N, K), dtype=torch.int32, device=states.device)
+    L = _lib.load()
+    nbytes = L.macbf_neighbor_workspace_bytes(B, N, M, top_k)
+    ws = torch.empty((max(nbytes, 16),), dtype=torch.uint8, device=states.device)
+    _lib.check(L.macbf_neighbor_topk_part(_p(states), _p(obstacles), B, N, M, top_k, part, nparts, _p(out), _p(ws), nbytes,
+                                          _stream()), "macbf_neighbor_topk_part")
+    return out
+
+
+def neighbor_topk_sharded(states, top_k, obstacles=None, group=None):
+    """One large env row-sharded over the ranks of `group` (positions replicated): every rank searches its share of
+    the queries, one all-reduce(sum) of the int32 index array assembles the full graph on every rank."""
+    import torch.distributed as dist
+    world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+    rank = dist.get_rank(group) if world > 1 else 0
+    idx = neighbor_topk_part(states, top_k, rank, world, obstacles)
+    if world > 1:
+        dist.all_reduce(idx, op=dist.ReduceOp.SUM, group=group)
+    return idx
+
+
 def dense_topk(x: torch.Tensor, k: int) -> torch.Tensor:
     """core.remove_distant_agents' selection on a materialised pair tensor x [N,C,F] -> idx [N,k] int32."""
     _need_cuda(x)

@@ -121,3 +121,28 @@ def test_c5_density_sweep_65536(ops, k):
     assert torch.isfinite(h).all() and torch.isfinite(u).all() and torch.isfinite(sn).all()
     frac_in_range = float((h != 0).float().mean())
     assert 0.2 < frac_in_range < 0.995                                # R holds K agents on average: most, not all, of the K nearest are inside
+
+
+@pytest.mark.parametrize("N,k,n_obs,nparts", [(65536, 12, 0, 8), (5000, 12, 2, 3), (700, 64, 0, 4), (200, 12, 0, 2), (9, 12, 0, 2)])
+def test_row_sharded_graph_parts_assemble_the_full_graph(ops, N, k, n_obs, nparts):
+    """one large env row-sharded over ranks - every part fills a disjoint set of rows and the sum of the
+    zero-initialised partial index arrays (what the all-reduce computes) is the full graph, bit for bit."""
+    import oracle.macbf_oracle as O
+    s, _ = O.synthetic_swarm(1, N, 5)
+    obs = O.synthetic_obstacles(1, N, n_obs, 0, 6).cuda() if n_obs else None
+    s = s.cuda()
+    full = ops.neighbor_topk(s, k, obs)
+    total = torch.zeros_like(full)
+    owners = torch.zeros(full.shape[:2], dtype=torch.int32, device="cuda")
+    for p in range(nparts):
+        marked = torch.full_like(full, -1)
+        ops.neighbor_topk_part(s, k, p, nparts, obs, out=marked)
+        rows = (marked >= 0).all(dim=2)
+        assert torch.equal((marked >= 0).any(dim=2), rows)            # a row is written completely or not at all
+        owners += rows.int()
+        total += ops.neighbor_topk_part(s, k, p, nparts, obs)
+    if N + (0 if obs is None else obs.shape[1]) > k:
+        assert int(owners.min()) == 1 and int(owners.max()) == 1      # disjoint cover
+        assert torch.equal(total, full)
+    else:
+        assert int(owners.min()) == nparts                            # tiny env: every part writes every row
