@@ -188,6 +188,15 @@ int macbf_controller_backward(const float* states, const float* goals, const flo
                               const float* grad_s_next, int B, int N, int M, int K,
                               double obs_radius, double dt, float* grad_params, float* grad_states,
                               float* grad_goals, void* scratch, size_t scratch_bytes, void* stream);
+/* Same, for a training step whose forward kept the pooled features and arg-max slots (macbf_step_forward_ex with
+ * MACBF_STEP_SAVE_WINNERS: pool at offset 0 and the slots at macbf_step_workspace_winners_offset() of its
+ * workspace): the edge-net recompute is skipped.  pool_saved is CONSUMED (it is overwritten by d/dpool). */
+int macbf_controller_backward_saved(const float* states, const float* goals, const float* obstacles,
+                                    const int32_t* idx, const float* ctrl_params, const float* grad_u,
+                                    const float* grad_s_next, int B, int N, int M, int K, double obs_radius,
+                                    double dt, float* pool_saved, const uint8_t* winners_saved,
+                                    float* grad_params, float* grad_states, float* grad_goals, void* scratch,
+                                    size_t scratch_bytes, void* stream);
 
 /* ---- the whole per-step path in one call (what bench.py times) ---------------------------
  * graph(S) -> u, S' -> graph(S') -> h(S), h(S') -> TTC mask -> scalars.  Workspace layout is
@@ -199,6 +208,11 @@ size_t macbf_step_workspace_bytes(int B, int N, int M, int top_k);
  * from; the reference itself recomputes, core.py:137, which stays the default): slot k of h and h' then
  * refer to the same neighbour and one of the two graph searches is saved.  idx_next receives a copy of idx. */
 #define MACBF_STEP_REUSE_INDICES 1
+/* MACBF_STEP_SAVE_WINNERS: the controller forward also stores, per (agent, pooled channel), the neighbour slot that
+ * won the max (uint8, 255 = the maximum is 0) at macbf_step_workspace_winners_offset() of the workspace, for
+ * macbf_controller_backward_saved.  Tensor-core (REPAIRED) path only. */
+#define MACBF_STEP_SAVE_WINNERS 2
+size_t macbf_step_workspace_winners_offset(int B, int N, int M, int top_k);
 int macbf_step_forward(const float* states, const float* goals, const float* obstacles,
                        const float* cbf_params, const float* ctrl_params, int B, int N, int M,
                        int top_k, int semantics, double dist_min_thres, double obs_radius, double ttc,

@@ -9,6 +9,7 @@ static thread_local char g_err[512] = "";
 static thread_local long long g_launches = 0;
 thread_local const int* tl_skip_flag = nullptr;
 thread_local QueryPart tl_query_part = {0, 1};
+thread_local uint8_t* tl_save_winners = nullptr;
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -52,9 +53,10 @@ size_t cbf_backward_scratch_bytes(int, int, int);
 int cbf_backward(const float*, const float*, const int32_t*, const float*, const float*, int, int, int, int, double,
                  double, float*, float*, void*, size_t, cudaStream_t);
 size_t controller_backward_scratch_bytes(int, int, int);
+bool controller_forward_is_tensor_core(int semantics);
 int controller_backward(const float*, const float*, const float*, const int32_t*, const float*, const float*,
                         const float*, int, int, int, int, double, double, float*, float*, float*, void*, size_t,
-                        cudaStream_t);
+                        cudaStream_t, float*, const uint8_t*);
 
 static int check_dims(const char* fn, int B, int N, int M, int K) {
   MACBF_CHECK_ARG(B >= 1 && B <= 65535, "%s: B=%d out of range [1,65535]", fn, B);
@@ -217,11 +219,34 @@ int macbf_controller_backward(const float* states, const float* goals, const flo
   MACBF_CHECK_ARG(grad_u != nullptr || grad_s_next != nullptr, "%s: no incoming gradient", fn);
   MACBF_CHECK_ARG(M == 0 || obstacles != nullptr, "%s: obstacles is NULL but M=%d", fn, M);
   return controller_backward(states, goals, obstacles, idx, ctrl_params, grad_u, grad_s_next, B, N, M, K, obs_radius,
-                             dt, grad_params, grad_states, grad_goals, scratch, scratch_bytes, (cudaStream_t)stream);
+                             dt, grad_params, grad_states, grad_goals, scratch, scratch_bytes, (cudaStream_t)stream, nullptr,
+                             nullptr);
+}
+
+int macbf_controller_backward_saved(const float* states, const float* goals, const float* obstacles, const int32_t* idx,
+                                    const float* ctrl_params, const float* grad_u, const float* grad_s_next, int B, int N,
+                                    int M, int K, double obs_radius, double dt, float* pool_saved,
+                                    const uint8_t* winners_saved, float* grad_params, float* grad_states,
+                                    float* grad_goals, void* scratch, size_t scratch_bytes, void* stream) {
+  const char* fn = "macbf_controller_backward_saved";
+  if (check_dims(fn, B, N, M, K)) return 1;
+  REQ_PTR(fn, states); REQ_PTR(fn, goals); REQ_PTR(fn, idx); REQ_PTR(fn, ctrl_params); REQ_PTR(fn, grad_params);
+  REQ_PTR(fn, scratch); REQ_PTR(fn, pool_saved); REQ_PTR(fn, winners_saved); REQ_A16(fn, states); REQ_A16(fn, pool_saved);
+  REQ_A16(fn, winners_saved);
+  MACBF_CHECK_ARG(grad_u != nullptr || grad_s_next != nullptr, "%s: no incoming gradient", fn);
+  MACBF_CHECK_ARG(M == 0 || obstacles != nullptr, "%s: obstacles is NULL but M=%d", fn, M);
+  return controller_backward(states, goals, obstacles, idx, ctrl_params, grad_u, grad_s_next, B, N, M, K, obs_radius,
+                             dt, grad_params, grad_states, grad_goals, scratch, scratch_bytes, (cudaStream_t)stream,
+                             pool_saved, winners_saved);
 }
 
 // workspace: [pool (B*N*128 f32)] [loss scratch] [neighbour-grid scratch]
 size_t macbf_step_workspace_bytes(int B, int N, int M, int top_k) {
+  const int K = macbf_neighbor_count(N, M, top_k);
+  return macbf_step_workspace_winners_offset(B, N, M, top_k) + align256((size_t)B * N * MACBF_POOL_DIM);
+}
+
+size_t macbf_step_workspace_winners_offset(int B, int N, int M, int top_k) {
   const int K = macbf_neighbor_count(N, M, top_k);
   return align256((size_t)B * N * MACBF_POOL_DIM * sizeof(float)) + align256(loss_scratch_bytes(B, N, K)) +
          align256(macbf_neighbor_workspace_bytes(B, N, M, top_k));
@@ -243,7 +268,7 @@ int macbf_step_forward_ex(const float* states, const float* goals, const float* 
                           int32_t* idx_next, float* u, float* s_next, float* h, float* h_next, uint8_t* ttc_mask_out,
                           float* scalars, void* workspace, size_t workspace_bytes, void* stream) {
   const char* fn = "macbf_step_forward";
-  MACBF_CHECK_ARG((flags & ~MACBF_STEP_REUSE_INDICES) == 0, "%s: unknown flags 0x%x", fn, flags);
+  MACBF_CHECK_ARG((flags & ~(MACBF_STEP_REUSE_INDICES | MACBF_STEP_SAVE_WINNERS)) == 0, "%s: unknown flags 0x%x", fn, flags);
   MACBF_CHECK_ARG(top_k >= 1 && top_k <= MACBF_MAX_K, "%s: top_k=%d out of range [1,%d]", fn, top_k, MACBF_MAX_K);
   const int K = macbf_neighbor_count(N, M, top_k);
   if (check_dims(fn, B, N, M, K)) return 1;
@@ -261,8 +286,13 @@ int macbf_step_forward_ex(const float* states, const float* goals, const float* 
   void* gscratch = gbytes ? (char*)lscratch + align256(loss_scratch_bytes(B, N, K)) : nullptr;
   int rc;
   if ((rc = neighbor_any(states, obstacles, B, N, M, top_k, idx, gscratch, gbytes, st))) return rc;
-  if ((rc = controller_forward(states, goals, obstacles, idx, ctrl_params, B, N, M, K, semantics, obs_radius, dt, pool,
-                               u, s_next, st))) return rc;
+  MACBF_CHECK_ARG(!(flags & MACBF_STEP_SAVE_WINNERS) || controller_forward_is_tensor_core(semantics),
+                  "%s: MACBF_STEP_SAVE_WINNERS needs the tensor-core controller (REPAIRED semantics, MACBF_CTRL_FFMA unset)", fn);
+  if (flags & MACBF_STEP_SAVE_WINNERS)
+    tl_save_winners = (uint8_t*)workspace + macbf_step_workspace_winners_offset(B, N, M, top_k);
+  rc = controller_forward(states, goals, obstacles, idx, ctrl_params, B, N, M, K, semantics, obs_radius, dt, pool, u, s_next, st);
+  tl_save_winners = nullptr;
+  if (rc) return rc;
   if (flags & MACBF_STEP_REUSE_INDICES) {   // h' on S's graph (the upstream `indices=` argument the reference dropped)
     MACBF_CHECK_CUDA(cudaMemcpyAsync(idx_next, idx, (size_t)B * N * K * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
   } else if ((rc = neighbor_any(s_next, obstacles, B, N, M, top_k, idx_next, gscratch, gbytes, st))) {   // core.py:137

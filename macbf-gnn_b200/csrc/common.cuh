@@ -31,6 +31,9 @@ extern thread_local const int* tl_skip_flag;
 // Query partition consulted by the neighbour-search launchers: part p of n handles a contiguous n-th of the queries
 // (of the cell-sorted order on the grid path, of the agent index otherwise) and leaves the other rows of idx
 // untouched.  macbf_neighbor_topk_part sets it around its launch (row-sharding one large env over several GPUs).
+// When set, the tensor-core controller forward also records the arg-max slot of every (agent, channel) there
+// (macbf_step_forward_ex with MACBF_STEP_SAVE_WINNERS: the training forward keeps what the backward needs).
+extern thread_local uint8_t* tl_save_winners;
 struct QueryPart { int part, nparts; };
 extern thread_local QueryPart tl_query_part;
 inline void query_range(int total, int* begin, int* end) {

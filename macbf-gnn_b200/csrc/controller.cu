@@ -234,6 +234,8 @@ static bool ctrl_force_ffma() {
   return v;
 }
 
+bool controller_forward_is_tensor_core(int semantics) { return semantics == MACBF_REPAIRED && !ctrl_force_ffma(); }
+
 // edge kernel only (REPAIRED): rebuilds the pooled features for the backward pass
 int controller_forward_pool_only(const float* states, const float* obstacles, const int32_t* idx,
                                  const float* params, int B, int N, int M, int K, double obs_radius, float* pool,
@@ -256,7 +258,7 @@ int controller_forward(const float* states, const float* goals, const float* obs
                        double dt, float* pool, float* u, float* s_next, cudaStream_t st) {
   const long long agents = (long long)B * N;
   if (semantics == MACBF_REPAIRED && !ctrl_force_ffma()) {
-    int rc = ctrl_edge_tc(states, obstacles, idx, params, B, N, M, K, obs_radius, pool, st);
+    int rc = ctrl_edge_tc(states, obstacles, idx, params, B, N, M, K, obs_radius, pool, st, tl_save_winners);
     if (rc) return rc;
   } else {
     const int TA = max(1, ce_smem::R / K);

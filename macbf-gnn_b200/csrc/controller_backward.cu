@@ -355,7 +355,7 @@ int ctrl_edge_bwd_tc_slices();
 size_t ctrl_edge_bwd_tc_scratch_bytes(int B, int N, int K);
 uint8_t* ctrl_edge_bwd_tc_argk(void* scratch);
 int ctrl_edge_bwd_tc(const float*, const float*, const int32_t*, const float*, const float*, int, int, int, int, float*,
-                     float*, void*, cudaStream_t);
+                     float*, void*, cudaStream_t, const uint8_t*);
 int ctrl_edge_tc(const float* states, const float* obstacles, const int32_t* idx, const float* params, int B, int N,
                  int M, int K, double obs_radius, float* pool, cudaStream_t st, uint8_t* argk);
 size_t ctrl_node_bwd_tc_scratch_bytes(int B, int N);
@@ -379,18 +379,24 @@ size_t controller_backward_scratch_bytes(int B, int N, int K) {
 int controller_backward(const float* states, const float* goals, const float* obstacles, const int32_t* idx,
                         const float* params, const float* grad_u, const float* grad_s_next, int B, int N, int M,
                         int K, double obs_radius, double dt, float* grad_params, float* grad_states,
-                        float* grad_goals, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+                        float* grad_goals, void* scratch, size_t scratch_bytes, cudaStream_t st, float* pool_saved,
+                        const uint8_t* argk_saved) {
   const long long agents = (long long)B * N;
   MACBF_CHECK_ARG(agents < (1ll << 31), "controller_backward: B*N must be < 2^31");
   const size_t need = controller_backward_scratch_bytes(B, N, K);
   MACBF_CHECK_ARG(scratch_bytes >= need, "controller_backward: scratch too small (%zu < %zu)", scratch_bytes, need);
-  float* pool = (float*)scratch;
+  // pooled features and arg-max slots kept by the training forward (macbf_step_forward_ex with
+  // MACBF_STEP_SAVE_WINNERS) make the edge-net recompute unnecessary; pool_saved is consumed (becomes d/dpool)
+  const bool saved = pool_saved != nullptr && argk_saved != nullptr && ctrl_edge_bwd_tc_applicable(K) && !ctrl_bwd_force_ffma();
+  float* pool = saved ? pool_saved : (float*)scratch;
   float* partial = (float*)((char*)scratch + a256((size_t)B * N * MACBF_POOL_DIM * sizeof(float)));
   MACBF_CHECK_CUDA(cudaMemsetAsync(partial, 0, (size_t)CTRL_SLICES * MACBF_CTRL_PARAMS * sizeof(float), st));
   const bool edge_tc = ctrl_edge_bwd_tc_applicable(K) && !ctrl_bwd_force_ffma();
   void* edge_scratch = (char*)partial + a256((size_t)CTRL_SLICES * MACBF_CTRL_PARAMS * sizeof(float));
-  int rc = edge_tc ? ctrl_edge_tc(states, obstacles, idx, params, B, N, M, K, obs_radius, pool, st, ctrl_edge_bwd_tc_argk(edge_scratch))
-                   : controller_forward_pool_only(states, obstacles, idx, params, B, N, M, K, obs_radius, pool, st);
+  int rc = 0;
+  if (!saved)
+    rc = edge_tc ? ctrl_edge_tc(states, obstacles, idx, params, B, N, M, K, obs_radius, pool, st, ctrl_edge_bwd_tc_argk(edge_scratch))
+                 : controller_forward_pool_only(states, obstacles, idx, params, B, N, M, K, obs_radius, pool, st);
   if (rc) return rc;
   if (!ctrl_bwd_force_ffma()) {
     // the node records live where the edge backward's winners / records go afterwards - except the winners, which the
@@ -408,7 +414,8 @@ int controller_backward(const float* states, const float* goals, const float* ob
     MACBF_CHECK_LAUNCH("ctrl_node_backward_kernel");
   }
   if (edge_tc) {
-    rc = ctrl_edge_bwd_tc(states, obstacles, idx, params, pool, B, N, M, K, partial, grad_states, edge_scratch, st);
+    rc = ctrl_edge_bwd_tc(states, obstacles, idx, params, pool, B, N, M, K, partial, grad_states, edge_scratch, st,
+                          saved ? argk_saved : nullptr);
     if (rc) return rc;
   } else {
     const int TA = max(1, ceb_smem::R / K);

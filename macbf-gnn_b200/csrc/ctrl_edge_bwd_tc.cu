@@ -287,12 +287,14 @@ uint8_t* ctrl_edge_bwd_tc_argk(void* scratch) { return (uint8_t*)(((uintptr_t)sc
 
 // dpool: d/dpool [B*N,128]; argk: winners from ctrl_edge_tc; slices: CE_GRID gradient slices (already zeroed)
 int ctrl_edge_bwd_tc(const float* states, const float* obstacles, const int32_t* idx, const float* params, const float* dpool,
-                     int B, int N, int M, int K, float* slices, float* grad_states, void* scratch, cudaStream_t st) {
+                     int B, int N, int M, int K, float* slices, float* grad_states, void* scratch, cudaStream_t st,
+                     const uint8_t* argk_saved) {
   const long long agents = (long long)B * N;
   const int TA = max(1, 128 / K);
   const long long nt = (agents + TA - 1) / TA;
-  const uint8_t* argk = ctrl_edge_bwd_tc_argk(scratch);
-  unsigned char* rec = (unsigned char*)argk + a1k((size_t)agents * 128);
+  const uint8_t* argk_own = ctrl_edge_bwd_tc_argk(scratch);
+  unsigned char* rec = (unsigned char*)argk_own + a1k((size_t)agents * 128);
+  const uint8_t* argk = argk_saved ? argk_saved : argk_own;      // winners kept by the training forward, or recomputed
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(ctrl_edge_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cebtc::smem_bytes));
   const long long CH = chunk_tiles();
   for (long long t0 = 0; t0 < nt; t0 += CH) {

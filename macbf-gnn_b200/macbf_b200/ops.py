@@ -253,6 +253,7 @@ def controller_backward(states, goals, idx, ctrl_params, grad_u, grad_s_next=Non
 
 
 STEP_REUSE_INDICES = 1   # include/macbf_b200.h: MACBF_STEP_REUSE_INDICES
+STEP_SAVE_WINNERS = 2    # MACBF_STEP_SAVE_WINNERS
 
 
 class StepBuffers:
@@ -275,11 +276,12 @@ class StepBuffers:
         self.h_next = torch.empty((B, N, K), dtype=f32, device=dev)
         self.ttc_mask = torch.empty((B, N, K), dtype=torch.uint8, device=dev)
         self.workspace = torch.empty((L.macbf_step_workspace_bytes(B, N, M, top_k),), dtype=torch.uint8, device=dev)
+        self.winners_offset = L.macbf_step_workspace_winners_offset(B, N, M, top_k)   # valid after save_winners=True
 
 
 def step_forward(states, goals, cbf_params, ctrl_params, buf: StepBuffers, obstacles=None, semantics=REPAIRED,
                  dist_min_thres=DIST_MIN_THRES, obs_radius=OBS_RADIUS, ttc=TIME_TO_COLLISION, dt=TIME_STEP,
-                 alpha=ALPHA_CBF, reuse_indices=False):
+                 alpha=ALPHA_CBF, reuse_indices=False, save_winners=False):
     """The whole per-step path (graph -> u, S' -> graph' -> h, h' -> TTC mask -> scalars) in one C call.
     reuse_indices=True evaluates h' on S's neighbour sets (MACBF_STEP_REUSE_INDICES; not the reference's default)."""
     _need_cuda(states, goals, cbf_params, ctrl_params, obstacles)
@@ -289,7 +291,8 @@ def step_forward(states, goals, cbf_params, ctrl_params, buf: StepBuffers, obsta
     L = _lib.load()
     _lib.check(L.macbf_step_forward_ex(_p(states), _p(goals), _p(obstacles), _p(cbf_params), _p(ctrl_params), B, N, M,
                                        buf.top_k, semantics, dist_min_thres, obs_radius, ttc, dt, alpha,
-                                       STEP_REUSE_INDICES if reuse_indices else 0, _p(buf.idx), _p(buf.idx_next),
+                                       (STEP_REUSE_INDICES if reuse_indices else 0) | (STEP_SAVE_WINNERS if save_winners else 0),
+                                       _p(buf.idx), _p(buf.idx_next),
                                        _p(buf.u), _p(buf.s_next), _p(buf.h), _p(buf.h_next), _p(buf.ttc_mask),
                                        _p(buf.scalars), _p(buf.workspace), buf.workspace.numel(), _stream()),
                "macbf_step_forward")

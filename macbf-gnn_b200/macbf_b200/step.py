@@ -54,7 +54,8 @@ class TrainStep:
         L = _lib.load()
         b = self.buf
         B, N, M, K = self.B, self.N, self.M, b.K
-        ops.step_forward(states, goals, cbf_params, ctrl_params, b, obstacles, reuse_indices=reuse_indices)
+        ops.step_forward(states, goals, cbf_params, ctrl_params, b, obstacles, reuse_indices=reuse_indices,
+                         save_winners=True)   # the controller backward below reuses pool and the max-pool winners
         st = torch.cuda.current_stream().cuda_stream
         p = ops._p
         obs = obstacles if (obstacles is not None and M > 0) else None
@@ -72,10 +73,12 @@ class TrainStep:
                                         ops.DIST_MIN_THRES, ops.OBS_RADIUS, p(self.grad_cbf), None,
                                         p(self.scratch), self.scratch.numel(), st), "macbf_cbf_backward(S)")
         # controller: d/du from the action loss, plus dt * d/dS'[v] through the Euler step
-        _lib.check(L.macbf_controller_backward(p(states), p(goals), p(obs), p(b.idx), p(ctrl_params), p(self.gu),
-                                               p(self.gs_next), B, N, M, K, ops.OBS_RADIUS, ops.TIME_STEP,
-                                               p(self.grad_ctrl), None, None, p(self.scratch), self.scratch.numel(),
-                                               st), "macbf_controller_backward")
+        ws = b.workspace.data_ptr()
+        _lib.check(L.macbf_controller_backward_saved(p(states), p(goals), p(obs), p(b.idx), p(ctrl_params), p(self.gu),
+                                                     p(self.gs_next), B, N, M, K, ops.OBS_RADIUS, ops.TIME_STEP, ws,
+                                                     ws + b.winners_offset, p(self.grad_ctrl), None, None,
+                                                     p(self.scratch), self.scratch.numel(), st),
+                   "macbf_controller_backward_saved")
         if all_reduce:
             sync_gradients(self.grad, self.world_size, self.group)
         return b.scalars, self.grad

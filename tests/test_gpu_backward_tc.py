@@ -87,3 +87,31 @@ def test_backward_is_run_to_run_deterministic_for_parameters(ops):
     a = _run(ops, *args)
     b = _run(ops, *args)
     assert torch.equal(a[0], b[0]) and torch.equal(a[2], b[2])   # parameter gradients: fixed reduction order
+
+
+def test_saved_pool_and_winners_give_the_same_gradients_as_the_recompute(ops):
+    """macbf_step_forward_ex(MACBF_STEP_SAVE_WINNERS) + macbf_controller_backward_saved skip the edge-net recompute:
+    the gradients must be bit-identical to macbf_controller_backward (same kernels, same inputs)."""
+    from macbf_b200 import lib
+    import oracle.macbf_oracle as O
+    B, N, K = 3, 333, 12
+    s, g, obs, idx, cf, tf, gh, gu, gs = _case(ops, B, N, K, 2, 4)
+    M = obs.shape[1]
+    buf = ops.StepBuffers(B, N, M, K, "cuda")
+    ops.step_forward(s, g, cf, tf, buf, obs, save_winners=True)
+    assert torch.equal(buf.idx, idx)
+    want, want_s, want_g = ops.controller_backward(s, g, idx, tf, gu, gs, obstacles=obs, want_grad_states=True, want_grad_goals=True)
+    L = lib.load()
+    grad = torch.zeros_like(want); gst = torch.zeros_like(want_s); gg = torch.zeros_like(want_g)
+    nb = L.macbf_controller_backward_scratch_bytes(B, N, K)
+    scratch = torch.empty((nb,), dtype=torch.uint8, device="cuda")
+    ws = buf.workspace.data_ptr()
+    lib.check(L.macbf_controller_backward_saved(s.data_ptr(), g.data_ptr(), obs.data_ptr(), idx.data_ptr(), tf.data_ptr(),
+                                                gu.data_ptr(), gs.data_ptr(), B, N, M, K, ops.OBS_RADIUS, ops.TIME_STEP, ws,
+                                                ws + buf.winners_offset, grad.data_ptr(), gst.data_ptr(), gg.data_ptr(),
+                                                scratch.data_ptr(), nb, None), "macbf_controller_backward_saved")
+    torch.cuda.synchronize()
+    assert torch.equal(grad, want)
+    assert torch.equal(gg, want_g)
+    assert _rel(gst, want_s) < 1e-6          # d/dstates goes through fp32 atomics (order varies)
+    assert float(grad.abs().max()) > 0
