@@ -149,7 +149,17 @@ def run_reference(args):
 
 
 def workload_config(args, envs_timed=None):
-    return {"workload": f"BASELINE configs[1]: {args.agents} agents x {args.envs} envs per GPU, top-k {args.top_k}, "
+    if (args.agents, args.envs, args.top_k, args.obstacles) == (1024, 64, 12, 0):
+        tag = "BASELINE configs[1]"
+    elif args.agents == 4096 and args.envs == 1 and args.obstacles > 0:
+        tag = "BASELINE configs[2]"
+    elif args.agents == 16384:
+        tag = "BASELINE configs[3] (per-GPU share of the 256 envs)"
+    elif args.agents == 65536 and args.envs == 1:
+        tag = "BASELINE configs[4] (one point of the density sweep)"
+    else:
+        tag = "custom"
+    return {"workload": f"{tag}: {args.agents} agents x {args.envs} envs per GPU, top-k {args.top_k}, "
                         f"{args.obstacles} obstacle points, {args.mode} step "
                         "(graph+controller+Euler+graph'+CBF(S)+CBF(S')+TTC+losses)",
             "agents": args.agents, "envs_per_gpu": args.envs, "top_k": args.top_k, "obstacles": args.obstacles,
