@@ -29,7 +29,7 @@ size_t neighbor_grid_workspace_bytes(int, int, int);
 bool neighbor_grid_applicable(int, int, int);
 int neighbor_topk_grid(const float*, const float*, int, int, int, int, int32_t*, void*, size_t, cudaStream_t);
 
-// grid search when it applies (K <= 32, enough candidates) and workspace was given, else brute force
+// grid search when it applies (K <= 128, enough candidates) and workspace was given, else brute force
 static int neighbor_any(const float* states, const float* obstacles, int B, int N, int M, int top_k, int32_t* idx,
                         void* ws, size_t ws_bytes, cudaStream_t st) {
   if (ws != nullptr && neighbor_grid_applicable(N, M, top_k))

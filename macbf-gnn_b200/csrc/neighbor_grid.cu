@@ -1,4 +1,4 @@
-// K1 (grid path) - exact K nearest candidates through a uniform grid (K <= 32).
+// K1 (grid path) - exact K nearest candidates through a uniform grid (K <= 128).
 //
 // Same contract as neighbor.cu (core.py:234-250; lexicographic (key, index) order, keys computed
 // with the reference's op sequence), but a query only looks at the candidates of the grid cells
@@ -169,6 +169,10 @@ __device__ __forceinline__ u64 warp_merge32(u64 list, u64 fresh, int lane) {
   return y;
 }
 
+// S = ceil(K / 32) entries of the sorted best list per lane: entry e lives in lane e % 32, slot e / 32 (S = 1: K <= 32,
+// with the bitonic merge for dense batches; S = 2, 4: K <= 64, 128 - the dense-neighbourhood end of the C5 sweep, where
+// the brute-force search costs O(N^2)).
+template <int S>
 __global__ void __launch_bounds__(GRID_QUERY_THREADS)
 knn_grid_kernel(const float* __restrict__ states, const float4* __restrict__ sorted,
                 const int* __restrict__ cell_start, const GridHeader* __restrict__ header, int N, int C, int G,
@@ -185,8 +189,18 @@ knn_grid_kernel(const float* __restrict__ states, const float4* __restrict__ sor
   const float qx = sq.x, qy = sq.y;
   const int cx = cell_coord(qx, g.ox, g.inv_cs, G), cy = cell_coord(qy, g.oy, g.inv_cs, G);
 
-  u64 list = ENTRY_INF;                                // entry e of the sorted best list lives in lane e
+  u64 list[S];                                         // entry e of the sorted best list: lane e % 32, slot e / 32
+#pragma unroll
+  for (int sl = 0; sl < S; ++sl) list[sl] = ENTRY_INF;
   float vthr = __int_as_float(0x7f800000);             // a candidate with v >= vthr cannot enter the list
+  const int kslot = (K - 1) >> 5, klane = (K - 1) & 31;
+  auto kth_entry = [&]() -> u64 {
+    u64 v = list[0];
+#pragma unroll
+    for (int sl = 1; sl < S; ++sl)
+      if (kslot == sl) v = list[sl];
+    return shfl64(v, klane);
+  };
 
   for (int r = 0; r < G; ++r) {
     // ---- the cell ranges of ring r, one per lane (chunks of 32 ranges) ----
@@ -243,31 +257,40 @@ knn_grid_kernel(const float* __restrict__ states, const float4* __restrict__ sor
         const unsigned pass = __ballot_sync(0xffffffffu, passf);
         if (pass == 0u) continue;
         const u64 cand = passf ? (((u64)__float_as_uint(__fsqrt_rn(v)) << 32) | (unsigned)cid) : ENTRY_INF;
-        if (__popc(pass) >= 6) {
-          list = warp_merge32(list, warp_sort32(cand, lane), lane);
+        if (S == 1 && __popc(pass) >= 6) {
+          list[0] = warp_merge32(list[0], warp_sort32(cand, lane), lane);
         } else {
           unsigned rem = pass;
           while (rem) {
             const int src = __ffs(rem) - 1;
             rem &= rem - 1;
             const u64 c = shfl64(cand, src);
-            const u64 kth = shfl64(list, K - 1);
-            if (c < kth) {                              // exact lexicographic test (key, index)
-              const int pos = __popc(__ballot_sync(0xffffffffu, list < c));
-              const u64 up = shfl64_up(list, 1);
-              if (lane > pos) list = up;
-              else if (lane == pos) list = c;
+            if (c < kth_entry()) {                      // exact lexicographic test (key, index)
+              int pos = 0;
+#pragma unroll
+              for (int sl = 0; sl < S; ++sl) pos += __popc(__ballot_sync(0xffffffffu, list[sl] < c));
+#pragma unroll
+              for (int sl = S - 1; sl >= 0; --sl) {
+                u64 up = shfl64_up(list[sl], 1);
+                if (sl > 0) {
+                  const u64 wrap = shfl64(list[sl - 1], 31);
+                  if (lane == 0) up = wrap;
+                }
+                const int e = sl * 32 + lane;
+                if (e > pos) list[sl] = up;
+                else if (e == pos) list[sl] = c;
+              }
             }
           }
         }
         // v >= RU(next(key_K)^2)  =>  sqrt_rn(v) > key_K: such a candidate can never enter
-        const float kK = __uint_as_float((unsigned)(shfl64(list, K - 1) >> 32));
+        const float kK = __uint_as_float((unsigned)(kth_entry() >> 32));
         const float kn = __uint_as_float(__float_as_uint(kK) + 1u);
         vthr = (kK < __int_as_float(0x7f800000)) ? __fmul_ru(kn, kn) : kK;
       }
     }
     // ---- stop test: everything not yet visited lies outside the square of rings 0..r ----
-    const float kK = __uint_as_float((unsigned)(shfl64(list, K - 1) >> 32));
+    const float kK = __uint_as_float((unsigned)(kth_entry() >> 32));
     float bound = __int_as_float(0x7f800000);
     if (cx - r > 0) bound = fminf(bound, qx - (g.ox + (float)(cx - r) * g.cs));
     if (cx + r < G - 1) bound = fminf(bound, (g.ox + (float)(cx + r + 1) * g.cs) - qx);
@@ -277,7 +300,9 @@ knn_grid_kernel(const float* __restrict__ states, const float4* __restrict__ sor
     // margin: cell assignment and the edge coordinates carry a few ulp of the coordinate range
     if (kK < bound * 0.9999f - 1e-5f * g.cs) break;
   }
-  if (lane < K) idx_out[((size_t)b * N + i) * K + lane] = (int32_t)(unsigned)list;
+#pragma unroll
+  for (int sl = 0; sl < S; ++sl)
+    if (sl * 32 + lane < K) idx_out[((size_t)b * N + i) * K + sl * 32 + lane] = (int32_t)(unsigned)list[sl];
 }
 
 // ---- one THREAD per query (K a compile-time constant) ------------------------------------------
@@ -383,7 +408,7 @@ size_t neighbor_grid_workspace_bytes(int B, int N, int M) {
 // true when the grid path applies (the caller falls back to the brute-force kernel otherwise)
 bool neighbor_grid_applicable(int N, int M, int top_k) {
   const int C = N + M;
-  return top_k <= 32 && C > top_k && C >= 256;
+  return top_k <= 128 && C > top_k && C >= 256;
 }
 
 int neighbor_topk_grid(const float* states, const float* obstacles, int B, int N, int M, int K, int32_t* idx,
@@ -426,8 +451,15 @@ int neighbor_topk_grid(const float* states, const float* obstacles, int B, int N
   query_range(N, &q_begin, &q_end);
   if (q_end <= q_begin) return 0;
   dim3 grid((q_end - q_begin + GRID_QUERY_THREADS / 32 - 1) / (GRID_QUERY_THREADS / 32), B);
-  knn_grid_kernel<<<grid, GRID_QUERY_THREADS, 0, st>>>(states, sorted, cell_start, header, N, C, G, K, idx, tl_skip_flag,
-                                                       q_begin, q_end);
+  if (K <= 32)
+    knn_grid_kernel<1><<<grid, GRID_QUERY_THREADS, 0, st>>>(states, sorted, cell_start, header, N, C, G, K, idx, tl_skip_flag,
+                                                            q_begin, q_end);
+  else if (K <= 64)
+    knn_grid_kernel<2><<<grid, GRID_QUERY_THREADS, 0, st>>>(states, sorted, cell_start, header, N, C, G, K, idx, tl_skip_flag,
+                                                            q_begin, q_end);
+  else
+    knn_grid_kernel<4><<<grid, GRID_QUERY_THREADS, 0, st>>>(states, sorted, cell_start, header, N, C, G, K, idx, tl_skip_flag,
+                                                            q_begin, q_end);
   MACBF_CHECK_LAUNCH("knn_grid_kernel");
   return 0;
 }

@@ -214,7 +214,7 @@ def _grid_vs_brute(ops, s, k, obs=None):
     return a
 
 
-@pytest.mark.parametrize("k", [1, 5, 12, 16, 32])
+@pytest.mark.parametrize("k", [1, 5, 12, 16, 32, 33, 40, 64, 100, 128])
 def test_grid_search_equals_brute_force_uniform(ops, k):
     from oracle import macbf_oracle as O
     s, _ = O.synthetic_swarm(3, 2000, seed=300 + k)
@@ -250,6 +250,10 @@ def test_grid_search_adversarial_layouts(ops):
     same = torch.zeros(1, 400, 4)                                    # every agent at the same point
     idx = _grid_vs_brute(ops, same, 12)
     assert np.array_equal(idx[0, :, :].cpu().numpy(), np.tile(np.arange(12), (400, 1)))
+    # the multi-slot lists of the dense-neighbourhood kernels (K = 64, 128) on the same layouts
+    for name, s in (("clustered", clustered), ("line", line), ("duplicates", dup), ("outliers", outl), ("same", same)):
+        for k in (64, 128):
+            _grid_vs_brute(ops, s, k)
 
 
 def test_remove_distant_agents_dense_api(ops):
