@@ -107,10 +107,13 @@ __global__ void loss_final_kernel(const float* __restrict__ partial, int nchunks
                                   int has_next, int has_u, float* __restrict__ scalars) {
   const int b = blockIdx.x;
   __shared__ double acc[LOSS_NACC];
-  if (threadIdx.x < LOSS_NACC) {
+  {  // warp q sums accumulator q: lanes stride over the chunks, then a fixed shuffle tree (deterministic)
+    const int q = threadIdx.x >> 5, lane = threadIdx.x & 31;
     double v = 0.0;
-    for (int c = 0; c < nchunks; ++c) v += (double)partial[((size_t)b * nchunks + c) * LOSS_NACC + threadIdx.x];
-    acc[threadIdx.x] = v;
+    for (int c = lane; c < nchunks; c += 32) v += (double)partial[((size_t)b * nchunks + c) * LOSS_NACC + q];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) acc[q] = v;
   }
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -217,7 +220,7 @@ int loss_forward(const float* states, const float* goals, const float* obstacles
                                                     (goals != nullptr) ? u : nullptr, N, M, K, r2, (float)ttc,
                                                     dt_alpha, mask, (float*)scratch);
   MACBF_CHECK_LAUNCH("loss_partial_kernel");
-  loss_final_kernel<<<B, 32, 0, st>>>((const float*)scratch, nchunks, N, K, h_next != nullptr,
+  loss_final_kernel<<<B, 32 * LOSS_NACC, 0, st>>>((const float*)scratch, nchunks, N, K, h_next != nullptr,
                                       (u != nullptr && goals != nullptr), scalars);
   MACBF_CHECK_LAUNCH("loss_final_kernel");
   return 0;

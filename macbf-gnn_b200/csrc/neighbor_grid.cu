@@ -23,7 +23,7 @@
 
 namespace macbf {
 
-constexpr int GRID_GMAX = 64;                 // cells per axis (shared-memory histogram of G*G ints)
+constexpr int GRID_GMAX = 160;                // cells per axis (dynamic shared-memory histogram of G*G + 1 ints <= 100 KB)
 constexpr int GRID_BUILD_THREADS = 1024;
 constexpr int GRID_QUERY_THREADS = 256;
 
@@ -41,8 +41,7 @@ grid_build_kernel(const float* __restrict__ states, const float* __restrict__ ob
                   float4* __restrict__ sorted, int* __restrict__ cell_start, GridHeader* __restrict__ header,
                   const int* __restrict__ skip) {
   MACBF_SKIP_IF_SET(skip);
-  __shared__ int cnt[GRID_GMAX * GRID_GMAX + 1];
-  __shared__ int cur[GRID_GMAX * GRID_GMAX];
+  extern __shared__ int cnt[];                  // G*G + 1: histogram -> cell starts -> scatter cursors
   __shared__ float red[4][32];
   __shared__ int wsum[32];
   __shared__ GridHeader hd;
@@ -50,10 +49,18 @@ grid_build_kernel(const float* __restrict__ states, const float* __restrict__ ob
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   // ---- bounding box ----
   float xmin = 3.0e38f, ymin = 3.0e38f, xmax = -3.0e38f, ymax = -3.0e38f;
-  for (int t = threadIdx.x; t < C; t += GRID_BUILD_THREADS) {
-    const float4 s = load_candidate(states, obstacles, b, t, N, M);
-    xmin = fminf(xmin, s.x); xmax = fmaxf(xmax, s.x);
-    ymin = fminf(ymin, s.y); ymax = fmaxf(ymax, s.y);
+  for (int t0 = threadIdx.x; t0 < C; t0 += 4 * GRID_BUILD_THREADS) {
+    float4 sv[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int t = t0 + u * GRID_BUILD_THREADS;
+      sv[u] = load_candidate(states, obstacles, b, t < C ? t : t0, N, M);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      xmin = fminf(xmin, sv[u].x); xmax = fmaxf(xmax, sv[u].x);
+      ymin = fminf(ymin, sv[u].y); ymax = fmaxf(ymax, sv[u].y);
+    }
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
@@ -79,10 +86,17 @@ grid_build_kernel(const float* __restrict__ states, const float* __restrict__ ob
   __syncthreads();
   const GridHeader g = hd;
   // ---- histogram ----
-  for (int t = threadIdx.x; t < C; t += GRID_BUILD_THREADS) {
-    const float4 s = load_candidate(states, obstacles, b, t, N, M);
-    const int cell = cell_coord(s.y, g.oy, g.inv_cs, G) * G + cell_coord(s.x, g.ox, g.inv_cs, G);
-    atomicAdd(&cnt[cell], 1);
+  for (int t0 = threadIdx.x; t0 < C; t0 += 4 * GRID_BUILD_THREADS) {
+    float4 sv[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int t = t0 + u * GRID_BUILD_THREADS;
+      sv[u] = load_candidate(states, obstacles, b, t < C ? t : t0, N, M);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (t0 + u * GRID_BUILD_THREADS < C)
+        atomicAdd(&cnt[cell_coord(sv[u].y, g.oy, g.inv_cs, G) * G + cell_coord(sv[u].x, g.ox, g.inv_cs, G)], 1);
   }
   __syncthreads();
   // ---- exclusive scan of cnt[0..cells) (each thread owns a contiguous chunk) ----
@@ -112,18 +126,30 @@ grid_build_kernel(const float* __restrict__ states, const float* __restrict__ ob
   for (int c = c_begin; c < c_end; ++c) {
     const int n = cnt[c];
     cnt[c] = run;
-    cur[c] = run;
     run += n;
   }
   if (threadIdx.x == GRID_BUILD_THREADS - 1) cnt[cells] = C;
   __syncthreads();
   for (int t = threadIdx.x; t <= cells; t += GRID_BUILD_THREADS) cell_start[(size_t)b * (GRID_GMAX * GRID_GMAX + 1) + t] = cnt[t];
-  // ---- scatter (order inside a cell is arbitrary: the query orders by (key, index) explicitly) ----
-  for (int t = threadIdx.x; t < C; t += GRID_BUILD_THREADS) {
-    const float4 s = load_candidate(states, obstacles, b, t, N, M);
-    const int cell = cell_coord(s.y, g.oy, g.inv_cs, G) * G + cell_coord(s.x, g.ox, g.inv_cs, G);
-    const int pos = atomicAdd(&cur[cell], 1);
-    sorted[(size_t)b * C + pos] = make_float4(s.x, s.y, __int_as_float(t), 0.f);
+  __syncthreads();                              // the starts are out: cnt now serves as the scatter cursors
+  // ---- scatter (order inside a cell is arbitrary: the query orders by (key, index) explicitly); four candidates in
+  //      flight per thread - a single CTA owns the whole env, so the loads' latency is what this loop costs ----
+  for (int t0 = threadIdx.x; t0 < C; t0 += 4 * GRID_BUILD_THREADS) {
+    float4 sv[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int t = t0 + u * GRID_BUILD_THREADS;
+      sv[u] = load_candidate(states, obstacles, b, t < C ? t : t0, N, M);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int t = t0 + u * GRID_BUILD_THREADS;
+      if (t < C) {
+        const int cell = cell_coord(sv[u].y, g.oy, g.inv_cs, G) * G + cell_coord(sv[u].x, g.ox, g.inv_cs, G);
+        const int pos = atomicAdd(&cnt[cell], 1);
+        sorted[(size_t)b * C + pos] = make_float4(sv[u].x, sv[u].y, __int_as_float(t), 0.f);
+      }
+    }
   }
 }
 
@@ -430,7 +456,11 @@ int neighbor_topk_grid(const float* states, const float* obstacles, int B, int N
   const float per_cell = cell_override > 0.f ? cell_override : fmaxf(3.0f, 0.25f * (float)K);
   int G = (int)floorf(sqrtf((float)C / per_cell));
   G = G < 1 ? 1 : (G > GRID_GMAX ? GRID_GMAX : G);
-  grid_build_kernel<<<B, GRID_BUILD_THREADS, 0, st>>>(states, obstacles, N, M, G, sorted, cell_start, header, tl_skip_flag);
+  const size_t build_smem = (size_t)(G * G + 1) * sizeof(int);
+  MACBF_CHECK_CUDA(cudaFuncSetAttribute(grid_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)((GRID_GMAX * GRID_GMAX + 1) * sizeof(int))));
+  grid_build_kernel<<<B, GRID_BUILD_THREADS, build_smem, st>>>(states, obstacles, N, M, G, sorted, cell_start, header,
+                                                               tl_skip_flag);
   MACBF_CHECK_LAUNCH("grid_build_kernel");
   static const bool force_warp = [] {
     const char* e = getenv("MACBF_KNN_WARP");
