@@ -41,7 +41,8 @@ constexpr int THREADS = WORKERS + 32;
 constexpr int R = 128;
 // TMEM columns: [0,64) dZ3_hi  [64,128) dZ3_lo  [128,256) dA2 -> dZ2_hi (in place)  [256,384) dZ2_lo  [384,448) dA1
 constexpr uint32_t C_Z3HI = 0, C_Z3LO = 64, C_DA2 = 128, C_Z2LO = 256, C_DA1 = 384;
-constexpr int DZS = 129;                       // row stride of the transposed dZ1 stage: conflict-free both ways
+constexpr int DZS = 132;                       // row stride of the transposed dZ1 stage: 16-B aligned rows, = 4 (mod 32) words:
+                                               // scalar stores down a column and LDS.128 along a row are conflict-free
 constexpr int oW3THI = 0;                      // B[n = in (128)][k = out (64)] = W3[k][n]
 constexpr int oW3TLO = oW3THI + 128 * 64;
 constexpr int oW2THI = oW3TLO + 128 * 64;      // B[n = in (64)][k = out (128)] = W2[k][n]
@@ -50,7 +51,7 @@ constexpr int oW1 = oW2TLO + 64 * 128;         // [64][8] plain
 constexpr int oW4 = oW1 + 64 * 8;
 // double-buffered hand-off of a tile's dZ1 to the (deferred) dW1 / d-states pass:
 constexpr int oDz1 = oW4 + 64;                 // [2][64][129]  dZ1^T
-constexpr int oXs = oDz1 + 2 * 64 * DZS;       // [2][128][8]   features f0..f5, 1 (bias column), d
+constexpr int oXs = oDz1 + 2 * 64 * DZS;       // [2][8][128]   per feature: f0..f5, 1 (bias column), d of every row
 constexpr int oXpart = oXs + 2 * 128 * 8;      // [2][4][5][128] d/d(f0,f1,f2,f3,f5) partials of the 4 column groups
 constexpr int total_floats = oXpart + 2 * 4 * 5 * 128;
 constexpr size_t smem_bytes = (size_t)total_floats * 4 + 1024;
@@ -216,14 +217,13 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
       const float* xsb = xs + b * (128 * 8);
       const float* xpb = xpart + b * (4 * 5 * 128);
       if (wf < 7) {     // dW1[c][f], db1[c] += sum over the tile's rows (rows without an edge have dZ1 = 0)
-        const float* dzr = dzb + wc * DZS;
+        const float4* dzr = reinterpret_cast<const float4*>(dzb + wc * DZS);
+        const float4* xr = reinterpret_cast<const float4*>(xsb + wf * R);
         float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-#pragma unroll 4
-        for (int e = 0; e < R; e += 4) {
-          s0 = fmaf(dzr[e + 0], xsb[(e + 0) * 8 + wf], s0);
-          s1 = fmaf(dzr[e + 1], xsb[(e + 1) * 8 + wf], s1);
-          s2 = fmaf(dzr[e + 2], xsb[(e + 2) * 8 + wf], s2);
-          s3 = fmaf(dzr[e + 3], xsb[(e + 3) * 8 + wf], s3);
+#pragma unroll 8
+        for (int e4 = 0; e4 < R / 4; ++e4) {
+          const float4 d = dzr[e4], x = xr[e4];
+          s0 = fmaf(d.x, x.x, s0); s1 = fmaf(d.y, x.y, s1); s2 = fmaf(d.z, x.z, s2); s3 = fmaf(d.w, x.w, s3);
         }
         accw1 += (s0 + s1) + (s2 + s3);
       }
@@ -236,10 +236,9 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
 #pragma unroll
           for (int f = 0; f < 5; ++f)
             d0[f] = (xpb[(0 * 5 + f) * R + r] + xpb[(1 * 5 + f) * R + r]) + (xpb[(2 * 5 + f) * R + r] + xpb[(3 * 5 + f) * R + r]);
-          const float4 xa = *reinterpret_cast<const float4*>(xsb + r * 8);
-          const float inv_d = 1.f / xsb[r * 8 + 7];
-          const float gx = d0[0] + d0[4] * xa.x * inv_d;
-          const float gy = d0[1] + d0[4] * xa.y * inv_d;
+          const float inv_d = 1.f / xsb[7 * R + r];
+          const float gx = d0[0] + d0[4] * xsb[0 * R + r] * inv_d;
+          const float gy = d0[1] + d0[4] * xsb[1 * R + r] * inv_d;
           const long long ga = a0 + r / K;
           const int b_env = (int)(ga / N);
           const int j = __ldg(idx + a0 * K + r);
@@ -322,8 +321,8 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
         for (int f = 0; f < 5; ++f) xpb[(cgrp * 5 + f) * R + r] = px[f];
         if (cgrp == 0) {
           float* xsb = xs + buf * (128 * 8);
-          *reinterpret_cast<float4*>(xsb + r * 8) = x0;
-          *reinterpret_cast<float4*>(xsb + r * 8 + 4) = make_float4(x1.x, x1.y, 1.f, x1.z);
+          xsb[0 * R + r] = x0.x; xsb[1 * R + r] = x0.y; xsb[2 * R + r] = x0.z; xsb[3 * R + r] = x0.w;
+          xsb[4 * R + r] = x1.x; xsb[5 * R + r] = x1.y; xsb[6 * R + r] = 1.f; xsb[7 * R + r] = x1.z;
         }
       }
       fence_before_sync();

@@ -30,11 +30,11 @@ constexpr int R = 128;
 constexpr uint32_t C_ZHI = 0, C_ZLO = 64, C_DA1 = 128;
 constexpr uint32_t BLK = 128 * 128;
 constexpr uint32_t Z2_HI = 0, Z2_LO = 2 * BLK, A1_HI = 4 * BLK, A1_LO = 5 * BLK, REC_BYTES = 6 * BLK;
-constexpr int DZS = 129;
+constexpr int DZS = 132;                       // 16-B aligned rows, = 4 (mod 32) words: conflict-free stores and LDS.128
 constexpr int oW2THI = 0;                      // B[n = in (64)][k = out (128)] = W2[k][n]
 constexpr int oW2TLO = oW2THI + 64 * 128;
 constexpr int oDz1 = oW2TLO + 64 * 128;        // dZ1^T stage [64][129]
-constexpr int oXs = oDz1 + 64 * DZS;           // [128][8]: features + bias column
+constexpr int oXs = oDz1 + 64 * DZS;           // [8][128]: per feature (f0..f4, then the bias column of ones) every row
 constexpr int oXpart = oXs + 128 * 8;          // [2][4][128]
 constexpr int oW1 = oXpart + 2 * 4 * 128;      // W1 plain [64][8] (5 used), b1 [64]
 constexpr int oB1 = oW1 + 64 * 8;
@@ -135,8 +135,9 @@ ctrl_edge_bwd_tc_kernel(const float* __restrict__ states, const float* __restric
         gj = (j < N) ? (long long)b * N + j : -1;
       }
       if (cgrp == 0) {
-        *reinterpret_cast<float4*>(xs + r * 8) = make_float4(f[0], f[1], f[2], f[3]);
-        *reinterpret_cast<float4*>(xs + r * 8 + 4) = make_float4(f[4], 1.f, 0.f, 0.f);
+#pragma unroll
+        for (int ff = 0; ff < 5; ++ff) xs[ff * R + r] = f[ff];
+        xs[5 * R + r] = 1.f;
       }
       // ---- a1 = relu(W1 x + b1), channels c0 .. c0+31: ReLU bits + bf16 image ----
       uint32_t mb1 = 0;
@@ -223,17 +224,18 @@ ctrl_edge_bwd_tc_kernel(const float* __restrict__ states, const float* __restric
       fence_before_sync();
       named_bar_sync(1, WORKERS);
       {
-        const float* dzr = dz1s + wc * DZS;
-        float s0 = 0.f, s1 = 0.f, t0 = 0.f, t1 = 0.f;
+        const float4* dzr = reinterpret_cast<const float4*>(dz1s + wc * DZS);
+        const float4* xr = reinterpret_cast<const float4*>(xs + wf * R);
         const int wf2 = wf + 4;                         // 4, 5 for wf = 0, 1; idle otherwise
-#pragma unroll 4
-        for (int e = 0; e < R; e += 2) {
-          const float d0 = dzr[e], d1 = dzr[e + 1];
-          s0 = fmaf(d0, xs[e * 8 + wf], s0);
-          s1 = fmaf(d1, xs[(e + 1) * 8 + wf], s1);
+        const float4* xr2 = reinterpret_cast<const float4*>(xs + (wf2 < 6 ? wf2 : wf) * R);
+        float s0 = 0.f, s1 = 0.f, t0 = 0.f, t1 = 0.f;
+#pragma unroll 8
+        for (int e4 = 0; e4 < R / 4; ++e4) {
+          const float4 d = dzr[e4], x = xr[e4];
+          s0 = fmaf(d.x, x.x, s0); s1 = fmaf(d.y, x.y, s1); s0 = fmaf(d.z, x.z, s0); s1 = fmaf(d.w, x.w, s1);
           if (wf2 < 6) {
-            t0 = fmaf(d0, xs[e * 8 + wf2], t0);
-            t1 = fmaf(d1, xs[(e + 1) * 8 + wf2], t1);
+            const float4 y = xr2[e4];
+            t0 = fmaf(d.x, y.x, t0); t1 = fmaf(d.y, y.y, t1); t0 = fmaf(d.z, y.z, t0); t1 = fmaf(d.w, y.w, t1);
           }
         }
         accw1a += s0 + s1;
