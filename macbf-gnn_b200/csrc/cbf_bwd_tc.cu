@@ -446,18 +446,25 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
     const int m = q * 32 + lane;
     const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16);
     float* gp = slices + (size_t)blockIdx.x * P;
+    // slice[base + e * stride] += v[e]: all 16 old values are fetched before the first store (a plain `+=` loop makes
+    // every load wait for the previous store - they may alias - and this serial tail then costs tens of microseconds)
+    auto accum16 = [&](float* base, int stride, const float* v) {
+      float old[16];
+#pragma unroll
+      for (int e = 0; e < 16; ++e) old[e] = __ldcg(base + e * stride);
+#pragma unroll
+      for (int e = 0; e < 16; ++e) base[e * stride] = old[e] + v[e];
+    };
     for (int c0 = 0; c0 < 64; c0 += 16) {
       float v[16];
       if (NST >= 2) {
         tmem_ld16(tlane + C_W3 + c0, v);                // dW3^T[m = in][n = out]
         wait_ld();
-#pragma unroll
-        for (int e = 0; e < 16; ++e) gp[offW3 + (c0 + e) * 128 + m] += v[e];
+        accum16(gp + offW3 + c0 * 128 + m, 128, v);
       }
       tmem_ld16(tlane + C_W2 + c0, v);                  // dW2[m = out][n = in]
       wait_ld();
-#pragma unroll
-      for (int e = 0; e < 16; ++e) gp[offW2 + m * 64 + c0 + e] += v[e];
+      accum16(gp + offW2 + m * 64 + c0, 1, v);
     }
     {
       float v[8];
@@ -470,8 +477,7 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
         float v[16];
         tmem_ld16(tlane + C_W1 + c0, v);                // dW1^T[m = pool channel][n = out]
         wait_ld();
-#pragma unroll
-        for (int e = 0; e < 16; ++e) gp[offW1 + (c0 + e) * ldW1 + m] += v[e];
+        accum16(gp + offW1 + c0 * ldW1 + m, ldW1, v);
       }
     }
     if (NST >= 2 && q == 0) {                                       // every lane holds the same db3 row; lane m < 32 writes channels 2m, 2m+1
@@ -479,10 +485,7 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
         float v[16];
         tmem_ld16(tlane + C_B3 + c0, v);
         wait_ld();
-        if (lane == 0) {
-#pragma unroll
-          for (int e = 0; e < 16; ++e) gp[offB3 + c0 + e] += v[e];
-        }
+        if (lane == 0) accum16(gp + offB3 + c0, 1, v);
       }
     }
   }
