@@ -230,7 +230,6 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
     }
     mbar_wait(&bar[1], par);
     fence_after_sync();
-#pragma unroll
     [[maybe_unused]] uint32_t bits2 = 0;
 #pragma unroll
     for (int half16 = 0; half16 < 2; ++half16) {   // bias + ReLU + split on 32 channels of D2: hi in place, lo aside
