@@ -13,7 +13,8 @@ namespace cbfrec {
 constexpr uint32_t BLK = 128 * 128;            // one 64-channel block of one image half: 16 KB
 // stage G3 (dW3^T = A2^T dZ3): 96 KB
 constexpr uint32_t A2_HI = 0, A2_LO = 2 * BLK, Z3_HI = 4 * BLK, Z3_LO = 5 * BLK;
-// stage G2 (dW2 = dZ2^T A1): 96 KB
+// stage G2 (dW2 = dZ2^T A1): 96 KB in shared memory, of which the record carries only the 64 KB of dZ2 - the A1 images
+// (offsets A1_HI / A1_LO of the stage) are rebuilt inside the wgrad kernel from XREC
 constexpr uint32_t G2 = 6 * BLK;
 constexpr uint32_t Z2_HI = G2 + 0, Z2_LO = G2 + 2 * BLK, A1_HI = G2 + 4 * BLK, A1_LO = G2 + 5 * BLK;
 constexpr uint32_t STAGE_BYTES = 6 * BLK;      // 98,304

@@ -354,22 +354,38 @@ constexpr uint32_t C_W3 = 0, C_W2 = 64, C_B3 = 128, C_B2 = 192, C_W1 = 256;
 // per tile: A = dZ2 (128 channels), B = A1 (64 channels) -> dW2[out][in], db2).  NST = 3: controller node net (G3, G2 and
 // a third stage A = pool (128 channels), B = dZ1 (64 channels) -> dW1[:, :128]^T, rows of W1 being `ldW1` floats long).
 // `rec_stride` bytes between tile records, P floats per gradient slice, off* = offsets of the parameter tensors in a slice.
+//
+// gen_w1 != NULL (NST = 1, 2): the B operand of the G2-type stage - the layer-1 activations a1 = relu(W1 x + b1), 64
+// channels - is not read from the record but REBUILT here from the tile's edge features (float[128][8] at byte
+// `gen_xoff` of the record) by the four otherwise idle epilogue warps, written as bf16 hi/lo images straight into the
+// stage buffer: a 6 -> 64 layer costs nothing next to an HBM-bound copy, and 256 B per edge of traffic (and the
+// producer kernel's work of dumping them) disappear.  gen_w1: W1 [64][gen_nf] row-major, gen_b1: b1 [64].
 template <int NST>
 __global__ void __launch_bounds__(cbfwg::THREADS, 1)
 wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long long ntiles, float* __restrict__ slices, int P,
-                int offW3, int offB3, int offW2, int offB2, int offW1, int ldW1) {
+                int offW3, int offB3, int offW2, int offB2, int offW1, int ldW1, const float* __restrict__ gen_w1,
+                const float* __restrict__ gen_b1, int gen_nf, uint32_t gen_xoff) {
   using namespace cbfwg;
   using namespace tc;
   extern __shared__ unsigned char smem_raw[];
   unsigned char* sm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   __shared__ uint64_t full[2], empty[2], done;
   __shared__ uint32_t tmem_base_s;
+  __shared__ __align__(16) float gW1[64 * 8];
+  __shared__ float gB1[64];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool gen = (NST != 3) && gen_w1 != nullptr;
   constexpr uint32_t TMEM_COLS = (NST == 3) ? 512 : 256;
   if (warp == 0) tmem_alloc(&tmem_base_s, TMEM_COLS);
   if (threadIdx.x == 32) {
-    mbar_init(&full[0], 1); mbar_init(&full[1], 1); mbar_init(&empty[0], 1); mbar_init(&empty[1], 1); mbar_init(&done, 1);
+    // a stage is full when its bulk copies have landed and, with `gen`, the four generator warps have passed it
+    mbar_init(&full[0], gen ? 5 : 1); mbar_init(&full[1], gen ? 5 : 1);
+    mbar_init(&empty[0], 1); mbar_init(&empty[1], 1); mbar_init(&done, 1);
     fence_mbar_init();
+  }
+  if (gen) {
+    for (int t = threadIdx.x; t < 64 * 8; t += THREADS) gW1[t] = ((t & 7) < gen_nf) ? __ldg(gen_w1 + (t >> 3) * gen_nf + (t & 7)) : 0.f;
+    for (int t = threadIdx.x; t < 64; t += THREADS) gB1[t] = __ldg(gen_b1 + t);
   }
   for (int t = threadIdx.x; t < 1024; t += THREADS) reinterpret_cast<uint32_t*>(sm + ONES)[t] = 0x3f803f80u;   // bf16 1.0 pairs
   fence_proxy_async_smem();
@@ -386,9 +402,10 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
         if (n >= 2) mbar_wait(&empty[buf], ((n >> 1) - 1) & 1);
         if (elect_one()) {
           const unsigned char* src = rec + (size_t)tile * rec_stride + (size_t)s * STAGE;
-          mbar_expect_tx(&full[buf], STAGE);
-#pragma unroll
-          for (int p = 0; p < 3; ++p) bulk_g2s(sm + buf * STAGE + p * (STAGE / 3), src + p * (STAGE / 3), STAGE / 3, &full[buf]);
+          // with `gen` the last third of a G2-type stage (the a1 images) is produced on chip
+          const int parts = (gen && ((NST == 1) || s == 1)) ? 2 : 3;
+          mbar_expect_tx(&full[buf], parts * (STAGE / 3));
+          for (int p = 0; p < parts; ++p) bulk_g2s(sm + buf * STAGE + p * (STAGE / 3), src + p * (STAGE / 3), STAGE / 3, &full[buf]);
         }
         __syncwarp();
       }
@@ -439,6 +456,49 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
     }
     if (elect_one()) mma_commit(&done);
   } else {
+    if (gen) {
+      // ---- generator: a1 images of every G2-type stage, row r of the tile per thread ----
+      const int r = (warp - 2) * 32 + lane;
+      uint32_t n = 0;
+      for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        for (int s0 = 0; s0 < NST; ++s0, ++n) {
+          const uint32_t buf = n & 1;
+          const bool g2 = (NST == 1) || s0 == 1;
+          float4 xa = make_float4(0.f, 0.f, 0.f, 0.f), xb = xa;
+          if (g2) {
+            const float4* xr = reinterpret_cast<const float4*>(rec + (size_t)tile * rec_stride + gen_xoff) + 2 * r;
+            xa = __ldg(xr); xb = __ldg(xr + 1);
+          }
+          if (n >= 2) mbar_wait(&empty[buf], ((n >> 1) - 1) & 1);
+          if (g2) {
+            unsigned char* img_hi = sm + buf * STAGE + 4 * cbfrec::BLK;
+            unsigned char* img_lo = sm + buf * STAGE + 5 * cbfrec::BLK;
+#pragma unroll 2
+            for (int c8 = 0; c8 < 8; ++c8) {
+              float x[8];
+#pragma unroll
+              for (int e = 0; e < 8; ++e) {
+                const int ch = c8 * 8 + e;
+                const float4 wa = *reinterpret_cast<const float4*>(gW1 + ch * 8);
+                const float4 wb = *reinterpret_cast<const float4*>(gW1 + ch * 8 + 4);
+                float z = fmaf(wa.x, xa.x, gB1[ch]);
+                z = fmaf(wa.y, xa.y, z); z = fmaf(wa.z, xa.z, z); z = fmaf(wa.w, xa.w, z);
+                z = fmaf(wb.x, xb.x, z); z = fmaf(wb.y, xb.y, z);
+                x[e] = fmaxf(z, 0.f);
+              }
+              uint4 bh, bl;
+              bf16_split8(x, bh, bl);
+              const uint32_t off = (uint32_t)r * 128u + (uint32_t)((c8 ^ (r & 7)) << 4);
+              *reinterpret_cast<uint4*>(img_hi + off) = bh;
+              *reinterpret_cast<uint4*>(img_lo + off) = bl;
+            }
+            fence_proxy_async_smem();
+          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&full[buf]);
+        }
+      }
+    }
     // final epilogue: accumulators -> this CTA's gradient slice
     mbar_wait(&done, 0);
     fence_after_sync();
@@ -498,16 +558,17 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
 int wgrad_tc_node(const unsigned char* rec, long long ntiles, float* slices, int grid, cudaStream_t st) {
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfwg::smem_bytes));
   wgrad_tc_kernel<3><<<grid, cbfwg::THREADS, cbfwg::smem_bytes, st>>>(rec, cnrec::BYTES, ntiles, slices, MACBF_CTRL_PARAMS, CT_NW3,
-                                                                     CT_NB3, CT_NW2, CT_NB2, CT_NW1, 132);
+                                                                     CT_NB3, CT_NW2, CT_NB2, CT_NW1, 132, nullptr, nullptr, 0, 0);
   MACBF_CHECK_LAUNCH("wgrad_tc_kernel<node>");
   return 0;
 }
 
 // controller edge net (ctrl_edge_bwd_tc.cu): one 96-KB stage per tile record
-int wgrad_tc_ctrl(const unsigned char* rec, size_t rec_stride, long long ntiles, float* slices, int grid, cudaStream_t st) {
+int wgrad_tc_ctrl(const unsigned char* rec, size_t rec_stride, long long ntiles, float* slices, int grid, cudaStream_t st,
+                  const float* params, uint32_t xoff) {
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfwg::smem_bytes));
   wgrad_tc_kernel<1><<<grid, cbfwg::THREADS, cbfwg::smem_bytes, st>>>(rec, rec_stride, ntiles, slices, MACBF_CTRL_PARAMS, 0, 0,
-                                                                     CT_EW2, CT_EB2, 0, 0);
+                                                                     CT_EW2, CT_EB2, 0, 0, params + CT_EW1, params + CT_EB1, 5, xoff);
   MACBF_CHECK_LAUNCH("wgrad_tc_kernel<ctrl>");
   return 0;
 }
@@ -561,7 +622,8 @@ int cbf_backward_tc(const float* states, const float* obstacles, const int32_t* 
                                                                         grad_states);
     MACBF_CHECK_LAUNCH("cbf_dgrad_tc_kernel");
     wgrad_tc_kernel<2><<<grid, cbfwg::THREADS, cbfwg::smem_bytes, st>>>(rec, cbfrec::BYTES, ct, slices, MACBF_CBF_PARAMS, CBF_W3,
-                                                                       CBF_B3, CBF_W2, CBF_B2, 0, 0);
+                                                                       CBF_B3, CBF_W2, CBF_B2, 0, 0, params + CBF_W1, params + CBF_B1,
+                                                                       6, cbfrec::XREC);
     MACBF_CHECK_LAUNCH("wgrad_tc_kernel<cbf>");
   }
   reduce_partials_kernel<<<(MACBF_CBF_PARAMS + 255) / 256, 256, 0, st>>>(slices, NUM_SMS, MACBF_CBF_PARAMS, grad_params);

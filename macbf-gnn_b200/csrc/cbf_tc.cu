@@ -289,7 +289,6 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
       wait_ld();
       [[maybe_unused]] uint32_t bits = 0;
       [[maybe_unused]] unsigned char* tr = DUMP ? rec + (size_t)(tile_e - tile_begin) * cbfrec::BYTES : nullptr;
-      [[maybe_unused]] uint4 bh[2], bl[2];
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
         float hi[8], lo[8];
@@ -311,14 +310,10 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
         if constexpr (DUMP) {
 #pragma unroll
           for (int e = 0; e < 8; ++e) bits |= (x[e] > 0.f ? 1u : 0u) << (half * 8 + e);
-          bf16_split8(x, bh[half], bl[half]);
         }
       }
-      if constexpr (DUMP) {
-        img_store16(tr + cbfrec::A1_HI, r, cgrp, bh[0], bh[1]);
-        img_store16(tr + cbfrec::A1_LO, r, cgrp, bl[0], bl[1]);
-        reinterpret_cast<uint32_t*>(tr + cbfrec::MASKS)[(0 * 4 + cgrp) * R + r] = bits;
-      }
+      // (the layer-1 activations themselves are not dumped: the wgrad kernel rebuilds them from the edge features)
+      if constexpr (DUMP) reinterpret_cast<uint32_t*>(tr + cbfrec::MASKS)[(0 * 4 + cgrp) * R + r] = bits;
       wait_st();
       warp_arrive_after_tmem(&a2_full);
     };

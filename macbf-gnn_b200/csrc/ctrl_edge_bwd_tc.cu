@@ -20,7 +20,8 @@
 
 namespace macbf {
 
-int wgrad_tc_ctrl(const unsigned char* rec, size_t rec_stride, long long ntiles, float* slices, int grid, cudaStream_t st);
+int wgrad_tc_ctrl(const unsigned char* rec, size_t rec_stride, long long ntiles, float* slices, int grid, cudaStream_t st,
+                  const float* params, uint32_t xoff);
 
 namespace cebtc {
 constexpr int WORKERS = 256;
@@ -29,7 +30,8 @@ constexpr int R = 128;
 // TMEM (256 columns): [0,64) dZ2_hi of the current chunk  [64,128) dZ2_lo  [128,192) dA1
 constexpr uint32_t C_ZHI = 0, C_ZLO = 64, C_DA1 = 128;
 constexpr uint32_t BLK = 128 * 128;
-constexpr uint32_t Z2_HI = 0, Z2_LO = 2 * BLK, A1_HI = 4 * BLK, A1_LO = 5 * BLK, REC_BYTES = 6 * BLK;
+// record: dZ2 images (64 KB), then the edge features float[128][8] from which the wgrad kernel rebuilds the a1 images
+constexpr uint32_t Z2_HI = 0, Z2_LO = 2 * BLK, XREC = 4 * BLK, REC_BYTES = 6 * BLK;
 constexpr int DZS = 132;                       // 16-B aligned rows, = 4 (mod 32) words: conflict-free stores and LDS.128
 constexpr int oW2THI = 0;                      // B[n = in (64)][k = out (128)] = W2[k][n]
 constexpr int oW2TLO = oW2THI + 64 * 128;
@@ -139,27 +141,20 @@ ctrl_edge_bwd_tc_kernel(const float* __restrict__ states, const float* __restric
         for (int ff = 0; ff < 5; ++ff) xs[ff * R + r] = f[ff];
         xs[5 * R + r] = 1.f;
       }
-      // ---- a1 = relu(W1 x + b1), channels c0 .. c0+31: ReLU bits + bf16 image ----
+      if (cgrp == 0) {   // the wgrad kernel rebuilds the a1 images from these (same fmaf chain as below)
+        float4* xr = reinterpret_cast<float4*>(tr + XREC) + 2 * r;
+        xr[0] = make_float4(f[0], f[1], f[2], f[3]);
+        xr[1] = make_float4(f[4], 0.f, 0.f, 0.f);
+      }
+      // ---- ReLU bits of a1 = relu(W1 x + b1), channels c0 .. c0+31 ----
       uint32_t mb1 = 0;
 #pragma unroll
-      for (int pair = 0; pair < 2; ++pair) {
-        uint4 bh[2], bl[2];
-#pragma unroll
-        for (int half = 0; half < 2; ++half) {
-          float x[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const int ch = c0 + pair * 16 + half * 8 + e;
-            const float4 wa = *reinterpret_cast<const float4*>(W1 + ch * 8);
-            float z = fmaf(wa.x, f[0], B1[ch]);
-            z = fmaf(wa.y, f[1], z); z = fmaf(wa.z, f[2], z); z = fmaf(wa.w, f[3], z); z = fmaf(W1[ch * 8 + 4], f[4], z);
-            x[e] = fmaxf(z, 0.f);
-            mb1 |= (x[e] > 0.f ? 1u : 0u) << (pair * 16 + half * 8 + e);
-          }
-          bf16_split8(x, bh[half], bl[half]);
-        }
-        img_store16(tr + A1_HI, r, 2 * cgrp + pair, bh[0], bh[1]);
-        img_store16(tr + A1_LO, r, 2 * cgrp + pair, bl[0], bl[1]);
+      for (int e = 0; e < 32; ++e) {
+        const int ch = c0 + e;
+        const float4 wa = *reinterpret_cast<const float4*>(W1 + ch * 8);
+        float z = fmaf(wa.x, f[0], B1[ch]);
+        z = fmaf(wa.y, f[1], z); z = fmaf(wa.z, f[2], z); z = fmaf(wa.w, f[3], z); z = fmaf(W1[ch * 8 + 4], f[4], z);
+        mb1 |= (z > 0.f ? 1u : 0u) << e;
       }
       // ---- per 64-channel chunk: dZ2 from the winners -> TMEM hi/lo + image; the MMA warp accumulates dA1 ----
 #pragma unroll
@@ -307,7 +302,7 @@ int ctrl_edge_bwd_tc(const float* states, const float* obstacles, const int32_t*
                                                                            agents, TA, t0, t1, rec, slices, grad_states);
     MACBF_CHECK_LAUNCH("ctrl_edge_bwd_tc_kernel");
     const int wgrid = (int)(ct < NUM_SMS ? ct : (long long)NUM_SMS);
-    if (int rc = wgrad_tc_ctrl(rec, cebtc::REC_BYTES, ct, slices, wgrid, st)) return rc;
+    if (int rc = wgrad_tc_ctrl(rec, cebtc::REC_BYTES, ct, slices, wgrid, st, params, cebtc::XREC)) return rc;
   }
   return 0;
 }
