@@ -184,11 +184,9 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
       }
       return z;
     };
-    auto build_z3 = [&](long long t, const RecZ& z) {
-      unsigned char* tr = rec + (size_t)(t - tile_begin) * cbfrec::BYTES;
+    auto build_z3 = [&](long long, const RecZ& z) {
       const uint32_t mb3 = z.mb3;
       const float gm = z.gm;
-      uint4 bh[2], bl[2];
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
         float x[8], hi[8], lo[8];
@@ -199,11 +197,8 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
         }
         tmem_st8(tlane + C_Z3HI + c0 + half * 8, hi);
         tmem_st8(tlane + C_Z3LO + c0 + half * 8, lo);
-        bf16_split8(x, bh[half], bl[half]);
       }
-      img_store16(tr + cbfrec::Z3_HI, r, cgrp, bh[0], bh[1]);
-      img_store16(tr + cbfrec::Z3_LO, r, cgrp, bl[0], bl[1]);
-      wait_st();
+      wait_st();     // (no dZ3 image: the wgrad kernel rebuilds it from gm and the ReLU bits)
       warp_arrive_after_tmem(&z3_full);
     };
     // Deferred tail of tile ordinal `ord` (buffer ord & 1): dW1 / db1 partial sums and d/dstates.  It runs one tile
@@ -360,11 +355,13 @@ constexpr uint32_t C_W3 = 0, C_W2 = 64, C_B3 = 128, C_B2 = 192, C_W1 = 256;
 // `gen_xoff` of the record) by the four otherwise idle epilogue warps, written as bf16 hi/lo images straight into the
 // stage buffer: a 6 -> 64 layer costs nothing next to an HBM-bound copy, and 256 B per edge of traffic (and the
 // producer kernel's work of dumping them) disappear.  gen_w1: W1 [64][gen_nf] row-major, gen_b1: b1 [64].
+// gen_w4 != NULL (NST = 2, CBF): likewise the B operand of the G3-type stage, dZ3 = gm * w4 * [z3 > 0], is rebuilt from
+// the record's gm and layer-3 ReLU bits (the same product the dgrad kernel feeds its own GEMM).
 template <int NST>
 __global__ void __launch_bounds__(cbfwg::THREADS, 1)
 wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long long ntiles, float* __restrict__ slices, int P,
                 int offW3, int offB3, int offW2, int offB2, int offW1, int ldW1, const float* __restrict__ gen_w1,
-                const float* __restrict__ gen_b1, int gen_nf, uint32_t gen_xoff) {
+                const float* __restrict__ gen_b1, int gen_nf, uint32_t gen_xoff, const float* __restrict__ gen_w4) {
   using namespace cbfwg;
   using namespace tc;
   extern __shared__ unsigned char smem_raw[];
@@ -373,6 +370,8 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
   __shared__ uint32_t tmem_base_s;
   __shared__ __align__(16) float gW1[64 * 8];
   __shared__ float gB1[64];
+  __shared__ float gW4[64];
+  const bool gen3 = (NST == 2) && gen_w4 != nullptr && gen_w1 != nullptr;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const bool gen = (NST != 3) && gen_w1 != nullptr;
   constexpr uint32_t TMEM_COLS = (NST == 3) ? 512 : 256;
@@ -386,6 +385,8 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
   if (gen) {
     for (int t = threadIdx.x; t < 64 * 8; t += THREADS) gW1[t] = ((t & 7) < gen_nf) ? __ldg(gen_w1 + (t >> 3) * gen_nf + (t & 7)) : 0.f;
     for (int t = threadIdx.x; t < 64; t += THREADS) gB1[t] = __ldg(gen_b1 + t);
+    if (gen3)
+      for (int t = threadIdx.x; t < 64; t += THREADS) gW4[t] = __ldg(gen_w4 + t);
   }
   for (int t = threadIdx.x; t < 1024; t += THREADS) reinterpret_cast<uint32_t*>(sm + ONES)[t] = 0x3f803f80u;   // bf16 1.0 pairs
   fence_proxy_async_smem();
@@ -403,7 +404,7 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
         if (elect_one()) {
           const unsigned char* src = rec + (size_t)tile * rec_stride + (size_t)s * STAGE;
           // with `gen` the last third of a G2-type stage (the a1 images) is produced on chip
-          const int parts = (gen && ((NST == 1) || s == 1)) ? 2 : 3;
+          const int parts = ((gen && ((NST == 1) || s == 1)) || (gen3 && s == 0)) ? 2 : 3;
           mbar_expect_tx(&full[buf], parts * (STAGE / 3));
           for (int p = 0; p < parts; ++p) bulk_g2s(sm + buf * STAGE + p * (STAGE / 3), src + p * (STAGE / 3), STAGE / 3, &full[buf]);
         }
@@ -469,7 +470,35 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
             const float4* xr = reinterpret_cast<const float4*>(rec + (size_t)tile * rec_stride + gen_xoff) + 2 * r;
             xa = __ldg(xr); xb = __ldg(xr + 1);
           }
+          const bool g3 = gen3 && s0 == 0;
+          float gm = 0.f;
+          uint32_t m3[4] = {0u, 0u, 0u, 0u};
+          if (g3) {
+            const unsigned char* tr = rec + (size_t)tile * rec_stride;
+            gm = __ldg(reinterpret_cast<const float*>(tr + cbfrec::GM) + r);
+#pragma unroll
+            for (int cg = 0; cg < 4; ++cg) m3[cg] = __ldg(reinterpret_cast<const uint32_t*>(tr + cbfrec::MASKS) + (3 * 4 + cg) * 128 + r);
+          }
           if (n >= 2) mbar_wait(&empty[buf], ((n >> 1) - 1) & 1);
+          if (g3) {
+            unsigned char* img_hi = sm + buf * STAGE + 4 * cbfrec::BLK;
+            unsigned char* img_lo = sm + buf * STAGE + 5 * cbfrec::BLK;
+#pragma unroll
+            for (int c8 = 0; c8 < 8; ++c8) {
+              float x[8];
+#pragma unroll
+              for (int e = 0; e < 8; ++e) {
+                const int ch = c8 * 8 + e;
+                x[e] = ((m3[ch >> 4] >> (ch & 15)) & 1u) ? gm * gW4[ch] : 0.f;
+              }
+              uint4 bh, bl;
+              bf16_split8(x, bh, bl);
+              const uint32_t off = (uint32_t)r * 128u + (uint32_t)((c8 ^ (r & 7)) << 4);
+              *reinterpret_cast<uint4*>(img_hi + off) = bh;
+              *reinterpret_cast<uint4*>(img_lo + off) = bl;
+            }
+            fence_proxy_async_smem();
+          }
           if (g2) {
             unsigned char* img_hi = sm + buf * STAGE + 4 * cbfrec::BLK;
             unsigned char* img_lo = sm + buf * STAGE + 5 * cbfrec::BLK;
@@ -558,7 +587,8 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
 int wgrad_tc_node(const unsigned char* rec, long long ntiles, float* slices, int grid, cudaStream_t st) {
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfwg::smem_bytes));
   wgrad_tc_kernel<3><<<grid, cbfwg::THREADS, cbfwg::smem_bytes, st>>>(rec, cnrec::BYTES, ntiles, slices, MACBF_CTRL_PARAMS, CT_NW3,
-                                                                     CT_NB3, CT_NW2, CT_NB2, CT_NW1, 132, nullptr, nullptr, 0, 0);
+                                                                     CT_NB3, CT_NW2, CT_NB2, CT_NW1, 132, nullptr, nullptr, 0, 0,
+                                                                     nullptr);
   MACBF_CHECK_LAUNCH("wgrad_tc_kernel<node>");
   return 0;
 }
@@ -568,7 +598,8 @@ int wgrad_tc_ctrl(const unsigned char* rec, size_t rec_stride, long long ntiles,
                   const float* params, uint32_t xoff) {
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfwg::smem_bytes));
   wgrad_tc_kernel<1><<<grid, cbfwg::THREADS, cbfwg::smem_bytes, st>>>(rec, rec_stride, ntiles, slices, MACBF_CTRL_PARAMS, 0, 0,
-                                                                     CT_EW2, CT_EB2, 0, 0, params + CT_EW1, params + CT_EB1, 5, xoff);
+                                                                     CT_EW2, CT_EB2, 0, 0, params + CT_EW1, params + CT_EB1, 5, xoff,
+                                                                     nullptr);
   MACBF_CHECK_LAUNCH("wgrad_tc_kernel<ctrl>");
   return 0;
 }
@@ -623,7 +654,7 @@ int cbf_backward_tc(const float* states, const float* obstacles, const int32_t* 
     MACBF_CHECK_LAUNCH("cbf_dgrad_tc_kernel");
     wgrad_tc_kernel<2><<<grid, cbfwg::THREADS, cbfwg::smem_bytes, st>>>(rec, cbfrec::BYTES, ct, slices, MACBF_CBF_PARAMS, CBF_W3,
                                                                        CBF_B3, CBF_W2, CBF_B2, 0, 0, params + CBF_W1, params + CBF_B1,
-                                                                       6, cbfrec::XREC);
+                                                                       6, cbfrec::XREC, params + CBF_W4);
     MACBF_CHECK_LAUNCH("wgrad_tc_kernel<cbf>");
   }
   reduce_partials_kernel<<<(MACBF_CBF_PARAMS + 255) / 256, 256, 0, st>>>(slices, NUM_SMS, MACBF_CBF_PARAMS, grad_params);
