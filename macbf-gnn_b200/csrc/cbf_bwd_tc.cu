@@ -337,6 +337,7 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
 // ================================ kernel 3: weight gradients ================================
 namespace cbfwg {
 constexpr int THREADS = 192;                   // warp 0: bulk-copy producer, warp 1: MMA issue, warps 2..5: final epilogue
+constexpr int MAX_THREADS = 64 + 512;          // with on-chip operand generation: up to 16 generator warps (warps 2..17)
 constexpr uint32_t STAGE = cbfrec::STAGE_BYTES;
 constexpr uint32_t ONES = 2 * STAGE;           // bf16 ones: 2 blocks x 16 rows x 128 B = 4 KB (A operand M = 128, K = 16)
 constexpr size_t smem_bytes = 2 * (size_t)STAGE + 4096 + 1024;
@@ -344,6 +345,16 @@ constexpr size_t smem_bytes = 2 * (size_t)STAGE + 4096 + 1024;
 //               [256,320) dW1^T[in][out] (NST = 3)
 constexpr uint32_t C_W3 = 0, C_W2 = 64, C_B3 = 128, C_B2 = 192, C_W1 = 256;
 }  // namespace cbfwg
+
+// Controller edge net only (NST = 1): with `dpool` set, the A operand - dZ2[row][c] = d/dpool[agent][c] on the row whose
+// slot won the max-pool, else 0 - is rebuilt from d/dpool and the winners too; nothing but the edge features is then
+// read from the record and the kernel stops being HBM-bound.
+struct WgradRoute {
+  const float* dpool;        // [agents][128] or NULL
+  const uint8_t* argk;       // [agents][128] winning slot, 255 = none
+  int K, TA;                 // rows per agent, agents per tile
+  long long agents, tile0;   // total agents; global index of the record chunk's first tile
+};
 
 // NST = 2: CBF (stage 0 = G3: dW3^T, db3; stage 1 = G2: dW2, db2).  NST = 1: controller edge net (one G2-type stage
 // per tile: A = dZ2 (128 channels), B = A1 (64 channels) -> dW2[out][in], db2).  NST = 3: controller node net (G3, G2 and
@@ -358,10 +369,11 @@ constexpr uint32_t C_W3 = 0, C_W2 = 64, C_B3 = 128, C_B2 = 192, C_W1 = 256;
 // gen_w4 != NULL (NST = 2, CBF): likewise the B operand of the G3-type stage, dZ3 = gm * w4 * [z3 > 0], is rebuilt from
 // the record's gm and layer-3 ReLU bits (the same product the dgrad kernel feeds its own GEMM).
 template <int NST>
-__global__ void __launch_bounds__(cbfwg::THREADS, 1)
+__global__ void __launch_bounds__(cbfwg::MAX_THREADS, 1)
 wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long long ntiles, float* __restrict__ slices, int P,
                 int offW3, int offB3, int offW2, int offB2, int offW1, int ldW1, const float* __restrict__ gen_w1,
-                const float* __restrict__ gen_b1, int gen_nf, uint32_t gen_xoff, const float* __restrict__ gen_w4) {
+                const float* __restrict__ gen_b1, int gen_nf, uint32_t gen_xoff, const float* __restrict__ gen_w4,
+                WgradRoute route) {
   using namespace cbfwg;
   using namespace tc;
   extern __shared__ unsigned char smem_raw[];
@@ -372,23 +384,25 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
   __shared__ float gB1[64];
   __shared__ float gW4[64];
   const bool gen3 = (NST == 2) && gen_w4 != nullptr && gen_w1 != nullptr;
+  const bool genA = (NST == 1) && route.dpool != nullptr && gen_w1 != nullptr;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const bool gen = (NST != 3) && gen_w1 != nullptr;
   constexpr uint32_t TMEM_COLS = (NST == 3) ? 512 : 256;
   if (warp == 0) tmem_alloc(&tmem_base_s, TMEM_COLS);
   if (threadIdx.x == 32) {
     // a stage is full when its bulk copies have landed and, with `gen`, the four generator warps have passed it
-    mbar_init(&full[0], gen ? 5 : 1); mbar_init(&full[1], gen ? 5 : 1);
+    const int gwarps = (int)(blockDim.x >> 5) - 2;
+    mbar_init(&full[0], gen ? 1 + gwarps : 1); mbar_init(&full[1], gen ? 1 + gwarps : 1);
     mbar_init(&empty[0], 1); mbar_init(&empty[1], 1); mbar_init(&done, 1);
     fence_mbar_init();
   }
   if (gen) {
-    for (int t = threadIdx.x; t < 64 * 8; t += THREADS) gW1[t] = ((t & 7) < gen_nf) ? __ldg(gen_w1 + (t >> 3) * gen_nf + (t & 7)) : 0.f;
-    for (int t = threadIdx.x; t < 64; t += THREADS) gB1[t] = __ldg(gen_b1 + t);
+    for (int t = threadIdx.x; t < 64 * 8; t += blockDim.x) gW1[t] = ((t & 7) < gen_nf) ? __ldg(gen_w1 + (t >> 3) * gen_nf + (t & 7)) : 0.f;
+    for (int t = threadIdx.x; t < 64; t += blockDim.x) gB1[t] = __ldg(gen_b1 + t);
     if (gen3)
-      for (int t = threadIdx.x; t < 64; t += THREADS) gW4[t] = __ldg(gen_w4 + t);
+      for (int t = threadIdx.x; t < 64; t += blockDim.x) gW4[t] = __ldg(gen_w4 + t);
   }
-  for (int t = threadIdx.x; t < 1024; t += THREADS) reinterpret_cast<uint32_t*>(sm + ONES)[t] = 0x3f803f80u;   // bf16 1.0 pairs
+  for (int t = threadIdx.x; t < 1024; t += blockDim.x) reinterpret_cast<uint32_t*>(sm + ONES)[t] = 0x3f803f80u;   // bf16 1.0 pairs
   fence_proxy_async_smem();
   fence_before_sync();
   __syncthreads();
@@ -404,7 +418,7 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
         if (elect_one()) {
           const unsigned char* src = rec + (size_t)tile * rec_stride + (size_t)s * STAGE;
           // with `gen` the last third of a G2-type stage (the a1 images) is produced on chip
-          const int parts = ((gen && ((NST == 1) || s == 1)) || (gen3 && s == 0)) ? 2 : 3;
+          const int parts = genA ? 0 : ((gen && ((NST == 1) || s == 1)) || (gen3 && s == 0)) ? 2 : 3;
           mbar_expect_tx(&full[buf], parts * (STAGE / 3));
           for (int p = 0; p < parts; ++p) bulk_g2s(sm + buf * STAGE + p * (STAGE / 3), src + p * (STAGE / 3), STAGE / 3, &full[buf]);
         }
@@ -458,9 +472,25 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
     if (elect_one()) mma_commit(&done);
   } else {
     if (gen) {
-      // ---- generator: a1 images of every G2-type stage, row r of the tile per thread ----
-      const int r = (warp - 2) * 32 + lane;
+      // ---- generators: operand images built on chip; thread = (row r of the tile, share `part` of the 16-byte chunks) ----
+      const int gidx = (int)threadIdx.x - 64, r = gidx & 127, part = gidx >> 7, nparts = ((int)blockDim.x - 64) >> 7;
       uint32_t n = 0;
+      float nx_v[8];
+      int nx_w[8];
+      auto load_route = [&](long long t) {             // d/dpool and winner of (agent (gidx >> 7) + 4 j, channel gidx & 127) of tile t
+        const long long a0 = (route.tile0 + t) * route.TA;
+        const int ch = gidx & 127;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int a = (gidx >> 7) + 4 * j;
+          nx_v[j] = 0.f; nx_w[j] = 255;
+          if (t < ntiles && a < route.TA && a0 + a < route.agents) {
+            nx_w[j] = __ldg(route.argk + (a0 + a) * 128 + ch);
+            nx_v[j] = __ldg(route.dpool + (a0 + a) * 128 + ch);
+          }
+        }
+      };
+      if (genA) load_route(blockIdx.x);
       for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         for (int s0 = 0; s0 < NST; ++s0, ++n) {
           const uint32_t buf = n & 1;
@@ -479,12 +509,23 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
 #pragma unroll
             for (int cg = 0; cg < 4; ++cg) m3[cg] = __ldg(reinterpret_cast<const uint32_t*>(tr + cbfrec::MASKS) + (3 * 4 + cg) * 128 + r);
           }
+          // dZ2 is sparse - per agent and channel ONE row (the max-pool winner) carries d/dpool, the rest is zero: the
+          // image is zero-filled with wide stores and the winners are scattered into it (512 generator threads:
+          // thread = (agent g >> 7 + 4 j of the tile, channel g & 127)); loads go out before the stage is waited for
+          float sc_v[8];
+          int sc_w[8];                                   // winner slot (255: none / no such agent)
+          const int sc_n = genA ? (route.TA + 3) >> 2 : 0;
+          if (genA) {
+            // this tile's values were fetched one tile ago (nx_*); fetch the next tile's now
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { sc_v[j] = nx_v[j]; sc_w[j] = nx_w[j]; }
+            load_route(tile + gridDim.x);
+          }
           if (n >= 2) mbar_wait(&empty[buf], ((n >> 1) - 1) & 1);
           if (g3) {
             unsigned char* img_hi = sm + buf * STAGE + 4 * cbfrec::BLK;
             unsigned char* img_lo = sm + buf * STAGE + 5 * cbfrec::BLK;
-#pragma unroll
-            for (int c8 = 0; c8 < 8; ++c8) {
+            for (int c8 = part; c8 < 8; c8 += nparts) {
               float x[8];
 #pragma unroll
               for (int e = 0; e < 8; ++e) {
@@ -499,11 +540,44 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
             }
             fence_proxy_async_smem();
           }
+          if (genA) {
+            unsigned char* a_hi = sm + buf * STAGE;
+            unsigned char* a_lo = sm + buf * STAGE + 2 * cbfrec::BLK;
+            uint4* z = reinterpret_cast<uint4*>(a_hi);                  // hi and lo halves are contiguous: 64 KB
+#pragma unroll
+            for (int i = 0; i < 8; ++i) z[gidx + 512 * i] = make_uint4(0u, 0u, 0u, 0u);
+            named_bar_sync(2, 512);                                     // every zero is in place before a winner lands
+            const int ch = gidx & 127;
+            for (int j = 0; j < sc_n; ++j) {
+              int row = -1;
+              float val = 0.f;
+              if (j < 8) {
+#pragma unroll
+                for (int jj = 0; jj < 8; ++jj)
+                  if (jj == j) { row = (sc_w[jj] < route.K) ? ((gidx >> 7) + 4 * jj) * route.K + sc_w[jj] : -1; val = sc_v[jj]; }
+              } else {                                                  // K < 4: more than 32 agents per tile
+                const long long a0 = (route.tile0 + tile) * route.TA;
+                const int a = (gidx >> 7) + 4 * j;
+                if (a < route.TA && a0 + a < route.agents) {
+                  const int w = __ldg(route.argk + (a0 + a) * 128 + ch);
+                  val = __ldg(route.dpool + (a0 + a) * 128 + ch);
+                  row = (w < route.K) ? a * route.K + w : -1;
+                }
+              }
+              if (row < 0) continue;
+              const uint32_t h = bf16x2_rn(val, 0.f) & 0xffffu;
+              const float lo_f = val - __uint_as_float(h << 16);
+              const uint32_t l = bf16x2_rn(lo_f, 0.f) & 0xffffu;
+              const uint32_t off = (uint32_t)(ch >> 6) * cbfrec::BLK + (uint32_t)row * 128u +
+                                   (uint32_t)((((ch & 63) >> 3) ^ (row & 7)) << 4) + (uint32_t)((ch & 7) << 1);
+              *reinterpret_cast<unsigned short*>(a_hi + off) = (unsigned short)h;
+              *reinterpret_cast<unsigned short*>(a_lo + off) = (unsigned short)l;
+            }
+          }
           if (g2) {
             unsigned char* img_hi = sm + buf * STAGE + 4 * cbfrec::BLK;
             unsigned char* img_lo = sm + buf * STAGE + 5 * cbfrec::BLK;
-#pragma unroll 2
-            for (int c8 = 0; c8 < 8; ++c8) {
+            for (int c8 = part; c8 < 8; c8 += nparts) {
               float x[8];
 #pragma unroll
               for (int e = 0; e < 8; ++e) {
@@ -528,7 +602,8 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
         }
       }
     }
-    // final epilogue: accumulators -> this CTA's gradient slice
+    if (warp < 6) {
+    // final epilogue (warps 2..5): accumulators -> this CTA's gradient slice
     mbar_wait(&done, 0);
     fence_after_sync();
     const int q = warp & 3;                             // TMEM lane quadrant this warp may read
@@ -577,6 +652,7 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
         if (lane == 0) accum16(gp + offB3 + c0, 1, v);
       }
     }
+    }
   }
   fence_before_sync();
   __syncthreads();
@@ -588,18 +664,19 @@ int wgrad_tc_node(const unsigned char* rec, long long ntiles, float* slices, int
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfwg::smem_bytes));
   wgrad_tc_kernel<3><<<grid, cbfwg::THREADS, cbfwg::smem_bytes, st>>>(rec, cnrec::BYTES, ntiles, slices, MACBF_CTRL_PARAMS, CT_NW3,
                                                                      CT_NB3, CT_NW2, CT_NB2, CT_NW1, 132, nullptr, nullptr, 0, 0,
-                                                                     nullptr);
+                                                                     nullptr, WgradRoute{});
   MACBF_CHECK_LAUNCH("wgrad_tc_kernel<node>");
   return 0;
 }
 
 // controller edge net (ctrl_edge_bwd_tc.cu): one 96-KB stage per tile record
 int wgrad_tc_ctrl(const unsigned char* rec, size_t rec_stride, long long ntiles, float* slices, int grid, cudaStream_t st,
-                  const float* params, uint32_t xoff) {
+                  const float* params, uint32_t xoff, const float* dpool, const uint8_t* argk, int K, int TA, long long agents,
+                  long long tile0) {
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfwg::smem_bytes));
-  wgrad_tc_kernel<1><<<grid, cbfwg::THREADS, cbfwg::smem_bytes, st>>>(rec, rec_stride, ntiles, slices, MACBF_CTRL_PARAMS, 0, 0,
+  wgrad_tc_kernel<1><<<grid, cbfwg::MAX_THREADS, cbfwg::smem_bytes, st>>>(rec, rec_stride, ntiles, slices, MACBF_CTRL_PARAMS, 0, 0,
                                                                      CT_EW2, CT_EB2, 0, 0, params + CT_EW1, params + CT_EB1, 5, xoff,
-                                                                     nullptr);
+                                                                     nullptr, WgradRoute{dpool, argk, K, TA, agents, tile0});
   MACBF_CHECK_LAUNCH("wgrad_tc_kernel<ctrl>");
   return 0;
 }
@@ -652,9 +729,9 @@ int cbf_backward_tc(const float* states, const float* obstacles, const int32_t* 
     cbf_dgrad_tc_kernel<<<grid, cbfdg::THREADS, cbfdg::smem_bytes, st>>>(idx, params, N, K, agents, TA, t0, t1, rec, slices,
                                                                         grad_states);
     MACBF_CHECK_LAUNCH("cbf_dgrad_tc_kernel");
-    wgrad_tc_kernel<2><<<grid, cbfwg::THREADS, cbfwg::smem_bytes, st>>>(rec, cbfrec::BYTES, ct, slices, MACBF_CBF_PARAMS, CBF_W3,
+    wgrad_tc_kernel<2><<<grid, 64 + 256, cbfwg::smem_bytes, st>>>(rec, cbfrec::BYTES, ct, slices, MACBF_CBF_PARAMS, CBF_W3,
                                                                        CBF_B3, CBF_W2, CBF_B2, 0, 0, params + CBF_W1, params + CBF_B1,
-                                                                       6, cbfrec::XREC, params + CBF_W4);
+                                                                       6, cbfrec::XREC, params + CBF_W4, WgradRoute{});
     MACBF_CHECK_LAUNCH("wgrad_tc_kernel<cbf>");
   }
   reduce_partials_kernel<<<(MACBF_CBF_PARAMS + 255) / 256, 256, 0, st>>>(slices, NUM_SMS, MACBF_CBF_PARAMS, grad_params);

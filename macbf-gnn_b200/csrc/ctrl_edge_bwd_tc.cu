@@ -6,13 +6,12 @@
 // else 0 (torch.max backward through "* mask" and ReLU).  ctrl_edge_bwd_tc_kernel, TWO co-resident CTAs per SM
 // (8 worker warps + 1 MMA-issue warp, 256 TMEM columns each - they hide each other's latencies), per tile of
 // 128 edge rows (floor(128/K) agents; thread = row r, 32 of every 64 channels):
-//   workers   edge features (controller.py:33-40); a1 = relu(W1 x + b1) on the CUDA cores (5 -> 64): ReLU bits,
-//             bf16 hi/lo image (wgrad operand)
-//   workers   per 64-channel chunk: dZ2 from winners + d/dpool: tf32 hi/lo -> TMEM, bf16 hi/lo image
+//   workers   edge features (controller.py:33-40) -> record; ReLU bits of a1 = relu(W1 x + b1) (5 -> 64, CUDA cores)
+//   workers   per 64-channel chunk: dZ2 from winners + d/dpool: tf32 hi/lo -> TMEM
 //   MMA       dA1 += dZ2[:, chunk] W2[chunk, :]  (A from TMEM, B = W2^T in shared memory, 3xTF32)
 //   workers   dZ1 = dA1 [z1 > 0]; dW1, db1; d/dstates through [dx, dy, dvx, dvy] (fp32 atomics)
-// dW2 = dZ2^T a1 and db2 are GEMMs over the EDGES: wgrad_tc_kernel<1> (cbf_bwd_tc.cu) reads the two images
-// with bulk copies (bf16x3, fp32 accumulation in TMEM).
+// dW2 = dZ2^T a1 and db2 are GEMMs over the EDGES: wgrad_tc_kernel<1> (cbf_bwd_tc.cu) rebuilds both operand images on
+// chip (a1 from the recorded edge features, dZ2 from d/dpool and the winners: bf16x3, fp32 accumulation in TMEM).
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -21,7 +20,8 @@
 namespace macbf {
 
 int wgrad_tc_ctrl(const unsigned char* rec, size_t rec_stride, long long ntiles, float* slices, int grid, cudaStream_t st,
-                  const float* params, uint32_t xoff);
+                  const float* params, uint32_t xoff, const float* dpool, const uint8_t* argk, int K, int TA, long long agents,
+                  long long tile0);
 
 namespace cebtc {
 constexpr int WORKERS = 256;
@@ -29,9 +29,9 @@ constexpr int THREADS = WORKERS + 32;
 constexpr int R = 128;
 // TMEM (256 columns): [0,64) dZ2_hi of the current chunk  [64,128) dZ2_lo  [128,192) dA1
 constexpr uint32_t C_ZHI = 0, C_ZLO = 64, C_DA1 = 128;
-constexpr uint32_t BLK = 128 * 128;
-// record: dZ2 images (64 KB), then the edge features float[128][8] from which the wgrad kernel rebuilds the a1 images
-constexpr uint32_t Z2_HI = 0, Z2_LO = 2 * BLK, XREC = 4 * BLK, REC_BYTES = 6 * BLK;
+// record: just the edge features float[128][8] - the wgrad kernel rebuilds both of its operand images (a1 from the
+// features, dZ2 from d/dpool and the winners)
+constexpr uint32_t XREC = 0, REC_BYTES = 128 * 8 * 4;
 constexpr int DZS = 132;                       // 16-B aligned rows, = 4 (mod 32) words: conflict-free stores and LDS.128
 constexpr int oW2THI = 0;                      // B[n = in (64)][k = out (128)] = W2[k][n]
 constexpr int oW2TLO = oW2THI + 64 * 128;
@@ -165,7 +165,6 @@ ctrl_edge_bwd_tc_kernel(const float* __restrict__ states, const float* __restric
         }
 #pragma unroll
         for (int pair = 0; pair < 2; ++pair) {
-          uint4 bh[2], bl[2];
           float4 dp[4];
 #pragma unroll
           for (int v4 = 0; v4 < 4; ++v4)
@@ -186,10 +185,7 @@ ctrl_edge_bwd_tc_kernel(const float* __restrict__ states, const float* __restric
             }
             tmem_st8(tlane + C_ZHI + c0 + pair * 16 + half * 8, hi);
             tmem_st8(tlane + C_ZLO + c0 + pair * 16 + half * 8, lo);
-            bf16_split8(x, bh[half], bl[half]);
           }
-          img_store16(tr + Z2_HI + c * BLK, r, 2 * cgrp + pair, bh[0], bh[1]);
-          img_store16(tr + Z2_LO + c * BLK, r, 2 * cgrp + pair, bl[0], bl[1]);
         }
         wait_st();
         warp_arrive_after_tmem(&z_full);
@@ -261,7 +257,7 @@ ctrl_edge_bwd_tc_kernel(const float* __restrict__ states, const float* __restric
 
 // ---- host side ----
 namespace {
-constexpr long long CE_CHUNK_TILES = 16384;    // 16384 x 96 KB = 1.5 GB of records per chunk
+constexpr long long CE_CHUNK_TILES = 1 << 20;   // records are 4 KB per tile
 constexpr int CE_GRID = 2 * NUM_SMS;           // two co-resident CTAs per SM
 static inline size_t a1k(size_t x) { return (x + 1023) & ~(size_t)1023; }
 inline long long chunk_tiles() {               // MACBF_BWD_CHUNK_TILES=<n>: see cbf_bwd_tc.cu
@@ -302,7 +298,8 @@ int ctrl_edge_bwd_tc(const float* states, const float* obstacles, const int32_t*
                                                                            agents, TA, t0, t1, rec, slices, grad_states);
     MACBF_CHECK_LAUNCH("ctrl_edge_bwd_tc_kernel");
     const int wgrid = (int)(ct < NUM_SMS ? ct : (long long)NUM_SMS);
-    if (int rc = wgrad_tc_ctrl(rec, cebtc::REC_BYTES, ct, slices, wgrid, st, params, cebtc::XREC)) return rc;
+    if (int rc = wgrad_tc_ctrl(rec, cebtc::REC_BYTES, ct, slices, wgrid, st, params, cebtc::XREC, dpool, argk, K, TA, agents, t0))
+      return rc;
   }
   return 0;
 }
