@@ -1,10 +1,12 @@
 // Per-tile record shared by the three kernels of the tensor-core CBF backward (cbf_bwd_tc.cu):
-//   K2b-1  cbf_forward_tc_kernel<true>   recompute + dump activations         (writes A1, A2, masks, xrec, gm)
-//   K2b-2  cbf_dgrad_tc_kernel           delta chain on the tensor core       (writes dZ3, dZ2)
-//   K2b-3  cbf_wgrad_tc_kernel           dW3, dW2, db3, db2 = GEMMs over edges (reads the four images)
+//   K2b-1  cbf_forward_tc_kernel<true>   recompute + dump                      (writes A2, masks, xrec, gm)
+//   K2b-2  cbf_dgrad_tc_kernel           delta chain on the tensor core       (writes dZ2)
+//   K2b-3  wgrad_tc_kernel<2>            dW3, dW2, db3, db2 = GEMMs over edges (reads A2, dZ2; rebuilds a1, dZ3)
 // A tile is 128 edge rows.  Activations / deltas are stored as bf16 (hi, lo) operand images in exactly
 // the shared-memory layout the wgrad MMAs read (MN-major SWIZZLE_128B: per 64-channel block 128 rows x
 // 128 B, 16-byte chunk c of row e at position c ^ (e & 7)), so K2b-3 stages them with plain bulk copies.
+// The slots of the a1 and dZ3 images exist in the record layout (and in the stage buffers) but are not
+// written to memory: the wgrad kernel rebuilds them on chip from XREC, GM and the layer-3 ReLU bits.
 #pragma once
 #include <stdint.h>
 

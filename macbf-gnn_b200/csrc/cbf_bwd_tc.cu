@@ -3,18 +3,19 @@
 // Three kernels per chunk of tiles (a tile = 128 edge rows; records in cbf_bwd_layout.cuh):
 //
 //   1. cbf_forward_tc_kernel<true> (cbf_tc.cu)  recompute the forward on the tensor core; dump the
-//      layer-1/2 activations as bf16 hi/lo operand images, the ReLU bit masks, the edge features and
+//      layer-2 activations as bf16 hi/lo operand images, the ReLU bit masks, the edge features and
 //      gm = dL/dh * radius mask; accumulate dW4, db4.
 //   2. cbf_dgrad_tc_kernel   delta chain  dZ3 = gm w4 [z3>0] -> dA2 = dZ3 W3 -> dZ2 = dA2 [z2>0] -> dA1 = dZ2 W2
 //      -> dZ1 = dA1 [z1>0]: the two GEMMs are 3xTF32 tcgen05.mma with A (deltas) in tensor memory and
 //      B = the TRANSPOSED weights resident in shared memory (same machinery as the forward's layers 2, 3).
-//      dZ3, dZ2 are dumped as bf16 hi/lo images; dW1, db1 and d/dstates (6 features, fp32 atomics) are
-//      finished here on the CUDA cores.
+//      dZ2 is dumped as bf16 hi/lo images; dW1, db1 and d/dstates (6 features, fp32 atomics) are finished
+//      here on the CUDA cores.
 //   3. wgrad_tc_kernel   dW3^T = A2^T dZ3, dW2 = dZ2^T A1, db3, db2: GEMMs whose contraction index is the
-//      EDGE, so both operands come from shared memory as MN-major bf16 images, staged by bulk copies
-//      (cp.async.bulk + mbarrier, two 96-KB stages), 3 products (hi*hi, lo*hi, hi*lo) per GEMM with fp32
-//      accumulation in tensor memory across all tiles of the CTA; bias gradients ride along as GEMMs against
-//      a constant block of ones.  HBM-bound (1.5 KB per edge).
+//      EDGE, so both operands come from shared memory as MN-major bf16 images: the expensive ones (A2, dZ2) are
+//      staged by bulk copies (cp.async.bulk + mbarrier, two 96-KB stage buffers), the cheap ones (a1 from the
+//      edge features, dZ3 from gm and the ReLU bits) are rebuilt on chip by generator warps; 3 products (hi*hi,
+//      lo*hi, hi*lo) per GEMM with fp32 accumulation in tensor memory across all tiles of the CTA; bias
+//      gradients ride along as GEMMs against a constant block of ones.  1 KB of HBM traffic per edge.
 //
 // Every kernel adds into its CTA's private slice of the gradient partial buffer (flat state_dict layout);
 // reduce_partials_kernel adds the slices in order, so parameter gradients are run-to-run deterministic.
