@@ -113,3 +113,24 @@ def test_ttc_topk_matches_dense_predicate():
     # dense numpy path promotes through float64 eye; compare away from the decision boundary
     gathered = dense[np.arange(128)[:, None], idx.numpy(), 0]
     assert (m == gathered).mean() > 0.995
+
+
+def test_stream_scenario_generator_keeps_the_reference_guarantees():
+    """oracle.generate_data_stream (the sequential restatement the device generator is checked against, bit for bit, in
+    tests/test_gpu_scenario.py) produces scenarios with the properties of core.py:45-71."""
+    import oracle.macbf_oracle as O
+    n, thres = 48, 0.07
+    s, g = O.generate_data_stream(1234, 0, n, thres)
+    s2, g2 = O.generate_data_stream(1234, 0, n, thres)
+    assert np.array_equal(s, s2) and np.array_equal(g, g2)                    # a pure function of (seed, env)
+    other, _ = O.generate_data_stream(1234, 1, n, thres)
+    assert not np.array_equal(s, other)
+    side = np.sqrt(max(1.0, n / 8.0))
+    assert s.dtype == np.float32 and s.shape == (n, 4) and g.shape == (n, 2)
+    assert np.all(s[:, 2:] == 0) and s[:, :2].min() >= 0 and s[:, :2].max() < side
+    assert np.abs(g - s[:, :2]).max() <= 0.5 + 1e-6
+    for p in (s[:, :2], g):
+        d = np.linalg.norm(p[:, None, :] - p[None, :, :], axis=2) + np.eye(n) * 10
+        assert d.min() > thres
+        assert np.linalg.norm(p, axis=1).min() > thres                         # unplaced rows sit at the origin
+    assert O.generate_data_stream(1, 0, 64, 0.2, n_candidates=64) is None     # too few candidates: reported, not padded
