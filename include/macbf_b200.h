@@ -169,7 +169,7 @@ int macbf_loss_backward(const float* states, const float* goals, const float* h,
  * accumulated into when non-NULL (caller zeroes it).  Activations are recomputed from
  * states + idx; nothing from the forward needs to be kept.  REPAIRED semantics only.
  * Scratch holds the per-CTA gradient slices and the tile records the tensor-core kernels hand to each
- * other (bf16 operand images, 205 KB per 128 edges, at most 8192 tiles = 1.6 GB at a time; larger
+ * other (bf16 operand images, 141 KB per 128 edges, at most 8192 tiles = 1.1 GB at a time; larger
  * problems are processed in chunks), so ask for its size - it is not small. */
 size_t macbf_cbf_backward_scratch_bytes(int B, int N, int K);
 int macbf_cbf_backward(const float* states, const float* obstacles, const int32_t* idx,

@@ -374,7 +374,7 @@ __global__ void __launch_bounds__(cbfwg::MAX_THREADS, 1)
 wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long long ntiles, float* __restrict__ slices, int P,
                 int offW3, int offB3, int offW2, int offB2, int offW1, int ldW1, const float* __restrict__ gen_w1,
                 const float* __restrict__ gen_b1, int gen_nf, uint32_t gen_xoff, const float* __restrict__ gen_w4,
-                WgradRoute route) {
+                WgradRoute route, uint32_t rec_stage) {
   using namespace cbfwg;
   using namespace tc;
   extern __shared__ unsigned char smem_raw[];
@@ -417,7 +417,7 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
         const uint32_t buf = n & 1;
         if (n >= 2) mbar_wait(&empty[buf], ((n >> 1) - 1) & 1);
         if (elect_one()) {
-          const unsigned char* src = rec + (size_t)tile * rec_stride + (size_t)s * STAGE;
+          const unsigned char* src = rec + (size_t)tile * rec_stride + (size_t)s * rec_stage;   // bytes of a stage in the record
           // with `gen` the last third of a G2-type stage (the a1 images) is produced on chip
           const int parts = genA ? 0 : ((gen && ((NST == 1) || s == 1)) || (gen3 && s == 0)) ? 2 : 3;
           mbar_expect_tx(&full[buf], parts * (STAGE / 3));
@@ -665,7 +665,7 @@ int wgrad_tc_node(const unsigned char* rec, long long ntiles, float* slices, int
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfwg::smem_bytes));
   wgrad_tc_kernel<3><<<grid, cbfwg::THREADS, cbfwg::smem_bytes, st>>>(rec, cnrec::BYTES, ntiles, slices, MACBF_CTRL_PARAMS, CT_NW3,
                                                                      CT_NB3, CT_NW2, CT_NB2, CT_NW1, 132, nullptr, nullptr, 0, 0,
-                                                                     nullptr, WgradRoute{});
+                                                                     nullptr, WgradRoute{}, cnrec::STAGE);
   MACBF_CHECK_LAUNCH("wgrad_tc_kernel<node>");
   return 0;
 }
@@ -677,14 +677,14 @@ int wgrad_tc_ctrl(const unsigned char* rec, size_t rec_stride, long long ntiles,
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfwg::smem_bytes));
   wgrad_tc_kernel<1><<<grid, cbfwg::MAX_THREADS, cbfwg::smem_bytes, st>>>(rec, rec_stride, ntiles, slices, MACBF_CTRL_PARAMS, 0, 0,
                                                                      CT_EW2, CT_EB2, 0, 0, params + CT_EW1, params + CT_EB1, 5, xoff,
-                                                                     nullptr, WgradRoute{dpool, argk, K, TA, agents, tile0});
+                                                                     nullptr, WgradRoute{dpool, argk, K, TA, agents, tile0}, 0);
   MACBF_CHECK_LAUNCH("wgrad_tc_kernel<ctrl>");
   return 0;
 }
 
 // ================================ host side ================================
 namespace {
-constexpr long long CHUNK_TILES = 8192;        // records of one chunk: 8192 x 205 KB = 1.6 GB
+constexpr long long CHUNK_TILES = 8192;        // records of one chunk: 8192 x 141 KB = 1.1 GB
 // MACBF_BWD_CHUNK_TILES=<n> shrinks the chunk (tests exercise the multi-chunk path on small problems)
 inline long long chunk_tiles() {
   const char* e = getenv("MACBF_BWD_CHUNK_TILES");
@@ -732,7 +732,8 @@ int cbf_backward_tc(const float* states, const float* obstacles, const int32_t* 
     MACBF_CHECK_LAUNCH("cbf_dgrad_tc_kernel");
     wgrad_tc_kernel<2><<<grid, 64 + 256, cbfwg::smem_bytes, st>>>(rec, cbfrec::BYTES, ct, slices, MACBF_CBF_PARAMS, CBF_W3,
                                                                        CBF_B3, CBF_W2, CBF_B2, 0, 0, params + CBF_W1, params + CBF_B1,
-                                                                       6, cbfrec::XREC, params + CBF_W4, WgradRoute{});
+                                                                       6, cbfrec::XREC, params + CBF_W4, WgradRoute{},
+                                                                       cbfrec::REC_STAGE);
     MACBF_CHECK_LAUNCH("wgrad_tc_kernel<cbf>");
   }
   reduce_partials_kernel<<<(MACBF_CBF_PARAMS + 255) / 256, 256, 0, st>>>(slices, NUM_SMS, MACBF_CBF_PARAMS, grad_params);
