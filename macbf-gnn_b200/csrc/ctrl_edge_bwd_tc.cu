@@ -124,6 +124,10 @@ ctrl_edge_bwd_tc_kernel(const float* __restrict__ states, const float* __restric
 #pragma unroll
         for (int h = 0; h < 2; ++h)
           wk[c][h] = live ? __ldg(reinterpret_cast<const uint4*>(argk + ga * 128 + c * 64 + c0) + h) : make_uint4(~0u, ~0u, ~0u, ~0u);
+      if (live) {   // this thread's two 128-byte lines of d/dpool: on their way to L1 while layer 1 is evaluated
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(dpool + ga * 128 + c0));
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(dpool + ga * 128 + 64 + c0));
+      }
       // ---- edge features (controller.py:33-40) ----
       float f[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
       long long gj = -1;
