@@ -62,8 +62,9 @@ int macbf_neighbor_count(int N, int M, int top_k);
 int macbf_neighbor_topk(const float* states, const float* obstacles, int B, int N, int M,
                         int top_k, int32_t* idx, void* stream);
 
-/* Same result through a uniform-grid search (used when top_k <= 32 and N + M >= 256; otherwise
- * this is the brute-force kernel and needs no workspace).  workspace: macbf_neighbor_workspace_bytes
+/* Same result through an exact uniform-grid search (used when top_k <= 128 and the env has enough candidates,
+ * i.e. whenever macbf_neighbor_workspace_bytes is non-zero; otherwise this is the brute-force kernel and needs
+ * no workspace).  workspace: macbf_neighbor_workspace_bytes
  * bytes, 16-byte aligned, contents private. */
 size_t macbf_neighbor_workspace_bytes(int B, int N, int M, int top_k);
 int macbf_neighbor_topk_ws(const float* states, const float* obstacles, int B, int N, int M,
@@ -128,7 +129,9 @@ int macbf_ttc_dense(const float* states, int B, int N, double dist_min_sq, doubl
  *   4 loss_dang_deriv, 5 loss_safe_deriv, 6 acc_dang_deriv, 7 acc_safe_deriv, 8 loss_action,
  *   9 total = 10*(2*l0 + l1 + 2*l4 + l5 + 0.01*l8), 10 n_dang, 11 n_safe.
  * h_next may be NULL (derivative terms = 0), u/goals may be NULL (action term = 0).
- * ttc_mask [B,N,K] is written (A9 is evaluated inside).  scratch: macbf_loss_scratch_bytes. */
+ * ttc_mask [B,N,K] is written (A9 is evaluated inside).  scratch: macbf_loss_scratch_bytes.
+ * Alignment (checked; a violation is an error code, nothing is launched): states 16 bytes, goals / u /
+ * obstacles 8 bytes. */
 size_t macbf_loss_scratch_bytes(int B, int N, int K);
 int macbf_loss_forward(const float* states, const float* goals, const float* obstacles,
                        const int32_t* idx, const float* h, const float* h_next, const float* u,
@@ -147,7 +150,9 @@ int macbf_loss_forward(const float* states, const float* goals, const float* obs
  * the array's device address (cudaGetSymbolAddress, with that device current); make that first
  * call before starting any stream capture.  All calls on a device share the one array: it keeps
  * the previous call's partial sums (every slot read is rewritten first, nothing needs clearing),
- * and two calls whose kernels overlap on the GPU (different streams, no ordering) race on it. */
+ * and two calls whose kernels overlap on the GPU (different streams, no ordering) race on it.
+ * The array is looked up for the CURRENT device: the buffers and the stream must belong to it (a states
+ * pointer owned by another device is rejected).  Same argument and alignment checks as macbf_loss_forward. */
 #define MACBF_LOSS_NOALLOC_MAX_FLOATS 65536
 int macbf_loss_forward_noalloc(const float* states, const float* goals, const float* obstacles,
                                const int32_t* idx, const float* h, const float* h_next, const float* u,

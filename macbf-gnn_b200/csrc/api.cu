@@ -45,6 +45,8 @@ int ttc_dense(const float*, int, int, double, double, int32_t*, uint8_t*, cudaSt
 size_t scenario_workspace_bytes(int, int, int);
 int scenario_generate(unsigned long long, int, int, int, double, float*, float*, int32_t*, void*, size_t, cudaStream_t);
 size_t loss_scratch_bytes(int, int, int);
+int loss_validate(const char*, const float*, const float*, const float*, const int32_t*, const float*, const float*, int,
+                  int, int, int, const uint8_t*, const float*);
 int loss_forward(const float*, const float*, const float*, const int32_t*, const float*, const float*, const float*,
                  int, int, int, int, double, double, double, double, uint8_t*, float*, void*, size_t, cudaStream_t);
 int loss_backward(const float*, const float*, const float*, const float*, const float*, const uint8_t*, const float*,
@@ -168,10 +170,8 @@ int macbf_loss_forward(const float* states, const float* goals, const float* obs
                        double dist_min_thres, double ttc, double dt, double alpha, uint8_t* ttc_mask_out,
                        float* scalars, void* scratch, size_t scratch_bytes, void* stream) {
   const char* fn = "macbf_loss_forward";
-  if (check_dims(fn, B, N, M, K)) return 1;
-  REQ_PTR(fn, states); REQ_PTR(fn, idx); REQ_PTR(fn, h); REQ_PTR(fn, ttc_mask_out); REQ_PTR(fn, scalars);
-  REQ_PTR(fn, scratch); REQ_A16(fn, states);
-  MACBF_CHECK_ARG(M == 0 || obstacles != nullptr, "%s: obstacles is NULL but M=%d", fn, M);
+  if (loss_validate(fn, states, goals, obstacles, idx, h, u, B, N, M, K, ttc_mask_out, scalars)) return 1;
+  REQ_PTR(fn, scratch);
   return loss_forward(states, goals, obstacles, idx, h, h_next, u, B, N, M, K, dist_min_thres, ttc, dt, alpha,
                       ttc_mask_out, scalars, scratch, scratch_bytes, (cudaStream_t)stream);
 }

@@ -206,6 +206,27 @@ size_t loss_scratch_bytes(int B, int N, int K) {
   return (size_t)B * loss_chunks(N, K) * LOSS_NACC * sizeof(float);
 }
 
+// Argument checks shared by macbf_loss_forward and macbf_loss_forward_noalloc: loss_partial_kernel reads states as
+// float4 and goals / u as float2, so a misaligned buffer must come back as an error code, not as a sticky fault.
+int loss_validate(const char* fn, const float* states, const float* goals, const float* obstacles, const int32_t* idx,
+                  const float* h, const float* u, int B, int N, int M, int K, const uint8_t* mask,
+                  const float* scalars) {
+  MACBF_CHECK_ARG(B >= 1 && B <= 65535, "%s: B=%d out of range [1,65535]", fn, B);
+  MACBF_CHECK_ARG(N >= 1 && M >= 0, "%s: bad extents N=%d M=%d", fn, N, M);
+  MACBF_CHECK_ARG(K >= 1 && K <= MACBF_MAX_K && K <= N + M, "%s: K=%d out of range (max %d, candidates %d)", fn, K,
+                  MACBF_MAX_K, N + M);
+  MACBF_CHECK_ARG((long long)B * N * K < (1ll << 40), "%s: problem too large", fn);
+  MACBF_CHECK_ARG(states != nullptr && idx != nullptr && h != nullptr && mask != nullptr && scalars != nullptr,
+                  "%s: states, idx, h, ttc_mask and scalars must not be NULL", fn);
+  MACBF_CHECK_ARG(M == 0 || obstacles != nullptr, "%s: obstacles is NULL but M=%d", fn, M);
+  MACBF_CHECK_ARG((((uintptr_t)states) & 15) == 0, "%s: states must be 16-byte aligned", fn);
+  MACBF_CHECK_ARG((((uintptr_t)goals) & 7) == 0 && (((uintptr_t)u) & 7) == 0 && (((uintptr_t)obstacles) & 7) == 0,
+                  "%s: goals, u and obstacles must be 8-byte aligned", fn);
+  MACBF_CHECK_ARG(((((uintptr_t)idx) | ((uintptr_t)h) | ((uintptr_t)scalars)) & 3) == 0,
+                  "%s: idx, h and scalars must be 4-byte aligned", fn);
+  return 0;
+}
+
 int loss_forward(const float* states, const float* goals, const float* obstacles, const int32_t* idx,
                  const float* h, const float* h_next, const float* u, int B, int N, int M, int K,
                  double dist_min, double ttc, double dt, double alpha, uint8_t* mask, float* scalars,
@@ -289,13 +310,19 @@ extern "C" int macbf_loss_forward_noalloc(const float* states, const float* goal
                                           double alpha, uint8_t* ttc_mask_out, float* scalars, void* stream) {
   using namespace macbf;
   const char* fn = "macbf_loss_forward_noalloc";
-  MACBF_CHECK_ARG(B >= 1 && B <= 65535, "%s: B=%d out of range [1,65535]", fn, B);
-  MACBF_CHECK_ARG(N >= 1 && M >= 0, "%s: bad extents N=%d M=%d", fn, N, M);
-  MACBF_CHECK_ARG(K >= 1 && K <= MACBF_MAX_K && K <= N + M, "%s: K=%d out of range (max %d, candidates %d)", fn, K,
-                  MACBF_MAX_K, N + M);
-  MACBF_CHECK_ARG(states != nullptr && idx != nullptr && h != nullptr && ttc_mask_out != nullptr && scalars != nullptr,
-                  "%s: states, idx, h, ttc_mask and scalars must not be NULL", fn);
-  MACBF_CHECK_ARG(M == 0 || obstacles != nullptr, "%s: obstacles is NULL but M=%d", fn, M);
+  if (loss_validate(fn, states, goals, obstacles, idx, h, u, B, N, M, K, ttc_mask_out, scalars)) return 1;
+  // The fixed array exists once per device and its address is looked up for the CURRENT device, so the buffers
+  // (and the stream) have to belong to the current device: refuse anything else instead of mixing two GPUs.
+  {
+    int cur = -1;
+    MACBF_CHECK_CUDA(cudaGetDevice(&cur));
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, states) == cudaSuccess && at.type == cudaMemoryTypeDevice)
+      MACBF_CHECK_ARG(at.device == cur, "%s: states lives on device %d but device %d is current; make the buffers' "
+                      "device current (cudaSetDevice) before the call", fn, at.device, cur);
+    else
+      (void)cudaGetLastError();
+  }
   const size_t need = loss_scratch_bytes(B, N, K);
   MACBF_CHECK_ARG(need <= sizeof(float) * (size_t)MACBF_LOSS_NOALLOC_MAX_FLOATS,
                   "%s: problem too large for the built-in scratch: B=%d N=%d K=%d needs %zu bytes of partial sums, "

@@ -190,10 +190,13 @@ int dense_topk(const float* x, int N, int C, int F, int K, int32_t* idx, cudaStr
   return 0;
 }
 
-// N + M <= top_k: every candidate, in index order (core.py:236-237, repair F3).
-__global__ void knn_all_kernel(int total, int C, int32_t* __restrict__ idx_out) {
-  int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t < total) idx_out[t] = t % C;
+// N + M <= top_k: every candidate, in index order (core.py:236-237, repair F3).  Only the rows [q_begin, q_end) of
+// every env are written, so the parts of macbf_neighbor_topk_part stay a disjoint cover here too.
+__global__ void knn_all_kernel(long long total, int N, int C, int q_begin, int q_end, int32_t* __restrict__ idx_out) {
+  long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= total) return;
+  const int row = (int)((t / C) % N);
+  if (row >= q_begin && row < q_end) idx_out[t] = (int32_t)(t % C);
 }
 
 template <int S, int Q>
@@ -212,8 +215,10 @@ int neighbor_topk(const float* states, const float* obstacles, int B, int N, int
                   int32_t* idx, cudaStream_t st) {
   const int C = N + M;
   if (C <= top_k) {
-    int total = B * N * C;                         // tiny problem: every part writes every row (identical values)
-    knn_all_kernel<<<(total + 255) / 256, 256, 0, st>>>(total, C, idx);
+    const long long total = (long long)B * N * C;
+    int q_begin, q_end;
+    query_range(N, &q_begin, &q_end);
+    knn_all_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(total, N, C, q_begin, q_end, idx);
     MACBF_CHECK_LAUNCH("knn_all_kernel");
     return 0;
   }

@@ -11,20 +11,11 @@ import torch
 
 from . import ops
 
-_pack_cache = {}
-
-
 def pack_params(params: Sequence[torch.Tensor]) -> torch.Tensor:
-    """state_dict-ordered parameters -> one flat fp32 buffer (the C ABI's layout).  Cached on
-    (storage, version) so an unchanged module is not repacked on every call."""
-    key = tuple((p.data_ptr(), p._version) for p in params)
-    slot = id(params[0])
-    hit = _pack_cache.get(slot)
-    if hit is not None and hit[0] == key:
-        return hit[1]
-    flat = torch.cat([p.detach().reshape(-1) for p in params]).contiguous()
-    _pack_cache[slot] = (key, flat)
-    return flat
+    """state_dict-ordered parameters -> one flat fp32 buffer (the C ABI's layout).  Repacked on every call:
+    the copy is 51k floats, and no cache key sees in-place edits made through `p.data` (they do not bump
+    `_version`), so a cache could silently serve stale weights."""
+    return torch.cat([p.detach().reshape(-1) for p in params]).contiguous()
 
 
 def _split_like(flat: torch.Tensor, params: Sequence[torch.Tensor]):

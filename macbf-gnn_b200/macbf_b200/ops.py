@@ -4,6 +4,7 @@ torch is used for device memory, streams and shapes only; all arithmetic happens
 libmacbf_b200.so.  Every function takes CUDA fp32 tensors with a leading env-batch dim
 (states [B,N,4], goals [B,N,2], obstacles [B,M,2] or None) and launches on the current stream.
 """
+import functools
 from typing import Optional, Tuple
 
 import torch
@@ -26,6 +27,8 @@ ALPHA_CBF = 1.0
 
 
 def _need_cuda(*tensors):
+    """All tensor arguments must be CUDA tensors of one device with a supported dtype."""
+    dev = None
     for t in tensors:
         if t is None:
             continue
@@ -33,6 +36,24 @@ def _need_cuda(*tensors):
             raise _lib.MacbfError("macbf_b200 has no CPU path: tensors must live on a CUDA device")
         if t.dtype not in (torch.float32, torch.int32, torch.uint8):
             raise _lib.MacbfError(f"unsupported dtype {t.dtype}")
+        if dev is None:
+            dev = t.device
+        elif t.device != dev:
+            raise _lib.MacbfError(f"tensor arguments live on different devices ({dev} and {t.device})")
+
+
+def _on_device_of(fn):
+    """Run `fn` with the device of its first tensor argument current: the kernels launch on that device's current
+    stream (not on whichever device happens to be current in the caller), and library state that is per device
+    (macbf_loss_forward_noalloc's scratch address) resolves to the device that owns the buffers."""
+    @functools.wraps(fn)
+    def wrapped(*args, **kwargs):
+        for a in list(args) + list(kwargs.values()):
+            if isinstance(a, torch.Tensor) and a.is_cuda:
+                with torch.cuda.device(a.device):
+                    return fn(*args, **kwargs)
+        return fn(*args, **kwargs)
+    return wrapped
 
 
 def _c(t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
@@ -63,6 +84,7 @@ def neighbor_count(N: int, M: int, top_k: int) -> int:
     return min(top_k, N + M)
 
 
+@_on_device_of
 def neighbor_topk(states: torch.Tensor, top_k: int = TOP_K, obstacles: Optional[torch.Tensor] = None,
                   brute_force: bool = False) -> torch.Tensor:
     """core.py:234-250 -> idx [B,N,K_eff] int32 (uniform-grid search when it applies, else brute force)."""
@@ -83,6 +105,7 @@ def neighbor_topk(states: torch.Tensor, top_k: int = TOP_K, obstacles: Optional[
     return idx
 
 
+@_on_device_of
 def neighbor_topk_part(states, top_k, part, nparts, obstacles=None, out=None):
     """Rows of the neighbour graph owned by part `part` of `nparts` (macbf_neighbor_topk_part); the other rows of
     `out` (default: zeros) are left as they are.  Summing the results of all parts gives neighbor_topk."""
@@ -112,6 +135,7 @@ def neighbor_topk_sharded(states, top_k, obstacles=None, group=None):
     return idx
 
 
+@_on_device_of
 def dense_topk(x: torch.Tensor, k: int) -> torch.Tensor:
     """core.remove_distant_agents' selection on a materialised pair tensor x [N,C,F] -> idx [N,k] int32."""
     _need_cuda(x)
@@ -123,6 +147,7 @@ def dense_topk(x: torch.Tensor, k: int) -> torch.Tensor:
     return idx
 
 
+@_on_device_of
 def cbf_forward(states, idx, cbf_params, obstacles=None, semantics=REPAIRED, dist_min_thres=DIST_MIN_THRES,
                 obs_radius=OBS_RADIUS) -> torch.Tensor:
     """cbf.py:21-45 -> h [B,N,K]."""
@@ -138,6 +163,7 @@ def cbf_forward(states, idx, cbf_params, obstacles=None, semantics=REPAIRED, dis
     return h
 
 
+@_on_device_of
 def controller_forward(states, goals, idx, ctrl_params, obstacles=None, semantics=REPAIRED, obs_radius=OBS_RADIUS,
                        dt=TIME_STEP, want_next=True) -> Tuple[torch.Tensor, Optional[torch.Tensor], torch.Tensor]:
     """controller.py:31-63 + train.py:70 -> (u [B,N,2], s_next [B,N,4] | None, pool [B,N,128])."""
@@ -157,6 +183,7 @@ def controller_forward(states, goals, idx, ctrl_params, obstacles=None, semantic
     return u, s_next, pool
 
 
+@_on_device_of
 def ttc_mask(states, idx, obstacles=None, dist_min_thres=DIST_MIN_THRES, ttc=TIME_TO_COLLISION) -> torch.Tensor:
     """core.py:187-209 -> uint8 [B,N,K]."""
     _need_cuda(states, idx, obstacles)
@@ -170,6 +197,7 @@ def ttc_mask(states, idx, obstacles=None, dist_min_thres=DIST_MIN_THRES, ttc=TIM
     return mask
 
 
+@_on_device_of
 def loss_forward(states, idx, h, h_next=None, u=None, goals=None, obstacles=None, dist_min_thres=DIST_MIN_THRES,
                  ttc=TIME_TO_COLLISION, dt=TIME_STEP, alpha=ALPHA_CBF):
     """core.py:89-184 -> (scalars [B,12], ttc_mask uint8 [B,N,K]).  Scalar layout: macbf_b200.h."""
@@ -189,6 +217,7 @@ def loss_forward(states, idx, h, h_next=None, u=None, goals=None, obstacles=None
     return scalars, mask
 
 
+@_on_device_of
 def loss_backward(states, goals, h, h_next, u, mask, scalars, grad_scalars, dt=TIME_STEP, alpha=ALPHA_CBF,
                   want_h=True, want_h_next=True, want_u=True, want_states=False):
     """Seeds dL/dh, dL/dh_next [B,N,K] and dL/du [B,N,2] from dL/dscalars [B,12]."""
@@ -208,6 +237,7 @@ def loss_backward(states, goals, h, h_next, u, mask, scalars, grad_scalars, dt=T
     return gh, ghn, gu, gst
 
 
+@_on_device_of
 def cbf_backward(states, idx, cbf_params, grad_h, obstacles=None, dist_min_thres=DIST_MIN_THRES,
                  obs_radius=OBS_RADIUS, grad_params=None, want_grad_states=False):
     """Autograd of cbf.py:21-45 -> (grad_params [17089] (accumulated if given), grad_states [B,N,4] | None)."""
@@ -228,6 +258,7 @@ def cbf_backward(states, idx, cbf_params, grad_h, obstacles=None, dist_min_thres
     return grad_params, gs
 
 
+@_on_device_of
 def controller_backward(states, goals, idx, ctrl_params, grad_u, grad_s_next=None, obstacles=None,
                         obs_radius=OBS_RADIUS, dt=TIME_STEP, grad_params=None, want_grad_states=False,
                         want_grad_goals=False):
@@ -279,6 +310,7 @@ class StepBuffers:
         self.winners_offset = L.macbf_step_workspace_winners_offset(B, N, M, top_k)   # valid after save_winners=True
 
 
+@_on_device_of
 def step_forward(states, goals, cbf_params, ctrl_params, buf: StepBuffers, obstacles=None, semantics=REPAIRED,
                  dist_min_thres=DIST_MIN_THRES, obs_radius=OBS_RADIUS, ttc=TIME_TO_COLLISION, dt=TIME_STEP,
                  alpha=ALPHA_CBF, reuse_indices=False, save_winners=False):
@@ -322,6 +354,7 @@ def generate_scenario(seed, B, N, dist_min_thres=DIST_MIN_THRES, device="cuda", 
     raise _lib.MacbfError(f"generate_scenario: could not place {N} agents (threshold {dist_min_thres})")
 
 
+@_on_device_of
 def ttc_dense(states, dist_min_check=0.07, ttc_check=0.1, want_mask=True, want_counts=True):
     """core.py:212-231 on the device: (counts [B,N] int32 | None, mask [B,N,N] uint8 | None), bit-exact."""
     _need_cuda(states)
@@ -336,6 +369,7 @@ def ttc_dense(states, dist_min_check=0.07, ttc_check=0.1, want_mask=True, want_c
     return counts, mask
 
 
+@_on_device_of
 def rollout_forward(states, goals, ctrl_params, max_steps, obstacles=None, noise=None, top_k=TOP_K, semantics=REPAIRED,
                     obs_radius=OBS_RADIUS, dt=TIME_STEP, dist_stop=0.07):
     """train.py:59-81 in one call, stop test on the device (no per-step host sync).

@@ -51,6 +51,10 @@ class TrainStep:
                          all_reduce: bool = True, reuse_indices: bool = False):
         """Returns (scalars [B,12], grad [51141] = [grad_cbf | grad_ctrl] of the env-mean objective).
         reuse_indices: h' on S's neighbour sets (ops.step_forward); the backward needs no change, idx_next = idx."""
+        with torch.cuda.device(states.device):     # launch on the device (and stream) that owns the buffers
+            return self._forward_backward(states, goals, cbf_params, ctrl_params, obstacles, all_reduce, reuse_indices)
+
+    def _forward_backward(self, states, goals, cbf_params, ctrl_params, obstacles, all_reduce, reuse_indices):
         L = _lib.load()
         b = self.buf
         B, N, M, K = self.B, self.N, self.M, b.K

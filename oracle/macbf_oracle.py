@@ -102,14 +102,17 @@ def candidate_states(states: torch.Tensor, obstacles: Optional[torch.Tensor]) ->
     return torch.cat([states, obs], dim=0)
 
 
-def pair_tensor(states: torch.Tensor, obstacles: Optional[torch.Tensor]) -> Tuple[torch.Tensor, torch.Tensor]:
+def pair_tensor(states: torch.Tensor, obstacles: Optional[torch.Tensor], rows: Optional[torch.Tensor] = None
+                ) -> Tuple[torch.Tensor, torch.Tensor]:
     """Dense (N, N+M, 4) relative states and the (N, N+M) identity indicator
-    (cbf.py:23,28 / controller.py:33-34 / core.py:188-190)."""
+    (cbf.py:23,28 / controller.py:33-34 / core.py:188-190).  rows (R,) int64: only these query rows (the row-chunked
+    form for N where the dense tensor does not fit; every row is independent of the others)."""
     cand = candidate_states(states, obstacles)
-    diff = states.unsqueeze(1) - cand.unsqueeze(0)
-    n, c = states.shape[0], cand.shape[0]
+    q = states if rows is None else states[rows]
+    diff = q.unsqueeze(1) - cand.unsqueeze(0)
+    n, c = q.shape[0], cand.shape[0]
     eye = torch.zeros(n, c, dtype=states.dtype)
-    eye[torch.arange(n), torch.arange(n)] = 1.0
+    eye[torch.arange(n), torch.arange(n) if rows is None else rows] = 1.0
     return diff, eye
 
 
@@ -172,19 +175,26 @@ def decidable_rows(states: torch.Tensor, k: int, obstacles: Optional[torch.Tenso
 # ----------------------------------------------------------------------------------------
 # edge features shared by CBF / controller / TTC
 # ----------------------------------------------------------------------------------------
-def _gather_edges(states, obstacles, k, extra_cbf_feature: bool, indices: Optional[torch.Tensor] = None):
+def _gather_edges(states, obstacles, k, extra_cbf_feature: bool, indices: Optional[torch.Tensor] = None,
+                  rows: Optional[torch.Tensor] = None):
     """indices (N, K) int64: gather these candidate columns instead of a fresh top-k (the `indices=` argument of the
-    code the reference derives from; the reference recomputes, core.py:137) - an opt-in extension."""
-    diff, eye = pair_tensor(states, obstacles)
+    code the reference derives from; the reference recomputes, core.py:137) - an opt-in extension.
+    rows: restrict the query rows (see pair_tensor)."""
+    diff, eye = pair_tensor(states, obstacles, rows)
     feats = [diff, eye.unsqueeze(2)]
     if extra_cbf_feature:
         d = torch.sqrt(torch.sum(torch.square(diff[:, :, :2]) + 1e-4, dim=2))   # cbf.py:24-25
         feats.append((d - DIST_MIN_THRES).unsqueeze(2))                         # cbf.py:29
     x = torch.cat(feats, dim=2)
     if indices is not None:
-        rows = torch.arange(x.shape[0]).unsqueeze(1).expand_as(indices)
-        return x[rows, indices], indices
-    return remove_distant_agents(x, k)
+        r = torch.arange(x.shape[0]).unsqueeze(1).expand_as(indices)
+        return x[r, indices], indices
+    if x.shape[1] <= k:            # the reference tests the row count (core.py:236); with a row subset the candidate
+        return x, None             # count is what decides
+    key = knn_keys(x[:, :, :2])
+    idx = torch.topk(-key, k)[1]                      # core.py:239
+    r = torch.arange(x.shape[0]).unsqueeze(1).expand_as(idx)
+    return x[r, idx], idx                             # core.py:240-248
 
 
 def _to_channels_first(x: torch.Tensor, semantics: int) -> torch.Tensor:
@@ -199,9 +209,10 @@ def _to_channels_first(x: torch.Tensor, semantics: int) -> torch.Tensor:
 # ----------------------------------------------------------------------------------------
 def cbf_forward(p: Dict[str, torch.Tensor], states: torch.Tensor, semantics: int = REPAIRED,
                 obstacles: Optional[torch.Tensor] = None, k: int = TOP_K,
-                obs_radius: float = OBS_RADIUS, indices: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """h (N, 1, K_eff)."""
-    x, _ = _gather_edges(states, obstacles, k, True, indices)
+                obs_radius: float = OBS_RADIUS, indices: Optional[torch.Tensor] = None,
+                rows: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """h (N, 1, K_eff)  [(R, 1, K_eff) for a row subset]."""
+    x, _ = _gather_edges(states, obstacles, k, True, indices, rows)
     dist = torch.sqrt(torch.sum(torch.square(x[:, :, :2]) + 1e-4, dim=2, keepdim=True))  # cbf.py:34-35
     mask = torch.less_equal(dist, obs_radius).type_as(x)
     mask = mask.reshape(-1, mask.shape[2], mask.shape[1])                                # cbf.py:37
@@ -216,25 +227,31 @@ def cbf_forward(p: Dict[str, torch.Tensor], states: torch.Tensor, semantics: int
 # ----------------------------------------------------------------------------------------
 # Controller  (controller.py:31-63)
 # ----------------------------------------------------------------------------------------
-def controller_pool(p, states, semantics=REPAIRED, obstacles=None, k=TOP_K, obs_radius=OBS_RADIUS):
-    """Edge net + masked pooling -> (N, 128).  LITERAL pools arg-max indices (int64)."""
-    x, _ = _gather_edges(states, obstacles, k, False)
+def controller_edge_values(p, states, semantics=REPAIRED, obstacles=None, k=TOP_K, obs_radius=OBS_RADIUS, rows=None):
+    """Edge net output times the sensing mask, (N, 128, K_eff): what controller.py:46 pools over."""
+    x, _ = _gather_edges(states, obstacles, k, False, None, rows)
     dist = torch.norm(x[:, :, :2], dim=2, keepdim=True)                                  # controller.py:38
     mask = torch.less(dist, obs_radius).type_as(x)
     mask = mask.reshape(-1, mask.shape[2], mask.shape[1])
     y = _to_channels_first(x, semantics)
     y = F.relu(F.conv1d(y, p["controller_centr_net.0.weight"], p["controller_centr_net.0.bias"]))
     y = F.relu(F.conv1d(y, p["controller_centr_net.2.weight"], p["controller_centr_net.2.bias"]))
-    pooled = torch.max(y * mask, dim=2)                                                  # controller.py:46
+    return y * mask
+
+
+def controller_pool(p, states, semantics=REPAIRED, obstacles=None, k=TOP_K, obs_radius=OBS_RADIUS, rows=None):
+    """Edge net + masked pooling -> (N, 128).  LITERAL pools arg-max indices (int64)."""
+    pooled = torch.max(controller_edge_values(p, states, semantics, obstacles, k, obs_radius, rows), dim=2)  # controller.py:46
     return pooled[1] if semantics == LITERAL else pooled[0]
 
 
 def controller_forward(p, states, goals, semantics=REPAIRED, obstacles=None, k=TOP_K,
-                       obs_radius=OBS_RADIUS) -> torch.Tensor:
-    """a (N, 2)."""
-    z = controller_pool(p, states, semantics, obstacles, k, obs_radius)
-    err = states[:, :2] - goals
-    vel = states[:, 2:]
+                       obs_radius=OBS_RADIUS, rows=None) -> torch.Tensor:
+    """a (N, 2)  [(R, 2) for a row subset]."""
+    z = controller_pool(p, states, semantics, obstacles, k, obs_radius, rows)
+    q, qg = (states, goals) if rows is None else (states[rows], goals[rows])
+    err = q[:, :2] - qg
+    vel = q[:, 2:]
     y = torch.cat([z, err, vel], dim=1)                                                  # controller.py:47
     y = F.relu(F.linear(y, p["controller_dec_net.0.weight"], p["controller_dec_net.0.bias"]))
     y = F.relu(F.linear(y, p["controller_dec_net.2.weight"], p["controller_dec_net.2.bias"]))
@@ -326,10 +343,14 @@ def loss_barrier(h, states, obstacles=None, k=TOP_K, r=DIST_MIN_THRES, ttc=TIME_
 
 def loss_derivatives(p_cbf, states, actions, h, semantics=REPAIRED, obstacles=None, k=TOP_K,
                      r=DIST_MIN_THRES, ttc=TIME_TO_COLLISION, dt=TIME_STEP, alpha=ALPHA_CBF,
-                     obs_radius=OBS_RADIUS, reuse_indices=False):
-    """core.py:132-171 (repair L8: the CBF is evaluated on states_next).  reuse_indices: h' on S's neighbour sets."""
+                     obs_radius=OBS_RADIUS, reuse_indices=False, indices_next=None):
+    """core.py:132-171 (repair L8: the CBF is evaluated on states_next).  reuse_indices: h' on S's neighbour sets.
+    indices_next (N, K) int64: checker hook - evaluate h' on these neighbour sets of S' instead of a fresh top-k, so
+    a test can still compare losses and gradients when a 1-ulp difference in u flipped a near-tie row of S''s graph."""
     states_next = euler_step(states, actions, dt)
     ind = neighbor_indices(states.detach(), k, obstacles).long() if reuse_indices else None
+    if indices_next is not None:
+        ind = indices_next.long()
     h_next = cbf_forward(p_cbf, states_next, semantics, obstacles, k, obs_radius, ind)
     deriv = h_next - h + dt * alpha * h
     dang = ttc_dangerous_mask(states, obstacles, k, r, ttc)
@@ -357,7 +378,7 @@ def total_loss(l_dang, l_safe, l_dang_d, l_safe_d, l_act):
 # ----------------------------------------------------------------------------------------
 def full_step(p_cbf, p_ctrl, states, goals, obstacles=None, k=TOP_K, semantics=REPAIRED,
               with_grad=False, r=DIST_MIN_THRES, ttc=TIME_TO_COLLISION, dt=TIME_STEP,
-              alpha=ALPHA_CBF, obs_radius=OBS_RADIUS, reuse_indices=False):
+              alpha=ALPHA_CBF, obs_radius=OBS_RADIUS, reuse_indices=False, indices_next=None):
     """graph(S) -> u -> S' -> graph(S') -> h, h' -> TTC mask -> 9 scalars [-> gradients].
     Returns a dict of tensors.  The action fed to the derivative loss keeps its autograd
     link to the controller (train.py:60-70 is not detached)."""
@@ -370,7 +391,7 @@ def full_step(p_cbf, p_ctrl, states, goals, obstacles=None, k=TOP_K, semantics=R
         h = cbf_forward(p_cbf, states, semantics, obstacles, k, obs_radius)
         lb = loss_barrier(h, states, obstacles, k, r, ttc)
         ld, h_next = loss_derivatives(p_cbf, states, u, h, semantics, obstacles, k, r, ttc, dt, alpha,
-                                      obs_radius, reuse_indices)
+                                      obs_radius, reuse_indices, indices_next)
         la = loss_actions(states, goals, u)
         total = total_loss(lb[0], lb[1], ld[0], ld[1], la)
         out = {

@@ -21,10 +21,7 @@ def available() -> bool:
     return os.path.isfile(os.path.join(REFERENCE_DIR, "core.py"))
 
 
-def load():
-    """Returns (core, cbf, controller, config) reference modules."""
-    if not available():
-        raise RuntimeError(f"reference not present at {REFERENCE_DIR}")
+def install_stubs():
     for name in ("tensorflow", "turtle"):
         if name not in sys.modules:
             m = types.ModuleType(name)
@@ -32,6 +29,13 @@ def load():
             if name == "turtle":
                 m.forward = None
             sys.modules[name] = m
+
+
+def load():
+    """Returns (core, cbf, controller, config) reference modules."""
+    if not available():
+        raise RuntimeError(f"reference not present at {REFERENCE_DIR}")
+    install_stubs()
     saved = {n: sys.modules.pop(n) for n in ("core", "cbf", "controller", "config") if n in sys.modules}
     sys.path.insert(0, REFERENCE_DIR)
     try:

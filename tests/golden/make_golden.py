@@ -10,8 +10,14 @@ Two families:
   generate_data (core.py:45-71).  These pin the oracle restatement.
 * ``oracle_*.npz`` - outputs of oracle/macbf_oracle.py (REPAIRED full step incl. parameter
   gradients) so the GPU tests do not depend on the CPU torch build of the GPU box.
+* ``ref_repaired_*.npz`` - outputs of the reference source with the Appendix-A repairs applied as the
+  committed list of exact text substitutions in oracle/repairs.py (each must match the stated number of
+  times) and executed under the same stubs: controller / CBF forwards, TTC mask (core.py:187-209), the 9
+  loss scalars (core.py:89-184), the total (train.py:93,98) and its autograd parameter gradients.  These pin
+  the REPAIRED restatement of the oracle for the rows whose reference code crashes as shipped.
 While generating, the script asserts that the oracle's LITERAL restatement reproduces the
-reference bit for bit.
+reference bit for bit, and that its REPAIRED restatement reproduces the patched reference
+(masks bit for bit, floats within 1e-6 scale-relative).
 """
 import os
 import sys
@@ -23,6 +29,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 from oracle import macbf_oracle as O  # noqa: E402
 from oracle import ref_loader  # noqa: E402
+from oracle import repairs  # noqa: E402
 
 OUT = os.path.dirname(os.path.abspath(__file__))
 
@@ -62,6 +69,43 @@ def ref_case(name, core, cbf_mod, ctrl_mod, states, goals, seed):
         **{"ctrl/" + k: v for k, v in sd_to_np(p_ctrl).items()},
     )
     print("wrote", name, "h", tuple(h.shape), "u", tuple(u.shape))
+
+
+def repaired_case(name, states, goals, p_cbf, p_ctrl, k, out):
+    """Run the mechanically repaired reference (oracle/repairs.py) on the inputs of an oracle case and pin the
+    oracle's REPAIRED outputs `out` (O.full_step) to it."""
+    mods = repairs.load_repaired()
+    core, cbf_mod, ctrl_mod, _ = mods
+    repairs.set_top_k(mods, k)
+    cbf_net, ctrl_net = cbf_mod.CBF(4), ctrl_mod.Controller(4)
+    cbf_net.load_state_dict(p_cbf)
+    ctrl_net.load_state_dict(p_ctrl)
+    a = ctrl_net(states, goals)                                               # train.py:64
+    h = cbf_net(states)                                                       # train.py:88
+    lb = core.loss_barrier(h, states)                                         # train.py:89
+    ld = core.loss_derivatives(states, a, h, cbf_net)                         # train.py:90-91
+    la = core.loss_actions(states, goals, a)                                  # train.py:92
+    total = 10 * sum([2 * lb[0], lb[1], 2 * ld[0], ld[1], 0.01 * la])         # train.py:93,98 (repair T1)
+    total.backward()                                                          # train.py:103
+    mask = core.ttc_dangerous_mask(states)
+    scalars = torch.stack([torch.as_tensor(x, dtype=torch.float32).detach().reshape(()) for x in (*lb, *ld, la)])
+    grad_cbf = torch.cat([cbf_net.state_dict(keep_vars=True)[n].grad.reshape(-1) for n in O.CBF_KEYS])
+    grad_ctrl = torch.cat([ctrl_net.state_dict(keep_vars=True)[n].grad.reshape(-1) for n in O.CTRL_KEYS])
+
+    def close(x, y, what):
+        x, y = x.detach().double(), y.detach().double()
+        err = float((x - y).abs().max() / y.abs().max().clamp_min(1e-30))
+        assert err <= 1e-6, (name, what, err)
+        return err
+    assert torch.equal(mask.reshape(-1), out["ttc_mask"].reshape(-1)), name
+    errs = {w: close(x, y, w) for w, x, y in (
+        ("u", out["u"], a), ("h", out["h"], h), ("scalars", out["scalars"], scalars), ("total", out["total"], total),
+        ("grad_cbf", out["grad_cbf"], grad_cbf), ("grad_ctrl", out["grad_ctrl"], grad_ctrl))}
+    np.savez_compressed(
+        os.path.join(OUT, "ref_repaired_" + name + ".npz"),
+        k=np.int32(k), u=a.detach().numpy(), h=h.detach().numpy(), ttc_mask=mask.numpy(), scalars=scalars.numpy(),
+        total=total.detach().numpy(), grad_cbf=grad_cbf.numpy(), grad_ctrl=grad_ctrl.numpy())
+    print("wrote ref_repaired_" + name, "oracle vs patched reference:", {w: f"{e:.1e}" for w, e in errs.items()})
 
 
 def oracle_case(name, n, m_circ, m_rect, k, seed, vel_std=0.3, generate_data=None):
@@ -104,6 +148,8 @@ def oracle_case(name, n, m_circ, m_rect, k, seed, vel_std=0.3, generate_data=Non
     )
     print("wrote", name, "scalars", out["scalars"].numpy().round(5), "total", float(out["total"]),
           "n_dang", int(out["ttc_mask"].sum()), "decidable", float(dec.float().mean()))
+    if obstacles is None:       # obstacles are an extension without reference semantics
+        repaired_case(name.replace("oracle_", ""), states, goals, p_cbf, p_ctrl, k, out)
 
 
 def main():

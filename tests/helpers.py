@@ -47,3 +47,41 @@ def dev(x, dtype=None):
 
 def flat_params_from_ref(z, prefix, keys):
     return np.concatenate([z[prefix + k].reshape(-1) for k in keys]).astype(np.float32)
+
+
+def oracle_params(z):
+    """(p_cbf, p_ctrl) dicts from the flat parameter vectors of an oracle_*.npz fixture."""
+    from oracle import macbf_oracle as O
+
+    def split(flat, shapes, keys):
+        parts = torch.split(torch.from_numpy(np.asarray(flat)), [int(np.prod(sh)) for sh in shapes])
+        return dict(zip(keys, [t.reshape(shp) for t, shp in zip(parts, shapes)]))
+    return split(z["cbf_flat"], O.CBF_SHAPES, O.CBF_KEYS), split(z["ctrl_flat"], O.CTRL_SHAPES, O.CTRL_KEYS)
+
+
+def oracle_step_on_device_graph(p_cbf, p_ctrl, s, g, obs, k, idx_next_dev, with_grad=True, min_same=0.99):
+    """The oracle's full step for a comparison that never has to be skipped.
+
+    S' is computed from u, and the device's u is ~1 ulp away from the oracle's, so a row of the S' graph whose
+    K-th and (K+1)-th keys are within a few ulp can select another neighbour on the device.  Such rows are first
+    PROVEN to be near-ties (the device's neighbour set and the oracle's have the same sorted keys on the oracle's S'
+    within 1e-6), then the oracle evaluates h' on the device's S' neighbour sets (checker hook `indices_next`), so
+    losses and gradients are compared on the same graph - always, not only when no row flipped.
+    Returns (oracle outputs, fraction of identical rows)."""
+    from oracle import macbf_oracle as O
+    ref = O.full_step(p_cbf, p_ctrl, s, g, obs, k, O.REPAIRED, with_grad=False)
+    idx_ref = O.neighbor_indices(ref["s_next"], k, obs, row_chunk=512).numpy()
+    idx_dev = np.asarray(idx_next_dev).astype(np.int64)
+    same = (idx_dev == idx_ref).all(axis=1)
+    assert same.mean() >= min_same, f"S' graph: only {same.mean():.4f} of the rows agree"
+    if not same.all():
+        cand = O.candidate_states(ref["s_next"], obs)
+        rows = np.nonzero(~same)[0]
+        d = ref["s_next"][rows, None, :2] - cand[None, :, :2]
+        keys = O.knn_keys(d)
+        kd = torch.gather(keys, 1, torch.from_numpy(idx_dev[rows])).sort(dim=1)[0]
+        kr = torch.gather(keys, 1, torch.from_numpy(idx_ref[rows])).sort(dim=1)[0]
+        assert float((kd - kr).abs().max()) <= 1e-6, "a row of the S' graph differs and is NOT a near-tie"
+    out = O.full_step(p_cbf, p_ctrl, s, g, obs, k, O.REPAIRED, with_grad=with_grad,
+                      indices_next=torch.from_numpy(idx_dev))
+    return out, float(same.mean())

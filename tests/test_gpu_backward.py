@@ -9,7 +9,10 @@ import numpy as np
 import pytest
 import torch
 
-from helpers import RTOL, assert_close, dev, load_npz, oracle_cases, rel_err
+import os
+
+from helpers import (GOLDEN, RTOL, assert_close, dev, load_npz, oracle_cases, oracle_params, oracle_step_on_device_graph,
+                     rel_err)
 
 pytestmark = pytest.mark.gpu
 GTOL = 5e-5
@@ -41,14 +44,28 @@ def test_fused_train_step_gradients(ops, case):
     ts = step.TrainStep(1, N, M, k, "cuda")
     scal, grad = ts.forward_backward(s, g, dev(z["cbf_flat"]), dev(z["ctrl_flat"]), obs)
     torch.cuda.synchronize()
-    same = (ts.buf.idx_next[0].cpu().numpy() == z["idx_next"]).all()
-    if not same:
-        pytest.skip("S' graph differs from the fixture on a near-tie row (u differs by 1 ulp); covered by unit tests")
-    assert abs(float(scal[0, 9]) - float(z["total"])) <= 2 * RTOL * abs(float(z["total"]))
+    if (ts.buf.idx_next[0].cpu().numpy() == z["idx_next"]).all():
+        ref = {n: torch.from_numpy(z[n]) for n in ("total", "grad_cbf", "grad_ctrl")}
+    else:   # a near-tie row of the S' graph flipped (u differs by 1 ulp): compare on the device's graph, never skip
+        p_cbf, p_ctrl = oracle_params(z)
+        ref, _ = oracle_step_on_device_graph(p_cbf, p_ctrl, torch.from_numpy(z["states"]), torch.from_numpy(z["goals"]),
+                                             torch.from_numpy(z["obstacles"]) if z["obstacles"].shape[0] else None,
+                                             k, ts.buf.idx_next[0].cpu().numpy())
+    assert abs(float(scal[0, 9]) - float(ref["total"])) <= 2 * RTOL * abs(float(ref["total"]))
     gc = grad[:ops.CBF_PARAMS].cpu().numpy()
     gt = grad[ops.CBF_PARAMS:].cpu().numpy()
-    assert_close(gc, z["grad_cbf"], GTOL, "grad_cbf")
-    assert_close(gt, z["grad_ctrl"], GTOL, "grad_ctrl")
+    assert_close(gc, ref["grad_cbf"].numpy(), GTOL, "grad_cbf")
+    assert_close(gt, ref["grad_ctrl"].numpy(), GTOL, "grad_ctrl")
+    # the same step pinned to the mechanically repaired reference (oracle/repairs.py), where it has semantics
+    rr = os.path.join(GOLDEN, case.replace("oracle_", "ref_repaired_"))
+    if os.path.isfile(rr) and (ts.buf.idx_next[0].cpu().numpy() == z["idx_next"]).all():
+        r = load_npz(os.path.basename(rr))
+        assert np.array_equal(ts.buf.ttc_mask[0].cpu().numpy().astype(bool).reshape(-1), r["ttc_mask"].reshape(-1))
+        sc = scal[0].cpu().numpy()
+        for q in range(9):
+            assert abs(float(sc[q]) - float(r["scalars"][q])) <= 2 * RTOL * max(abs(float(r["scalars"][q])), 1e-3), q
+        assert_close(gc, r["grad_cbf"], GTOL, "grad_cbf vs repaired reference")
+        assert_close(gt, r["grad_ctrl"], GTOL, "grad_ctrl vs repaired reference")
 
 
 def _oracle_params(z):
@@ -177,3 +194,24 @@ def test_env_sharded_gradient_equals_single_gpu(ops):
         out = O.full_step(p_cbf, p_ctrl, s[b], g[b], with_grad=True)
         ref += np.concatenate([out["grad_cbf"].numpy(), out["grad_ctrl"].numpy()]) / B
     assert_close(g_full.cpu().numpy(), ref, GTOL, "batched gradient")
+
+
+def test_dropin_module_sees_in_place_parameter_edits(ops):
+    """Edits made through `p.data` do not bump the tensor version: the drop-in modules must not serve packed
+    weights from before the edit (forward and backward)."""
+    import cbf as cbf_mod
+    import controller as ctrl_mod
+    from oracle import macbf_oracle as O
+    s, g = O.synthetic_swarm(1, 120, 77)
+    s, g = s[0].cuda(), g[0].cuda()
+    net_h, net_u = cbf_mod.CBF(4).cuda(), ctrl_mod.Controller(4).cuda()
+    h0, u0 = net_h(s).detach().clone(), net_u(s, g).detach().clone()
+    with torch.no_grad():
+        for p in list(net_h.parameters()) + list(net_u.parameters()):
+            p.data.mul_(0.5)
+    h1, u1 = net_h(s), net_u(s, g)
+    assert not torch.allclose(h0, h1) and not torch.allclose(u0, u1)
+    p_cbf = {n: t.detach().cpu() for n, t in net_h.state_dict().items()}
+    p_ctrl = {n: t.detach().cpu() for n, t in net_u.state_dict().items()}
+    assert_close(h1.detach().cpu().numpy(), O.cbf_forward(p_cbf, s.cpu()).numpy(), RTOL, "h after p.data edit")
+    assert_close(u1.detach().cpu().numpy(), O.controller_forward(p_ctrl, s.cpu(), g.cpu()).numpy(), RTOL, "u after edit")

@@ -115,3 +115,35 @@ def test_saved_pool_and_winners_give_the_same_gradients_as_the_recompute(ops):
     assert torch.equal(gg, want_g)
     assert _rel(gst, want_s) < 1e-6          # d/dstates goes through fp32 atomics (order varies)
     assert float(grad.abs().max()) > 0
+
+
+@pytest.mark.parametrize("K,N,n_obs", [(1, 150, 0), (5, 333, 2), (20, 150, 3), (64, 150, 0), (128, 200, 0)])
+def test_tensor_core_backward_matches_oracle_autograd(ops, K, N, n_obs):
+    """The same tile geometries against torch autograd of the ORACLE (not only against the FFMA twin): for random
+    cotangents, d/d(params, states, goals) of sum(h * gh) and of sum(u * gu) + sum(s' * gs)
+    (autograd of cbf.py:21-45 and controller.py:31-63 + train.py:70 on a fixed neighbour graph)."""
+    import oracle.macbf_oracle as O
+    B = 2
+    s, g, obs, idx, cf, tf, gh, gu, gs = _case(ops, B, N, K, n_obs, 40 + K)
+    tc = _run(ops, s, g, obs, idx, cf, tf, gh, gu, gs)
+    p_cbf, p_ctrl = O.init_params(40 + K)
+    pc = {n: t.clone().requires_grad_(True) for n, t in p_cbf.items()}
+    pt = {n: t.clone().requires_grad_(True) for n, t in p_ctrl.items()}
+    want = [None, torch.zeros(B, N, 4), None, torch.zeros(B, N, 4), torch.zeros(B, N, 2)]
+    for b in range(B):
+        sb = s[b].cpu().clone().requires_grad_(True)
+        gb = g[b].cpu().clone().requires_grad_(True)
+        ob = obs[b].cpu() if obs is not None else None
+        ind = idx[b].cpu().long()
+        assert torch.equal(ind, O.neighbor_indices(sb.detach(), K, ob))
+        h = O.cbf_forward(pc, sb, O.REPAIRED, ob, K)
+        (h[:, 0, :] * gh[b].cpu()).sum().backward()
+        want[1][b] = sb.grad.clone()
+        sb.grad = None
+        u = O.controller_forward(pt, sb, gb, O.REPAIRED, ob, K)
+        ((u * gu[b].cpu()).sum() + (O.euler_step(sb, u) * gs[b].cpu()).sum()).backward()
+        want[3][b], want[4][b] = sb.grad.clone(), gb.grad.clone()
+    want[0] = torch.cat([pc[n].grad.reshape(-1) for n in O.CBF_KEYS])
+    want[2] = torch.cat([pt[n].grad.reshape(-1) for n in O.CTRL_KEYS])
+    for name, a, b in zip(NAMES, tc, want):
+        assert _rel(a.cpu(), b) < GTOL, f"K={K}: {name} differs from oracle autograd by {_rel(a.cpu(), b):.2e}"

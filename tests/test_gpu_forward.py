@@ -7,7 +7,8 @@ import numpy as np
 import pytest
 import torch
 
-from helpers import RTOL, assert_close, dev, flat_params_from_ref, load_npz, oracle_cases, ref_cases, rel_err
+from helpers import (RTOL, assert_close, dev, flat_params_from_ref, load_npz, oracle_cases, oracle_params,
+                     oracle_step_on_device_graph, ref_cases, rel_err)
 
 pytestmark = pytest.mark.gpu
 
@@ -99,16 +100,21 @@ def test_step_forward_fused(ops, case):
     assert np.array_equal(buf.idx[0].cpu().numpy(), z["idx"])
     assert_close(buf.u[0].cpu().numpy(), z["u"], RTOL, "u")
     assert_close(buf.h[0].cpu().numpy(), z["h"][:, 0, :], RTOL, "h")
-    # s' comes from the GPU's own u (1 ulp away from the oracle's): the S' graph may differ on rows
-    # whose K-th/K+1-th keys are within a few ulp; compare h' on rows with identical neighbour sets
-    same = (buf.idx_next[0].cpu().numpy() == z["idx_next"]).all(axis=1)
-    assert same.mean() > 0.99
-    assert_close(buf.h_next[0].cpu().numpy()[same], z["h_next"][:, 0, :][same], 2 * RTOL, "h_next")
-    if same.all():
-        sc = buf.scalars[0].cpu().numpy()
-        for q in range(9):
-            ref = float(z["scalars"][q])
-            assert abs(float(sc[q]) - ref) <= 2 * RTOL * max(abs(ref), 1e-3), (q, sc[q], ref)
+    # s' comes from the GPU's own u (1 ulp away from the oracle's): a near-tie row of the S' graph may select another
+    # neighbour; h' and the scalars are then compared on the device's graph (proven near-tie first), never skipped
+    idx_next = buf.idx_next[0].cpu().numpy()
+    if (idx_next == z["idx_next"]).all():
+        ref = {"h_next": torch.from_numpy(z["h_next"]), "scalars": torch.from_numpy(z["scalars"])}
+    else:
+        p_cbf, p_ctrl = oracle_params(z)
+        ref, _ = oracle_step_on_device_graph(p_cbf, p_ctrl, torch.from_numpy(z["states"]), torch.from_numpy(z["goals"]),
+                                             torch.from_numpy(z["obstacles"]) if z["obstacles"].shape[0] else None,
+                                             k, idx_next, with_grad=False)
+    assert_close(buf.h_next[0].cpu().numpy(), ref["h_next"][:, 0, :].numpy(), 2 * RTOL, "h_next")
+    sc = buf.scalars[0].cpu().numpy()
+    for q in range(9):
+        r = float(ref["scalars"][q])
+        assert abs(float(sc[q]) - r) <= 2 * RTOL * max(abs(r), 1e-3), (q, sc[q], r)
 
 
 @pytest.mark.parametrize("case", ref_cases())
@@ -125,10 +131,23 @@ def test_literal_forwards_match_reference(ops, case):
     h = ops.cbf_forward(s, idx, cbf_flat, semantics=ops.LITERAL)[0].cpu().numpy()
     assert_close(h, z["h"][:, 0, :], RTOL, "h literal")
     u, _, pool = ops.controller_forward(s, g, idx, ctrl_flat, semantics=ops.LITERAL)
-    # arg-max pooling is discontinuous: an agent whose two best slots differ by ~1 ulp may flip
+    # arg-max pooling (controller.py:46 pools the INDEX) is discontinuous: where the two best slots of an (agent,
+    # channel) are within rounding of each other, another evaluation order may pick the other slot and u moves by
+    # O(1).  Classify instead of tolerating: every (agent, channel) whose pooled index differs from the oracle's must
+    # be such a near-tie (the value at the device's slot within 1e-5 of the maximum), and EVERY agent without a
+    # differing channel must have u within tolerance.
+    p_ctrl = {k[len("ctrl/"):]: torch.from_numpy(v) for k, v in z.items() if k.startswith("ctrl/")}
+    vals = O.controller_edge_values(p_ctrl, torch.from_numpy(z["states"]), O.LITERAL)          # (N, 128, K)
+    best, arg = vals.max(dim=2)
+    pool_dev = pool[0].cpu().round().long()
+    differs = pool_dev != arg
+    at_dev = torch.gather(vals, 2, pool_dev.clamp(0, vals.shape[2] - 1).unsqueeze(2))[:, :, 0]
+    near_tie = (best - at_dev).abs() <= 1e-5 * float(vals.abs().max())
+    assert bool((near_tie | ~differs).all()), "a pooled arg-max index differs where the slots are not tied"
+    clean = ~differs.any(dim=1).numpy()
     du = np.abs(u[0].cpu().numpy() - z["u"]).max(axis=1)
-    ok = du <= RTOL * max(np.abs(z["u"]).max(), 1.0)
-    assert ok.mean() >= 0.95, ok.mean()
+    assert clean.mean() >= 0.9
+    assert (du[clean] <= RTOL * max(np.abs(z["u"]).max(), 1.0)).all()
     # dynamics (core.py:74-86) + Euler step from the reference's own u
     dsdt = z["dsdt"]
     assert np.array_equal(dsdt[:, :2], z["states"][:, 2:])

@@ -71,3 +71,30 @@ def test_noalloc_rejects_problems_beyond_the_fixed_array():
     assert rc != 0
     msg = L.macbf_last_error().decode()
     assert "too large" in msg and "macbf_loss_forward" in msg
+
+
+def test_noalloc_rejects_misaligned_buffers_with_an_error_code():
+    """A caller that carves its buffers out of one block can hand over a misaligned pointer; the kernels read states
+    as float4 and goals / u as float2, so this has to come back as an error code, not as a GPU fault."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from macbf_b200 import lib, ops
+    L = lib.load()
+    s, g, h, hn, u = _problem(13, 2, 64)
+    idx = ops.neighbor_topk(s, 12)
+    B, N, K = h.shape
+    mask = torch.zeros((B, N, K), dtype=torch.uint8, device="cuda")
+    scal = torch.zeros((B, 12), dtype=torch.float32, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    for which in ("states", "goals", "u"):
+        ptr = {"states": s.data_ptr(), "goals": g.data_ptr(), "u": u.data_ptr()}
+        ptr[which] += 4
+        for entry, extra in ((L.macbf_loss_forward_noalloc, ()),
+                             (L.macbf_loss_forward, (scal.data_ptr(), 1 << 20))):   # scratch unused: rejected before
+            args = [ptr["states"], ptr["goals"], None, idx.data_ptr(), h.data_ptr(), hn.data_ptr(), ptr["u"], B, N, 0, K,
+                    0.07, 2.0, 0.1, 1.0, mask.data_ptr(), scal.data_ptr(), *extra, st]
+            assert entry(*args) != 0
+            assert "aligned" in L.macbf_last_error().decode()
+    torch.cuda.synchronize()     # no sticky fault: the device still answers
+    rc, _, _ = _call_noalloc(L, s, g, idx, h, hn, u)
+    assert rc == 0
