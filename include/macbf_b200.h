@@ -252,6 +252,17 @@ int macbf_rollout_forward(const float* states0, const float* goals, const float*
  * the per-step delta as gpu_launches). */
 long long macbf_launch_count(void);
 
+/* Per-launch device timing, a measurement aid (no counterpart in the reference; bench.py's live per-kernel
+ * breakdown).  Between macbf_timing_begin(stream) and macbf_timing_end every kernel this library launches from the
+ * calling thread is followed by a CUDA event on `stream` (pass the stream the calls use).  macbf_timing_end waits
+ * for the last event and returns, per launch in launch order, its name (NUL-terminated, name_stride bytes apiece)
+ * and the milliseconds since the previous mark - on one stream with back-to-back launches that is the kernel's
+ * duration plus whatever other work the caller put on the stream in between.  Returns minus the number of marks
+ * written (0 = none), or a positive error code.  At most 4096 launches are recorded; events are created on first
+ * use and kept.  Not for use inside a timed region: every mark costs an event record. */
+int macbf_timing_begin(void* stream);
+int macbf_timing_end(int max_marks, char* names, int name_stride, float* ms);
+
 #ifdef __cplusplus
 }
 #endif

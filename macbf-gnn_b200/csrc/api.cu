@@ -19,6 +19,29 @@ void set_error(const char* fmt, ...) {
 }
 void count_launch(int n) { g_launches += n; }
 
+// ---- per-launch timing -------------------------------------------------------------------------
+constexpr int kTimingMaxMarks = 4096;
+struct TimingState {
+  bool on = false;
+  cudaStream_t stream = nullptr;
+  int used = 0;
+  cudaEvent_t ev[kTimingMaxMarks];
+  int created = 0;
+  const char* name[kTimingMaxMarks];
+};
+static thread_local TimingState* g_timing = nullptr;
+
+void timing_mark(const char* name) {
+  TimingState* t = g_timing;
+  if (t == nullptr || !t->on || t->used >= kTimingMaxMarks) return;
+  if (t->used >= t->created) {
+    if (cudaEventCreate(&t->ev[t->created]) != cudaSuccess) { (void)cudaGetLastError(); return; }
+    ++t->created;
+  }
+  if (cudaEventRecord(t->ev[t->used], t->stream) != cudaSuccess) { (void)cudaGetLastError(); return; }
+  t->name[t->used++] = name;
+}
+
 // implemented in the kernel translation units
 int neighbor_topk(const float*, const float*, int, int, int, int, int32_t*, cudaStream_t);
 int dense_topk(const float*, int, int, int, int, int32_t*, cudaStream_t);
@@ -83,6 +106,32 @@ extern "C" {
 const char* macbf_last_error(void) { return g_err; }
 int macbf_version(void) { return 100; }
 long long macbf_launch_count(void) { return g_launches; }
+
+int macbf_timing_begin(void* stream) {
+  if (g_timing == nullptr) g_timing = new TimingState();
+  g_timing->on = true;
+  g_timing->stream = (cudaStream_t)stream;
+  g_timing->used = 0;
+  timing_mark("(begin)");
+  return g_timing->used == 1 ? 0 : 2;
+}
+
+int macbf_timing_end(int max_marks, char* names, int name_stride, float* ms) {
+  TimingState* t = g_timing;
+  MACBF_CHECK_ARG(t != nullptr && t->on, "macbf_timing_end: macbf_timing_begin was not called on this thread");
+  t->on = false;
+  MACBF_CHECK_ARG(names != nullptr && ms != nullptr && name_stride >= 8, "macbf_timing_end: bad output buffers");
+  if (t->used > 0) MACBF_CHECK_CUDA(cudaEventSynchronize(t->ev[t->used - 1]));
+  int n = 0;
+  for (int i = 1; i < t->used && n < max_marks; ++i, ++n) {
+    float v = 0.f;
+    MACBF_CHECK_CUDA(cudaEventElapsedTime(&v, t->ev[i - 1], t->ev[i]));
+    ms[n] = v;
+    strncpy(names + (size_t)n * name_stride, t->name[i], name_stride - 1);
+    names[(size_t)n * name_stride + name_stride - 1] = 0;
+  }
+  return -n;   // <= 0: minus the number of marks returned; > 0: error
+}
 int macbf_neighbor_count(int N, int M, int top_k) { return (N + M) < top_k ? (N + M) : top_k; }
 
 int macbf_neighbor_topk(const float* states, const float* obstacles, int B, int N, int M, int top_k, int32_t* idx,

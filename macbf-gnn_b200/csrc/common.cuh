@@ -42,6 +42,9 @@ inline void query_range(int total, int* begin, int* end) {
 }
 #define MACBF_SKIP_IF_SET(skip) do { if ((skip) != nullptr && *(skip) != 0) return; } while (0)
 void count_launch(int n = 1);
+// Per-launch device timing (macbf_timing_begin / macbf_timing_end): when switched on, every launch site records a
+// CUDA event on the profiled stream right after its kernel; off (the default) this is one thread-local test.
+void timing_mark(const char* name);
 #define MACBF_CHECK_ARG(cond, ...)      \
   do {                                  \
     if (!(cond)) {                      \
@@ -57,6 +60,7 @@ void count_launch(int n = 1);
       return 2;                                                                      \
     }                                                                                \
     macbf::count_launch();                                                           \
+    macbf::timing_mark(name);                                                        \
   } while (0)
 #define MACBF_CHECK_CUDA(expr)                                                       \
   do {                                                                               \

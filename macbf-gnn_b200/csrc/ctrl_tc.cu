@@ -328,8 +328,8 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
   if (warp == 0) tmem_dealloc(tbase, 512);
 }
 
-int ctrl_edge_tc(const float* states, const float* obstacles, const int32_t* idx, const float* params, int B, int N,
-                 int M, int K, double obs_radius, float* pool, cudaStream_t st, uint8_t* argk) {
+int ctrl_edge_tc_v1(const float* states, const float* obstacles, const int32_t* idx, const float* params, int B, int N,
+                    int M, int K, double obs_radius, float* pool, cudaStream_t st, uint8_t* argk) {
   const long long agents = (long long)B * N;
   MACBF_CHECK_ARG(agents < (1ll << 31), "controller_forward: B*N must be < 2^31");
   const int TA = max(1, cetc::R / K);

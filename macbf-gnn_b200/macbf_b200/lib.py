@@ -20,6 +20,8 @@ SIGNATURES = {
     "macbf_last_error": (ctypes.c_char_p, []),
     "macbf_version": (I, []),
     "macbf_launch_count": (ctypes.c_longlong, []),
+    "macbf_timing_begin": (I, [c_void]),
+    "macbf_timing_end": (I, [I, ctypes.c_char_p, I, ctypes.c_void_p]),
     "macbf_neighbor_count": (I, [I, I, I]),
     "macbf_neighbor_topk": (I, [c_f32p, c_f32p, I, I, I, I, c_i32p, c_void]),
     "macbf_neighbor_workspace_bytes": (SZ, [I, I, I, I]),

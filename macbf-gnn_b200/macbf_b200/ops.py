@@ -394,3 +394,21 @@ def rollout_forward(states, goals, ctrl_params, max_steps, obstacles=None, noise
 
 def launch_count() -> int:
     return int(_lib.load().macbf_launch_count())
+
+
+def timing_begin():
+    """Start recording one CUDA event per library launch on the current stream (macbf_timing_begin)."""
+    _lib.check(_lib.load().macbf_timing_begin(_stream()), "macbf_timing_begin")
+
+
+def timing_end():
+    """-> [(kernel name, ms since the previous launch mark), ...] in launch order (macbf_timing_end; synchronises)."""
+    import ctypes
+    n_max, stride = 4096, 48
+    names = ctypes.create_string_buffer(n_max * stride)
+    ms = (ctypes.c_float * n_max)()
+    rc = _lib.load().macbf_timing_end(n_max, names, stride, ctypes.cast(ms, ctypes.c_void_p))
+    if rc > 0:
+        _lib.check(rc, "macbf_timing_end")
+    raw = names.raw
+    return [(raw[i * stride:(i + 1) * stride].split(b"\0", 1)[0].decode(), float(ms[i])) for i in range(-rc)]

@@ -6,8 +6,10 @@ objective: mean over envs of the per-env reference loss
 backward : loss seeds -> CBF backward on (S', graph') and on (S, graph) -> controller backward with
            d/du = d l_act/du + dt * d/dS'[v]  (S' = S + [v,u] dt couples the CBF and controller
            gradients, core.py:133-137)
-sync     : one all-reduce (sum) of the flat 51,141-float gradient buffer across ranks, after
-           which every rank holds the gradient of the global env-mean.
+sync     : all-reduce (sum) of the flat 51,141-float gradient buffer across ranks, after which every
+           rank holds the gradient of the global env-mean.  The CBF part [0,17089) is
+           finished before the controller backward starts, so its all-reduce is issued there and
+           overlaps it; the controller part follows at the end.
 All arithmetic runs in libmacbf_b200.so; torch provides buffers, the stream and NCCL.
 """
 from typing import Optional
@@ -46,6 +48,10 @@ class TrainStep:
         self.grad_scalars = gsc.to(dev)
         nb = max(L.macbf_cbf_backward_scratch_bytes(B, N, K), L.macbf_controller_backward_scratch_bytes(B, N, K), 256)
         self.scratch = torch.empty((nb,), dtype=torch.uint8, device=dev)
+        self.overlap_allreduce = True
+        # optional probes (bench.py): recorded on the current stream after the last backward kernel / after the sync
+        self.ev_backward_done = None
+        self.ev_sync_done = None
 
     def forward_backward(self, states, goals, cbf_params, ctrl_params, obstacles: Optional[torch.Tensor] = None,
                          all_reduce: bool = True, reuse_indices: bool = False):
@@ -76,6 +82,13 @@ class TrainStep:
         _lib.check(L.macbf_cbf_backward(p(states), p(obs), p(b.idx), p(cbf_params), p(self.gh), B, N, M, K,
                                         ops.DIST_MIN_THRES, ops.OBS_RADIUS, p(self.grad_cbf), None,
                                         p(self.scratch), self.scratch.numel(), st), "macbf_cbf_backward(S)")
+        # The CBF half of the flat gradient is final here: start its all-reduce now, on NCCL's own stream, so it runs
+        # under the controller backward (the controller half follows after it; SURVEY 8e's one collective, split in two
+        # messages so that only the second one is exposed).
+        cbf_work = None
+        if all_reduce and self.world_size > 1 and self.overlap_allreduce:
+            import torch.distributed as dist
+            cbf_work = dist.all_reduce(self.grad_cbf, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
         # controller: d/du from the action loss, plus dt * d/dS'[v] through the Euler step
         ws = b.workspace.data_ptr()
         _lib.check(L.macbf_controller_backward_saved(p(states), p(goals), p(obs), p(b.idx), p(ctrl_params), p(self.gu),
@@ -83,8 +96,18 @@ class TrainStep:
                                                      ws + b.winners_offset, p(self.grad_ctrl), None, None,
                                                      p(self.scratch), self.scratch.numel(), st),
                    "macbf_controller_backward_saved")
+        if self.ev_backward_done is not None:
+            self.ev_backward_done.record()
         if all_reduce:
-            sync_gradients(self.grad, self.world_size, self.group)
+            if cbf_work is not None:
+                import torch.distributed as dist
+                ctrl_work = dist.all_reduce(self.grad_ctrl, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+                cbf_work.wait()          # stream-level waits: the host does not block
+                ctrl_work.wait()
+            else:
+                sync_gradients(self.grad, self.world_size, self.group)
+        if self.ev_sync_done is not None:
+            self.ev_sync_done.record()
         return b.scalars, self.grad
 
 

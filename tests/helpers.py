@@ -85,3 +85,20 @@ def oracle_step_on_device_graph(p_cbf, p_ctrl, s, g, obs, k, idx_next_dev, with_
     out = O.full_step(p_cbf, p_ctrl, s, g, obs, k, O.REPAIRED, with_grad=with_grad,
                       indices_next=torch.from_numpy(idx_dev))
     return out, float(same.mean())
+
+
+def assert_scalars_close(sc, ref_scalars, h_scale, n_dang, n_safe, where=""):
+    """The 9 loss / accuracy scalars (include/macbf_b200.h layout) against the oracle's.
+
+    The hinge losses (0, 1, 4, 5) are means of max(+-h + eps, 0) resp. of max(-(h' - h + dt alpha h) + eps, 0): their
+    absolute error is the absolute error of h, so the 1e-5 is taken relative to the magnitude of h (`h_scale` =
+    max|h|), exactly as for h itself - a small mean of differences of O(1) values cannot be more accurate than the
+    values.  The accuracies (2, 3, 6, 7) are counts / n: an element within rounding of zero may fall on the other side,
+    so up to 3 such elements of the smaller set are allowed.  The action loss (8) is a plain mean: relative 2e-5."""
+    sc = np.asarray(sc, np.float64)
+    ref = np.asarray(ref_scalars, np.float64)
+    for q in (0, 1, 4, 5):
+        assert abs(sc[q] - ref[q]) <= 2 * RTOL * max(abs(ref[q]), float(h_scale)), (where, q, sc[q], ref[q])
+    for q, n in ((2, n_dang), (3, n_safe), (6, n_dang), (7, n_safe)):
+        assert abs(sc[q] - ref[q]) <= 3.0 / max(float(n), 1.0) + 2 * RTOL, (where, q, sc[q], ref[q])
+    assert abs(sc[8] - ref[8]) <= 2 * RTOL * max(abs(ref[8]), 1e-3), (where, 8, sc[8], ref[8])

@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 import torch
 
-from helpers import (RTOL, assert_close, dev, flat_params_from_ref, load_npz, oracle_cases, oracle_params,
+from helpers import (RTOL, assert_close, assert_scalars_close, dev, flat_params_from_ref, load_npz, oracle_cases, oracle_params,
                      oracle_step_on_device_graph, ref_cases, rel_err)
 
 pytestmark = pytest.mark.gpu
@@ -112,9 +112,7 @@ def test_step_forward_fused(ops, case):
                                              k, idx_next, with_grad=False)
     assert_close(buf.h_next[0].cpu().numpy(), ref["h_next"][:, 0, :].numpy(), 2 * RTOL, "h_next")
     sc = buf.scalars[0].cpu().numpy()
-    for q in range(9):
-        r = float(ref["scalars"][q])
-        assert abs(float(sc[q]) - r) <= 2 * RTOL * max(abs(r), 1e-3), (q, sc[q], r)
+    assert_scalars_close(sc, ref["scalars"].numpy(), float(np.abs(z["h"]).max()), sc[10], sc[11], case)
 
 
 @pytest.mark.parametrize("case", ref_cases())
