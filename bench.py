@@ -247,11 +247,12 @@ class Arm:
             self.bufs = [ops.StepBuffers(B, N, M, k, dev) for _ in range(n_slots)]
         self.ops = ops
 
-    def run(self, slot, s, g):
+    def run(self, slot, s, g, all_reduce=True):
         if self.trainers is None:
             self.ops.step_forward(s, g, self.cf, self.tf, self.bufs[slot], self.obs_d, reuse_indices=self.args.reuse_indices)
         else:
-            self.trainers[slot].forward_backward(s, g, self.cf, self.tf, self.obs_d, reuse_indices=self.args.reuse_indices)
+            self.trainers[slot].forward_backward(s, g, self.cf, self.tf, self.obs_d, all_reduce=all_reduce,
+                                                 reuse_indices=self.args.reuse_indices)
 
 
 def measure_device(arm, s_d, g_d, steps, warmup, flush, barrier, dist, world, dev, local_rank, ops):
@@ -387,7 +388,7 @@ def kernel_breakdown(arm, s_d, g_d, flush, reps, edges, agents, peaks):
         flush.zero_()
         torch.cuda.synchronize()
         ops.timing_begin()
-        arm.run(0, s_d, g_d)
+        arm.run(0, s_d, g_d, all_reduce=False)     # rank 0 only: no collective here (its cost is `allreduce_exposed_ms`)
         for name, ms in ops.timing_end():
             if name not in agg:
                 agg[name] = [0, 0.0]

@@ -104,6 +104,13 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
   __shared__ uint32_t tmem_base_s;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#ifdef MACBF_TRACE
+  if (blockIdx.x == 0 && threadIdx.x == 0) {       // entry: SM clock and wall clock (ns), to derive the clock rate
+    unsigned long long gt;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+    g_tc_trace[1][4090] = clock64(); g_tc_trace[1][4091] = gt;
+  }
+#endif
 
   if (warp == 0) tmem_alloc(&tmem_base_s, 512);
   if (threadIdx.x == 32) {
@@ -149,13 +156,22 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
     const uint64_t d_w3hi = smem_desc_sw128(smem_u32(W3hi)), d_w3lo = smem_desc_sw128(smem_u32(W3lo));
     const uint32_t tb = __shfl_sync(0xffffffffu, tbase, 0);
     constexpr uint32_t IDESC = idesc_tf32(128, 64);
+    // A whole batch of MMAs sits under ONE elect_one(), and stepping a weight descriptor along K or to another row block
+    // only changes its low word (the 14-bit address field): one 32-bit add per MMA.  With an elect and 64-bit
+    // descriptor arithmetic per MMA the issuing warp needed about as long per 128x64x8 MMA (35 cycles on the tensor
+    // core) as the tensor core itself, and starved it.
+    const uint32_t w2hi_lo = (uint32_t)d_w2hi, w2lo_lo = (uint32_t)d_w2lo, w3hi_lo = (uint32_t)d_w3hi, w3lo_lo = (uint32_t)d_w3lo;
+    const uint32_t w_hi32 = (uint32_t)(d_w2hi >> 32);      // identical for every SWIZZLE_128B K-major operand
     auto issue_layer1 = [&](uint32_t parity) {       // D1 = A1 * W1^T, one k-step of 8 per term
       mbar_wait(&a1_full, parity);
       fence_after_sync();
-      if (elect_one()) mma_tf32_ss(tb + C_A2HI, d_a1lo, d_w1hi, IDESC, 0u);
-      if (elect_one()) mma_tf32_ss(tb + C_A2HI, d_a1hi, d_w1lo, IDESC, 1u);
-      if (elect_one()) mma_tf32_ss(tb + C_A2HI, d_a1hi, d_w1hi, IDESC, 1u);
-      if (elect_one()) mma_commit(&d1_full);
+      if (elect_one()) {
+        mma_tf32_ss(tb + C_A2HI, d_a1lo, d_w1hi, IDESC, 0u);
+        mma_tf32_ss(tb + C_A2HI, d_a1hi, d_w1lo, IDESC, 1u);
+        mma_tf32_ss(tb + C_A2HI, d_a1hi, d_w1hi, IDESC, 1u);
+        mma_commit(&d1_full);
+      }
+      __syncwarp();
     };
     issue_layer1(0);
     uint32_t par = 0;
@@ -165,50 +181,54 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
       fence_after_sync();
       TC_TRACE(1, 1);
       // layer 2, output columns [64c, 64c+64): B rows 64c.. of every 32-wide K block
+      if (elect_one()) {
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {
+        for (int c = 0; c < 2; ++c) {
 #pragma unroll
-        for (int term = 0; term < 3; ++term) {         // lo*hi, hi*lo, hi*hi (small terms first)
-          const uint32_t a_col = tb + (term == 0 ? C_A2LO : C_A2HI);
-          const uint64_t b_desc = desc_advance((term == 1) ? d_w2lo : d_w2hi, c * (64 * 128));
+          for (int term = 0; term < 3; ++term) {         // lo*hi, hi*lo, hi*hi (small terms first)
+            const uint32_t a_col = tb + (term == 0 ? C_A2LO : C_A2HI);
+            const uint32_t b_lo = ((term == 1) ? w2lo_lo : w2hi_lo) + ((c * (64 * 128)) >> 4);
 #pragma unroll
-          for (int ks = 0; ks < 8; ++ks) {
-            const uint64_t bd = desc_advance(b_desc, (ks >> 2) * (128 * 128) + (ks & 3) * 32);
-            if (elect_one()) mma_tf32_ts(tb + C_Y + c * 64, a_col + ks * 8, bd, IDESC, (term | ks) ? 1u : 0u);
+            for (int ks = 0; ks < 8; ++ks)
+              mma_tf32_ts_split(tb + C_Y + c * 64, a_col + ks * 8, b_lo + (((ks >> 2) * (128 * 128) + (ks & 3) * 32) >> 4),
+                                w_hi32, IDESC, (term | ks) ? 1u : 0u);
           }
+          mma_commit(&d2_full[c]);
         }
-        if (elect_one()) mma_commit(&d2_full[c]);
       }
+      __syncwarp();
       TC_TRACE(1, 2);
       // layer 1 of the next tile: its D1 lands in the A2 columns this tile's layer 2 has just finished reading
       if (tile + gridDim.x < ntiles) issue_layer1(par ^ 1);
       // layer 3 accumulates into ONE tile D3: the cross terms of both 64-wide K chunks first (each as
       // soon as its A3 chunk exists), the two hi*hi passes last - small terms still meet a small sum,
-      // and the epilogue reads 64 TMEM columns instead of 128 (tcgen05.ld bandwidth, 64 B/clk/SM, is
-      // what bounds the epilogues).
+      // and the epilogue reads 64 TMEM columns instead of 128.
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
         mbar_wait(&a3_full[c], par);
         if (c == 0 && it > 0) mbar_wait(&d3_free, par ^ 1);   // previous tile's D3 has been read
         fence_after_sync();
         TC_TRACE(1, 3 + c);
+        if (elect_one()) {
 #pragma unroll
-        for (int term = 0; term < 2; ++term) {         // lo*hi, hi*lo of K chunk [64c, 64c+64)
-          const uint32_t a_col = tb + (term == 0 ? C_A3LO : C_Y) + c * 64;
-          const uint64_t b_desc = desc_advance((term == 1) ? d_w3lo : d_w3hi, (2 * c) * (64 * 128));
+          for (int term = 0; term < 2; ++term) {         // lo*hi, hi*lo of K chunk [64c, 64c+64)
+            const uint32_t a_col = tb + (term == 0 ? C_A3LO : C_Y) + c * 64;
+            const uint32_t b_lo = ((term == 1) ? w3lo_lo : w3hi_lo) + (((2 * c) * (64 * 128)) >> 4);
 #pragma unroll
-          for (int ks = 0; ks < 8; ++ks) {
-            const uint64_t bd = desc_advance(b_desc, (ks >> 2) * (64 * 128) + (ks & 3) * 32);
-            if (elect_one()) mma_tf32_ts(tb + C_D3, a_col + ks * 8, bd, IDESC, (c | term | ks) ? 1u : 0u);
+            for (int ks = 0; ks < 8; ++ks)
+              mma_tf32_ts_split(tb + C_D3, a_col + ks * 8, b_lo + (((ks >> 2) * (64 * 128) + (ks & 3) * 32) >> 4), w_hi32, IDESC,
+                                (c | term | ks) ? 1u : 0u);
           }
         }
+        __syncwarp();
       }
+      if (elect_one()) {
 #pragma unroll
-      for (int ks = 0; ks < 16; ++ks) {                // hi*hi over the whole K = 128
-        const uint64_t bd = desc_advance(d_w3hi, (ks >> 2) * (64 * 128) + (ks & 3) * 32);
-        if (elect_one()) mma_tf32_ts(tb + C_D3, tb + C_Y + ks * 8, bd, IDESC, 1u);
+        for (int ks = 0; ks < 16; ++ks)                  // hi*hi over the whole K = 128
+          mma_tf32_ts_split(tb + C_D3, tb + C_Y + ks * 8, w3hi_lo + (((ks >> 2) * (64 * 128) + (ks & 3) * 32) >> 4), w_hi32, IDESC, 1u);
+        mma_commit(&d3_full);
       }
-      if (elect_one()) mma_commit(&d3_full);
+      __syncwarp();
       TC_TRACE(1, 5);
     }
   } else {
@@ -468,6 +488,13 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
   }
   fence_before_sync();
   __syncthreads();
+#ifdef MACBF_TRACE
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    unsigned long long gt;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+    g_tc_trace[1][4092] = clock64(); g_tc_trace[1][4093] = gt;
+  }
+#endif
   if (warp == 0) tmem_dealloc(tbase, 512);
 }
 

@@ -66,44 +66,6 @@ constexpr int total_floats = oMask + 8 * 128;
 constexpr size_t smem_bytes = (size_t)total_floats * 4 + 1024;
 }  // namespace cet2
 
-namespace tc {
-// K-major operand with 32-byte rows (K = 8 tf32): SWIZZLE_32B, the two 16-byte chunks of row r swapped when
-// (r >> 2) & 1; 8-row groups 256 B apart.
-__device__ __forceinline__ uint64_t smem_desc_sw32(uint32_t addr) {
-  uint64_t d = 0;
-  d |= (uint64_t)((addr >> 4) & 0x3FFF);
-  d |= (uint64_t)1 << 16;
-  d |= (uint64_t)(256 >> 4) << 32;
-  d |= (uint64_t)1 << 46;
-  d |= (uint64_t)6 << 61;
-  return d;
-}
-__device__ __forceinline__ void tmem_ld4(uint32_t taddr, float* v) {
-  uint32_t* r = reinterpret_cast<uint32_t*>(v);
-  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
-               : "r"(taddr));
-}
-__device__ __forceinline__ void tmem_ld1(uint32_t taddr, float* v) {
-  uint32_t* r = reinterpret_cast<uint32_t*>(v);
-  asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r[0]) : "r"(taddr));
-}
-// TS-mode MMA with the shared-memory descriptor given as two 32-bit halves: stepping along K only changes the low word
-// (the 14-bit address field), so the issuing warp does one 32-bit add per MMA instead of 64-bit descriptor arithmetic.
-__device__ __forceinline__ void mma_tf32_ts_split(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_lo, uint32_t b_hi, uint32_t idesc,
-                                                  uint32_t accumulate) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      ".reg .b64 bd;\n\t"
-      "setp.ne.b32 p, %5, 0;\n\t"
-      "mov.b64 bd, {%2, %3};\n\t"
-      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], bd, %4, p;\n\t"
-      "}\n" ::"r"(d_tmem), "r"(a_tmem), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-}  // namespace tc
-
 // WIN = true (training forward / backward pass): also writes the first arg-max slot of every (agent, channel) to `argk`
 // (255 = the maximum is 0: no gradient).  KT = 12: the reference's TOP_K fully unrolled; KT = 0: any K.
 template <bool WIN, int KT>

@@ -27,6 +27,8 @@ fn.argtypes = [ctypes.c_void_p]
 assert fn(buf.ctypes.data) == 0
 names = {0: {1: "E2c0.start", 2: "E2c0.end", 3: "E2c1.start", 4: "E2c1.end", 5: "L1next.end", 6: "E3.start", 7: "E3.end", 8: "L1.features", 9: "L1.half0", 10: "L1.half1", 11: "L1.begin"},
          1: {1: "a2.ready", 2: "mma2.issued", 3: "a3[0].ready", 4: "a3[1].ready", 5: "mma3.issued"}}
+c0, g0, c1, g1 = (int(x) for x in buf[1][4090:4094])
+buf[1][4090:4094] = 0
 ev = []
 for who in (0, 1):
     for v in buf[who]:
@@ -44,3 +46,7 @@ for t, who, name in ev[:int(os.environ.get("NEV", 150))]:
             extra = f"   <-- tile period {t - last_a2}"
         last_a2 = t
     print(f"{t - t0:9d}  {'worker0' if who == 0 else 'MMA    '}  {name}{extra}")
+
+first_a2 = min(t for t, who, n in ev if n == "a2.ready")
+print(f"kernel (CTA 0): {c1 - c0} SM cycles in {g1 - g0} ns -> SM clock {(c1 - c0) / max(g1 - g0, 1):.3f} GHz; "
+      f"entry -> first a2.ready {first_a2 - c0} cycles; tiles {sum(1 for t, w, n in ev if n == 'a2.ready')}")
