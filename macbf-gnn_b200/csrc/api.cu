@@ -336,7 +336,7 @@ int macbf_step_forward_ex(const float* states, const float* goals, const float* 
   int rc;
   if ((rc = neighbor_any(states, obstacles, B, N, M, top_k, idx, gscratch, gbytes, st))) return rc;
   MACBF_CHECK_ARG(!(flags & MACBF_STEP_SAVE_WINNERS) || controller_forward_is_tensor_core(semantics),
-                  "%s: MACBF_STEP_SAVE_WINNERS needs the tensor-core controller (REPAIRED semantics, MACBF_CTRL_FFMA unset)", fn);
+                  "%s: MACBF_STEP_SAVE_WINNERS needs the tensor-core controller (REPAIRED semantics)", fn);
   if (flags & MACBF_STEP_SAVE_WINNERS)
     tl_save_winners = (uint8_t*)workspace + macbf_step_workspace_winners_offset(B, N, M, top_k);
   rc = controller_forward(states, goals, obstacles, idx, ctrl_params, B, N, M, K, semantics, obs_radius, dt, pool, u, s_next, st);

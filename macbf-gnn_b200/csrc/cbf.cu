@@ -126,28 +126,18 @@ int cbf_forward_tc(const float* states, const float* obstacles, const int32_t* i
 int cbf_forward(const float* states, const float* obstacles, const int32_t* idx, const float* params,
                 int B, int N, int M, int K, int semantics, double dist_min, double obs_radius,
                 float* h, cudaStream_t st) {
-  // REPAIRED runs on the tensor cores (cbf_tc.cu).  The FP32-FFMA kernel below serves LITERAL
-  // (its feature scramble crosses rows) and, with MACBF_CBF_FFMA=1 in the environment, A/B checks.
-  static const bool force_ffma = [] {
-    const char* e = getenv("MACBF_CBF_FFMA");
-    return e != nullptr && e[0] == '1';
-  }();
-  if (semantics == MACBF_REPAIRED && !force_ffma)
+  // REPAIRED runs on the tensor cores (cbf_tc.cu).  The FP32 kernel above serves LITERAL only: its feature scramble
+  // (cbf.py:40) crosses rows, which the tensor-core tile layout does not express.
+  if (semantics == MACBF_REPAIRED)
     return cbf_forward_tc(states, obstacles, idx, params, B, N, M, K, dist_min, obs_radius, h, st);
   const long long agents = (long long)B * N;
   const int TA = max(1, cbf_smem::R / K);
   const long long ntiles = (agents + TA - 1) / TA;
   const int grid = (int)(ntiles < NUM_SMS ? ntiles : (long long)NUM_SMS);
   const size_t smem = cbf_smem::total * sizeof(float);
-  if (semantics == MACBF_LITERAL) {
-    MACBF_CHECK_CUDA(cudaFuncSetAttribute(cbf_forward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    cbf_forward_kernel<true><<<grid, MLP_THREADS, smem, st>>>(states, obstacles, idx, params, N, M, K, agents, TA,
-                                                             (float)dist_min, (float)obs_radius, h);
-  } else {
-    MACBF_CHECK_CUDA(cudaFuncSetAttribute(cbf_forward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    cbf_forward_kernel<false><<<grid, MLP_THREADS, smem, st>>>(states, obstacles, idx, params, N, M, K, agents, TA,
-                                                              (float)dist_min, (float)obs_radius, h);
-  }
+  MACBF_CHECK_CUDA(cudaFuncSetAttribute(cbf_forward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  cbf_forward_kernel<true><<<grid, MLP_THREADS, smem, st>>>(states, obstacles, idx, params, N, M, K, agents, TA,
+                                                           (float)dist_min, (float)obs_radius, h);
   MACBF_CHECK_LAUNCH("cbf_forward_kernel");
   return 0;
 }

@@ -113,151 +113,22 @@ ctrl_edge_kernel(const float* __restrict__ states, const float* __restrict__ obs
   }
 }
 
-namespace cn_smem {  // node kernel
-constexpr int R = 128;
-constexpr int KP1 = 136;              // 132 inputs padded to a multiple of 4
-constexpr int WS1 = 140, WS2 = 68, WS3 = 132, WS4 = 68;
-constexpr int RS0 = 132;
-constexpr int oW1 = 0;
-constexpr int oB1 = oW1 + 64 * WS1;
-constexpr int oW2 = oB1 + 64;
-constexpr int oB2 = oW2 + 128 * WS2;
-constexpr int oW3 = oB2 + 128;
-constexpr int oB3 = oW3 + 64 * WS3;
-constexpr int oW4 = oB3 + 64;
-constexpr int oB4 = oW4 + 4 * WS4;
-constexpr int oX = oB4 + 4;            // A0 [136][132], later A2 [128][128]
-constexpr int oY = oX + KP1 * RS0;     // A1 [64][128], later A3 [64][128]
-constexpr int total = oY + 64 * R;
-}  // namespace cn_smem
-
-__global__ void __launch_bounds__(MLP_THREADS, 1)
-ctrl_node_kernel(const float* __restrict__ states, const float* __restrict__ goals,
-                 const float* __restrict__ pool, const float* __restrict__ params, long long agents_total,
-                 float dt, float* __restrict__ u, float* __restrict__ s_next) {
-  using namespace cn_smem;
-  extern __shared__ __align__(16) float smem[];
-  float* W1 = smem + oW1; float* B1 = smem + oB1;
-  float* W2 = smem + oW2; float* B2 = smem + oB2;
-  float* W3 = smem + oW3; float* B3 = smem + oB3;
-  float* W4 = smem + oW4; float* B4 = smem + oB4;
-  float* X = smem + oX; float* Y = smem + oY;
-
-  load_weight<64, 132, KP1, WS1>(params + CT_NW1, W1);
-  load_weight<128, 64, 64, WS2>(params + CT_NW2, W2);
-  load_weight<64, 128, 128, WS3>(params + CT_NW3, W3);
-  load_weight<4, 64, 64, WS4>(params + CT_NW4, W4);
-  for (int t = threadIdx.x; t < 64; t += blockDim.x) {
-    B1[t] = __ldg(params + CT_NB1 + t);
-    B3[t] = __ldg(params + CT_NB3 + t);
-  }
-  for (int t = threadIdx.x; t < 128; t += blockDim.x) B2[t] = __ldg(params + CT_NB2 + t);
-  if (threadIdx.x < 4) B4[threadIdx.x] = __ldg(params + CT_NB4 + threadIdx.x);
-
-  const long long ntiles = (agents_total + R - 1) / R;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-    const long long a0 = tile * R;
-    const int rows = (int)min((long long)R, agents_total - a0);
-    __syncthreads();
-    // ---- A0 = [pool(128), p - g, v, 0-pad]^T  (controller.py:47) ----
-    {
-      const int rr = lane & 7, cc = lane >> 3;  // 8 rows x 4 float4 chunks per warp step
-      for (int it = warp; it < 16 * 8; it += MLP_THREADS / 32) {
-        const int r = (it >> 3) * 8 + rr, c4 = (it & 7) * 4 + cc;  // channel chunk of 4
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (r < rows) v = __ldg(reinterpret_cast<const float4*>(pool + (a0 + r) * 128) + c4);
-        X[(4 * c4 + 0) * RS0 + r] = v.x; X[(4 * c4 + 1) * RS0 + r] = v.y;
-        X[(4 * c4 + 2) * RS0 + r] = v.z; X[(4 * c4 + 3) * RS0 + r] = v.w;
-      }
-      if (threadIdx.x < R) {
-        const int r = threadIdx.x;
-        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-        float2 g = make_float2(0.f, 0.f);
-        if (r < rows) {
-          s = __ldg(reinterpret_cast<const float4*>(states) + a0 + r);
-          g = __ldg(reinterpret_cast<const float2*>(goals) + a0 + r);
-        }
-        X[128 * RS0 + r] = xsub(s.x, g.x); X[129 * RS0 + r] = xsub(s.y, g.y);
-        X[130 * RS0 + r] = s.z; X[131 * RS0 + r] = s.w;
-        X[132 * RS0 + r] = 0.f; X[133 * RS0 + r] = 0.f; X[134 * RS0 + r] = 0.f; X[135 * RS0 + r] = 0.f;
-      }
-    }
-    __syncthreads();
-    layer_nk<R, KP1, 64, RS0, R, WS1, true>(X, W1, B1, Y);
-    __syncthreads();
-    layer_nk<R, 64, 128, R, R, WS2, true>(Y, W2, B2, X);
-    __syncthreads();
-    layer_nk<R, 128, 64, R, R, WS3, true>(X, W3, B3, Y);
-    __syncthreads();
-    // ---- 64 -> 4, gains, action, Euler step (controller.py:50-61, train.py:70) ----
-    if (threadIdx.x < rows) {
-      const int r = threadIdx.x;
-      float o[4] = {B4[0], B4[1], B4[2], B4[3]};
-#pragma unroll 4
-      for (int c = 0; c < 64; ++c) {
-        const float a = Y[c * R + r];
-#pragma unroll
-        for (int q = 0; q < 4; ++q) o[q] = fmaf(W4[q * WS4 + c], a, o[q]);
-      }
-      float kk[4];
-#pragma unroll
-      for (int q = 0; q < 4; ++q) kk[q] = 2.0f * (1.0f / (1.0f + expf(-o[q]))) + 0.2f;
-      const float4 s = __ldg(reinterpret_cast<const float4*>(states) + a0 + r);
-      const float2 g = __ldg(reinterpret_cast<const float2*>(goals) + a0 + r);
-      const float ex = xsub(s.x, g.x), ey = xsub(s.y, g.y);
-      const float ax = xadd(xmul(ex, -kk[0]), xmul(s.z, -kk[1]));
-      const float ay = xadd(xmul(ey, -kk[2]), xmul(s.w, -kk[3]));
-      reinterpret_cast<float2*>(u)[a0 + r] = make_float2(ax, ay);
-      if (s_next != nullptr) {
-        float4 n;
-        n.x = xadd(s.x, xmul(s.z, dt)); n.y = xadd(s.y, xmul(s.w, dt));
-        n.z = xadd(s.z, xmul(ax, dt)); n.w = xadd(s.w, xmul(ay, dt));
-        reinterpret_cast<float4*>(s_next)[a0 + r] = n;
-      }
-    }
-  }
-}
-
 int ctrl_edge_tc(const float* states, const float* obstacles, const int32_t* idx, const float* params, int B, int N,
                  int M, int K, double obs_radius, float* pool, cudaStream_t st, uint8_t* argk = nullptr);
 int ctrl_node_tc(const float* states, const float* goals, const float* pool, const float* params, long long agents,
                  double dt, float* u, float* s_next, cudaStream_t st);
 
-// REPAIRED edge net runs on the tensor cores (ctrl_tc.cu); MACBF_CTRL_FFMA=1 forces the FP32-FFMA
-// kernel for A/B checks.  LITERAL always uses the FFMA kernel (row-crossing feature scramble).
-static bool ctrl_force_ffma() {
-  static const bool v = [] {
-    const char* e = getenv("MACBF_CTRL_FFMA");
-    return e != nullptr && e[0] == '1';
-  }();
-  return v;
-}
-
-bool controller_forward_is_tensor_core(int semantics) { return semantics == MACBF_REPAIRED && !ctrl_force_ffma(); }
-
-// edge kernel only (REPAIRED): rebuilds the pooled features for the backward pass
-int controller_forward_pool_only(const float* states, const float* obstacles, const int32_t* idx,
-                                 const float* params, int B, int N, int M, int K, double obs_radius, float* pool,
-                                 cudaStream_t st) {
-  if (!ctrl_force_ffma()) return ctrl_edge_tc(states, obstacles, idx, params, B, N, M, K, obs_radius, pool, st);
-  const long long agents = (long long)B * N;
-  const int TA = max(1, ce_smem::R / K);
-  const long long ntiles = (agents + TA - 1) / TA;
-  const int grid = (int)(ntiles < NUM_SMS ? ntiles : (long long)NUM_SMS);
-  const size_t smem = ce_smem::total * sizeof(float);
-  MACBF_CHECK_CUDA(cudaFuncSetAttribute(ctrl_edge_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  ctrl_edge_kernel<false><<<grid, MLP_THREADS, smem, st>>>(states, obstacles, idx, params, N, M, K, agents, TA,
-                                                          (float)obs_radius, pool);
-  MACBF_CHECK_LAUNCH("ctrl_edge_kernel");
-  return 0;
-}
+// The REPAIRED edge net and the node net run on the tensor cores (ctrl_tc.cu, ctrl_node_tc.cu).  LITERAL keeps the FP32
+// edge kernel above: its feature scramble (controller.py:43) crosses rows and it pools arg-max INDICES
+// (controller.py:46), which the tensor-core tile layout does not express; its node net is the tensor-core one
+// (LITERAL only changes what `pool` holds).
+bool controller_forward_is_tensor_core(int semantics) { return semantics == MACBF_REPAIRED; }
 
 int controller_forward(const float* states, const float* goals, const float* obstacles, const int32_t* idx,
                        const float* params, int B, int N, int M, int K, int semantics, double obs_radius,
                        double dt, float* pool, float* u, float* s_next, cudaStream_t st) {
   const long long agents = (long long)B * N;
-  if (semantics == MACBF_REPAIRED && !ctrl_force_ffma()) {
+  if (semantics == MACBF_REPAIRED) {
     int rc = ctrl_edge_tc(states, obstacles, idx, params, B, N, M, K, obs_radius, pool, st, tl_save_winners);
     if (rc) return rc;
   } else {
@@ -265,29 +136,12 @@ int controller_forward(const float* states, const float* goals, const float* obs
     const long long ntiles = (agents + TA - 1) / TA;
     const int grid = (int)(ntiles < NUM_SMS ? ntiles : (long long)NUM_SMS);
     const size_t smem = ce_smem::total * sizeof(float);
-    if (semantics == MACBF_LITERAL) {
-      MACBF_CHECK_CUDA(cudaFuncSetAttribute(ctrl_edge_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      ctrl_edge_kernel<true><<<grid, MLP_THREADS, smem, st>>>(states, obstacles, idx, params, N, M, K, agents, TA,
-                                                             (float)obs_radius, pool);
-    } else {
-      MACBF_CHECK_CUDA(cudaFuncSetAttribute(ctrl_edge_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      ctrl_edge_kernel<false><<<grid, MLP_THREADS, smem, st>>>(states, obstacles, idx, params, N, M, K, agents, TA,
-                                                              (float)obs_radius, pool);
-    }
+    MACBF_CHECK_CUDA(cudaFuncSetAttribute(ctrl_edge_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ctrl_edge_kernel<true><<<grid, MLP_THREADS, smem, st>>>(states, obstacles, idx, params, N, M, K, agents, TA,
+                                                           (float)obs_radius, pool);
     MACBF_CHECK_LAUNCH("ctrl_edge_kernel");
   }
-  if (!ctrl_force_ffma()) {
-    // node net on the tensor cores (either semantics: LITERAL only changes what `pool` holds)
-    return ctrl_node_tc(states, goals, pool, params, agents, dt, u, s_next, st);
-  } else {
-    const long long ntiles = (agents + cn_smem::R - 1) / cn_smem::R;
-    const int grid = (int)(ntiles < NUM_SMS ? ntiles : (long long)NUM_SMS);
-    const size_t smem = cn_smem::total * sizeof(float);
-    MACBF_CHECK_CUDA(cudaFuncSetAttribute(ctrl_node_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    ctrl_node_kernel<<<grid, MLP_THREADS, smem, st>>>(states, goals, pool, params, agents, (float)dt, u, s_next);
-    MACBF_CHECK_LAUNCH("ctrl_node_kernel");
-  }
-  return 0;
+  return ctrl_node_tc(states, goals, pool, params, agents, dt, u, s_next, st);
 }
 
 }  // namespace macbf

@@ -17,8 +17,6 @@
 //
 // Exactness does not depend on how the agents are distributed: a clustered swarm only makes
 // the rings grow until the stop test holds (worst case: the whole grid = brute force).
-#include <stdlib.h>
-
 #include "common.cuh"
 
 namespace macbf {
@@ -446,14 +444,9 @@ int neighbor_topk_grid(const float* states, const float* obstacles, int B, int N
   float4* sorted = (float4*)workspace;
   int* cell_start = (int*)((char*)workspace + (size_t)B * C * sizeof(float4));
   GridHeader* header = (GridHeader*)((char*)cell_start + (size_t)B * (GRID_GMAX * GRID_GMAX + 1) * sizeof(int));
-  // p = candidates per cell (MACBF_KNN_CELL overrides it).  Measured on 1024 agents x 64 envs, K = 12
-  // (scripts/knn_cell_sweep.py): p = 2 / 3 / 4 / 5 / 7 / 9 -> 64 / 59 / 63 / 65 / 67 / 73 us: small cells
-  // with an occasional third ring beat big cells that always stop after ring 1.
-  static const float cell_override = [] {
-    const char* e = getenv("MACBF_KNN_CELL");
-    return e != nullptr ? (float)atof(e) : 0.f;
-  }();
-  const float per_cell = cell_override > 0.f ? cell_override : fmaxf(3.0f, 0.25f * (float)K);
+  // p = candidates per cell.  Measured on 1024 agents x 64 envs, K = 12: p = 2 / 3 / 4 / 5 / 7 / 9 -> 64 / 59 / 63 / 65 /
+  // 67 / 73 us: small cells with an occasional third ring beat big cells that always stop after ring 1.
+  const float per_cell = fmaxf(3.0f, 0.25f * (float)K);
   int G = (int)floorf(sqrtf((float)C / per_cell));
   G = G < 1 ? 1 : (G > GRID_GMAX ? GRID_GMAX : G);
   const size_t build_smem = (size_t)(G * G + 1) * sizeof(int);
@@ -462,11 +455,7 @@ int neighbor_topk_grid(const float* states, const float* obstacles, int B, int N
   grid_build_kernel<<<B, GRID_BUILD_THREADS, build_smem, st>>>(states, obstacles, N, M, G, sorted, cell_start, header,
                                                                tl_skip_flag);
   MACBF_CHECK_LAUNCH("grid_build_kernel");
-  static const bool force_warp = [] {
-    const char* e = getenv("MACBF_KNN_WARP");
-    return e != nullptr && e[0] == '1';
-  }();
-  if (!force_warp) {
+  {
     switch (K) {   // thread-per-query instantiations for the common neighbour counts
       case 4: return launch_tpq<4>(sorted, cell_start, header, B, N, C, G, idx, st);
       case 8: return launch_tpq<8>(sorted, cell_start, header, B, N, C, G, idx, st);

@@ -1,6 +1,6 @@
-"""GPU: the tensor-core backward kernels (cbf_bwd_tc.cu, ctrl_edge_bwd_tc.cu) against the FP32-FFMA backward
-kernels they replace (which tests/test_gpu_backward.py pins to torch autograd of the oracle), over tile
-geometries the golden fixtures do not reach: K from 1 to 128, ragged last tiles, obstacles, multi-chunk records."""
+"""GPU: the tensor-core backward kernels (cbf_bwd_tc.cu, ctrl_edge_bwd_tc.cu, ctrl_node_bwd_tc.cu) against torch autograd
+of the oracle over tile geometries the golden fixtures do not reach: K from 1 to 128, ragged last tiles, obstacles,
+multi-chunk records; run-to-run determinism; saved winners vs recompute."""
 import os
 
 import pytest
@@ -63,16 +63,6 @@ def _with_env(env, fn):
 NAMES = ["cbf params", "cbf grad_states", "ctrl params", "ctrl grad_states", "ctrl grad_goals"]
 
 
-@pytest.mark.parametrize("K,N,n_obs", [(1, 150, 0), (3, 150, 0), (5, 333, 2), (12, 150, 0), (20, 150, 3), (64, 150, 0), (128, 200, 0)])
-def test_tensor_core_backward_matches_ffma(ops, K, N, n_obs):
-    args = _case(ops, 3, N, K, n_obs, 10 + K)
-    tc = _run(ops, *args)
-    ff = _with_env({"MACBF_CBF_BWD_FFMA": "1", "MACBF_CTRL_BWD_FFMA": "1"}, lambda: _run(ops, *args))
-    for name, a, b in zip(NAMES, tc, ff):
-        assert _rel(a, b) < GTOL, f"K={K}: {name} differs by {_rel(a, b):.2e}"
-    assert float(tc[0].abs().max()) > 0 and float(tc[2].abs().max()) > 0
-
-
 def test_multi_chunk_records_match_single_chunk(ops):
     args = _case(ops, 4, 257, 12, 0, 5)          # 1028 agents / 10 per tile = 103 tiles
     one = _run(ops, *args)
@@ -117,7 +107,7 @@ def test_saved_pool_and_winners_give_the_same_gradients_as_the_recompute(ops):
     assert float(grad.abs().max()) > 0
 
 
-@pytest.mark.parametrize("K,N,n_obs", [(1, 150, 0), (5, 333, 2), (20, 150, 3), (64, 150, 0), (128, 200, 0)])
+@pytest.mark.parametrize("K,N,n_obs", [(1, 150, 0), (3, 150, 0), (5, 333, 2), (12, 150, 0), (20, 150, 3), (64, 150, 0), (128, 200, 0)])
 def test_tensor_core_backward_matches_oracle_autograd(ops, K, N, n_obs):
     """The same tile geometries against torch autograd of the ORACLE (not only against the FFMA twin): for random
     cotangents, d/d(params, states, goals) of sum(h * gh) and of sum(u * gu) + sum(s' * gs)
