@@ -128,17 +128,7 @@ ctrl_node_dgrad_tc_kernel(const float* __restrict__ params, const float* __restr
     __syncthreads();
     if (warp == 0) {   // ---- dA2 = dZ3 W3 ----
       fence_after_sync();
-#pragma unroll
-      for (int term = 0; term < 3; ++term) {
-        const uint32_t a_col = tb + (term == 0 ? C_Z3LO : C_Z3HI);
-        const uint64_t b_desc = (term == 1) ? d_w3lo : d_w3hi;
-#pragma unroll
-        for (int ks = 0; ks < 8; ++ks) {
-          const uint64_t bd = desc_advance(b_desc, (ks >> 2) * (128 * 128) + (ks & 3) * 32);
-          if (elect_one()) mma_tf32_ts(tb + C_DA2, a_col + ks * 8, bd, IDESC128, (term | ks) ? 1u : 0u);
-        }
-      }
-      if (elect_one()) mma_commit(&bar[0]);
+      mma_3xtf32_ts_commit<8>(tb + C_DA2, tb + C_Z3HI, tb + C_Z3LO, d_w3hi, d_w3lo, (128 * 128), IDESC128, &bar[0]);
     }
     mbar_wait(&bar[0], par);
     fence_after_sync();
@@ -169,17 +159,7 @@ ctrl_node_dgrad_tc_kernel(const float* __restrict__ params, const float* __restr
     __syncthreads();
     if (warp == 0) {   // ---- dA1 = dZ2 W2 ----
       fence_after_sync();
-#pragma unroll
-      for (int term = 0; term < 3; ++term) {
-        const uint32_t a_col = tb + (term == 0 ? C_Z2LO : C_DA2);
-        const uint64_t b_desc = (term == 1) ? d_w2lo : d_w2hi;
-#pragma unroll
-        for (int ks = 0; ks < 16; ++ks) {
-          const uint64_t bd = desc_advance(b_desc, (ks >> 2) * (64 * 128) + (ks & 3) * 32);
-          if (elect_one()) mma_tf32_ts(tb + C_DA1, a_col + ks * 8, bd, IDESC64, (term | ks) ? 1u : 0u);
-        }
-      }
-      if (elect_one()) mma_commit(&bar[1]);
+      mma_3xtf32_ts_commit<16>(tb + C_DA1, tb + C_DA2, tb + C_Z2LO, d_w2hi, d_w2lo, (64 * 128), IDESC64, &bar[1]);
     }
     mbar_wait(&bar[1], par);
     fence_after_sync();
@@ -216,17 +196,7 @@ ctrl_node_dgrad_tc_kernel(const float* __restrict__ params, const float* __restr
     __syncthreads();
     if (warp == 0) {   // ---- dA0 = dZ1 W1 (N = 144) ----
       fence_after_sync();
-#pragma unroll
-      for (int term = 0; term < 3; ++term) {
-        const uint32_t a_col = tb + (term == 0 ? C_Z1LO : C_DA1);
-        const uint64_t b_desc = (term == 1) ? d_w1lo : d_w1hi;
-#pragma unroll
-        for (int ks = 0; ks < 8; ++ks) {
-          const uint64_t bd = desc_advance(b_desc, (ks >> 2) * (N1 * 128) + (ks & 3) * 32);
-          if (elect_one()) mma_tf32_ts(tb + C_DA0, a_col + ks * 8, bd, IDESC144, (term | ks) ? 1u : 0u);
-        }
-      }
-      if (elect_one()) mma_commit(&bar[2]);
+      mma_3xtf32_ts_commit<8>(tb + C_DA0, tb + C_DA1, tb + C_Z1LO, d_w1hi, d_w1lo, (N1 * 128), IDESC144, &bar[2]);
     }
     if (threadIdx.x < 320) {   // (e, v) columns of dW1 and db1: the 4 lane-quadrant warps of channel group cg, in order
       const int c = threadIdx.x & 63, f = threadIdx.x >> 6, cg = c >> 4, e = c & 15;

@@ -21,6 +21,21 @@
 
 namespace macbf {
 
+// Optional phase timeline (build with -DMACBF_TRACE; tools/node_trace.py reads it back): CTA 0, warp 0.
+#ifdef MACBF_TRACE
+__device__ unsigned long long g_node_trace[4096];
+#define MACBF_TRACE_MARK(who, ev)                                                                          \
+  do {                                                                                                     \
+    if (blockIdx.x == 0 && lane == 0 && trace_n < 4096)                                                    \
+      g_node_trace[trace_n++] = ((unsigned long long)(ev) << 56) | (clock64() & 0x00ffffffffffffffull);    \
+  } while (0)
+extern "C" int macbf_debug_node_trace(unsigned long long* host_out) {
+  return (int)cudaMemcpyFromSymbol(host_out, g_node_trace, sizeof(g_node_trace));
+}
+#else
+#define MACBF_TRACE_MARK(who, ev) do { } while (0)
+#endif
+
 namespace cntc {
 constexpr int THREADS = 512;
 constexpr int R = 128;
@@ -74,6 +89,8 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q = warp & 3, cgrp = warp >> 2;
   const int r = q * 32 + lane;
+  [[maybe_unused]] int trace_n = 0;
+  if (warp == 0) MACBF_TRACE_MARK(0, 1);
 
   if (warp == 0) tmem_alloc(&tmem_base_s, 512);
   if (threadIdx.x == 32) {
@@ -117,20 +134,49 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
   constexpr uint32_t IDESC64 = idesc_tf32(128, 64), IDESC128 = idesc_tf32(128, 128);
 
   const long long ntiles = (agents_total + R - 1) / R;
+  // This thread's inputs of a tile (32 pooled channels of agent row r; column group 3 also the state and the goal) are
+  // requested one tile ahead, right after the previous tile's have been written to tensor memory: the 64 KB of a tile
+  // then arrive under that tile's three GEMMs instead of in front of them.
+  float4 pfp[8];
+  float4 pf_s = make_float4(0.f, 0.f, 0.f, 0.f);
+  float2 pf_g = make_float2(0.f, 0.f);
+  auto load_tile = [&](long long tile) {
+    if (tile >= ntiles) return;                     // warp-uniform
+    // rows past the end read the last agent's row (never used: `valid` zeroes them when the tile is built) - an
+    // unconditional load has no select hanging on it, so nothing waits for the data before the next tile needs it
+    const long long ga = min(tile * R + r, agents_total - 1);
+    const float4* prow = reinterpret_cast<const float4*>(pool + ga * 128 + cgrp * 32);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) pfp[i] = __ldg(prow + i);
+    if (cgrp == 3) {
+      pf_s = __ldg(reinterpret_cast<const float4*>(states) + ga);
+      pf_g = __ldg(reinterpret_cast<const float2*>(goals) + ga);
+    }
+  };
+  if (warp == 0) MACBF_TRACE_MARK(0, 2);
+  load_tile(blockIdx.x);
   uint32_t par = 0;
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, par ^= 1) {
     const long long a0 = tile * R;
     const bool valid = a0 + r < agents_total;
     [[maybe_unused]] unsigned char* tr = DUMP ? rec + (size_t)tile * cnrec::BYTES : nullptr;
+    if (warp == 0) MACBF_TRACE_MARK(0, 3);
+    // state and goal of this row for the head at the end of the tile (column group 0): requested now, so that the
+    // head does not start with an L2 round trip while every other warp waits at the barrier behind it
+    float4 hs = make_float4(0.f, 0.f, 0.f, 0.f);
+    float2 hg = make_float2(0.f, 0.f);
+    if (cgrp == 0 && valid) {
+      hs = __ldg(reinterpret_cast<const float4*>(states) + a0 + r);
+      hg = __ldg(reinterpret_cast<const float2*>(goals) + a0 + r);
+    }
     // ---- A0 = [pool, p - g, v, 0]: this thread's 32 pooled channels (+ the 8 tail columns) ----
     {
-      const float4* prow = reinterpret_cast<const float4*>(pool + (a0 + r) * 128 + cgrp * 32);
       [[maybe_unused]] uint4 pbh[2], pbl[2];
 #pragma unroll
       for (int part8 = 0; part8 < 4; ++part8) {
-        float4 x0 = make_float4(0.f, 0.f, 0.f, 0.f), x1 = x0;
-        if (valid) { x0 = __ldg(prow + 2 * part8); x1 = __ldg(prow + 2 * part8 + 1); }
-        const float v[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+        const float4 x0 = pfp[2 * part8], x1 = pfp[2 * part8 + 1];
+        const float vz = valid ? 1.f : 0.f;           // rows past the end are exact zeros
+        const float v[8] = {x0.x * vz, x0.y * vz, x0.z * vz, x0.w * vz, x1.x * vz, x1.y * vz, x1.z * vz, x1.w * vz};
         float hi[8], lo[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) tf32_split_trunc(v[e], hi[e], lo[e]);
@@ -147,8 +193,8 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
       if (cgrp == 3) {
         float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         if (valid) {
-          const float4 s = __ldg(reinterpret_cast<const float4*>(states) + a0 + r);
-          const float2 g = __ldg(reinterpret_cast<const float2*>(goals) + a0 + r);
+          const float4 s = pf_s;
+          const float2 g = pf_g;
           v[0] = xsub(s.x, g.x); v[1] = xsub(s.y, g.y); v[2] = s.z; v[3] = s.w;   // controller.py:47
         }
         float hi[8], lo[8];
@@ -159,24 +205,18 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
       }
       wait_st();
     }
+    if (warp == 0) MACBF_TRACE_MARK(0, 4);
+    // the head below still needs this tile's state and goal (column group 0 re-reads them from L1/L2)
+    load_tile(tile + gridDim.x);
     fence_before_sync();
     __syncthreads();
     if (warp == 0) {   // ---- layer 1 ----
       fence_after_sync();
-#pragma unroll
-      for (int term = 0; term < 3; ++term) {           // lo*hi, hi*lo, hi*hi (small terms first)
-        const uint32_t a_col = tb + (term == 0 ? C_A0LO : C_A0HI);
-        const uint64_t b_desc = (term == 1) ? d_w1lo : d_w1hi;
-#pragma unroll
-        for (int ks = 0; ks < K1 / 8; ++ks) {
-          const uint64_t bd = desc_advance(b_desc, (ks >> 2) * (64 * 128) + (ks & 3) * 32);
-          if (elect_one()) mma_tf32_ts(tb + C_D1, a_col + ks * 8, bd, IDESC64, (term | ks) ? 1u : 0u);
-        }
-      }
-      if (elect_one()) mma_commit(&bar[0]);
+      mma_3xtf32_ts_commit<K1 / 8>(tb + C_D1, tb + C_A0HI, tb + C_A0LO, d_w1hi, d_w1lo, (64 * 128), IDESC64, &bar[0]);
     }
     mbar_wait(&bar[0], par);
     fence_after_sync();
+    if (warp == 0) MACBF_TRACE_MARK(0, 5);
     {  // bias + ReLU + split on this thread's 16 channels of D1 -> A1
       const int c0 = cgrp * 16;
       float v[16];
@@ -216,20 +256,12 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
     __syncthreads();
     if (warp == 0) {   // ---- layer 2 ----
       fence_after_sync();
-#pragma unroll
-      for (int term = 0; term < 3; ++term) {
-        const uint32_t a_col = tb + (term == 0 ? C_A1LO : C_A1HI);
-        const uint64_t b_desc = (term == 1) ? d_w2lo : d_w2hi;
-#pragma unroll
-        for (int ks = 0; ks < 8; ++ks) {
-          const uint64_t bd = desc_advance(b_desc, (ks >> 2) * (128 * 128) + (ks & 3) * 32);
-          if (elect_one()) mma_tf32_ts(tb + C_Y, a_col + ks * 8, bd, IDESC128, (term | ks) ? 1u : 0u);
-        }
-      }
-      if (elect_one()) mma_commit(&bar[1]);
+      mma_3xtf32_ts_commit<8>(tb + C_Y, tb + C_A1HI, tb + C_A1LO, d_w2hi, d_w2lo, (128 * 128), IDESC128, &bar[1]);
     }
+    if (warp == 0) MACBF_TRACE_MARK(0, 6);
     mbar_wait(&bar[1], par);
     fence_after_sync();
+    if (warp == 0) MACBF_TRACE_MARK(0, 7);
     [[maybe_unused]] uint32_t bits2 = 0;
 #pragma unroll
     for (int half16 = 0; half16 < 2; ++half16) {   // bias + ReLU + split on 32 channels of D2: hi in place, lo aside
@@ -270,20 +302,12 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
     __syncthreads();
     if (warp == 0) {   // ---- layer 3 ----
       fence_after_sync();
-#pragma unroll
-      for (int term = 0; term < 3; ++term) {
-        const uint32_t a_col = tb + (term == 0 ? C_A2LO : C_Y);
-        const uint64_t b_desc = (term == 1) ? d_w3lo : d_w3hi;
-#pragma unroll
-        for (int ks = 0; ks < 16; ++ks) {
-          const uint64_t bd = desc_advance(b_desc, (ks >> 2) * (64 * 128) + (ks & 3) * 32);
-          if (elect_one()) mma_tf32_ts(tb + C_D3, a_col + ks * 8, bd, IDESC64, (term | ks) ? 1u : 0u);
-        }
-      }
-      if (elect_one()) mma_commit(&bar[2]);
+      mma_3xtf32_ts_commit<16>(tb + C_D3, tb + C_Y, tb + C_A2LO, d_w3hi, d_w3lo, (64 * 128), IDESC64, &bar[2]);
     }
+    if (warp == 0) MACBF_TRACE_MARK(0, 8);
     mbar_wait(&bar[2], par);
     fence_after_sync();
+    if (warp == 0) MACBF_TRACE_MARK(0, 9);
     {  // bias + ReLU and the 64 -> 4 layer over this thread's 16 channels
       const int c0 = cgrp * 16;
       float v[16];
@@ -317,8 +341,8 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
             sg[qq] = 1.0f / (1.0f + expf(-o));
             kk[qq] = 2.0f * sg[qq] + 0.2f;
           }
-          const float4 s = __ldg(reinterpret_cast<const float4*>(states) + a0 + r);
-          const float2 g = __ldg(reinterpret_cast<const float2*>(goals) + a0 + r);
+          const float4 s = hs;
+          const float2 g = hg;
           ev[0] = xsub(s.x, g.x); ev[1] = xsub(s.y, g.y); ev[2] = s.z; ev[3] = s.w;
           float gux = 0.f, guy = 0.f;
           if (grad_u != nullptr) {
@@ -377,8 +401,8 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
         const float o = B4[qq] + ((part[qq * R + r] + part[(4 + qq) * R + r]) + (part[(8 + qq) * R + r] + part[(12 + qq) * R + r]));
         kk[qq] = 2.0f * (1.0f / (1.0f + expf(-o))) + 0.2f;          // controller.py:53
       }
-      const float4 s = __ldg(reinterpret_cast<const float4*>(states) + a0 + r);
-      const float2 g = __ldg(reinterpret_cast<const float2*>(goals) + a0 + r);
+      const float4 s = hs;
+      const float2 g = hg;
       const float ex = xsub(s.x, g.x), ey = xsub(s.y, g.y);
       const float ax = xadd(xmul(ex, -kk[0]), xmul(s.z, -kk[1]));   // controller.py:54-61
       const float ay = xadd(xmul(ey, -kk[2]), xmul(s.w, -kk[3]));
@@ -399,6 +423,7 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
   }
   fence_before_sync();
   __syncthreads();
+  if (warp == 0) MACBF_TRACE_MARK(0, 10);
   if (warp == 0) tmem_dealloc(tbase, 512);
 }
 

@@ -164,6 +164,27 @@ __device__ __forceinline__ void mma_tf32_ts_split(uint32_t d_tmem, uint32_t a_tm
       "}\n" ::"r"(d_tmem), "r"(a_tmem), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// One whole 3xTF32 product  D = A * B^T  (A: hi / lo column blocks in tensor memory, B: hi / lo SWIZZLE_128B K-major
+// operands whose 32-wide K blocks are `slab_bytes` apart; KS k-steps of 8; small terms first) issued under ONE
+// elect_one(), then committed to `bar`.  Call with the whole warp converged.
+template <int KS>
+__device__ __forceinline__ void mma_3xtf32_ts_commit(uint32_t d_tmem, uint32_t a_hi, uint32_t a_lo, uint64_t b_hi, uint64_t b_lo,
+                                                     uint32_t slab_bytes, uint32_t idesc, uint64_t* bar) {
+  const uint32_t bhi_lo = (uint32_t)b_hi, blo_lo = (uint32_t)b_lo, b_hi32 = (uint32_t)(b_hi >> 32);
+  if (elect_one()) {
+#pragma unroll
+    for (int term = 0; term < 3; ++term) {           // lo*hi, hi*lo, hi*hi
+      const uint32_t a_col = (term == 0) ? a_lo : a_hi;
+      const uint32_t bl = (term == 1) ? blo_lo : bhi_lo;
+#pragma unroll
+      for (int ks = 0; ks < KS; ++ks)
+        mma_tf32_ts_split(d_tmem, a_col + ks * 8, bl + (((ks >> 2) * slab_bytes + (ks & 3) * 32) >> 4), b_hi32, idesc,
+                          (term | ks) ? 1u : 0u);
+    }
+    mma_commit(bar);
+  }
+  __syncwarp();
+}
 // generic-proxy shared-memory writes -> visible to the tensor core (async proxy)
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
