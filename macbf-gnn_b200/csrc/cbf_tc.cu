@@ -248,12 +248,25 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
       pf_valid = false;
       pf_tile = t;
       if (cgrp == 0 && t < ntiles) {
-        const int ga = (int)(t * TA) + a_loc;      // B*N < 2^31 is checked by the host
-        if (a_loc < TA && ga < (int)agents_total) {
-          pf_b = ga / N; pf_i = ga - pf_b * N;
-          pf_j = __ldg(idx + (size_t)(t * TA) * K + r);
-          pf_si = __ldg(reinterpret_cast<const float4*>(states) + ga);
-          pf_valid = true;
+        if (!DUMP && TA == 0) {
+          // edge tiles (plain forward): 128 consecutive edges, whatever agents they belong to - h is per edge, so a
+          // tile need not hold whole agents and no row is padding (128 / K agents per tile would waste 128 % K rows)
+          const long long e = t * R + r;           // B*N*K < 2^31 is checked by the host
+          if (e < agents_total * K) {
+            const int ga = (int)e / K;
+            pf_b = ga / N; pf_i = ga - pf_b * N;
+            pf_j = __ldg(idx + e);
+            pf_si = __ldg(reinterpret_cast<const float4*>(states) + ga);
+            pf_valid = true;
+          }
+        } else {
+          const int ga = (int)(t * TA) + a_loc;    // B*N < 2^31 is checked by the host
+          if (a_loc < TA && ga < (int)agents_total) {
+            pf_b = ga / N; pf_i = ga - pf_b * N;
+            pf_j = __ldg(idx + (size_t)(t * TA) * K + r);
+            pf_si = __ldg(reinterpret_cast<const float4*>(states) + ga);
+            pf_valid = true;
+          }
         }
       }
     };
@@ -361,8 +374,9 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
     uint32_t par = 0;
     for (long long tile = first; tile < ntiles; tile += g, par ^= 1) {
       [[maybe_unused]] unsigned char* tr = DUMP ? rec + (size_t)(tile - tile_begin) * cbfrec::BYTES : nullptr;
-      const long long a0 = tile * TA;
-      const int rows = (int)min((long long)TA, agents_total - a0) * K;
+      const long long row0 = (!DUMP && TA == 0) ? tile * R : tile * TA * K;      // first edge of the tile
+      const int rows = (!DUMP && TA == 0) ? (int)min((long long)R, agents_total * K - row0)
+                                 : (int)min((long long)TA, agents_total - tile * TA) * K;
       const float mk = m0;
       const bool has_next = tile + g < ntiles;
       prefetch_sj();                                   // endpoints of tile + 2g (their idx arrived last iteration)
@@ -458,7 +472,7 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
           named_bar_sync(1, WORKERS);
           if (cgrp == 0 && r < rows) {
             const float t = (hp[r] + hp[R + r]) + (hp[2 * R + r] + hp[3 * R + r]);
-            h[a0 * K + r] = (t + B4[0]) * mk;          // cbf.py:43
+            h[row0 + r] = (t + B4[0]) * mk;            // cbf.py:43
           }
         }
       }
@@ -502,8 +516,10 @@ int cbf_forward_tc(const float* states, const float* obstacles, const int32_t* i
                    int M, int K, double dist_min, double obs_radius, float* h, cudaStream_t st) {
   const long long agents = (long long)B * N;
   MACBF_CHECK_ARG(agents < (1ll << 31), "cbf_forward: B*N must be < 2^31");
-  const int TA = max(1, cbftc::R / K);
-  const long long ntiles = (agents + TA - 1) / TA;
+  // edge tiles (TA = 0) whenever the edge count fits 32-bit arithmetic, else tiles of whole agents
+  const bool edge_tiles = agents * K < (1ll << 31);
+  const int TA = edge_tiles ? 0 : max(1, cbftc::R / K);
+  const long long ntiles = edge_tiles ? (agents * K + cbftc::R - 1) / cbftc::R : (agents + TA - 1) / TA;
   const int grid = (int)(ntiles < NUM_SMS ? ntiles : (long long)NUM_SMS);
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(cbf_forward_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)cbftc::smem_bytes));
