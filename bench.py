@@ -415,6 +415,90 @@ def kernel_breakdown(arm, s_d, g_d, flush, reps, edges, agents, peaks):
                    "the timed steps have, so the sum is slightly above ms_per_step"}
 
 
+def run_rowshard(args):
+    """--row-shard: ONE large env (BASELINE configs[4], the density sweep's swarm) with its query rows sharded over the
+    ranks (macbf_b200/rowshard.py): positions replicated, two small collectives per step (all-gather of s_next, all-reduce
+    of the loss partial sums), both inside the timed region.  Strong scaling: the total work is fixed."""
+    from macbf_b200 import ops, rowshard
+    from oracle import macbf_oracle as O
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    N, k, M = args.agents, args.top_k, args.obstacles
+    s_h, g_h, obs_h = make_inputs(1, N, M, 1234 + 5000 + k)          # the same swarm on every rank
+    p_cbf, p_ctrl = O.init_params(5)
+    cf = O.flatten_params(p_cbf, O.CBF_KEYS).to(dev)
+    tf = O.flatten_params(p_ctrl, O.CTRL_KEYS).to(dev)
+    s_d, g_d = s_h.to(dev), g_h.to(dev)
+    obs_d = obs_h.to(dev) if obs_h is not None else None
+    step = rowshard.RowShardedStep(N, M, k, dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step.forward(s_d, g_d, cf, tf, obs_d)
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    l0 = ops.launch_count()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    barrier()
+    for a, b in evs:
+        flush.zero_()
+        a.record()
+        step.forward(s_d, g_d, cf, tf, obs_d)
+        b.record()
+    barrier()
+    launches = ops.launch_count() - l0
+    clocks = sampler.stop()
+    mine = sum(a.elapsed_time(b) for a, b in evs)
+    t = torch.tensor([mine], dtype=torch.float64, device=dev)
+    per_rank = [mine / args.steps]
+    if world > 1:
+        gathered = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(gathered, t)
+        per_rank = [float(x.item()) / args.steps for x in gathered]
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t.item())
+    # parity on hardware: every rank's rows against the unsharded step computed locally on rank 0's GPU
+    parity = None
+    own = {n: getattr(step.buf, n)[0, step.lo:step.hi].clone() for n in ("idx", "idx_next", "u", "h", "h_next")}
+    scal = step.buf.scalars.clone()
+    ref = ops.StepBuffers(1, N, M, k, dev)
+    ops.step_forward(s_d, g_d, cf, tf, ref, obs_d)
+    ok = all(torch.equal(own[n], getattr(ref, n)[0, step.lo:step.hi]) for n in own)
+    ok = ok and bool(((scal - ref.scalars).abs() <= 1e-6 * ref.scalars.abs().clamp_min(1.0)).all())
+    flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device=dev)
+    if world > 1:
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    parity = bool(int(flag.item()))
+    if rank == 0:
+        value = N * args.steps / (total_ms * 1e-3)
+        cfg = workload_config(args)
+        cfg["workload"] = (f"BASELINE configs[4] (one point of the density sweep): ONE env of {N} agents, top-k {k}, forward step, "
+                           f"query rows sharded over {world} GPU(s)")
+        cfg["parallelism"] = f"row-sharded x{world} (positions replicated; all-gather of s_next + all-reduce of loss partial sums per step)"
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic", "config": cfg, "gpu_launches": launches, "clocks": clocks,
+                "per_rank_ms_per_step": per_rank, "rows_per_rank": [hi - lo for lo, hi in step.ranges],
+                "rows_equal_unsharded_step": parity,
+                "e2e": None, "roofline": None, "cpu_baseline": None}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -431,6 +515,8 @@ def main():
     ap.add_argument("--cpu-envs", type=int, default=4, help="envs per CPU-arm step (bounded sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-train-block", action="store_true")
+    ap.add_argument("--row-shard", action="store_true",
+                    help="one env (--envs 1) with its query rows sharded over the ranks (SURVEY 8f-4); strong scaling")
     ap.add_argument("--reuse-indices", action="store_true",
                     help="opt-in variant (not the reference's default): h' on S's neighbour sets, one graph search per step")
     args = ap.parse_args()
@@ -438,6 +524,10 @@ def main():
 
     if args.impl == "reference":
         run_reference(args)
+        return
+    if args.row_shard:
+        assert args.envs == 1, "--row-shard is for ONE large env (--envs 1)"
+        run_rowshard(args)
         return
 
     from macbf_b200 import ops

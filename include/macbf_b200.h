@@ -248,6 +248,33 @@ int macbf_rollout_forward(const float* states0, const float* goals, const float*
                           float* traj_states, float* traj_actions, int32_t* steps_run, void* workspace,
                           size_t workspace_bytes, void* stream);
 
+/* ---- 8f-4: forward step of ONE large env row-sharded over several GPUs (no counterpart in the reference: its dense
+ * (N,N,C) tensors of cbf.py:23-30 / controller.py:33 / core.py:188 do not exist at the sizes where this matters) --------
+ * The step of macbf_step_forward for B = 1, REPAIRED semantics, restricted to the agents [row_begin, row_end) as
+ * queries; every agent (and obstacle point) stays a candidate, so `states` (and, for _b, the complete `s_next`) are the
+ * full arrays on every rank, and all output arrays are full-size with only the rows of the range written.  Range
+ * bounds are multiples of MACBF_ROW_SHARD_ALIGN agents (or N), which keeps tiles and reduction chunks whole.
+ *   _a  graph(S) rows -> idx; controller -> u, s_next rows                          (core.py:234-250, controller.py:31-63)
+ *       then the ranks exchange their s_next rows (one all-gather of 16 B per agent)
+ *   _b  graph(S') rows -> idx_next; CBF(S), CBF(S') -> h, h_next rows; TTC mask rows; the loss reduction's partial
+ *       sums of the rows into loss_partial (macbf_loss_scratch_bytes(1, N, K) bytes, zeroed here first)
+ *       then the ranks add their loss_partial arrays (one all-reduce, sum)
+ *   _c  summed partial sums -> scalars[12]                                          (core.py:89-184, train.py:93-98)
+ * Every row's values are those of the unsharded step bit for bit; the scalars differ from it only by the order of the
+ * fp32 additions of the action term.  workspace: macbf_step_workspace_bytes(1, N, M, top_k).  Forward only. */
+#define MACBF_ROW_SHARD_ALIGN 1024
+int macbf_step_forward_rows_a(const float* states, const float* goals, const float* obstacles,
+                              const float* ctrl_params, int N, int M, int top_k, int semantics, double obs_radius,
+                              double dt, int row_begin, int row_end, int32_t* idx, float* u, float* s_next,
+                              void* workspace, size_t workspace_bytes, void* stream);
+int macbf_step_forward_rows_b(const float* states, const float* s_next, const float* goals, const float* obstacles,
+                              const float* cbf_params, int N, int M, int top_k, int semantics, double dist_min_thres,
+                              double obs_radius, double ttc, double dt, double alpha, int row_begin, int row_end,
+                              const int32_t* idx, int32_t* idx_next, const float* u, float* h, float* h_next,
+                              uint8_t* ttc_mask, float* loss_partial, void* workspace, size_t workspace_bytes,
+                              void* stream);
+int macbf_step_forward_rows_c(const float* loss_partial_sum, int N, int K, float* scalars, void* stream);
+
 /* Kernel launches issued by this library on the calling thread since load (bench.py reports
  * the per-step delta as gpu_launches). */
 long long macbf_launch_count(void);

@@ -9,6 +9,7 @@ static thread_local char g_err[512] = "";
 static thread_local long long g_launches = 0;
 thread_local const int* tl_skip_flag = nullptr;
 thread_local QueryPart tl_query_part = {0, 1};
+thread_local RowRange tl_row_range = {0, -1};
 thread_local uint8_t* tl_save_winners = nullptr;
 
 void set_error(const char* fmt, ...) {
@@ -68,6 +69,7 @@ int ttc_dense(const float*, int, int, double, double, int32_t*, uint8_t*, cudaSt
 size_t scenario_workspace_bytes(int, int, int);
 int scenario_generate(unsigned long long, int, int, int, double, float*, float*, int32_t*, void*, size_t, cudaStream_t);
 size_t loss_scratch_bytes(int, int, int);
+int loss_finalize(const void*, int, int, int, int, int, float*, cudaStream_t);
 int loss_validate(const char*, const float*, const float*, const float*, const int32_t*, const float*, const float*, int,
                   int, int, int, const uint8_t*, const float*);
 int loss_forward(const float*, const float*, const float*, const int32_t*, const float*, const float*, const float*,
@@ -353,6 +355,85 @@ int macbf_step_forward_ex(const float* states, const float* goals, const float* 
                         h_next, st))) return rc;
   return loss_forward(states, goals, obstacles, idx, h, h_next, u, B, N, M, K, dist_min_thres, ttc, dt, alpha,
                       ttc_mask_out, scalars, lscratch, loss_scratch_bytes(B, N, K), st);
+}
+
+// ---- row-sharded forward step of ONE env ---------------------------------------------------------------------------
+struct RowScope {     // sets the thread-local row range for the launchers called inside the scope
+  RowScope(int b, int e) { tl_row_range = RowRange{b, e}; }
+  ~RowScope() { tl_row_range = RowRange{0, -1}; }
+};
+static int check_rows(const char* fn, int N, int row_begin, int row_end) {
+  MACBF_CHECK_ARG(row_begin >= 0 && row_begin <= row_end && row_end <= N, "%s: row range [%d, %d) outside [0, %d)", fn,
+                  row_begin, row_end, N);
+  MACBF_CHECK_ARG(row_begin % MACBF_ROW_SHARD_ALIGN == 0 && (row_end == N || row_end % MACBF_ROW_SHARD_ALIGN == 0),
+                  "%s: row range bounds must be multiples of %d agents (or N)", fn, MACBF_ROW_SHARD_ALIGN);
+  return 0;
+}
+
+int macbf_step_forward_rows_a(const float* states, const float* goals, const float* obstacles, const float* ctrl_params,
+                              int N, int M, int top_k, int semantics, double obs_radius, double dt, int row_begin,
+                              int row_end, int32_t* idx, float* u, float* s_next, void* workspace, size_t workspace_bytes,
+                              void* stream) {
+  const char* fn = "macbf_step_forward_rows_a";
+  MACBF_CHECK_ARG(top_k >= 1 && top_k <= MACBF_MAX_K, "%s: top_k=%d out of range [1,%d]", fn, top_k, MACBF_MAX_K);
+  const int K = macbf_neighbor_count(N, M, top_k);
+  if (check_dims(fn, 1, N, M, K) || check_rows(fn, N, row_begin, row_end)) return 1;
+  MACBF_CHECK_ARG(semantics == MACBF_REPAIRED, "%s: REPAIRED semantics only", fn);
+  REQ_PTR(fn, states); REQ_PTR(fn, goals); REQ_PTR(fn, ctrl_params); REQ_PTR(fn, idx); REQ_PTR(fn, u); REQ_PTR(fn, s_next);
+  REQ_PTR(fn, workspace); REQ_A16(fn, states); REQ_A16(fn, s_next); REQ_A16(fn, workspace);
+  MACBF_CHECK_ARG(M == 0 || obstacles != nullptr, "%s: obstacles is NULL but M=%d", fn, M);
+  MACBF_CHECK_ARG(workspace_bytes >= macbf_step_workspace_bytes(1, N, M, top_k), "%s: workspace too small (%zu < %zu)", fn,
+                  workspace_bytes, macbf_step_workspace_bytes(1, N, M, top_k));
+  if (row_end == row_begin) return 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  float* pool = (float*)workspace;
+  void* lscratch = (char*)workspace + align256((size_t)N * MACBF_POOL_DIM * sizeof(float));
+  const size_t gbytes = macbf_neighbor_workspace_bytes(1, N, M, top_k);
+  void* gscratch = gbytes ? (char*)lscratch + align256(loss_scratch_bytes(1, N, K)) : nullptr;
+  RowScope scope(row_begin, row_end);
+  int rc;
+  if ((rc = neighbor_any(states, obstacles, 1, N, M, top_k, idx, gscratch, gbytes, st))) return rc;
+  return controller_forward(states, goals, obstacles, idx, ctrl_params, 1, N, M, K, semantics, obs_radius, dt, pool, u, s_next, st);
+}
+
+int macbf_step_forward_rows_b(const float* states, const float* s_next, const float* goals, const float* obstacles,
+                              const float* cbf_params, int N, int M, int top_k, int semantics, double dist_min_thres,
+                              double obs_radius, double ttc, double dt, double alpha, int row_begin, int row_end,
+                              const int32_t* idx, int32_t* idx_next, const float* u, float* h, float* h_next,
+                              uint8_t* ttc_mask_out, float* loss_partial, void* workspace, size_t workspace_bytes,
+                              void* stream) {
+  const char* fn = "macbf_step_forward_rows_b";
+  MACBF_CHECK_ARG(top_k >= 1 && top_k <= MACBF_MAX_K, "%s: top_k=%d out of range [1,%d]", fn, top_k, MACBF_MAX_K);
+  const int K = macbf_neighbor_count(N, M, top_k);
+  if (check_dims(fn, 1, N, M, K) || check_rows(fn, N, row_begin, row_end)) return 1;
+  MACBF_CHECK_ARG(semantics == MACBF_REPAIRED, "%s: REPAIRED semantics only", fn);
+  REQ_PTR(fn, states); REQ_PTR(fn, s_next); REQ_PTR(fn, goals); REQ_PTR(fn, cbf_params); REQ_PTR(fn, idx);
+  REQ_PTR(fn, idx_next); REQ_PTR(fn, u); REQ_PTR(fn, h); REQ_PTR(fn, h_next); REQ_PTR(fn, ttc_mask_out);
+  REQ_PTR(fn, loss_partial); REQ_PTR(fn, workspace); REQ_A16(fn, states); REQ_A16(fn, s_next); REQ_A16(fn, workspace);
+  MACBF_CHECK_ARG(M == 0 || obstacles != nullptr, "%s: obstacles is NULL but M=%d", fn, M);
+  MACBF_CHECK_ARG(workspace_bytes >= macbf_step_workspace_bytes(1, N, M, top_k), "%s: workspace too small (%zu < %zu)", fn,
+                  workspace_bytes, macbf_step_workspace_bytes(1, N, M, top_k));
+  cudaStream_t st = (cudaStream_t)stream;
+  MACBF_CHECK_CUDA(cudaMemsetAsync(loss_partial, 0, loss_scratch_bytes(1, N, K), st));   // rows of other ranges contribute 0
+  if (row_end == row_begin) return 0;
+  void* lscratch = (char*)workspace + align256((size_t)N * MACBF_POOL_DIM * sizeof(float));
+  const size_t gbytes = macbf_neighbor_workspace_bytes(1, N, M, top_k);
+  void* gscratch = gbytes ? (char*)lscratch + align256(loss_scratch_bytes(1, N, K)) : nullptr;
+  RowScope scope(row_begin, row_end);
+  int rc;
+  if ((rc = neighbor_any(s_next, obstacles, 1, N, M, top_k, idx_next, gscratch, gbytes, st))) return rc;   // core.py:137
+  if ((rc = cbf_forward(states, obstacles, idx, cbf_params, 1, N, M, K, semantics, dist_min_thres, obs_radius, h, st))) return rc;
+  if ((rc = cbf_forward(s_next, obstacles, idx_next, cbf_params, 1, N, M, K, semantics, dist_min_thres, obs_radius, h_next, st)))
+    return rc;
+  return loss_forward(states, goals, obstacles, idx, h, h_next, u, 1, N, M, K, dist_min_thres, ttc, dt, alpha, ttc_mask_out,
+                      nullptr, loss_partial, loss_scratch_bytes(1, N, K), st);
+}
+
+int macbf_step_forward_rows_c(const float* loss_partial_sum, int N, int K, float* scalars, void* stream) {
+  const char* fn = "macbf_step_forward_rows_c";
+  MACBF_CHECK_ARG(N >= 1 && K >= 1 && K <= MACBF_MAX_K, "%s: bad extents N=%d K=%d", fn, N, K);
+  REQ_PTR(fn, loss_partial_sum); REQ_PTR(fn, scalars);
+  return loss_finalize(loss_partial_sum, 1, N, K, 1, 1, scalars, (cudaStream_t)stream);
 }
 
 int macbf_ttc_dense(const float* states, int B, int N, double dist_min_sq, double ttc, int32_t* counts, uint8_t* mask,

@@ -80,7 +80,7 @@ template <bool DUMP>
 __global__ void __launch_bounds__(cbftc::THREADS, 1)
 cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict__ obstacles,
                       const int32_t* __restrict__ idx, const float* __restrict__ params, int N, int M, int K,
-                      long long agents_total, int TA, float dist_min, float obs_radius, float* __restrict__ h,
+                      long long agents_total, int agent_begin, int TA, float dist_min, float obs_radius, float* __restrict__ h,
                       long long tile_begin, long long tile_end, const float* __restrict__ grad_h,
                       unsigned char* __restrict__ rec, float* __restrict__ slices) {
   using namespace cbftc;
@@ -251,7 +251,7 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
         if (!DUMP && TA == 0) {
           // edge tiles (plain forward): 128 consecutive edges, whatever agents they belong to - h is per edge, so a
           // tile need not hold whole agents and no row is padding (128 / K agents per tile would waste 128 % K rows)
-          const long long e = t * R + r;           // B*N*K < 2^31 is checked by the host
+          const long long e = (long long)agent_begin * K + t * R + r;   // B*N*K < 2^31 is checked by the host
           if (e < agents_total * K) {
             const int ga = (int)e / K;
             pf_b = ga / N; pf_i = ga - pf_b * N;
@@ -374,7 +374,7 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
     uint32_t par = 0;
     for (long long tile = first; tile < ntiles; tile += g, par ^= 1) {
       [[maybe_unused]] unsigned char* tr = DUMP ? rec + (size_t)(tile - tile_begin) * cbfrec::BYTES : nullptr;
-      const long long row0 = (!DUMP && TA == 0) ? tile * R : tile * TA * K;      // first edge of the tile
+      const long long row0 = (!DUMP && TA == 0) ? (long long)agent_begin * K + tile * R : tile * TA * K;      // first edge of the tile
       const int rows = (!DUMP && TA == 0) ? (int)min((long long)R, agents_total * K - row0)
                                  : (int)min((long long)TA, agents_total - tile * TA) * K;
       const float mk = m0;
@@ -518,13 +518,21 @@ int cbf_forward_tc(const float* states, const float* obstacles, const int32_t* i
   MACBF_CHECK_ARG(agents < (1ll << 31), "cbf_forward: B*N must be < 2^31");
   // edge tiles (TA = 0) whenever the edge count fits 32-bit arithmetic, else tiles of whole agents
   const bool edge_tiles = agents * K < (1ll << 31);
+  long long a_end = agents;
+  int a_begin = 0;
+  if (rows_active()) {                             // a row range of one env (macbf_step_forward_rows_*)
+    MACBF_CHECK_ARG(B == 1 && edge_tiles, "cbf_forward: a row range needs B = 1 and N*K < 2^31");
+    a_begin = tl_row_range.begin;
+    a_end = tl_row_range.end < agents ? tl_row_range.end : agents;
+    if (a_end <= a_begin) return 0;
+  }
   const int TA = edge_tiles ? 0 : max(1, cbftc::R / K);
-  const long long ntiles = edge_tiles ? (agents * K + cbftc::R - 1) / cbftc::R : (agents + TA - 1) / TA;
+  const long long ntiles = edge_tiles ? ((a_end - a_begin) * K + cbftc::R - 1) / cbftc::R : (agents + TA - 1) / TA;
   const int grid = (int)(ntiles < NUM_SMS ? ntiles : (long long)NUM_SMS);
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(cbf_forward_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)cbftc::smem_bytes));
   cbf_forward_tc_kernel<false><<<grid, cbftc::THREADS, cbftc::smem_bytes, st>>>(
-      states, obstacles, idx, params, N, M, K, agents, TA, (float)dist_min, (float)obs_radius, h, 0, ntiles, nullptr,
+      states, obstacles, idx, params, N, M, K, a_end, a_begin, TA, (float)dist_min, (float)obs_radius, h, 0, ntiles, nullptr,
       nullptr, nullptr);
   MACBF_CHECK_LAUNCH("cbf_forward_tc_kernel");
   return 0;
@@ -540,7 +548,7 @@ int cbf_forward_tc_dump(const float* states, const float* obstacles, const int32
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(cbf_forward_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)cbftc::smem_bytes));
   cbf_forward_tc_kernel<true><<<grid, cbftc::THREADS, cbftc::smem_bytes, st>>>(
-      states, obstacles, idx, params, N, M, K, agents, TA, (float)dist_min, (float)obs_radius, nullptr, tile_begin, tile_end,
+      states, obstacles, idx, params, N, M, K, agents, 0, TA, (float)dist_min, (float)obs_radius, nullptr, tile_begin, tile_end,
       grad_h, rec, slices);
   MACBF_CHECK_LAUNCH("cbf_forward_tc_kernel<dump>");
   return 0;

@@ -36,7 +36,14 @@ extern thread_local const int* tl_skip_flag;
 extern thread_local uint8_t* tl_save_winners;
 struct QueryPart { int part, nparts; };
 extern thread_local QueryPart tl_query_part;
+// Row range consulted by the launchers of the forward kernels (macbf_step_forward_rows_*): when active (end >= 0) only the
+// agents [begin, end) of a single env are processed as queries / rows - their neighbour search, controller, CBF and
+// loss partial sums - while every agent stays a candidate.  One large env row-sharded over several GPUs.
+struct RowRange { int begin, end; };
+extern thread_local RowRange tl_row_range;
+inline bool rows_active() { return tl_row_range.end >= 0; }
 inline void query_range(int total, int* begin, int* end) {
+  if (rows_active()) { *begin = tl_row_range.begin; *end = tl_row_range.end < total ? tl_row_range.end : total; return; }
   *begin = (int)((long long)total * tl_query_part.part / tl_query_part.nparts);
   *end = (int)((long long)total * (tl_query_part.part + 1) / tl_query_part.nparts);
 }

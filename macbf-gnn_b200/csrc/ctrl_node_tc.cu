@@ -68,7 +68,7 @@ template <bool DUMP>
 __global__ void __launch_bounds__(cntc::THREADS, 1)
 ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ goals,
                     const float* __restrict__ pool, const float* __restrict__ params, long long agents_total,
-                    float dt, float* __restrict__ u, float* __restrict__ s_next, const int* __restrict__ skip,
+                    int agent_begin, float dt, float* __restrict__ u, float* __restrict__ s_next, const int* __restrict__ skip,
                     const float* __restrict__ grad_u, const float* __restrict__ grad_s_next,
                     unsigned char* __restrict__ rec, float* __restrict__ slices) {
   MACBF_SKIP_IF_SET(skip);
@@ -133,7 +133,8 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
   const uint64_t d_w3hi = smem_desc_sw128(smem_u32(W3hi)), d_w3lo = smem_desc_sw128(smem_u32(W3lo));
   constexpr uint32_t IDESC64 = idesc_tf32(128, 64), IDESC128 = idesc_tf32(128, 128);
 
-  const long long ntiles = (agents_total + R - 1) / R;
+  // tiles cover the agents [agent_begin, agents_total) (agent_begin > 0: a row range; never with DUMP)
+  const long long ntiles = (agents_total - agent_begin + R - 1) / R;
   // This thread's inputs of a tile (32 pooled channels of agent row r; column group 3 also the state and the goal) are
   // requested one tile ahead, right after the previous tile's have been written to tensor memory: the 64 KB of a tile
   // then arrive under that tile's three GEMMs instead of in front of them.
@@ -144,7 +145,7 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
     if (tile >= ntiles) return;                     // warp-uniform
     // rows past the end read the last agent's row (never used: `valid` zeroes them when the tile is built) - an
     // unconditional load has no select hanging on it, so nothing waits for the data before the next tile needs it
-    const long long ga = min(tile * R + r, agents_total - 1);
+    const long long ga = min(agent_begin + tile * R + r, agents_total - 1);
     const float4* prow = reinterpret_cast<const float4*>(pool + ga * 128 + cgrp * 32);
 #pragma unroll
     for (int i = 0; i < 8; ++i) pfp[i] = __ldg(prow + i);
@@ -157,7 +158,7 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
   load_tile(blockIdx.x);
   uint32_t par = 0;
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, par ^= 1) {
-    const long long a0 = tile * R;
+    const long long a0 = agent_begin + tile * R;
     const bool valid = a0 + r < agents_total;
     [[maybe_unused]] unsigned char* tr = DUMP ? rec + (size_t)tile * cnrec::BYTES : nullptr;
     if (warp == 0) MACBF_TRACE_MARK(0, 3);
@@ -429,11 +430,18 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
 
 int ctrl_node_tc(const float* states, const float* goals, const float* pool, const float* params, long long agents,
                  double dt, float* u, float* s_next, cudaStream_t st) {
-  const long long ntiles = (agents + cntc::R - 1) / cntc::R;
+  long long a_end = agents;
+  int a_begin = 0;
+  if (rows_active()) {
+    a_begin = tl_row_range.begin;
+    a_end = tl_row_range.end < agents ? tl_row_range.end : agents;
+    if (a_end <= a_begin) return 0;
+  }
+  const long long ntiles = (a_end - a_begin + cntc::R - 1) / cntc::R;
   const int grid = (int)(ntiles < NUM_SMS ? ntiles : (long long)NUM_SMS);
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(ctrl_node_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)cntc::smem_bytes));
-  ctrl_node_tc_kernel<false><<<grid, cntc::THREADS, cntc::smem_bytes, st>>>(states, goals, pool, params, agents, (float)dt, u,
+  ctrl_node_tc_kernel<false><<<grid, cntc::THREADS, cntc::smem_bytes, st>>>(states, goals, pool, params, a_end, a_begin, (float)dt, u,
                                                                            s_next, tl_skip_flag, nullptr, nullptr, nullptr,
                                                                            nullptr);
   MACBF_CHECK_LAUNCH("ctrl_node_tc_kernel");
@@ -448,7 +456,7 @@ int ctrl_node_tc_dump(const float* states, const float* goals, const float* pool
   const int grid = (int)(ntiles < NUM_SMS ? ntiles : (long long)NUM_SMS);
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(ctrl_node_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)cntc::smem_bytes));
-  ctrl_node_tc_kernel<true><<<grid, cntc::THREADS, cntc::smem_bytes, st>>>(states, goals, pool, params, agents, (float)dt,
+  ctrl_node_tc_kernel<true><<<grid, cntc::THREADS, cntc::smem_bytes, st>>>(states, goals, pool, params, agents, 0, (float)dt,
                                                                           nullptr, nullptr, nullptr, grad_u, grad_s_next, rec,
                                                                           slices);
   MACBF_CHECK_LAUNCH("ctrl_node_tc_kernel<dump>");

@@ -72,7 +72,7 @@ template <bool WIN, int KT>
 __global__ void __launch_bounds__(cet2::THREADS, 1)
 ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ obstacles,
                      const int32_t* __restrict__ idx, const float* __restrict__ params, int N, int M, int Krt,
-                     long long agents_total, int TA, float obs_radius, float* __restrict__ pool,
+                     long long agents_total, int agent_begin, int TA, float obs_radius, float* __restrict__ pool,
                      const int* __restrict__ skip, uint8_t* __restrict__ argk) {
   MACBF_SKIP_IF_SET(skip);
   using namespace cet2;
@@ -133,7 +133,8 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
-  const long long ntiles = (agents_total + TA - 1) / TA;
+  // tiles cover the agents [agent_begin, agents_total) (agent_begin > 0: a row range of one env, B = 1)
+  const long long ntiles = (agents_total - agent_begin + TA - 1) / TA;
   const long long gdim = gridDim.x;
   const int nj = (ntiles > blockIdx.x) ? (int)((ntiles - blockIdx.x + gdim - 1) / gdim) : 0;   // tiles of this CTA
   if (warp == 0) CE2_TRACE(0, 11);
@@ -151,10 +152,10 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
     p.j = 0; p.b = 0; p.i = 0; p.valid = false; p.si = make_float4(0.f, 0.f, 0.f, 0.f);
     if (j < nj) {
       const long long t = blockIdx.x + (long long)j * gdim;
-      const int ga = (int)(t * TA) + a_loc;        // B*N < 2^31 is checked by the host
+      const int ga = agent_begin + (int)(t * TA) + a_loc;        // B*N < 2^31 is checked by the host
       if (a_loc < TA && ga < (int)agents_total) {
         p.b = ga / N; p.i = ga - p.b * N;
-        p.j = __ldg(idx + (size_t)(t * TA) * K + r);
+        p.j = __ldg(idx + (size_t)(agent_begin + t * TA) * K + r);
         p.si = __ldg(reinterpret_cast<const float4*>(states) + ga);
         p.valid = true;
       }
@@ -330,7 +331,7 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
         nxt = load_ij(j + 6);
       }
       const long long t = blockIdx.x + (long long)j * gdim;
-      const long long a0 = t * TA;
+      const long long a0 = agent_begin + t * TA;
       const int na = (int)min((long long)TA, agents_total - a0);
       mbar_wait(&d2_full[b], (j >> 1) & 1);
       fence_after_sync();
@@ -447,10 +448,11 @@ ctrl_edge_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
 
 template <bool WIN, int KT>
 static int launch_ce2(const float* states, const float* obstacles, const int32_t* idx, const float* params, int N, int M, int K,
-                      long long agents, int TA, float obs_radius, float* pool, cudaStream_t st, uint8_t* argk, int grid) {
+                      long long agents, int agent_begin, int TA, float obs_radius, float* pool, cudaStream_t st, uint8_t* argk,
+                      int grid) {
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(ctrl_edge_tc_kernel<WIN, KT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)cet2::smem_bytes));
-  ctrl_edge_tc_kernel<WIN, KT><<<grid, cet2::THREADS, cet2::smem_bytes, st>>>(states, obstacles, idx, params, N, M, K, agents, TA,
+  ctrl_edge_tc_kernel<WIN, KT><<<grid, cet2::THREADS, cet2::smem_bytes, st>>>(states, obstacles, idx, params, N, M, K, agents, agent_begin, TA,
                                                                              obs_radius, pool, tl_skip_flag, argk);
   return 0;
 }
@@ -460,14 +462,22 @@ int ctrl_edge_tc(const float* states, const float* obstacles, const int32_t* idx
   const long long agents = (long long)B * N;
   MACBF_CHECK_ARG(agents < (1ll << 31), "controller_forward: B*N must be < 2^31");
   const int TA = max(1, cet2::R / K);
-  const long long ntiles = (agents + TA - 1) / TA;
+  long long a_end = agents;
+  int a_begin = 0;
+  if (rows_active()) {
+    MACBF_CHECK_ARG(B == 1, "controller_forward: a row range needs B = 1");
+    a_begin = tl_row_range.begin;
+    a_end = tl_row_range.end < agents ? tl_row_range.end : agents;
+    if (a_end <= a_begin) return 0;
+  }
+  const long long ntiles = (a_end - a_begin + TA - 1) / TA;
   const int grid = (int)(ntiles < NUM_SMS ? ntiles : (long long)NUM_SMS);
   const float rad = (float)obs_radius;
   int rc;
-  if (K == 12) rc = argk ? launch_ce2<true, 12>(states, obstacles, idx, params, N, M, K, agents, TA, rad, pool, st, argk, grid)
-                         : launch_ce2<false, 12>(states, obstacles, idx, params, N, M, K, agents, TA, rad, pool, st, argk, grid);
-  else rc = argk ? launch_ce2<true, 0>(states, obstacles, idx, params, N, M, K, agents, TA, rad, pool, st, argk, grid)
-                 : launch_ce2<false, 0>(states, obstacles, idx, params, N, M, K, agents, TA, rad, pool, st, argk, grid);
+  if (K == 12) rc = argk ? launch_ce2<true, 12>(states, obstacles, idx, params, N, M, K, a_end, a_begin, TA, rad, pool, st, argk, grid)
+                         : launch_ce2<false, 12>(states, obstacles, idx, params, N, M, K, a_end, a_begin, TA, rad, pool, st, argk, grid);
+  else rc = argk ? launch_ce2<true, 0>(states, obstacles, idx, params, N, M, K, a_end, a_begin, TA, rad, pool, st, argk, grid)
+                 : launch_ce2<false, 0>(states, obstacles, idx, params, N, M, K, a_end, a_begin, TA, rad, pool, st, argk, grid);
   if (rc) return rc;
   MACBF_CHECK_LAUNCH("ctrl_edge_tc_kernel");
   return 0;

@@ -39,8 +39,10 @@ loss_partial_kernel(const float* __restrict__ states, const float* __restrict__ 
                     const float* __restrict__ obstacles, const int32_t* __restrict__ idx,
                     const float* __restrict__ h, const float* __restrict__ h_next, const float* __restrict__ u,
                     int N, int M, int K, float r2, float ttc, float dt_alpha, uint8_t* __restrict__ mask,
-                    float* __restrict__ partial) {
-  const int b = blockIdx.y, chunk = blockIdx.x, nchunks = gridDim.x;
+                    float* __restrict__ partial, int chunk0, int nchunks, int agent_begin, int agent_end) {
+  // the launched chunks are [chunk0, chunk0 + gridDim.x) of the env's nchunks; the action term covers the agents
+  // [agent_begin, agent_end), striped over the launched chunks (the whole env unless a row range is set)
+  const int b = blockIdx.y, chunk = chunk0 + blockIdx.x;
   const long long rows_env = (long long)N * K;
   const long long r_begin = (long long)chunk * LOSS_ROWS_PER_CTA;
   const long long r_end = min(rows_env, r_begin + LOSS_ROWS_PER_CTA);
@@ -80,7 +82,7 @@ loss_partial_kernel(const float* __restrict__ states, const float* __restrict__ 
   if (u != nullptr) {
     // core.py:174-184: a_ref = -(p - g) - sqrt(3) v, agents striped over the env's chunks
     const float s3 = 1.7320508075688772f;
-    for (int i = chunk * LOSS_THREADS + threadIdx.x; i < N; i += nchunks * LOSS_THREADS) {
+    for (int i = agent_begin + blockIdx.x * LOSS_THREADS + threadIdx.x; i < agent_end; i += gridDim.x * LOSS_THREADS) {
       const float4 s = __ldg(reinterpret_cast<const float4*>(states) + (size_t)b * N + i);
       const float2 g = __ldg(reinterpret_cast<const float2*>(goals) + (size_t)b * N + i);
       const float2 a = __ldg(reinterpret_cast<const float2*>(u) + (size_t)b * N + i);
@@ -236,13 +238,34 @@ int loss_forward(const float* states, const float* goals, const float* obstacles
                   scratch_bytes, loss_scratch_bytes(B, N, K));
   const float r2 = (float)(dist_min * dist_min);
   const float dt_alpha = (float)(dt * alpha);     // python: TIME_STEP * ALPHA_CBF in double, then cast
-  dim3 grid(nchunks, B);
+  int chunk0 = 0, nlaunch = nchunks, a_begin = 0, a_end = N;
+  if (rows_active()) {
+    // a row range of one env: only its chunks are computed (the caller zeroed the scratch; the partial sums of all
+    // ranges are added - one all-reduce - before loss_final).  Range bounds are multiples of 1024 agents = whole chunks.
+    MACBF_CHECK_ARG(B == 1, "loss_forward: a row range needs B = 1");
+    a_begin = tl_row_range.begin;
+    a_end = tl_row_range.end < N ? tl_row_range.end : N;
+    if (a_end <= a_begin) return 0;
+    MACBF_CHECK_ARG(((long long)a_begin * K) % LOSS_ROWS_PER_CTA == 0 && (a_end == N || ((long long)a_end * K) % LOSS_ROWS_PER_CTA == 0),
+                    "loss_forward: row range [%d, %d) does not fall on reduction chunks (use multiples of 1024 agents)", a_begin, a_end);
+    chunk0 = (int)(((long long)a_begin * K) / LOSS_ROWS_PER_CTA);
+    nlaunch = (int)((((long long)a_end * K) + LOSS_ROWS_PER_CTA - 1) / LOSS_ROWS_PER_CTA) - chunk0;
+  }
+  dim3 grid(nlaunch, B);
   loss_partial_kernel<<<grid, LOSS_THREADS, 0, st>>>(states, goals, obstacles, idx, h, h_next,
                                                     (goals != nullptr) ? u : nullptr, N, M, K, r2, (float)ttc,
-                                                    dt_alpha, mask, (float*)scratch);
+                                                    dt_alpha, mask, (float*)scratch, chunk0, nchunks, a_begin, a_end);
   MACBF_CHECK_LAUNCH("loss_partial_kernel");
+  if (rows_active()) return 0;                    // loss_finalize() after the partial sums of all ranges were added
   loss_final_kernel<<<B, 32 * LOSS_NACC, 0, st>>>((const float*)scratch, nchunks, N, K, h_next != nullptr,
                                       (u != nullptr && goals != nullptr), scalars);
+  MACBF_CHECK_LAUNCH("loss_final_kernel");
+  return 0;
+}
+
+// second stage alone: partial sums (scratch) -> the 12 scalars per env
+int loss_finalize(const void* scratch, int B, int N, int K, int has_next, int has_u, float* scalars, cudaStream_t st) {
+  loss_final_kernel<<<B, 32 * LOSS_NACC, 0, st>>>((const float*)scratch, loss_chunks(N, K), N, K, has_next, has_u, scalars);
   MACBF_CHECK_LAUNCH("loss_final_kernel");
   return 0;
 }

@@ -339,7 +339,7 @@ template <int K>
 __global__ void __launch_bounds__(128)
 knn_grid_tpq_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start,
                     const GridHeader* __restrict__ header, int N, int C, int G, int32_t* __restrict__ idx_out,
-                    const int* __restrict__ skip, int part, int nparts) {
+                    const int* __restrict__ skip, int part, int nparts, int row_begin, int row_end) {
   MACBF_SKIP_IF_SET(skip);
   const int b = blockIdx.y;
   const int p0 = blockIdx.x * blockDim.x + threadIdx.x;
@@ -355,6 +355,7 @@ knn_grid_tpq_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
   // row sharding: a query belongs to the part that owns its CELL (by the cell's start in the sorted order) - the order
   // of the candidates inside a cell is not reproducible between two builds of the grid, cell membership is
   if (nparts > 1 && (int)((long long)cs[cy * G + cx] * nparts / C) != part) return;
+  if (row_end >= 0 && (i < row_begin || i >= row_end)) return;   // contiguous row range (macbf_step_forward_rows_*)
 
   u64 list[K];
 #pragma unroll
@@ -418,7 +419,7 @@ static int launch_tpq(const float4* sorted, const int* cell_start, const GridHea
                       int32_t* idx, cudaStream_t st) {
   dim3 grid((C + 127) / 128, B);
   knn_grid_tpq_kernel<K><<<grid, 128, 0, st>>>(sorted, cell_start, header, N, C, G, idx, tl_skip_flag, tl_query_part.part,
-                                               tl_query_part.nparts);
+                                               tl_query_part.nparts, tl_row_range.begin, tl_row_range.end);
   MACBF_CHECK_LAUNCH("knn_grid_tpq_kernel");
   return 0;
 }

@@ -55,6 +55,11 @@ SIGNATURES = {
     "macbf_step_workspace_winners_offset": (SZ, [I, I, I, I]),
     "macbf_controller_backward_saved": (I, [c_f32p, c_f32p, c_f32p, c_i32p, c_f32p, c_f32p, c_f32p, I, I, I, I, D, D, c_f32p,
                                             c_u8p, c_f32p, c_f32p, c_f32p, c_void, SZ, c_void]),
+    "macbf_step_forward_rows_a": (I, [c_f32p, c_f32p, c_f32p, c_f32p, I, I, I, I, D, D, I, I, c_i32p, c_f32p, c_f32p, c_void, SZ,
+                                      c_void]),
+    "macbf_step_forward_rows_b": (I, [c_f32p, c_f32p, c_f32p, c_f32p, c_f32p, I, I, I, I, D, D, D, D, D, I, I, c_i32p, c_i32p,
+                                      c_f32p, c_f32p, c_f32p, c_u8p, c_f32p, c_void, SZ, c_void]),
+    "macbf_step_forward_rows_c": (I, [c_f32p, I, I, c_f32p, c_void]),
     "macbf_step_forward": (I, [c_f32p, c_f32p, c_f32p, c_f32p, c_f32p, I, I, I, I, I, D, D, D, D, D, c_i32p, c_i32p,
                                c_f32p, c_f32p, c_f32p, c_f32p, c_u8p, c_f32p, c_void, SZ, c_void]),
     "macbf_step_forward_ex": (I, [c_f32p, c_f32p, c_f32p, c_f32p, c_f32p, I, I, I, I, I, D, D, D, D, D, I, c_i32p, c_i32p,

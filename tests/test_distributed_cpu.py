@@ -67,3 +67,17 @@ def test_env_sharding_and_single_allreduce_gloo(tmp_path):
         ref += torch.cat([out["grad_cbf"], out["grad_ctrl"]]).numpy().astype(np.float64) / B
     scale = np.abs(ref).max()
     assert np.abs(g0 - ref).max() <= 1e-5 * scale
+
+
+def test_row_ranges_cover_the_env_on_aligned_bounds():
+    """Row sharding of one large env: the ranges are a disjoint cover with bounds on multiples of 1024
+    agents (whole tiles and reduction chunks), also when there are more ranks than aligned blocks."""
+    from macbf_b200 import rowshard
+    for N, parts in ((65536, 8), (65536, 3), (5000, 3), (1000, 4), (4096, 8)):
+        rs = rowshard.row_ranges(N, parts)
+        assert len(rs) == parts and rs[0][0] == 0 and rs[-1][1] == N
+        for (lo, hi), (lo2, _) in zip(rs, rs[1:]):
+            assert hi == lo2 and lo <= hi
+        for lo, hi in rs:
+            assert lo % rowshard.ROW_SHARD_ALIGN == 0 and (hi == N or hi % rowshard.ROW_SHARD_ALIGN == 0)
+    assert rowshard.row_ranges(65536, 8)[3] == (24576, 32768)
