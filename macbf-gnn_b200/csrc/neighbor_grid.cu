@@ -151,6 +151,147 @@ grid_build_kernel(const float* __restrict__ states, const float* __restrict__ ob
   }
 }
 
+// ---- the same grid for LARGE envs, built by many CTAs per env (one CTA would spend ~100 us on 65,536 points) ----
+//   grid_big_bbox_kernel     per-CTA bounding box -> ordered-integer atomicMin / atomicMax per env
+//   grid_big_hist_kernel     header from the box; cell histogram with global atomics
+//   grid_big_scan_kernel     one CTA per env: exclusive scan -> cell_start, and a copy as the scatter cursors
+//   grid_big_scatter_kernel  sorted[cursor[cell]++] = (x, y, index)
+// Scratch per env (behind the header array): bbox[4] as ordered uints, cursors[G*G + 1].
+constexpr int GRID_BIG_THREADS = 256;
+constexpr int GRID_BIG_PER_CTA = 2048;                 // candidates per CTA
+constexpr int GRID_BIG_MIN_C = 8192;                   // envs with at least this many candidates take this path
+
+__device__ __forceinline__ unsigned f2ord(float f) {   // order-preserving float -> uint
+  const unsigned b = __float_as_uint(f);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float ord2f(unsigned u) {
+  return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
+}
+__device__ __forceinline__ GridHeader header_from_box(const unsigned* __restrict__ box, int G) {
+  const float x0 = ord2f(box[0]), y0 = ord2f(box[1]), x1 = ord2f(box[2]), y1 = ord2f(box[3]);
+  float cs = fmaxf(x1 - x0, y1 - y0) / (float)G;
+  if (!(cs > 0.f) || !(cs < 3.0e38f)) cs = 1.f;          // all candidates coincide (or non-finite input)
+  GridHeader hd;
+  hd.ox = x0; hd.oy = y0; hd.cs = cs; hd.inv_cs = 1.f / cs;
+  return hd;
+}
+
+__global__ void __launch_bounds__(GRID_BIG_THREADS)
+grid_big_init_kernel(unsigned* __restrict__ box, int* __restrict__ cursors, int cells_p1, const int* __restrict__ skip) {
+  MACBF_SKIP_IF_SET(skip);
+  const int b = blockIdx.y;
+  for (int t = blockIdx.x * GRID_BIG_THREADS + threadIdx.x; t < cells_p1; t += gridDim.x * GRID_BIG_THREADS)
+    cursors[(size_t)b * (GRID_GMAX * GRID_GMAX + 1) + t] = 0;
+  if (blockIdx.x == 0 && threadIdx.x < 4) box[b * 4 + threadIdx.x] = threadIdx.x < 2 ? 0xffffffffu : 0u;
+}
+
+__global__ void __launch_bounds__(GRID_BIG_THREADS)
+grid_big_bbox_kernel(const float* __restrict__ states, const float* __restrict__ obstacles, int N, int M,
+                     unsigned* __restrict__ box, const int* __restrict__ skip) {
+  MACBF_SKIP_IF_SET(skip);
+  const int b = blockIdx.y, C = N + M;
+  const int t_begin = blockIdx.x * GRID_BIG_PER_CTA, t_end = min(C, t_begin + GRID_BIG_PER_CTA);
+  float xmin = 3.0e38f, ymin = 3.0e38f, xmax = -3.0e38f, ymax = -3.0e38f;
+  for (int t = t_begin + threadIdx.x; t < t_end; t += GRID_BIG_THREADS) {
+    const float4 sv = load_candidate(states, obstacles, b, t, N, M);
+    xmin = fminf(xmin, sv.x); xmax = fmaxf(xmax, sv.x);
+    ymin = fminf(ymin, sv.y); ymax = fmaxf(ymax, sv.y);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    xmin = fminf(xmin, __shfl_xor_sync(0xffffffffu, xmin, o));
+    ymin = fminf(ymin, __shfl_xor_sync(0xffffffffu, ymin, o));
+    xmax = fmaxf(xmax, __shfl_xor_sync(0xffffffffu, xmax, o));
+    ymax = fmaxf(ymax, __shfl_xor_sync(0xffffffffu, ymax, o));
+  }
+  if ((threadIdx.x & 31) == 0 && xmin <= xmax) {
+    atomicMin(&box[b * 4 + 0], f2ord(xmin)); atomicMin(&box[b * 4 + 1], f2ord(ymin));
+    atomicMax(&box[b * 4 + 2], f2ord(xmax)); atomicMax(&box[b * 4 + 3], f2ord(ymax));
+  }
+}
+
+__global__ void __launch_bounds__(GRID_BIG_THREADS)
+grid_big_hist_kernel(const float* __restrict__ states, const float* __restrict__ obstacles, int N, int M, int G,
+                     const unsigned* __restrict__ box, int* __restrict__ cursors, GridHeader* __restrict__ header,
+                     const int* __restrict__ skip) {
+  MACBF_SKIP_IF_SET(skip);
+  const int b = blockIdx.y, C = N + M;
+  const GridHeader g = header_from_box(box + b * 4, G);
+  if (blockIdx.x == 0 && threadIdx.x == 0) header[b] = g;
+  int* cnt = cursors + (size_t)b * (GRID_GMAX * GRID_GMAX + 1);
+  const int t_begin = blockIdx.x * GRID_BIG_PER_CTA, t_end = min(C, t_begin + GRID_BIG_PER_CTA);
+  for (int t = t_begin + threadIdx.x; t < t_end; t += GRID_BIG_THREADS) {
+    const float4 sv = load_candidate(states, obstacles, b, t, N, M);
+    atomicAdd(&cnt[cell_coord(sv.y, g.oy, g.inv_cs, G) * G + cell_coord(sv.x, g.ox, g.inv_cs, G)], 1);
+  }
+}
+
+__global__ void __launch_bounds__(GRID_BUILD_THREADS)
+grid_big_scan_kernel(int C, int G, int* __restrict__ cursors, int* __restrict__ cell_start, const int* __restrict__ skip) {
+  MACBF_SKIP_IF_SET(skip);
+  extern __shared__ int cnt[];                  // the env's histogram, staged with coalesced loads
+  __shared__ int wsum[32];
+  const int b = blockIdx.x, cells = G * G;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int* cur = cursors + (size_t)b * (GRID_GMAX * GRID_GMAX + 1);
+  int* cst = cell_start + (size_t)b * (GRID_GMAX * GRID_GMAX + 1);
+  for (int t = threadIdx.x; t < cells; t += GRID_BUILD_THREADS) cnt[t] = cur[t];
+  __syncthreads();
+  const int per = (cells + GRID_BUILD_THREADS - 1) / GRID_BUILD_THREADS;
+  const int c_begin = min(threadIdx.x * per, cells), c_end = min(c_begin + per, cells);
+  int local = 0;
+  for (int c = c_begin; c < c_end; ++c) local += cnt[c];
+  int incl = local;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    int v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  if (lane == 31) wsum[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    int v = wsum[lane], s = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      int u = __shfl_up_sync(0xffffffffu, s, o);
+      if (lane >= o) s += u;
+    }
+    wsum[lane] = s - v;
+  }
+  __syncthreads();
+  int run = wsum[warp] + incl - local;
+  for (int c = c_begin; c < c_end; ++c) {
+    const int n = cnt[c];
+    cnt[c] = run;
+    run += n;
+  }
+  __syncthreads();
+  for (int t = threadIdx.x; t < cells; t += GRID_BUILD_THREADS) {
+    const int v = cnt[t];
+    cur[t] = v;                                   // scatter cursor
+    cst[t] = v;
+  }
+  if (threadIdx.x == 0) cst[cells] = C;
+}
+
+__global__ void __launch_bounds__(GRID_BIG_THREADS)
+grid_big_scatter_kernel(const float* __restrict__ states, const float* __restrict__ obstacles, int N, int M, int G,
+                        const GridHeader* __restrict__ header, int* __restrict__ cursors, float4* __restrict__ sorted,
+                        const int* __restrict__ skip) {
+  MACBF_SKIP_IF_SET(skip);
+  const int b = blockIdx.y, C = N + M;
+  const GridHeader g = header[b];
+  int* cur = cursors + (size_t)b * (GRID_GMAX * GRID_GMAX + 1);
+  const int t_begin = blockIdx.x * GRID_BIG_PER_CTA, t_end = min(C, t_begin + GRID_BIG_PER_CTA);
+  for (int t = t_begin + threadIdx.x; t < t_end; t += GRID_BIG_THREADS) {
+    const float4 sv = load_candidate(states, obstacles, b, t, N, M);
+    const int cell = cell_coord(sv.y, g.oy, g.inv_cs, G) * G + cell_coord(sv.x, g.ox, g.inv_cs, G);
+    const int pos = atomicAdd(&cur[cell], 1);
+    sorted[(size_t)b * C + pos] = make_float4(sv.x, sv.y, __int_as_float(t), 0.f);
+  }
+}
+
 // ---- packed (key, index) entries: key bits in the high word (keys are positive floats, so the
 //      unsigned order of the bits is the numeric order), candidate index in the low word ----------
 typedef unsigned long long u64;
@@ -426,8 +567,11 @@ static int launch_tpq(const float4* sorted, const int* cell_start, const GridHea
 
 size_t neighbor_grid_workspace_bytes(int B, int N, int M) {
   const size_t C = (size_t)N + M;
-  return (size_t)B * C * sizeof(float4) + (size_t)B * (GRID_GMAX * GRID_GMAX + 1) * sizeof(int) +
-         (size_t)B * sizeof(GridHeader) + 256;
+  size_t bytes = (size_t)B * C * sizeof(float4) + (size_t)B * (GRID_GMAX * GRID_GMAX + 1) * sizeof(int) +
+                 (size_t)B * sizeof(GridHeader) + 256;
+  if (C >= (size_t)GRID_BIG_MIN_C)                      // multi-CTA build: scatter cursors + bounding boxes
+    bytes += (size_t)B * (GRID_GMAX * GRID_GMAX + 1) * sizeof(int) + (size_t)B * 16 + 256;
+  return bytes;
 }
 
 // true when the grid path applies (the caller falls back to the brute-force kernel otherwise)
@@ -453,9 +597,28 @@ int neighbor_topk_grid(const float* states, const float* obstacles, int B, int N
   const size_t build_smem = (size_t)(G * G + 1) * sizeof(int);
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(grid_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)((GRID_GMAX * GRID_GMAX + 1) * sizeof(int))));
-  grid_build_kernel<<<B, GRID_BUILD_THREADS, build_smem, st>>>(states, obstacles, N, M, G, sorted, cell_start, header,
-                                                               tl_skip_flag);
-  MACBF_CHECK_LAUNCH("grid_build_kernel");
+  if (C >= GRID_BIG_MIN_C) {
+    char* extra = (char*)header + (((size_t)B * sizeof(GridHeader) + 255) & ~(size_t)255);
+    int* cursors = (int*)extra;
+    unsigned* box = (unsigned*)(extra + (size_t)B * (GRID_GMAX * GRID_GMAX + 1) * sizeof(int));
+    const dim3 gpts((C + GRID_BIG_PER_CTA - 1) / GRID_BIG_PER_CTA, B);
+    grid_big_init_kernel<<<dim3(8, B), GRID_BIG_THREADS, 0, st>>>(box, cursors, G * G + 1, tl_skip_flag);
+    MACBF_CHECK_LAUNCH("grid_big_init_kernel");
+    grid_big_bbox_kernel<<<gpts, GRID_BIG_THREADS, 0, st>>>(states, obstacles, N, M, box, tl_skip_flag);
+    MACBF_CHECK_LAUNCH("grid_big_bbox_kernel");
+    grid_big_hist_kernel<<<gpts, GRID_BIG_THREADS, 0, st>>>(states, obstacles, N, M, G, box, cursors, header, tl_skip_flag);
+    MACBF_CHECK_LAUNCH("grid_big_hist_kernel");
+    MACBF_CHECK_CUDA(cudaFuncSetAttribute(grid_big_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)((GRID_GMAX * GRID_GMAX + 1) * sizeof(int))));
+    grid_big_scan_kernel<<<B, GRID_BUILD_THREADS, build_smem, st>>>(C, G, cursors, cell_start, tl_skip_flag);
+    MACBF_CHECK_LAUNCH("grid_big_scan_kernel");
+    grid_big_scatter_kernel<<<gpts, GRID_BIG_THREADS, 0, st>>>(states, obstacles, N, M, G, header, cursors, sorted, tl_skip_flag);
+    MACBF_CHECK_LAUNCH("grid_big_scatter_kernel");
+  } else {
+    grid_build_kernel<<<B, GRID_BUILD_THREADS, build_smem, st>>>(states, obstacles, N, M, G, sorted, cell_start, header,
+                                                                 tl_skip_flag);
+    MACBF_CHECK_LAUNCH("grid_build_kernel");
+  }
   {
     switch (K) {   // thread-per-query instantiations for the common neighbour counts
       case 4: return launch_tpq<4>(sorted, cell_start, header, B, N, C, G, idx, st);
