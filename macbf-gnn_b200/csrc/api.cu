@@ -99,6 +99,28 @@ static int check_dims(const char* fn, int B, int N, int M, int K) {
 
 static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
+// ---- side stream of the fused step ---------------------------------------------------------------------------------
+// The neighbour search on S' (grid build + one thread per query: latency-bound, 14 warps per SM, no shared memory)
+// only needs s_next, and CBF(S) only needs idx: the fused step runs the search on a second stream UNDER the tensor-core
+// CBF(S) kernel, whose persistent CTAs leave a quarter of the register file and most issue slots idle.  Fork / join by
+// events (capturable).  The stream and the two events are created once per (host thread, device) on first use and kept.
+struct SideStream { cudaStream_t stream = nullptr; cudaEvent_t fork = nullptr, join = nullptr; };
+static int side_stream_for_current_device(SideStream** out) {
+  static thread_local SideStream side[64];        // per host thread: two threads never share fork / join events
+  int dev = -1;
+  MACBF_CHECK_CUDA(cudaGetDevice(&dev));
+  MACBF_CHECK_ARG(dev >= 0 && dev < 64, "device ordinal %d not supported", dev);
+  SideStream& s = side[dev];
+  if (s.stream == nullptr) {
+    MACBF_CHECK_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    MACBF_CHECK_CUDA(cudaEventCreateWithFlags(&s.fork, cudaEventDisableTiming));
+    MACBF_CHECK_CUDA(cudaEventCreateWithFlags(&s.join, cudaEventDisableTiming));
+  }
+  *out = &s;
+  return 0;
+}
+
+
 }  // namespace macbf
 
 using namespace macbf;
@@ -346,11 +368,20 @@ int macbf_step_forward_ex(const float* states, const float* goals, const float* 
   if (rc) return rc;
   if (flags & MACBF_STEP_REUSE_INDICES) {   // h' on S's graph (the upstream `indices=` argument the reference dropped)
     MACBF_CHECK_CUDA(cudaMemcpyAsync(idx_next, idx, (size_t)B * N * K * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
-  } else if ((rc = neighbor_any(s_next, obstacles, B, N, M, top_k, idx_next, gscratch, gbytes, st))) {   // core.py:137
-    return rc;
+    if ((rc = cbf_forward(states, obstacles, idx, cbf_params, B, N, M, K, semantics, dist_min_thres, obs_radius, h, st)))
+      return rc;
+  } else {
+    // graph(S') (core.py:137) on the side stream, under CBF(S) on the caller's stream
+    SideStream* side = nullptr;
+    if ((rc = side_stream_for_current_device(&side))) return rc;
+    MACBF_CHECK_CUDA(cudaEventRecord(side->fork, st));
+    MACBF_CHECK_CUDA(cudaStreamWaitEvent(side->stream, side->fork, 0));
+    if ((rc = neighbor_any(s_next, obstacles, B, N, M, top_k, idx_next, gscratch, gbytes, side->stream))) return rc;
+    MACBF_CHECK_CUDA(cudaEventRecord(side->join, side->stream));
+    if ((rc = cbf_forward(states, obstacles, idx, cbf_params, B, N, M, K, semantics, dist_min_thres, obs_radius, h, st)))
+      return rc;
+    MACBF_CHECK_CUDA(cudaStreamWaitEvent(st, side->join, 0));
   }
-  if ((rc = cbf_forward(states, obstacles, idx, cbf_params, B, N, M, K, semantics, dist_min_thres, obs_radius, h, st)))
-    return rc;
   if ((rc = cbf_forward(s_next, obstacles, idx_next, cbf_params, B, N, M, K, semantics, dist_min_thres, obs_radius,
                         h_next, st))) return rc;
   return loss_forward(states, goals, obstacles, idx, h, h_next, u, B, N, M, K, dist_min_thres, ttc, dt, alpha,

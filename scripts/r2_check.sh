@@ -17,3 +17,4 @@ if t:
     print(t.get('roofline'))
 print('cpu',d.get('cpu_baseline'))
 PY
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -3
