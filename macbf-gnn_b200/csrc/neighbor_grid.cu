@@ -476,7 +476,13 @@ knn_grid_kernel(const float* __restrict__ states, const float4* __restrict__ sor
 // list in registers (packed (key, index) words) and streams the candidates of its rings one at a
 // time; an instruction now serves 32 queries instead of one, which is ~3x fewer issue slots per
 // query than the warp-per-query kernel above.  Same rings, same stop test, same exact pre-filter.
-template <int K>
+// The kernel is bound by the serial compare-exchange chain of the sorted insertion (~85 instructions per accepted
+// candidate, ~100 loop trips per warp): staging the candidates in shared memory bought 4 %, and two lanes per query
+// with a bitonic merge of their lists per ring was slower (47 vs 43 us) - more parallelism, but more instructions.
+// STAGE: the env's sorted candidates and cell starts are first copied into shared memory (coalesced), so that the
+// dependent per-candidate loads of the loop below are LDS round trips (~30 cycles) instead of L1/L2 ones (the cell
+// starts of 64 envs do not fit L1: every ring paid two ~300-cycle L2 loads per cell range).
+template <int K, bool STAGE>
 __global__ void __launch_bounds__(128)
 knn_grid_tpq_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start,
                     const GridHeader* __restrict__ header, int N, int C, int G, int32_t* __restrict__ idx_out,
@@ -484,11 +490,20 @@ knn_grid_tpq_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
   MACBF_SKIP_IF_SET(skip);
   const int b = blockIdx.y;
   const int p0 = blockIdx.x * blockDim.x + threadIdx.x;
-  if (p0 >= C) return;
   const GridHeader g = header[b];
   const int* cs = cell_start + (size_t)b * (GRID_GMAX * GRID_GMAX + 1);
   const float4* pts = sorted + (size_t)b * C;
-  const float4 me = __ldg(pts + p0);
+  if constexpr (STAGE) {
+    extern __shared__ float4 s_pts[];                  // [C] candidates, then [G*G + 1] cell starts
+    int* s_cs = reinterpret_cast<int*>(s_pts + C);
+    for (int t = threadIdx.x; t < C; t += blockDim.x) s_pts[t] = __ldg(pts + t);
+    for (int t = threadIdx.x; t <= G * G; t += blockDim.x) s_cs[t] = __ldg(cs + t);
+    __syncthreads();
+    pts = s_pts;
+    cs = s_cs;
+  }
+  if (p0 >= C) return;
+  const float4 me = pts[p0];
   const int i = __float_as_int(me.z);
   if (i >= N) return;                                  // obstacle points are candidates, not queries
   const float qx = me.x, qy = me.y;
@@ -516,10 +531,10 @@ knn_grid_tpq_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
       }
       x0 = max(x0, 0); x1 = min(x1, G - 1);
       if (y < 0 || y >= G || x0 > x1) continue;
-      int p = __ldg(cs + y * G + x0);
-      const int pend = __ldg(cs + y * G + x1 + 1);
+      int p = cs[y * G + x0];
+      const int pend = cs[y * G + x1 + 1];
       for (; p < pend; ++p) {
-        const float4 c = __ldg(pts + p);
+        const float4 c = pts[p];
         // core.py:238, op by op
         const float dx = xsub(qx, c.x), dy = xsub(qy, c.y);
         const float v = xadd(xadd(xmul(dx, dx), 1e-6f), xadd(xmul(dy, dy), 1e-6f));
@@ -558,9 +573,18 @@ knn_grid_tpq_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
 template <int K>
 static int launch_tpq(const float4* sorted, const int* cell_start, const GridHeader* header, int B, int N, int C, int G,
                       int32_t* idx, cudaStream_t st) {
+  const size_t stage_bytes = (size_t)C * sizeof(float4) + (size_t)(G * G + 1) * sizeof(int);
   dim3 grid((C + 127) / 128, B);
-  knn_grid_tpq_kernel<K><<<grid, 128, 0, st>>>(sorted, cell_start, header, N, C, G, idx, tl_skip_flag, tl_query_part.part,
-                                               tl_query_part.nparts, tl_row_range.begin, tl_row_range.end);
+  if (stage_bytes <= 96 * 1024) {                      // small envs: candidates + cell starts through shared memory
+    MACBF_CHECK_CUDA(cudaFuncSetAttribute(knn_grid_tpq_kernel<K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+    knn_grid_tpq_kernel<K, true><<<grid, 128, stage_bytes, st>>>(sorted, cell_start, header, N, C, G, idx, tl_skip_flag,
+                                                                 tl_query_part.part, tl_query_part.nparts, tl_row_range.begin,
+                                                                 tl_row_range.end);
+  } else {
+    knn_grid_tpq_kernel<K, false><<<grid, 128, 0, st>>>(sorted, cell_start, header, N, C, G, idx, tl_skip_flag,
+                                                        tl_query_part.part, tl_query_part.nparts, tl_row_range.begin,
+                                                        tl_row_range.end);
+  }
   MACBF_CHECK_LAUNCH("knn_grid_tpq_kernel");
   return 0;
 }
