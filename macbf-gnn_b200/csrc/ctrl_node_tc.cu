@@ -207,14 +207,13 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
       wait_st();
     }
     if (warp == 0) MACBF_TRACE_MARK(0, 4);
-    // the head below still needs this tile's state and goal (column group 0 re-reads them from L1/L2)
-    load_tile(tile + gridDim.x);
     fence_before_sync();
     __syncthreads();
     if (warp == 0) {   // ---- layer 1 ----
       fence_after_sync();
       mma_3xtf32_ts_commit<K1 / 8>(tb + C_D1, tb + C_A0HI, tb + C_A0LO, d_w1hi, d_w1lo, (64 * 128), IDESC64, &bar[0]);
     }
+    load_tile(tile + gridDim.x);                   // next tile's inputs, requested once layer 1 is on its way
     mbar_wait(&bar[0], par);
     fence_after_sync();
     if (warp == 0) MACBF_TRACE_MARK(0, 5);
