@@ -30,7 +30,7 @@
 
 namespace macbf {
 
-__global__ void reduce_partials_kernel(const float* __restrict__ partial, int nslices, int P, float* __restrict__ out);
+int reduce_partials(const float* partial, int nslices, int P, float* out, cudaStream_t st);
 int cbf_forward_tc_dump(const float* states, const float* obstacles, const int32_t* idx, const float* params, int N, int M,
                         int K, long long agents, double dist_min, double obs_radius, long long tile_begin,
                         long long tile_end, const float* grad_h, unsigned char* rec, float* slices, cudaStream_t st);
@@ -736,9 +736,7 @@ int cbf_backward_tc(const float* states, const float* obstacles, const int32_t* 
                                                                        cbfrec::REC_STAGE);
     MACBF_CHECK_LAUNCH("wgrad_tc_kernel<cbf>");
   }
-  reduce_partials_kernel<<<(MACBF_CBF_PARAMS + 255) / 256, 256, 0, st>>>(slices, NUM_SMS, MACBF_CBF_PARAMS, grad_params);
-  MACBF_CHECK_LAUNCH("reduce_partials_kernel");
-  return 0;
+  return reduce_partials(slices, NUM_SMS, MACBF_CBF_PARAMS, grad_params, st);
 }
 
 }  // namespace macbf

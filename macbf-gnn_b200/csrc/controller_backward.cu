@@ -11,8 +11,7 @@
 
 namespace macbf {
 
-__global__ void reduce_partials_kernel(const float* __restrict__ partial, int nslices, int P,
-                                       float* __restrict__ out);
+int reduce_partials(const float* partial, int nslices, int P, float* out, cudaStream_t st);
 
 
 static inline size_t a256(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -66,10 +65,7 @@ int controller_backward(const float* states, const float* goals, const float* ob
   rc = ctrl_edge_bwd_tc(states, obstacles, idx, params, pool, B, N, M, K, partial, grad_states, edge_scratch, st,
                         saved ? argk_saved : nullptr);
   if (rc) return rc;
-  reduce_partials_kernel<<<(MACBF_CTRL_PARAMS + 255) / 256, 256, 0, st>>>(partial, CTRL_SLICES, MACBF_CTRL_PARAMS,
-                                                                          grad_params);
-  MACBF_CHECK_LAUNCH("reduce_partials_kernel");
-  return 0;
+  return reduce_partials(partial, CTRL_SLICES, MACBF_CTRL_PARAMS, grad_params, st);
 }
 
 }  // namespace macbf

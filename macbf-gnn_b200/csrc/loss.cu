@@ -12,6 +12,7 @@ namespace macbf {
 constexpr int LOSS_THREADS = 256;
 constexpr int LOSS_ROWS_PER_CTA = 1024;
 constexpr int LOSS_NACC = 10;
+static_assert(LOSS_ROWS_PER_CTA % LOSS_THREADS == 0, "whole rows per thread");
 
 static inline int loss_chunks(int N, int K) {
   long long rows = (long long)N * K;
@@ -50,15 +51,37 @@ loss_partial_kernel(const float* __restrict__ states, const float* __restrict__ 
 #pragma unroll
   for (int q = 0; q < LOSS_NACC; ++q) acc[q] = 0.f;
 
-  for (long long r = r_begin + threadIdx.x; r < r_end; r += LOSS_THREADS) {
+  // a thread's LOSS_ROWS_PER_CTA / LOSS_THREADS rows: all neighbour indices first, then all endpoint states, then the
+  // arithmetic - three rounds of dependent loads per CTA instead of three per row
+  constexpr int RPT = LOSS_ROWS_PER_CTA / LOSS_THREADS;
+  int jj[RPT];
+  float4 si_[RPT], sj_[RPT];
+  float hv_[RPT], hn_[RPT];
+#pragma unroll
+  for (int q = 0; q < RPT; ++q) {
+    const long long r = r_begin + threadIdx.x + q * LOSS_THREADS;
+    jj[q] = -1; hv_[q] = 0.f; hn_[q] = 0.f;
+    if (r < r_end) {
+      const long long e = (long long)b * rows_env + r;
+      jj[q] = __ldg(idx + e);
+      hv_[q] = __ldg(h + e);
+      if (h_next != nullptr) hn_[q] = __ldg(h_next + e);
+      si_[q] = __ldg(reinterpret_cast<const float4*>(states) + (size_t)b * N + (int)(r / K));
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < RPT; ++q)
+    if (jj[q] >= 0) sj_[q] = load_candidate(states, obstacles, b, jj[q], N, M);
+#pragma unroll
+  for (int q = 0; q < RPT; ++q) {
+    const long long r = r_begin + threadIdx.x + q * LOSS_THREADS;
+    if (r >= r_end) continue;
     const int i = (int)(r / K);
     const long long e = (long long)b * rows_env + r;
-    const int j = __ldg(idx + e);
-    const float4 si = __ldg(reinterpret_cast<const float4*>(states) + (size_t)b * N + i);
-    const float4 sj = load_candidate(states, obstacles, b, j, N, M);
-    const bool dang = ttc_dangerous(edge_geom(si, sj, i, j), r2, ttc);
+    const int j = jj[q];
+    const bool dang = ttc_dangerous(edge_geom(si_[q], sj_[q], i, j), r2, ttc);
     mask[e] = dang ? 1 : 0;
-    const float hv = __ldg(h + e);
+    const float hv = hv_[q];
     if (dang) {
       acc[8] += 1.f;
       acc[0] += fmaxf(xadd(hv, 1e-3f), 0.f);   // core.py:114-115
@@ -69,7 +92,7 @@ loss_partial_kernel(const float* __restrict__ states, const float* __restrict__ 
     }
     if (h_next != nullptr) {
       // core.py:139: h_next - h + TIME_STEP * ALPHA_CBF * h
-      const float d = xadd(xsub(__ldg(h_next + e), hv), xmul(dt_alpha, hv));
+      const float d = xadd(xsub(hn_[q], hv), xmul(dt_alpha, hv));
       if (dang) {
         acc[4] += fmaxf(xadd(-d, 1e-3f), 0.f);
         acc[6] += (d >= 0.f) ? 1.f : 0.f;
