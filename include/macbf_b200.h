@@ -251,6 +251,23 @@ int macbf_rollout_forward(const float* states0, const float* goals, const float*
                           float* traj_states, float* traj_actions, int32_t* steps_run, void* workspace,
                           size_t workspace_bytes, void* stream);
 
+/* Backward through the rollout.  The reference does not detach its trajectory (train.py:59-81 builds the visited states
+ * and actions inside autograd, train.py:88-100 backpropagates the losses through all of them), so the gradient of a
+ * loss L(s_0 .. s_{T-1}, a_0 .. a_{T-1}) runs back through every controller call and Euler step:
+ *   G_T = 0;  t = T-1 .. 0:  graph(s_t), controller backward at s_t with d/du = dL/da_t + dt G_{t+1}[v],
+ *   G_t = dL/ds_t + (d u_t / d s_t)^T d/du + the Euler step's direct terms.
+ * traj_states [>= steps, B,N,4] as written by macbf_rollout_forward; grad_traj_states [steps, B,N,4] (may be NULL = 0)
+ * and grad_traj_actions [steps, B,N,2] are dL/ds_t, dL/da_t and must be ZERO in the slots of an env beyond its
+ * steps_run (they are not part of its trajectory).  grad_params [34052] and grad_goals [B,N,2] (optional) are
+ * accumulated into; grad_states0 [B,N,4] (optional) is overwritten with dL/ds_0.  Graphs and activations are
+ * recomputed per step; nothing but the trajectory is kept from the forward.  REPAIRED semantics.  No host sync. */
+size_t macbf_rollout_backward_scratch_bytes(int B, int N, int M, int top_k);
+int macbf_rollout_backward(const float* traj_states, const float* goals, const float* obstacles,
+                           const float* ctrl_params, const float* grad_traj_states,
+                           const float* grad_traj_actions, int B, int N, int M, int top_k, int steps,
+                           double obs_radius, double dt, float* grad_params, float* grad_states0,
+                           float* grad_goals, void* scratch, size_t scratch_bytes, void* stream);
+
 /* ---- 8f-4: forward step of ONE large env row-sharded over several GPUs (no counterpart in the reference: its dense
  * (N,N,C) tensors of cbf.py:23-30 / controller.py:33 / core.py:188 do not exist at the sizes where this matters) --------
  * The step of macbf_step_forward for B = 1, REPAIRED semantics, restricted to the agents [row_begin, row_end) as

@@ -47,6 +47,9 @@ void timing_mark(const char* name) {
 int neighbor_topk(const float*, const float*, int, int, int, int, int32_t*, cudaStream_t);
 int dense_topk(const float*, int, int, int, int, int32_t*, cudaStream_t);
 size_t rollout_workspace_bytes(int, int, int, int);
+size_t rollout_backward_scratch_bytes(int, int, int, int);
+int rollout_backward(const float*, const float*, const float*, const float*, const float*, const float*, int, int, int, int, int,
+                     double, double, float*, float*, float*, void*, size_t, cudaStream_t);
 int rollout_forward(const float*, const float*, const float*, const float*, const float*, int, int, int, int, int, int, double, double,
                     double, float*, float*, int32_t*, void*, size_t, cudaStream_t);
 size_t neighbor_grid_workspace_bytes(int, int, int);
@@ -505,6 +508,29 @@ int macbf_rollout_forward(const float* states0, const float* goals, const float*
   MACBF_CHECK_ARG(semantics == MACBF_LITERAL || semantics == MACBF_REPAIRED, "%s: bad semantics %d", fn, semantics);
   return rollout_forward(states0, goals, obstacles, ctrl_params, noise, B, N, M, top_k, max_steps, semantics, obs_radius, dt,
                          dist_stop, traj_states, traj_actions, steps_run, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+size_t macbf_rollout_backward_scratch_bytes(int B, int N, int M, int top_k) {
+  return rollout_backward_scratch_bytes(B, N, M, top_k);
+}
+
+int macbf_rollout_backward(const float* traj_states, const float* goals, const float* obstacles, const float* ctrl_params,
+                           const float* grad_traj_states, const float* grad_traj_actions, int B, int N, int M, int top_k,
+                           int steps, double obs_radius, double dt, float* grad_params, float* grad_states0,
+                           float* grad_goals, void* scratch, size_t scratch_bytes, void* stream) {
+  const char* fn = "macbf_rollout_backward";
+  MACBF_CHECK_ARG(top_k >= 1 && top_k <= MACBF_MAX_K, "%s: top_k=%d out of range [1,%d]", fn, top_k, MACBF_MAX_K);
+  if (check_dims(fn, B, N, M, macbf_neighbor_count(N, M, top_k))) return 1;
+  MACBF_CHECK_ARG(steps >= 1, "%s: steps=%d must be >= 1", fn, steps);
+  REQ_PTR(fn, traj_states); REQ_PTR(fn, goals); REQ_PTR(fn, ctrl_params); REQ_PTR(fn, grad_traj_actions);
+  REQ_PTR(fn, grad_params); REQ_PTR(fn, scratch);
+  REQ_A16(fn, traj_states); REQ_A16(fn, scratch);
+  MACBF_CHECK_ARG(grad_traj_states == nullptr || (((uintptr_t)grad_traj_states) & 15) == 0,
+                  "%s: grad_traj_states must be 16-byte aligned", fn);
+  MACBF_CHECK_ARG(grad_states0 == nullptr || (((uintptr_t)grad_states0) & 15) == 0, "%s: grad_states0 must be 16-byte aligned", fn);
+  MACBF_CHECK_ARG(M == 0 || obstacles != nullptr, "%s: obstacles is NULL but M=%d", fn, M);
+  return rollout_backward(traj_states, goals, obstacles, ctrl_params, grad_traj_states, grad_traj_actions, B, N, M, top_k, steps,
+                          obs_radius, dt, grad_params, grad_states0, grad_goals, scratch, scratch_bytes, (cudaStream_t)stream);
 }
 
 }  // extern "C"

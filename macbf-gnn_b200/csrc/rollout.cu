@@ -128,4 +128,63 @@ int rollout_forward(const float* states0, const float* goals, const float* obsta
   return rc;
 }
 
+// ---- backward through the rollout (the reference's trajectory is NOT detached, train.py:59-81: autograd runs back
+// through every controller call and Euler step) ------------------------------------------------------------------
+// Given dL/ds_t (t = 0 .. T-1, optional) and dL/da_t, with s_{t+1} = s_t + [v_t, a_t] dt and a_t = u_t (+ noise):
+//   G_T = 0;  for t = T-1 .. 0:  graph(s_t);  controller backward at s_t with d/du = dL/da_t + dt G_{t+1}[v]
+//   (macbf_controller_backward's grad_s_next argument) -> parameter gradients (accumulated), G_t = dL/ds_t + d u/d s_t
+//   + the Euler step's direct terms.  The trajectory is the only thing kept from the forward; graphs and activations
+//   are recomputed step by step, all enqueued back to back on the stream.
+size_t controller_backward_scratch_bytes(int B, int N, int K);
+int controller_backward(const float*, const float*, const float*, const int32_t*, const float*, const float*, const float*,
+                        int, int, int, int, double, double, float*, float*, float*, void*, size_t, cudaStream_t, float*,
+                        const uint8_t*);
+
+// scratch: [idx B*N*K][G ping][G pong][grid scratch][controller backward scratch]
+size_t rollout_backward_scratch_bytes(int B, int N, int M, int top_k) {
+  const int K = (N + M) < top_k ? (N + M) : top_k;
+  const size_t g = neighbor_grid_applicable(N, M, top_k) ? neighbor_grid_workspace_bytes(B, N, M) : 0;
+  return a256((size_t)B * N * K * sizeof(int32_t)) + 2 * a256((size_t)B * N * 4 * sizeof(float)) + a256(g) +
+         a256(controller_backward_scratch_bytes(B, N, K));
+}
+
+int rollout_backward(const float* traj_states, const float* goals, const float* obstacles, const float* ctrl_params,
+                     const float* grad_traj_states, const float* grad_traj_actions, int B, int N, int M, int top_k, int steps,
+                     double obs_radius, double dt, float* grad_params, float* grad_states0, float* grad_goals, void* scratch,
+                     size_t scratch_bytes, cudaStream_t st) {
+  const int K = (N + M) < top_k ? (N + M) : top_k;
+  MACBF_CHECK_ARG(scratch_bytes >= rollout_backward_scratch_bytes(B, N, M, top_k), "rollout_backward: scratch too small (%zu < %zu)",
+                  scratch_bytes, rollout_backward_scratch_bytes(B, N, M, top_k));
+  const size_t sbytes = (size_t)B * N * 4 * sizeof(float);
+  char* w = (char*)scratch;
+  int32_t* idx = (int32_t*)w; w += a256((size_t)B * N * K * sizeof(int32_t));
+  float* G[2];
+  G[0] = (float*)w; w += a256(sbytes);
+  G[1] = (float*)w; w += a256(sbytes);
+  const size_t gbytes = neighbor_grid_applicable(N, M, top_k) ? neighbor_grid_workspace_bytes(B, N, M) : 0;
+  void* gscratch = gbytes ? (void*)w : nullptr;
+  w += a256(gbytes);
+  void* cscratch = (void*)w;
+  const size_t cbytes = controller_backward_scratch_bytes(B, N, K);
+  int rc = 0;
+  for (int t = steps - 1; t >= 0 && rc == 0; --t) {
+    const float* s_t = traj_states + (size_t)t * B * N * 4;
+    float* g_t = G[t & 1];
+    const float* g_next = (t == steps - 1) ? nullptr : G[(t + 1) & 1];      // G_T = 0: the loss does not see s_T
+    if (grad_traj_states != nullptr) {
+      MACBF_CHECK_CUDA(cudaMemcpyAsync(g_t, grad_traj_states + (size_t)t * B * N * 4, sbytes, cudaMemcpyDeviceToDevice, st));
+    } else {
+      MACBF_CHECK_CUDA(cudaMemsetAsync(g_t, 0, sbytes, st));
+    }
+    rc = gscratch ? neighbor_topk_grid(s_t, obstacles, B, N, M, K, idx, gscratch, gbytes, st)
+                  : neighbor_topk(s_t, obstacles, B, N, M, top_k, idx, st);
+    if (rc) break;
+    rc = controller_backward(s_t, goals, obstacles, idx, ctrl_params, grad_traj_actions + (size_t)t * B * N * 2, g_next, B, N,
+                             M, K, obs_radius, dt, grad_params, g_t, grad_goals, cscratch, cbytes, st, nullptr, nullptr);
+  }
+  if (rc == 0 && grad_states0 != nullptr)
+    MACBF_CHECK_CUDA(cudaMemcpyAsync(grad_states0, G[0], sbytes, cudaMemcpyDeviceToDevice, st));
+  return rc;
+}
+
 }  // namespace macbf

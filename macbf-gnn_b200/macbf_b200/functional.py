@@ -120,3 +120,44 @@ class HingeLossFunction(torch.autograd.Function):
                                              want_u=has_u and ctx.needs_input_grad[2],
                                              want_states=has_u and ctx.needs_input_grad[3])
         return gh, ghn, gu, gst, None, None, None
+
+
+class RolloutFunction(torch.autograd.Function):
+    """The closed loop of train.py:59-81 as ONE autograd node: forward = macbf_rollout_forward (stop test on the device, a
+    single host read of the step counts at the end), backward = macbf_rollout_backward (BPTT through every controller
+    call and Euler step of the saved trajectory; the reference does not detach it).
+    -> (traj_states [T,B,N,4], traj_actions [T,B,N,2], steps_run [B]) with T = max over envs of steps_run; slots of an
+    env beyond its own steps_run hold its continued simulation and receive no gradient."""
+
+    @staticmethod
+    def forward(ctx, states0, goals, obstacles, noise, max_steps, top_k, dist_stop, *params):
+        flat = pack_params(params)
+        ts, ta, steps = ops.rollout_forward(states0, goals, flat, max_steps, obstacles, noise, top_k=top_k,
+                                            semantics=ops.REPAIRED, dist_stop=dist_stop)
+        T = int(steps.max().item())          # the one host synchronisation of the rollout
+        ctx.traj, ctx.steps, ctx.T = ts, steps, T
+        ctx.save_for_backward(goals, flat, obstacles if obstacles is not None else states0.new_empty(0))
+        ctx.has_obs = obstacles is not None
+        ctx.top_k = top_k
+        ctx.param_shapes = [p.shape for p in params]
+        ctx.mark_non_differentiable(steps)
+        return ts[:T], ta[:T], steps
+
+    @staticmethod
+    def backward(ctx, g_ts, g_ta, _g_steps):
+        goals, flat, obs = ctx.saved_tensors
+        obs = obs if ctx.has_obs else None
+        T, steps = ctx.T, ctx.steps
+        live = (torch.arange(T, device=steps.device)[:, None] < steps[None, :]).to(torch.float32)[:, :, None, None]
+        g_ta = (g_ta * live).contiguous() if g_ta is not None else torch.zeros_like(ctx.traj[:T, ..., :2])
+        g_ts = (g_ts * live).contiguous() if g_ts is not None else None
+        gp, gs0, gg = ops.rollout_backward(ctx.traj, goals, flat, g_ta, g_ts, obs, top_k=ctx.top_k,
+                                           want_grad_states0=ctx.needs_input_grad[0],
+                                           want_grad_goals=ctx.needs_input_grad[1])
+        ctx.traj = None
+        grads, off = [], 0
+        for shp in ctx.param_shapes:
+            n = int(torch.Size(shp).numel())
+            grads.append(gp[off:off + n].view(shp))
+            off += n
+        return (gs0, gg, None, None, None, None, None, *grads)

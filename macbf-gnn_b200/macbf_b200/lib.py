@@ -51,6 +51,9 @@ SIGNATURES = {
     "macbf_rollout_workspace_bytes": (SZ, [I, I, I, I]),
     "macbf_rollout_forward": (I, [c_f32p, c_f32p, c_f32p, c_f32p, c_f32p, I, I, I, I, I, I, D, D, D, c_f32p, c_f32p, c_i32p,
                                   c_void, SZ, c_void]),
+    "macbf_rollout_backward_scratch_bytes": (SZ, [I, I, I, I]),
+    "macbf_rollout_backward": (I, [c_f32p, c_f32p, c_f32p, c_f32p, c_f32p, c_f32p, I, I, I, I, I, D, D, c_f32p, c_f32p, c_f32p,
+                                   c_void, SZ, c_void]),
     "macbf_step_workspace_bytes": (SZ, [I, I, I, I]),
     "macbf_step_workspace_winners_offset": (SZ, [I, I, I, I]),
     "macbf_controller_backward_saved": (I, [c_f32p, c_f32p, c_f32p, c_i32p, c_f32p, c_f32p, c_f32p, I, I, I, I, D, D, c_f32p,

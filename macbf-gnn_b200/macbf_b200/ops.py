@@ -392,6 +392,35 @@ def rollout_forward(states, goals, ctrl_params, max_steps, obstacles=None, noise
     return ts, ta, steps
 
 
+@_on_device_of
+def rollout_backward(traj_states, goals, ctrl_params, grad_traj_actions, grad_traj_states=None, obstacles=None, top_k=TOP_K,
+                     obs_radius=OBS_RADIUS, dt=TIME_STEP, grad_params=None, want_grad_states0=False, want_grad_goals=False):
+    """Autograd of the rollout (train.py:59-81 is not detached): dL/da_t [T,B,N,2] and dL/ds_t [T,B,N,4] (optional), zero
+    beyond an env's steps_run -> (grad_params [34052], dL/ds_0 | None, grad_goals | None).  traj_states: the first T (or
+    more) slots of rollout_forward's trajectory."""
+    _need_cuda(traj_states, goals, ctrl_params, grad_traj_actions, grad_traj_states, obstacles, grad_params)
+    traj_states, goals, ctrl_params, grad_traj_actions, grad_traj_states, obstacles = map(
+        _c, (traj_states, goals, ctrl_params, grad_traj_actions, grad_traj_states, obstacles))
+    T = grad_traj_actions.shape[0]
+    B, N, M, obstacles = _dims(traj_states[0], obstacles)
+    if traj_states.shape[0] < T or tuple(grad_traj_actions.shape) != (T, B, N, 2):
+        raise ValueError(f"grad_traj_actions must be [T<={traj_states.shape[0]}, {B}, {N}, 2], got {tuple(grad_traj_actions.shape)}")
+    if grad_traj_states is not None and tuple(grad_traj_states.shape) != (T, B, N, 4):
+        raise ValueError(f"grad_traj_states must be [{T}, {B}, {N}, 4], got {tuple(grad_traj_states.shape)}")
+    dev = traj_states.device
+    if grad_params is None:
+        grad_params = torch.zeros((CTRL_PARAMS,), dtype=torch.float32, device=dev)
+    gs0 = torch.empty((B, N, 4), dtype=torch.float32, device=dev) if want_grad_states0 else None
+    gg = torch.zeros((B, N, 2), dtype=torch.float32, device=dev) if want_grad_goals else None
+    L = _lib.load()
+    nbytes = L.macbf_rollout_backward_scratch_bytes(B, N, M, top_k)
+    scratch = torch.empty((max(nbytes, 256),), dtype=torch.uint8, device=dev)
+    _lib.check(L.macbf_rollout_backward(_p(traj_states), _p(goals), _p(obstacles), _p(ctrl_params), _p(grad_traj_states),
+                                        _p(grad_traj_actions), B, N, M, top_k, T, obs_radius, dt, _p(grad_params), _p(gs0),
+                                        _p(gg), _p(scratch), scratch.numel(), _stream()), "macbf_rollout_backward")
+    return grad_params, gs0, gg
+
+
 def launch_count() -> int:
     return int(_lib.load().macbf_launch_count())
 

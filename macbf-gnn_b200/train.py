@@ -20,6 +20,7 @@ import torch.optim as optim
 
 import cbf
 import controller
+import core as _core
 from config import *  # noqa: F401,F403
 from core import *  # noqa: F401,F403
 
@@ -35,9 +36,10 @@ def parse_args(argv=None):
     return parser.parse_args(argv)
 
 
-def rollout(policy, states, goals):
-    """Up to INNER_LOOPS closed-loop Euler steps (train.py:59-81); returns the concatenated
-    (states, goals, actions) of the visited time steps: T*N pseudo-agents in ONE graph (T2)."""
+def rollout_stepwise(policy, states, goals):
+    """Up to INNER_LOOPS closed-loop Euler steps (train.py:59-81), one Python iteration and one host read of the stop
+    test per step, as the reference does; returns the concatenated (states, goals, actions) of the visited time steps:
+    T*N pseudo-agents in ONE graph (T2).  Kept as the cross-check of `rollout` (tests/test_gpu_train_driver.py)."""
     visited_s, visited_g, visited_a = [], [], []
     for _ in range(INNER_LOOPS):
         visited_s.append(states)
@@ -51,6 +53,41 @@ def rollout(policy, states, goals):
         if bool(reached):          # host sync per step, as in the reference (train.py:78)
             break
     return torch.cat(visited_s, dim=0), torch.cat(visited_g, dim=0), torch.cat(visited_a, dim=0)
+
+
+def _draw_noise(n_steps, shape, device):
+    """The reference's draws for `n_steps` visited steps (train.py:65-66): one np.random coin per step, one torch.randn
+    per hit.  -> [n_steps, *shape] with zero rows where the coin said no, or None when no step drew noise."""
+    hits = [np.random.uniform() < ADD_NOISE_PROB for _ in range(n_steps)]
+    if not any(hits):
+        return None
+    noise = torch.zeros((n_steps,) + tuple(shape), device=device)
+    for t, hit in enumerate(hits):
+        if hit:
+            noise[t] = torch.randn(shape, device=device) * NOISE_SCALE
+    return noise
+
+
+def rollout(policy, states, goals):
+    """The same trajectory from ONE fused call (macbf_rollout_forward: the stop test runs on the device, the host reads
+    the step count once) whose autograd is macbf_rollout_backward: BPTT through every controller call, as in the
+    reference, without a Python graph of T nodes.  The random streams are consumed exactly as the step-by-step loop
+    consumes them: noise for all INNER_LOOPS steps is drawn up front, and once the number of visited steps is known
+    the generators are rewound and advanced by the visited steps only."""
+    from macbf_b200 import functional as _F
+    np_state = np.random.get_state()
+    th_state = torch.cuda.get_rng_state(states.device)
+    n = states.shape[0]
+    noise = _draw_noise(INNER_LOOPS, (n, 2), states.device)
+    obs = _core._obstacles_for(states.unsqueeze(0))
+    ts, ta, steps = _F.RolloutFunction.apply(states.unsqueeze(0).contiguous(), goals.unsqueeze(0).contiguous(), obs,
+                                             None if noise is None else noise.unsqueeze(1).contiguous(), INNER_LOOPS, TOP_K,
+                                             DIST_MIN_CHECK, *policy._params())
+    T = ts.shape[0]
+    np.random.set_state(np_state)
+    torch.cuda.set_rng_state(th_state, states.device)
+    _draw_noise(T, (n, 2), states.device)
+    return ts.reshape(T * n, 4), goals.repeat(T, 1), ta.reshape(T * n, 2)
 
 
 def trajectory_losses(certificate, traj_s, traj_g, traj_a):

@@ -115,3 +115,64 @@ def test_rollout_rejects_small_workspace(ops):
     rc = L.macbf_rollout_forward(s.data_ptr(), g.data_ptr(), None, flat.data_ptr(), None, 1, 64, 0, 12, 2, 1, 1.0, 0.05,
                                  0.07, ts.data_ptr(), ta.data_ptr(), st.data_ptr(), ws.data_ptr(), 64, None)
     assert rc == 1 and b"workspace too small" in L.macbf_last_error()
+
+
+@pytest.mark.parametrize("N,n_obs,with_noise", [(32, 0, False), (200, 2, True)])
+def test_rollout_backward_matches_oracle_bptt(ops, N, n_obs, with_noise):
+    """macbf_rollout_backward (BPTT through the saved trajectory, train.py:59-81 is not detached) against torch
+    autograd of the oracle's loop, for envs that stop after 1, a few and all T steps; the loss touches every visited
+    state and action of every env.  Gradients on slots beyond an env's own steps_run must not count."""
+    import oracle.macbf_oracle as O
+    from macbf_b200 import functional as F
+    T = 6
+    _, p_ctrl = O.init_params(5)
+    s, g = _swarm(O, N, 11)
+    obs = O.synthetic_obstacles(3, N, n_obs, 0, 4) if n_obs else None
+    noise = None
+    if with_noise:
+        gen = torch.Generator().manual_seed(3)
+        noise = torch.randn(T, 3, N, 2, generator=gen) * 0.05
+        noise[1] = 0.0
+        noise[:, 0] = 0.0
+    gen = torch.Generator().manual_seed(9)
+    cs = torch.randn(T, 3, N, 4, generator=gen)         # L = sum_live cs . s_t + 0.5 |a_t|^2 + ca . a_t
+    ca = torch.randn(T, 3, N, 2, generator=gen)
+
+    params = [dev(p_ctrl[k]).requires_grad_(True) for k in O.CTRL_KEYS]
+    s_d, g_d = dev(s).requires_grad_(True), dev(g).requires_grad_(True)
+    ts, ta, steps = F.RolloutFunction.apply(s_d, g_d, None if obs is None else dev(obs), None if noise is None else dev(noise),
+                                            T, 12, DIST_STOP, *params)
+    Tm = ts.shape[0]
+    # NO mask here: dead slots (an env's continued simulation) get gradients from this loss, the Function drops them
+    loss = (dev(cs)[:Tm] * ts).sum() + (0.5 * ta * ta + dev(ca)[:Tm] * ta).sum()
+    loss.backward()
+    steps = steps.cpu().numpy()
+
+    ref_p = {k: p_ctrl[k].clone().requires_grad_(True) for k in O.CTRL_KEYS}
+    s_r, g_r = s.clone().requires_grad_(True), g.clone().requires_grad_(True)
+    total = 0.0
+    for b in range(3):
+        ob = None if obs is None else obs[b]
+        vis, act, _ = _oracle_rollout(O, ref_p, s_r[b], g_r[b], ob, T, None if noise is None else noise[:, b])
+        assert len(vis) == steps[b]
+        for t in range(len(vis)):
+            total = total + (cs[t, b] * vis[t]).sum() + (0.5 * act[t] * act[t] + ca[t, b] * act[t]).sum()
+    total.backward()
+    assert steps.tolist()[0] == 1 and steps[1] == T
+    gp = torch.cat([p.grad.reshape(-1) for p in params]).cpu().numpy()
+    gp_ref = torch.cat([ref_p[k].grad.reshape(-1) for k in O.CTRL_KEYS]).numpy()
+    assert_close(gp, gp_ref, 1e-4, "grad_ctrl (rollout BPTT)")
+    assert_close(s_d.grad.cpu().numpy(), s_r.grad.numpy(), 1e-4, "d/ds_0 (rollout BPTT)")
+    assert_close(g_d.grad.cpu().numpy(), g_r.grad.numpy(), 1e-4, "d/dgoals (rollout BPTT)")
+
+
+def test_rollout_backward_rejects_small_scratch(ops):
+    from macbf_b200 import lib
+    L = lib.load()
+    ts = torch.zeros(3, 1, 64, 4, device="cuda"); g = torch.zeros(1, 64, 2, device="cuda")
+    flat = torch.zeros(34052, device="cuda"); ga = torch.zeros(2, 1, 64, 2, device="cuda")
+    gp = torch.zeros(34052, device="cuda"); ws = torch.zeros(64, dtype=torch.uint8, device="cuda")
+    rc = L.macbf_rollout_backward(ts.data_ptr(), g.data_ptr(), None, flat.data_ptr(), None, ga.data_ptr(), 1, 64, 0, 12, 2, 1.0,
+                                  0.05, gp.data_ptr(), None, None, ws.data_ptr(), 64, None)
+    assert rc == 1 and b"scratch too small" in L.macbf_last_error()
+    assert L.macbf_rollout_backward_scratch_bytes(1, 64, 0, 12) > 64

@@ -74,6 +74,39 @@ def test_one_training_iteration_matches_oracle_bptt():
     assert_close(gt, gt_ref, 1e-4, "grad_ctrl (BPTT)")
 
 
+def test_fused_rollout_equals_the_step_by_step_loop():
+    """train.rollout (one fused call + macbf_rollout_backward) against train.rollout_stepwise (the reference's Python
+    loop over the per-step autograd Functions): same length, same trajectory, same gradients of a loss over it, and the
+    same consumption of np.random (the draws that follow must agree)."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import controller as ctrl_mod
+    import core
+    import train
+    torch.manual_seed(0)
+    policy = ctrl_mod.Controller(4).cuda()
+    np.random.seed(3)
+    s0, g0 = core.generate_data(48, 0.07)
+    s0 = torch.from_numpy(s0); g0 = torch.from_numpy(g0)
+    s0[:, 2:] = torch.randn(48, 2, generator=torch.Generator().manual_seed(5)) * 0.2
+    out = {}
+    for name, fn in (("fused", train.rollout), ("stepwise", train.rollout_stepwise)):
+        np.random.seed(11)
+        policy.zero_grad()
+        S, G, A = fn(policy, s0.cuda(), g0.cuda())
+        w = torch.linspace(-1.0, 1.0, S.numel(), device="cuda").view_as(S)
+        ((w * S).sum() + (A * A).sum()).backward()
+        out[name] = (S.detach().cpu().numpy(), G.detach().cpu().numpy(), A.detach().cpu().numpy(),
+                     torch.cat([p.grad.reshape(-1) for p in policy._params()]).cpu().numpy(), np.random.uniform())
+    f, r = out["fused"], out["stepwise"]
+    assert f[0].shape == r[0].shape and f[0].shape[0] > 48          # more than one step was visited
+    assert_close(f[0], r[0], RTOL, "trajectory states")
+    assert np.array_equal(f[1], r[1])
+    assert_close(f[2], r[2], RTOL, "trajectory actions")
+    assert_close(f[3], r[3], 1e-5, "grad_ctrl fused vs stepwise")
+    assert f[4] == r[4], "np.random was consumed differently"
+
+
 def test_driver_runs_and_updates_parameters():
     if not torch.cuda.is_available():
         pytest.skip("no CUDA device")
