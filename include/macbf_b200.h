@@ -234,6 +234,14 @@ int macbf_step_forward_ex(const float* states, const float* goals, const float* 
                        float* s_next, float* h, float* h_next, uint8_t* ttc_mask, float* scalars,
                        void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- A0: obstacle point sets on the device (core.py:7-42 generate_obstacle_circle / generate_obstacle_rectangle) ----
+ * kinds [n] (0 = circle, 1 = rectangle), centers [n,2], sizes [n,2] ((radius, unused) or the side lengths (a, b)),
+ * all on the device; points [n * num, 2] float64 receives `num` points per obstacle in the reference's order (circle:
+ * angles 2 pi i / num; rectangle: clockwise from the top-left corner with the reference's per-side counts), computed
+ * in float64 in numpy's operation order.  Cast to float32 for the `obstacles` argument of the other entry points. */
+int macbf_generate_obstacles(const int32_t* kinds, const double* centers, const double* sizes, int n_obstacles,
+                             int num, double* points, void* stream);
+
 /* ---- closed-loop rollout (train.py:59-81) with the stop test on the device ------------------
  * For t = 0 .. max_steps-1: record s_t; u_t = Controller(s_t, goals); s_{t+1} = s_t + [v,u_t] dt; record
  * u_t; an env stops after the first t with mean_i |p_{t+1} - g| < dist_stop (train.py:78-81).

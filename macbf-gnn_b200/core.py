@@ -43,6 +43,13 @@ def generate_obstacle_rectangle(center, sides, num=12):
     return np.concatenate([top, right, bottom, left], axis=0) + np.asarray(center)
 
 
+def generate_obstacles_cuda(specs, num=12, device="cuda"):
+    """generate_obstacle_circle / generate_obstacle_rectangle for a list of obstacles on the device
+    (macbf_generate_obstacles): specs = [("circle", center, radius) | ("rectangle", center, (a, b)), ...]
+    -> CUDA float64 tensor (len(specs) * num, 2), the concatenation of the reference's point sets."""
+    return _ops.generate_obstacles(specs, num, device)
+
+
 def _rejection_fill(out, draw, min_sep):
     """Fill `out` row by row; a draw is rejected when it is within `min_sep` of ANY row of `out`,
     including rows still at their initial zero (the reference's behaviour, core.py:51-56)."""

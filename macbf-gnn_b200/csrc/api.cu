@@ -46,6 +46,7 @@ void timing_mark(const char* name) {
 // implemented in the kernel translation units
 int neighbor_topk(const float*, const float*, int, int, int, int, int32_t*, cudaStream_t);
 int dense_topk(const float*, int, int, int, int, int32_t*, cudaStream_t);
+int obstacle_points(const int32_t*, const double*, const double*, int, int, double*, cudaStream_t);
 size_t rollout_workspace_bytes(int, int, int, int);
 size_t rollout_backward_scratch_bytes(int, int, int, int);
 int rollout_backward(const float*, const float*, const float*, const float*, const float*, const float*, int, int, int, int, int,
@@ -508,6 +509,17 @@ int macbf_rollout_forward(const float* states0, const float* goals, const float*
   MACBF_CHECK_ARG(semantics == MACBF_LITERAL || semantics == MACBF_REPAIRED, "%s: bad semantics %d", fn, semantics);
   return rollout_forward(states0, goals, obstacles, ctrl_params, noise, B, N, M, top_k, max_steps, semantics, obs_radius, dt,
                          dist_stop, traj_states, traj_actions, steps_run, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int macbf_generate_obstacles(const int32_t* kinds, const double* centers, const double* sizes, int n_obstacles, int num,
+                             double* points, void* stream) {
+  const char* fn = "macbf_generate_obstacles";
+  MACBF_CHECK_ARG(n_obstacles >= 1 && num >= 1 && (long long)n_obstacles * num < (1ll << 30), "%s: bad extents n_obstacles=%d num=%d",
+                  fn, n_obstacles, num);
+  REQ_PTR(fn, kinds); REQ_PTR(fn, centers); REQ_PTR(fn, sizes); REQ_PTR(fn, points);
+  MACBF_CHECK_ARG(((((uintptr_t)centers) | ((uintptr_t)sizes) | ((uintptr_t)points)) & 7) == 0,
+                  "%s: centers, sizes and points must be 8-byte aligned", fn);
+  return obstacle_points(kinds, centers, sizes, n_obstacles, num, points, (cudaStream_t)stream);
 }
 
 size_t macbf_rollout_backward_scratch_bytes(int B, int N, int M, int top_k) {

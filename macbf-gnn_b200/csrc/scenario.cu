@@ -229,4 +229,44 @@ int scenario_generate(unsigned long long seed, int B, int N, int T, double dist_
   return 0;
 }
 
+// ---- obstacle point sets (core.py:7-42) ----------------------------------------------------------------------
+// `num` points per obstacle on a circle (kind 0: size = (radius, unused)) or on a rectangle's perimeter, clockwise
+// from the top-left corner (kind 1: size = (a, b)); float64 arithmetic in numpy's operation order (np.linspace with
+// endpoint=False is i * ((stop - start) / n) + start, the centre is added last), one thread per point.
+__device__ __forceinline__ double lin(double start, double stop, int n, int i) {
+  return __dadd_rn(__dmul_rn((double)i, __ddiv_rn(__dsub_rn(stop, start), (double)n)), start);
+}
+__global__ void obstacle_points_kernel(const int32_t* __restrict__ kinds, const double* __restrict__ centers,
+                                       const double* __restrict__ sizes, int n_obstacles, int num, double* __restrict__ out) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_obstacles * num) return;
+  const int o = t / num, i = t - o * num;
+  const double cx = centers[2 * o], cy = centers[2 * o + 1];
+  double x, y;
+  if (kinds[o] == 0) {
+    const double r = sizes[2 * o];
+    const double th = lin(0.0, __dmul_rn(3.141592653589793, 2.0), num, i);
+    x = __dmul_rn(cos(th), r); y = __dmul_rn(sin(th), r);
+  } else {
+    const double a = sizes[2 * o], b = sizes[2 * o + 1];
+    const int n1 = (int)__ddiv_rn(__dmul_rn((double)(num / 2), a), __dadd_rn(a, b));     // int(num // 2 * a / (a + b))
+    const int n2 = num / 2 - n1, n3 = n1;
+    const double ha = __ddiv_rn(a, 2.0), hb = __ddiv_rn(b, 2.0);
+    if (i < n1) { x = lin(-ha, ha, n1, i); y = hb; }                                      // top
+    else if (i < n1 + n2) { x = ha; y = lin(hb, -hb, n2, i - n1); }                       // right
+    else if (i < n1 + n2 + n3) { x = lin(ha, -ha, n3, i - n1 - n2); y = -hb; }            // bottom
+    else { x = -ha; y = lin(-hb, hb, num - n1 - n2 - n3, i - n1 - n2 - n3); }             // left
+  }
+  out[2 * t] = __dadd_rn(x, cx);
+  out[2 * t + 1] = __dadd_rn(y, cy);
+}
+
+int obstacle_points(const int32_t* kinds, const double* centers, const double* sizes, int n_obstacles, int num, double* out,
+                    cudaStream_t st) {
+  const int total = n_obstacles * num;
+  obstacle_points_kernel<<<(total + 127) / 128, 128, 0, st>>>(kinds, centers, sizes, n_obstacles, num, out);
+  MACBF_CHECK_LAUNCH("obstacle_points_kernel");
+  return 0;
+}
+
 }  // namespace macbf

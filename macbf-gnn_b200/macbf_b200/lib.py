@@ -48,6 +48,7 @@ SIGNATURES = {
     "macbf_scenario_workspace_bytes": (SZ, [I, I, I]),
     "macbf_generate_scenario": (I, [ctypes.c_ulonglong, I, I, I, D, c_f32p, c_f32p, c_i32p, c_void, SZ, c_void]),
     "macbf_ttc_dense": (I, [c_f32p, I, I, D, D, c_i32p, c_u8p, c_void]),
+    "macbf_generate_obstacles": (I, [c_i32p, c_void, c_void, I, I, c_void, c_void]),
     "macbf_rollout_workspace_bytes": (SZ, [I, I, I, I]),
     "macbf_rollout_forward": (I, [c_f32p, c_f32p, c_f32p, c_f32p, c_f32p, I, I, I, I, I, I, D, D, D, c_f32p, c_f32p, c_i32p,
                                   c_void, SZ, c_void]),

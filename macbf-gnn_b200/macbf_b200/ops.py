@@ -369,6 +369,32 @@ def ttc_dense(states, dist_min_check=0.07, ttc_check=0.1, want_mask=True, want_c
     return counts, mask
 
 
+def generate_obstacles(specs, num=12, device="cuda"):
+    """core.py:7-42 on the device.  specs: sequence of ("circle", (cx, cy), radius) / ("rectangle", (cx, cy), (a, b)).
+    -> float64 [len(specs) * num, 2] point set in the reference's order (cast to float32 for `obstacles=`)."""
+    dev = torch.device(device)
+    if dev.type != "cuda":
+        raise _lib.MacbfError("macbf_b200 has no CPU path: obstacle point sets are generated on a CUDA device")
+    kinds, centers, sizes = [], [], []
+    for kind, center, size in specs:
+        if kind == "circle":
+            kinds.append(0); sizes.append((float(size), 0.0))
+        elif kind == "rectangle":
+            kinds.append(1); sizes.append((float(size[0]), float(size[1])))
+        else:
+            raise ValueError(f"unknown obstacle kind {kind!r}")
+        centers.append((float(center[0]), float(center[1])))
+    n = len(kinds)
+    k = torch.tensor(kinds, dtype=torch.int32, device=dev)
+    c = torch.tensor(centers, dtype=torch.float64, device=dev)
+    z = torch.tensor(sizes, dtype=torch.float64, device=dev)
+    out = torch.empty((n * num, 2), dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(_lib.load().macbf_generate_obstacles(_p(k), _p(c), _p(z), n, int(num), _p(out), _stream()),
+                   "macbf_generate_obstacles")
+    return out
+
+
 @_on_device_of
 def rollout_forward(states, goals, ctrl_params, max_steps, obstacles=None, noise=None, top_k=TOP_K, semantics=REPAIRED,
                     obs_radius=OBS_RADIUS, dt=TIME_STEP, dist_stop=0.07):

@@ -152,7 +152,26 @@ def oracle_case(name, n, m_circ, m_rect, k, seed, vel_std=0.3, generate_data=Non
         repaired_case(name.replace("oracle_", ""), states, goals, p_cbf, p_ctrl, k, out)
 
 
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from helpers import OBSTACLE_SPECS  # noqa: E402  (tests/helpers.py)
+
+
+def obstacle_case(core):
+    """core.py:7-42 of the unmodified reference on OBSTACLE_SPECS (12 points each, and 7 / 30 for the first two)."""
+    out = {}
+    for i, (kind, center, size) in enumerate(OBSTACLE_SPECS):
+        fn = core.generate_obstacle_circle if kind == "circle" else core.generate_obstacle_rectangle
+        out[f"p{i}"] = fn(center, size)
+    out["circle_num7"] = core.generate_obstacle_circle((1.0, 2.0), 0.3, num=7)
+    out["rect_num30"] = core.generate_obstacle_rectangle((0.0, 0.0), (0.6, 0.4), num=30)
+    np.savez_compressed(os.path.join(OUT, "ref_obstacles.npz"), **out)
+    print("ref_obstacles:", {k: v.shape for k, v in out.items()})
+
+
 def main():
+    if "--obstacles-only" in sys.argv:
+        obstacle_case(ref_loader.load()[0])
+        return
     torch.set_num_threads(max(1, os.cpu_count() or 1))
     print("torch", torch.__version__, "capability", torch.backends.cpu.get_cpu_capability())
     core, cbf_mod, ctrl_mod, _ = ref_loader.load()
@@ -168,6 +187,8 @@ def main():
     np.random.seed(3)
     s, g = core.generate_data(64, 0.07)
     np.savez_compressed(os.path.join(OUT, "ref_generate_data_n64_seed3.npz"), states=s, goals=g)
+
+    obstacle_case(core)
 
     # --- oracle family (REPAIRED, with gradients) ---
     oracle_case("oracle_c1_n32", 32, 0, 0, 12, seed=100, generate_data=core.generate_data)

@@ -102,3 +102,8 @@ def assert_scalars_close(sc, ref_scalars, h_scale, n_dang, n_safe, where=""):
     for q, n in ((2, n_dang), (3, n_safe), (6, n_dang), (7, n_safe)):
         assert abs(sc[q] - ref[q]) <= 3.0 / max(float(n), 1.0) + 2 * RTOL, (where, q, sc[q], ref[q])
     assert abs(sc[8] - ref[8]) <= 2 * RTOL * max(abs(ref[8]), 1e-3), (where, 8, sc[8], ref[8])
+
+
+# obstacle specs of tests/golden/ref_obstacles.npz (made by make_golden.py: obstacle_case from the unmodified reference)
+OBSTACLE_SPECS = [("circle", (1.0, 2.0), 0.3), ("rectangle", (0.0, 0.0), (0.6, 0.4)), ("circle", (-0.37, 5.11), 0.125),
+                  ("rectangle", (2.5, -1.25), (0.3, 0.9)), ("rectangle", (1.0, 1.0), (1.0, 0.1)), ("circle", (0.0, 0.0), 1.0)]

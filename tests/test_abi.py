@@ -98,3 +98,11 @@ def test_host_generators_match_reference():
     assert r.shape == (12, 2) and np.abs(r[:, 0]).max() <= 0.3 + 1e-12 and np.abs(r[:, 1]).max() <= 0.2 + 1e-12
     zz = np.load(os.path.join(ROOT, "tests", "golden", "ref_n200_vel.npz"))
     assert np.array_equal(core.ttc_dangerous_mask_np(zz["states"]), zz["ttc_np"])
+    # obstacle point sets: bit-identical to the unmodified reference's (tests/golden/make_golden.py: obstacle_case)
+    from helpers import OBSTACLE_SPECS
+    zo = np.load(os.path.join(ROOT, "tests", "golden", "ref_obstacles.npz"))
+    for i, (kind, center, size) in enumerate(OBSTACLE_SPECS):
+        fn = core.generate_obstacle_circle if kind == "circle" else core.generate_obstacle_rectangle
+        assert np.array_equal(fn(center, size), zo[f"p{i}"]), (kind, center, size)
+    assert np.array_equal(core.generate_obstacle_circle((1.0, 2.0), 0.3, num=7), zo["circle_num7"])
+    assert np.array_equal(core.generate_obstacle_rectangle((0.0, 0.0), (0.6, 0.4), num=30), zo["rect_num30"])

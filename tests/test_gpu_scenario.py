@@ -67,3 +67,31 @@ def test_device_scenario_feeds_the_step(ops):
     want = O.full_step(p_cbf, p_ctrl, s[1].cpu(), g[1].cpu())
     assert np.array_equal(buf.idx[1].cpu().numpy(), O.neighbor_indices(s[1].cpu(), 12).numpy())
     np.testing.assert_allclose(buf.scalars[1, :9].cpu().numpy(), want["scalars"].numpy(), rtol=2e-5, atol=1e-6)
+
+
+def test_device_obstacle_point_sets_equal_reference(ops):
+    """macbf_generate_obstacles (core.py:7-42 on the device) against the point sets the unmodified reference produced
+    (tests/golden/ref_obstacles.npz): straight segments bit-identical in float64; circle points within 2 ulp in float64
+    (device cos/sin vs libm) and identical once cast to the float32 the kernels consume."""
+    import os
+    from helpers import OBSTACLE_SPECS
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    z = np.load(os.path.join(root, "tests", "golden", "ref_obstacles.npz"))
+    got = ops.generate_obstacles(OBSTACLE_SPECS, 12).cpu().numpy().reshape(len(OBSTACLE_SPECS), 12, 2)
+    for i, (kind, _, _) in enumerate(OBSTACLE_SPECS):
+        want = z[f"p{i}"]
+        if kind == "rectangle":
+            assert np.array_equal(got[i], want), f"rectangle {i}"
+        else:
+            assert np.abs(got[i] - want).max() <= 2 * np.spacing(np.abs(want).max()), f"circle {i}"
+        assert np.array_equal(got[i].astype(np.float32), want.astype(np.float32)), f"obstacle {i} as float32"
+    g7 = ops.generate_obstacles([OBSTACLE_SPECS[0]], 7).cpu().numpy()
+    assert np.array_equal(g7.astype(np.float32), z["circle_num7"].astype(np.float32))
+    g30 = ops.generate_obstacles([OBSTACLE_SPECS[1]], 30).cpu().numpy()
+    assert np.array_equal(g30, z["rect_num30"])
+    # and as candidate columns of the neighbour search: same graph as with the host-made point set
+    import oracle.macbf_oracle as O
+    s, _ = O.synthetic_swarm(1, 64, 3)
+    pts = ops.generate_obstacles(OBSTACLE_SPECS[:2], 12).to(torch.float32).unsqueeze(0)
+    host = torch.from_numpy(np.concatenate([z["p0"], z["p1"]]).astype(np.float32)).unsqueeze(0).cuda()
+    assert torch.equal(ops.neighbor_topk(s.cuda(), 12, pts), ops.neighbor_topk(s.cuda(), 12, host))
