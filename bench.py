@@ -53,6 +53,7 @@ def bytes_per_agent(K, mode):
 KERNEL_WORK = {
     "cbf_forward_tc_kernel": ("tensor", CBF_EDGE_FLOP, 0),
     "cbf_forward_tc_kernel<dump>": ("tensor", CBF_EDGE_FLOP, 0),
+    "cbf_forward_tc_kernel<record>": ("tensor", CBF_EDGE_FLOP, 0),     # training: the forward pass that writes the tile records
     "ctrl_edge_tc_kernel": ("tensor", CTRL_EDGE_FLOP, 0),
     "ctrl_node_tc_kernel": ("tensor", 0, NODE_FLOP),
     "ctrl_node_tc_kernel<dump>": ("tensor", 0, NODE_FLOP),
@@ -665,7 +666,7 @@ def main():
             blk = train if train is not None else head
             # slowest kernel of the backward pass, from the live table (timed inside the step -> sustained peak)
             bwd = [r for r in blk["kernel_breakdown"]["kernels"]
-                   if any(t in r["kernel"] for t in ("dgrad", "wgrad", "<dump>", "bwd", "backward")) and "tflops" in r]
+                   if any(t in r["kernel"] for t in ("dgrad", "wgrad", "<dump>", "<record>", "bwd", "backward")) and "tflops" in r]
             if bwd:
                 top = max(bwd, key=lambda r: r["ms_per_launch"] * r["launches_per_step"])
                 blk["roofline"] = {

@@ -182,6 +182,23 @@ int macbf_cbf_backward(const float* states, const float* obstacles, const int32_
                        double dist_min_thres, double obs_radius, float* grad_params,
                        float* grad_states, void* scratch, size_t scratch_bytes, void* stream);
 
+/* Training steps: instead of discarding the forward pass and recomputing it in macbf_cbf_backward, the forward can WRITE
+ * the tile records (macbf_cbf_forward_record: h as macbf_cbf_forward, REPAIRED semantics, tensor-core path) and the
+ * backward then starts at the delta chain (macbf_cbf_backward_record: dL/dh -> grad_params accumulated, grad_states
+ * accumulated when non-NULL, as macbf_cbf_backward).  One CBF forward per pass less; the price is memory: the record
+ * buffer holds ALL tiles of the problem, macbf_cbf_record_bytes = 173 KB per 128 edge rows (1.16 GB for 64 x 1024
+ * agents, K = 12), and stays live between the two calls.  The backward only adds to the record (dL/dh-dependent
+ * parts), so one record serves any number of backward calls.  scratch: macbf_cbf_backward_record_scratch_bytes()
+ * (the per-CTA gradient slices). */
+size_t macbf_cbf_record_bytes(int B, int N, int K);
+size_t macbf_cbf_backward_record_scratch_bytes(void);
+int macbf_cbf_forward_record(const float* states, const float* obstacles, const int32_t* idx,
+                             const float* cbf_params, int B, int N, int M, int K, double dist_min_thres,
+                             double obs_radius, float* h, void* record, size_t record_bytes, void* stream);
+int macbf_cbf_backward_record(const int32_t* idx, const float* cbf_params, const float* grad_h, int B, int N,
+                              int K, void* record, size_t record_bytes, float* grad_params, float* grad_states,
+                              void* scratch, size_t scratch_bytes, void* stream);
+
 /* ---- backward of A6-A8 (autograd of controller.py:31-63 + Euler step) --------------------
  * grad_u [B,N,2] and (optional) grad_s_next [B,N,4] are the incoming gradients; grad_params
  * [34052] and (optional) grad_states [B,N,4], grad_goals [B,N,2] are accumulated into.
@@ -233,6 +250,18 @@ int macbf_step_forward_ex(const float* states, const float* goals, const float* 
                        double dt, double alpha, int flags, int32_t* idx, int32_t* idx_next, float* u,
                        float* s_next, float* h, float* h_next, uint8_t* ttc_mask, float* scalars,
                        void* workspace, size_t workspace_bytes, void* stream);
+
+/* macbf_step_forward_ex for a training step: with record / record_next non-NULL (each macbf_cbf_record_bytes(B, N, K)
+ * bytes, K = macbf_neighbor_count) the two CBF passes are recording forwards (macbf_cbf_forward_record) and
+ * macbf_cbf_backward_record(idx, .., record) / (idx_next, .., record_next) replace the two macbf_cbf_backward calls.
+ * Both NULL: identical to macbf_step_forward_ex. */
+int macbf_step_forward_train(const float* states, const float* goals, const float* obstacles,
+                             const float* cbf_params, const float* ctrl_params, int B, int N, int M,
+                             int top_k, int semantics, double dist_min_thres, double obs_radius, double ttc,
+                             double dt, double alpha, int flags, int32_t* idx, int32_t* idx_next, float* u,
+                             float* s_next, float* h, float* h_next, uint8_t* ttc_mask, float* scalars,
+                             void* workspace, size_t workspace_bytes, void* record, void* record_next,
+                             size_t record_bytes, void* stream);
 
 /* ---- A0: obstacle point sets on the device (core.py:7-42 generate_obstacle_circle / generate_obstacle_rectangle) ----
  * kinds [n] (0 = circle, 1 = rectangle), centers [n,2], sizes [n,2] ((radius, unused) or the side lengths (a, b)),

@@ -37,6 +37,6 @@ class CBF(nn.Module):
         sb, squeeze = _F._batched(states, 4)
         obs = core._obstacles_for(sb)
         idx = indices if indices is not None else _ops.neighbor_topk(sb.detach(), TOP_K, obs)
-        h = _F.CBFFunction.apply(sb.contiguous(), obs, idx, core.SEMANTICS, *self._params())
+        h = _F.CBFFunction.apply_auto(sb.contiguous(), obs, idx, core.SEMANTICS, *self._params())
         h = h.unsqueeze(2)                      # [B,N,1,K]: the reference's channels-first (N,1,K)
         return h[0] if squeeze else h

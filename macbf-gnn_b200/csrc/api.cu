@@ -81,6 +81,12 @@ int loss_forward(const float*, const float*, const float*, const int32_t*, const
 int loss_backward(const float*, const float*, const float*, const float*, const float*, const uint8_t*, const float*,
                   const float*, int, int, int, double, double, float*, float*, float*, float*, cudaStream_t);
 size_t cbf_backward_scratch_bytes(int, int, int);
+size_t cbf_record_bytes(int, int, int);
+size_t cbf_backward_record_scratch_bytes();
+int cbf_forward_record(const float*, const float*, const int32_t*, const float*, int, int, int, int, double, double, float*, void*,
+                       size_t, cudaStream_t);
+int cbf_backward_record(const int32_t*, const float*, const float*, int, int, int, void*, size_t, float*, float*, void*, size_t,
+                        cudaStream_t);
 int cbf_backward(const float*, const float*, const int32_t*, const float*, const float*, int, int, int, int, double,
                  double, float*, float*, void*, size_t, cudaStream_t);
 size_t controller_backward_scratch_bytes(int, int, int);
@@ -281,6 +287,31 @@ int macbf_cbf_backward(const float* states, const float* obstacles, const int32_
                       grad_states, scratch, scratch_bytes, (cudaStream_t)stream);
 }
 
+size_t macbf_cbf_record_bytes(int B, int N, int K) { return cbf_record_bytes(B, N, K); }
+size_t macbf_cbf_backward_record_scratch_bytes(void) { return cbf_backward_record_scratch_bytes(); }
+
+int macbf_cbf_forward_record(const float* states, const float* obstacles, const int32_t* idx, const float* cbf_params, int B,
+                             int N, int M, int K, double dist_min_thres, double obs_radius, float* h, void* record,
+                             size_t record_bytes, void* stream) {
+  const char* fn = "macbf_cbf_forward_record";
+  if (check_dims(fn, B, N, M, K)) return 1;
+  REQ_PTR(fn, states); REQ_PTR(fn, idx); REQ_PTR(fn, cbf_params); REQ_PTR(fn, h); REQ_PTR(fn, record); REQ_A16(fn, states);
+  MACBF_CHECK_ARG(M == 0 || obstacles != nullptr, "%s: obstacles is NULL but M=%d", fn, M);
+  return cbf_forward_record(states, obstacles, idx, cbf_params, B, N, M, K, dist_min_thres, obs_radius, h, record, record_bytes,
+                            (cudaStream_t)stream);
+}
+
+int macbf_cbf_backward_record(const int32_t* idx, const float* cbf_params, const float* grad_h, int B, int N, int K,
+                              void* record, size_t record_bytes, float* grad_params, float* grad_states, void* scratch,
+                              size_t scratch_bytes, void* stream) {
+  const char* fn = "macbf_cbf_backward_record";
+  if (check_dims(fn, B, N, 0, K)) return 1;
+  REQ_PTR(fn, idx); REQ_PTR(fn, cbf_params); REQ_PTR(fn, grad_h); REQ_PTR(fn, record); REQ_PTR(fn, grad_params);
+  REQ_PTR(fn, scratch); REQ_A16(fn, scratch);
+  return cbf_backward_record(idx, cbf_params, grad_h, B, N, K, record, record_bytes, grad_params, grad_states, scratch,
+                             scratch_bytes, (cudaStream_t)stream);
+}
+
 size_t macbf_controller_backward_scratch_bytes(int B, int N, int K) {
   return controller_backward_scratch_bytes(B, N, K);
 }
@@ -344,7 +375,26 @@ int macbf_step_forward_ex(const float* states, const float* goals, const float* 
                           double obs_radius, double ttc, double dt, double alpha, int flags, int32_t* idx,
                           int32_t* idx_next, float* u, float* s_next, float* h, float* h_next, uint8_t* ttc_mask_out,
                           float* scalars, void* workspace, size_t workspace_bytes, void* stream) {
+  return macbf_step_forward_train(states, goals, obstacles, cbf_params, ctrl_params, B, N, M, top_k, semantics, dist_min_thres,
+                                  obs_radius, ttc, dt, alpha, flags, idx, idx_next, u, s_next, h, h_next, ttc_mask_out, scalars,
+                                  workspace, workspace_bytes, nullptr, nullptr, 0, stream);
+}
+
+int macbf_step_forward_train(const float* states, const float* goals, const float* obstacles, const float* cbf_params,
+                             const float* ctrl_params, int B, int N, int M, int top_k, int semantics, double dist_min_thres,
+                             double obs_radius, double ttc, double dt, double alpha, int flags, int32_t* idx,
+                             int32_t* idx_next, float* u, float* s_next, float* h, float* h_next, uint8_t* ttc_mask_out,
+                             float* scalars, void* workspace, size_t workspace_bytes, void* record, void* record_next,
+                             size_t record_bytes, void* stream) {
   const char* fn = "macbf_step_forward";
+  MACBF_CHECK_ARG((record == nullptr) == (record_next == nullptr), "%s: record and record_next go together", fn);
+  MACBF_CHECK_ARG(record == nullptr || semantics == MACBF_REPAIRED, "%s: records need REPAIRED semantics", fn);
+  // CBF forward, plain or recording (macbf_cbf_forward_record)
+  auto cbf_fwd = [&](const float* s_, const int32_t* idx_, float* h_, void* rec_, int K_, cudaStream_t st_) -> int {
+    if (rec_ != nullptr)
+      return cbf_forward_record(s_, obstacles, idx_, cbf_params, B, N, M, K_, dist_min_thres, obs_radius, h_, rec_, record_bytes, st_);
+    return cbf_forward(s_, obstacles, idx_, cbf_params, B, N, M, K_, semantics, dist_min_thres, obs_radius, h_, st_);
+  };
   MACBF_CHECK_ARG((flags & ~(MACBF_STEP_REUSE_INDICES | MACBF_STEP_SAVE_WINNERS)) == 0, "%s: unknown flags 0x%x", fn, flags);
   MACBF_CHECK_ARG(top_k >= 1 && top_k <= MACBF_MAX_K, "%s: top_k=%d out of range [1,%d]", fn, top_k, MACBF_MAX_K);
   const int K = macbf_neighbor_count(N, M, top_k);
@@ -372,8 +422,7 @@ int macbf_step_forward_ex(const float* states, const float* goals, const float* 
   if (rc) return rc;
   if (flags & MACBF_STEP_REUSE_INDICES) {   // h' on S's graph (the upstream `indices=` argument the reference dropped)
     MACBF_CHECK_CUDA(cudaMemcpyAsync(idx_next, idx, (size_t)B * N * K * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
-    if ((rc = cbf_forward(states, obstacles, idx, cbf_params, B, N, M, K, semantics, dist_min_thres, obs_radius, h, st)))
-      return rc;
+    if ((rc = cbf_fwd(states, idx, h, record, K, st))) return rc;
   } else {
     // graph(S') (core.py:137) on the side stream, under CBF(S) on the caller's stream
     SideStream* side = nullptr;
@@ -382,12 +431,10 @@ int macbf_step_forward_ex(const float* states, const float* goals, const float* 
     MACBF_CHECK_CUDA(cudaStreamWaitEvent(side->stream, side->fork, 0));
     if ((rc = neighbor_any(s_next, obstacles, B, N, M, top_k, idx_next, gscratch, gbytes, side->stream))) return rc;
     MACBF_CHECK_CUDA(cudaEventRecord(side->join, side->stream));
-    if ((rc = cbf_forward(states, obstacles, idx, cbf_params, B, N, M, K, semantics, dist_min_thres, obs_radius, h, st)))
-      return rc;
+    if ((rc = cbf_fwd(states, idx, h, record, K, st))) return rc;
     MACBF_CHECK_CUDA(cudaStreamWaitEvent(st, side->join, 0));
   }
-  if ((rc = cbf_forward(s_next, obstacles, idx_next, cbf_params, B, N, M, K, semantics, dist_min_thres, obs_radius,
-                        h_next, st))) return rc;
+  if ((rc = cbf_fwd(s_next, idx_next, h_next, record_next, K, st))) return rc;
   return loss_forward(states, goals, obstacles, idx, h, h_next, u, B, N, M, K, dist_min_thres, ttc, dt, alpha,
                       ttc_mask_out, scalars, lscratch, loss_scratch_bytes(B, N, K), st);
 }

@@ -23,7 +23,11 @@ constexpr uint32_t Z2_HI = REC_STAGE, Z2_LO = REC_STAGE + 2 * BLK;        // sta
 constexpr uint32_t MASKS = 2 * REC_STAGE;      // which: 0 = layer 1, 1/2 = layer 2 chunk 0/1, 3 = layer 3
 constexpr uint32_t XREC = MASKS + 4 * 4 * 128 * 4;    // float[128][8]: the 6 edge features, d, unused
 constexpr uint32_t GM = XREC + 128 * 8 * 4;           // float[128]: dL/dh * radius mask (0 for padding rows)
-constexpr uint32_t BYTES = GM + 128 * 4 + 512;        // 144,384 = 141 * 1024
+constexpr uint32_t GMASK = GM + 128 * 4;              // float[128]: the radius mask alone (recording forward: dL/dh comes later;
+                                                      // cbf_dgrad_tc_kernel then writes gm = dL/dh * mask into GM)
+constexpr uint32_t BYTES = GMASK + 128 * 4;           // 144,384 = 141 * 1024
+constexpr uint32_t A3_BYTES = 4 * 128 * 16 * 4;       // recording forward only: layer-3 activations [cgrp][4][row][4] fp32, kept in a
+                                                      // separate array behind the records (32 KB per tile)
 static_assert(BYTES % 1024 == 0, "tile records must keep 1024-B alignment");
 }  // namespace cbfrec
 }  // namespace macbf

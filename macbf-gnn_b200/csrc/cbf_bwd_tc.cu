@@ -33,12 +33,14 @@ namespace macbf {
 int reduce_partials(const float* partial, int nslices, int P, float* out, cudaStream_t st);
 int cbf_forward_tc_dump(const float* states, const float* obstacles, const int32_t* idx, const float* params, int N, int M,
                         int K, long long agents, double dist_min, double obs_radius, long long tile_begin,
-                        long long tile_end, const float* grad_h, unsigned char* rec, float* slices, cudaStream_t st);
+                        long long tile_end, const float* grad_h, unsigned char* rec, float* slices, cudaStream_t st,
+                        float* h, float* a3buf);
 
 // ================================ kernel 2: delta chain ================================
 namespace cbfdg {
 constexpr int WORKERS = 512;
 constexpr int THREADS = WORKERS + 32;
+constexpr int THREADS_RECORD = THREADS + 96;   // + three dW4 / db4 warps: 20 warps keep the 96-register budget of 17
 constexpr int R = 128;
 // TMEM columns: [0,64) dZ3_hi  [64,128) dZ3_lo  [128,256) dA2 -> dZ2_hi (in place)  [256,384) dZ2_lo  [384,448) dA1
 constexpr uint32_t C_Z3HI = 0, C_Z3LO = 64, C_DA2 = 128, C_Z2LO = 256, C_DA1 = 384;
@@ -58,10 +60,15 @@ constexpr int total_floats = oXpart + 2 * 4 * 5 * 128;
 constexpr size_t smem_bytes = (size_t)total_floats * 4 + 1024;
 }  // namespace cbfdg
 
-__global__ void __launch_bounds__(cbfdg::THREADS, 1)
+template <bool RECORD>
+__global__ void __launch_bounds__(RECORD ? cbfdg::THREADS_RECORD : cbfdg::THREADS, 1)
 cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ params, int N, int K,
                     long long agents_total, int TA, long long tile_begin, long long tile_end,
-                    unsigned char* __restrict__ rec, float* __restrict__ slices, float* __restrict__ grad_states) {
+                    unsigned char* __restrict__ rec, float* __restrict__ slices, float* __restrict__ grad_states,
+                    const float* __restrict__ grad_h, const float* __restrict__ a3buf) {
+  // RECORD: the records come from the recording forward (cbf_forward_tc_kernel<true> without dL/dh): gm = dL/dh *
+  // mask is formed here (and written to the record for the wgrad kernel), and dW4 / db4 = sum gm * a3, sum gm are
+  // accumulated here from the recorded layer-3 activations.
   using namespace cbfdg;
   using namespace tc;
   extern __shared__ unsigned char smem_raw[];
@@ -148,6 +155,60 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
       // in order, so its writes to the dA2 columns follow this tile's reads of dZ2_hi from the same columns.
       if (tile + gridDim.x < tile_end) issue_da2(par ^ 1);
     }
+  } else if (RECORD && warp > WORKERS / 32) {
+    // ======================= dW4 / db4 warps (records of the recording forward) =======================
+    // dW4[c] = sum_e gm_e a3_e[c] (cbf.py:19) straight from the recorded layer-3 activations: three warps stream this
+    // CTA's tiles on their own (no barrier shared with the delta chain).  a3buf is [tile][combo = channel / 4][row] float4;
+    // warp w owns the combos [cb0, cb0 + ncb), a lane the rows lane + 32 k: every load instruction reads 512 B in a row.
+    const int w = warp - WORKERS / 32 - 1;
+    const int cb0 = (w == 0) ? 0 : (w == 1 ? 6 : 11), ncb = (w == 0) ? 6 : 5;
+    float acc[6][4];
+    float accb = 0.f;
+#pragma unroll
+    for (int c = 0; c < 6; ++c) acc[c][0] = acc[c][1] = acc[c][2] = acc[c][3] = 0.f;
+    for (long long t = first; t < tile_end; t += gridDim.x) {
+      const unsigned char* tr = rec + (size_t)(t - tile_begin) * cbfrec::BYTES;
+      float gm[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int r = lane + 32 * k;
+        gm[k] = 0.f;
+        if (r < TA * K && t * TA + r / K < agents_total)
+          gm[k] = __ldg(grad_h + (size_t)(t * TA) * K + r) * __ldg(reinterpret_cast<const float*>(tr + cbfrec::GMASK) + r);
+      }
+      const float4* src = reinterpret_cast<const float4*>(a3buf) + ((size_t)(t - tile_begin) * 16 + cb0) * R + lane;
+      // three batches of two combos: the 8 loads of a batch are all issued before the first of them is used (one
+      // memory round trip per batch; a plain loop over the combos made it one round trip per combo, 7 us per tile)
+#pragma unroll
+      for (int b = 0; b < 3; ++b) {
+        float4 v[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int c = 2 * b + (i >> 2), k = i & 3;
+          v[i] = (c < ncb) ? __ldcs(src + c * R + 32 * k) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int c = 2 * b + (i >> 2), k = i & 3;
+          acc[c][0] = fmaf(gm[k], v[i].x, acc[c][0]); acc[c][1] = fmaf(gm[k], v[i].y, acc[c][1]);
+          acc[c][2] = fmaf(gm[k], v[i].z, acc[c][2]); acc[c][3] = fmaf(gm[k], v[i].w, acc[c][3]);
+        }
+      }
+      if (w == 0) accb += (gm[0] + gm[1]) + (gm[2] + gm[3]);
+    }
+    float* gp = slices + (size_t)blockIdx.x * MACBF_CBF_PARAMS;
+#pragma unroll
+    for (int c = 0; c < 6; ++c) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float sw = warp_sum(acc[c][e]);
+        if (lane == 0 && c < ncb) gp[CBF_W4 + (cb0 + c) * 4 + e] += sw;
+      }
+    }
+    if (w == 0) {
+      const float sb = warp_sum(accb);
+      if (lane == 0) gp[CBF_B4] += sb;
+    }
   } else {
     // ================================= worker warps =================================
     const int q = warp & 3, cgrp = warp >> 2;
@@ -179,9 +240,16 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
       RecZ z;
       z.mb3 = 0u; z.gm = 0.f;
       if (t < tile_end) {
-        const unsigned char* tr = rec + (size_t)(t - tile_begin) * cbfrec::BYTES;
+        unsigned char* tr = rec + (size_t)(t - tile_begin) * cbfrec::BYTES;
         z.mb3 = reinterpret_cast<const uint32_t*>(tr + cbfrec::MASKS)[(3 * 4 + cgrp) * R + r];
-        z.gm = reinterpret_cast<const float*>(tr + cbfrec::GM)[r];
+        if constexpr (!RECORD) {
+          z.gm = reinterpret_cast<const float*>(tr + cbfrec::GM)[r];
+        } else {
+          const long long a = t * TA + r / K;           // rows beyond the tile's agents are padding (mask 0)
+          if (r < TA * K && a < agents_total)
+            z.gm = __ldg(grad_h + (size_t)(t * TA) * K + r) * reinterpret_cast<const float*>(tr + cbfrec::GMASK)[r];
+          if (cgrp == 0) reinterpret_cast<float*>(tr + cbfrec::GM)[r] = z.gm;      // for the wgrad kernel's dZ3
+        }
       }
       return z;
     };
@@ -717,7 +785,7 @@ int cbf_backward_tc(const float* states, const float* obstacles, const int32_t* 
   const int TA = max(1, 128 / K);
   const long long nt = cbf_bwd_tiles(agents, K);
   MACBF_CHECK_CUDA(cudaMemsetAsync(slices, 0, slice_bytes, st));
-  MACBF_CHECK_CUDA(cudaFuncSetAttribute(cbf_dgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfdg::smem_bytes));
+  MACBF_CHECK_CUDA(cudaFuncSetAttribute(cbf_dgrad_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfdg::smem_bytes));
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfwg::smem_bytes));
   const long long CH = chunk_tiles();
   for (long long t0 = 0; t0 < nt; t0 += CH) {
@@ -725,10 +793,10 @@ int cbf_backward_tc(const float* states, const float* obstacles, const int32_t* 
     const long long ct = t1 - t0;
     const int grid = (int)(ct < NUM_SMS ? ct : (long long)NUM_SMS);
     if (int rc = cbf_forward_tc_dump(states, obstacles, idx, params, N, M, K, agents, dist_min, obs_radius, t0, t1, grad_h, rec,
-                                     slices, st))
+                                     slices, st, nullptr, nullptr))
       return rc;
-    cbf_dgrad_tc_kernel<<<grid, cbfdg::THREADS, cbfdg::smem_bytes, st>>>(idx, params, N, K, agents, TA, t0, t1, rec, slices,
-                                                                        grad_states);
+    cbf_dgrad_tc_kernel<false><<<grid, cbfdg::THREADS, cbfdg::smem_bytes, st>>>(idx, params, N, K, agents, TA, t0, t1, rec, slices,
+                                                                               grad_states, nullptr, nullptr);
     MACBF_CHECK_LAUNCH("cbf_dgrad_tc_kernel");
     wgrad_tc_kernel<2><<<grid, 64 + 256, cbfwg::smem_bytes, st>>>(rec, cbfrec::BYTES, ct, slices, MACBF_CBF_PARAMS, CBF_W3,
                                                                        CBF_B3, CBF_W2, CBF_B2, 0, 0, params + CBF_W1, params + CBF_B1,
@@ -736,6 +804,60 @@ int cbf_backward_tc(const float* states, const float* obstacles, const int32_t* 
                                                                        cbfrec::REC_STAGE);
     MACBF_CHECK_LAUNCH("wgrad_tc_kernel<cbf>");
   }
+  return reduce_partials(slices, NUM_SMS, MACBF_CBF_PARAMS, grad_params, st);
+}
+
+// ---- training step: the forward pass writes the records, the backward pass starts at the delta chain ----
+// record buffer: [nt tile records of cbfrec::BYTES][nt x cbfrec::A3_BYTES layer-3 activations], nt = all tiles of the
+// problem (173 KB per 128 / K agents: the caller decides whether it has the memory; macbf_cbf_backward needs none of it)
+size_t cbf_record_bytes(int B, int N, int K) {
+  const long long nt = cbf_bwd_tiles((long long)B * N, K);
+  return (size_t)nt * (cbfrec::BYTES + cbfrec::A3_BYTES) + 1024;
+}
+size_t cbf_backward_record_scratch_bytes() { return (size_t)NUM_SMS * MACBF_CBF_PARAMS * sizeof(float); }
+
+static inline unsigned char* rec_base(void* record) { return (unsigned char*)(((uintptr_t)record + 1023) & ~(uintptr_t)1023); }
+
+int cbf_forward_record(const float* states, const float* obstacles, const int32_t* idx, const float* params, int B, int N,
+                       int M, int K, double dist_min, double obs_radius, float* h, void* record, size_t record_bytes,
+                       cudaStream_t st) {
+  const long long agents = (long long)B * N;
+  MACBF_CHECK_ARG(agents * K < (1ll << 31), "cbf_forward_record: B*N*K must be < 2^31");
+  MACBF_CHECK_ARG(K <= 128, "cbf_forward_record: K=%d out of range (max 128)", K);
+  MACBF_CHECK_ARG(record_bytes >= cbf_record_bytes(B, N, K), "cbf_forward_record: record buffer too small (%zu < %zu)",
+                  record_bytes, cbf_record_bytes(B, N, K));
+  const long long nt = cbf_bwd_tiles(agents, K);
+  unsigned char* rec = rec_base(record);
+  float* a3 = (float*)(rec + (size_t)nt * cbfrec::BYTES);
+  return cbf_forward_tc_dump(states, obstacles, idx, params, N, M, K, agents, dist_min, obs_radius, 0, nt, nullptr, rec, nullptr,
+                             st, h, a3);
+}
+
+int cbf_backward_record(const int32_t* idx, const float* params, const float* grad_h, int B, int N, int K, void* record,
+                        size_t record_bytes, float* grad_params, float* grad_states, void* scratch, size_t scratch_bytes,
+                        cudaStream_t st) {
+  const long long agents = (long long)B * N;
+  MACBF_CHECK_ARG(agents * K < (1ll << 31) && K <= 128, "cbf_backward_record: B*N*K must be < 2^31 and K <= 128");
+  MACBF_CHECK_ARG(record_bytes >= cbf_record_bytes(B, N, K), "cbf_backward_record: record buffer too small (%zu < %zu)",
+                  record_bytes, cbf_record_bytes(B, N, K));
+  MACBF_CHECK_ARG(scratch_bytes >= cbf_backward_record_scratch_bytes(), "cbf_backward_record: scratch too small (%zu < %zu)",
+                  scratch_bytes, cbf_backward_record_scratch_bytes());
+  const long long nt = cbf_bwd_tiles(agents, K);
+  const int TA = max(1, 128 / K);
+  unsigned char* rec = rec_base(record);
+  const float* a3 = (const float*)(rec + (size_t)nt * cbfrec::BYTES);
+  float* slices = (float*)scratch;
+  MACBF_CHECK_CUDA(cudaMemsetAsync(slices, 0, cbf_backward_record_scratch_bytes(), st));
+  MACBF_CHECK_CUDA(cudaFuncSetAttribute(cbf_dgrad_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfdg::smem_bytes));
+  MACBF_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfwg::smem_bytes));
+  const int grid = (int)(nt < NUM_SMS ? nt : (long long)NUM_SMS);
+  cbf_dgrad_tc_kernel<true><<<grid, cbfdg::THREADS_RECORD, cbfdg::smem_bytes, st>>>(idx, params, N, K, agents, TA, 0, nt, rec, slices,
+                                                                            grad_states, grad_h, a3);
+  MACBF_CHECK_LAUNCH("cbf_dgrad_tc_kernel");
+  wgrad_tc_kernel<2><<<grid, 64 + 256, cbfwg::smem_bytes, st>>>(rec, cbfrec::BYTES, nt, slices, MACBF_CBF_PARAMS, CBF_W3, CBF_B3,
+                                                                CBF_W2, CBF_B2, 0, 0, params + CBF_W1, params + CBF_B1, 6,
+                                                                cbfrec::XREC, params + CBF_W4, WgradRoute{}, cbfrec::REC_STAGE);
+  MACBF_CHECK_LAUNCH("wgrad_tc_kernel<cbf>");
   return reduce_partials(slices, NUM_SMS, MACBF_CBF_PARAMS, grad_params, st);
 }
 

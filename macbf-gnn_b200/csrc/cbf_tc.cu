@@ -76,15 +76,20 @@ constexpr size_t smem_bytes = (size_t)total_floats * 4 + 1024;
 // tiles [tile_begin, tile_end), that also writes per tile (record `tile - tile_begin`, cbf_bwd_layout.cuh)
 // the bf16 hi/lo images of the layer-1/2 activations, the ReLU bit masks of all three layers, the edge
 // features and gm = dL/dh * radius mask, and accumulates dW4 / db4 into this CTA's gradient slice.
-template <bool DUMP>
+// DUMP with grad_h == NULL is the RECORDING FORWARD of a training step (macbf_cbf_forward_record): dL/dh does not
+// exist yet, so the record's GM slot receives the radius mask alone, h is written as by the plain forward, the
+// layer-3 activations go to `a3buf` ([tile][column group][4][row][4] fp32; dW4 needs their values, not only their
+// signs) and no gradient slice is touched - cbf_dgrad_tc_kernel finishes gm, dW4 and db4 when dL/dh arrives.
+template <int MODE>       // 0: plain forward, 1: DUMP (first kernel of the backward), 2: DUMP as the recording forward
 __global__ void __launch_bounds__(cbftc::THREADS, 1)
 cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict__ obstacles,
                       const int32_t* __restrict__ idx, const float* __restrict__ params, int N, int M, int K,
                       long long agents_total, int agent_begin, int TA, float dist_min, float obs_radius, float* __restrict__ h,
                       long long tile_begin, long long tile_end, const float* __restrict__ grad_h,
-                      unsigned char* __restrict__ rec, float* __restrict__ slices) {
+                      unsigned char* __restrict__ rec, float* __restrict__ slices, float* __restrict__ a3buf) {
   using namespace cbftc;
   using namespace tc;
+  constexpr bool DUMP = MODE != 0, RECORD = MODE == 2;
   extern __shared__ unsigned char smem_raw[];
   float* sm = reinterpret_cast<float*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
   float* W2hi = sm + oW2HI; float* W2lo = sm + oW2LO;
@@ -287,17 +292,20 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
         unsigned char* tr = rec + (size_t)(pf_tile - tile_begin) * cbfrec::BYTES;
         float gm = 0.f, dd = 1.f;
         if (pf_valid) {
-          gm = __ldg(grad_h + (size_t)(pf_tile * TA) * K + r) * mk;      // d h / d y4 = mask (cbf.py:43)
+          gm = RECORD ? mk : __ldg(grad_h + (size_t)(pf_tile * TA) * K + r) * mk;      // d h / d y4 = mask (cbf.py:43)
           dd = xadd(f[5], dist_min);
         }
         float4* xr = reinterpret_cast<float4*>(tr + cbfrec::XREC) + 2 * r;
         xr[0] = make_float4(f[0], f[1], f[2], f[3]);
         xr[1] = make_float4(f[4], f[5], dd, 0.f);
         reinterpret_cast<float*>(tr + cbfrec::GM)[r] = gm;
-        gms[(pf_slot & 3) * R + r] = gm;
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&gm_full[pf_slot & 3]);
-        ++pf_slot;
+        if constexpr (RECORD) reinterpret_cast<float*>(tr + cbfrec::GMASK)[r] = gm;    // recording forward: the mask alone
+        if constexpr (!RECORD) {
+          gms[(pf_slot & 3) * R + r] = gm;
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&gm_full[pf_slot & 3]);
+          ++pf_slot;
+        }
       }
       float hi[8], lo[8];
 #pragma unroll
@@ -366,7 +374,7 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
     [[maybe_unused]] float acc4[16];
     [[maybe_unused]] float accb4 = 0.f;
     [[maybe_unused]] int gslot = 0;
-    if constexpr (DUMP) {
+    if constexpr (DUMP && !RECORD) {
 #pragma unroll
       for (int q = 0; q < 16; ++q) acc4[q] = 0.f;
     }
@@ -444,17 +452,31 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
         wait_ld();
         warp_arrive_after_tmem(&d3_free);
         if constexpr (DUMP) {
-          mbar_wait(&gm_full[gslot & 3], (gslot >> 2) & 1);   // published >= 1 tile ago: an acquire, not a wait
-          const float gm = gms[(gslot & 3) * R + r];
-          ++gslot;
           uint32_t bits = 0;
+          if constexpr (RECORD) {                       // recording forward: the activations themselves, for dW4 later
+            float4* dst = reinterpret_cast<float4*>(a3buf) + ((size_t)(tile - tile_begin) * 4 + cgrp) * 4 * R + r;   // [j4][row]: a warp's store is 512 B
 #pragma unroll
-          for (int q = 0; q < 16; ++q) {
-            const float z = fmaxf(v[q] + B3[c0 + q], 0.f);
-            bits |= (z > 0.f ? 1u : 0u) << q;
-            acc4[q] = fmaf(gm, z, acc4[q]);              // dW4 (cbf.py:19)
+            for (int j4 = 0; j4 < 4; ++j4) {
+              float z[4];
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                z[q] = fmaxf(v[4 * j4 + q] + B3[c0 + 4 * j4 + q], 0.f);
+                bits |= (z[q] > 0.f ? 1u : 0u) << (4 * j4 + q);
+              }
+              dst[j4 * R] = make_float4(z[0], z[1], z[2], z[3]);
+            }
+          } else {
+            mbar_wait(&gm_full[gslot & 3], (gslot >> 2) & 1);   // published >= 1 tile ago: an acquire, not a wait
+            const float gm = gms[(gslot & 3) * R + r];
+            ++gslot;
+#pragma unroll
+            for (int q = 0; q < 16; ++q) {
+              const float z = fmaxf(v[q] + B3[c0 + q], 0.f);
+              bits |= (z > 0.f ? 1u : 0u) << q;
+              acc4[q] = fmaf(gm, z, acc4[q]);              // dW4 (cbf.py:19)
+            }
+            if (cgrp == 0) accb4 += gm;
           }
-          if (cgrp == 0) accb4 += gm;
           reinterpret_cast<uint32_t*>(tr + cbfrec::MASKS)[(3 * 4 + cgrp) * R + r] = bits;
         }
         float2 s2 = make_float2(0.f, 0.f);
@@ -479,7 +501,7 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
       if (warp == 0) TC_TRACE(0, 7);
       m0 = m1; m1 = m2;
     }
-    if constexpr (DUMP) {
+    if constexpr (DUMP && !RECORD) {
       // dW4 / db4 of this CTA: lanes, then the 4 lane-quadrant warps of each column group
       named_bar_sync(1, WORKERS);
 #pragma unroll
@@ -529,27 +551,41 @@ int cbf_forward_tc(const float* states, const float* obstacles, const int32_t* i
   const int TA = edge_tiles ? 0 : max(1, cbftc::R / K);
   const long long ntiles = edge_tiles ? ((a_end - a_begin) * K + cbftc::R - 1) / cbftc::R : (agents + TA - 1) / TA;
   const int grid = (int)(ntiles < NUM_SMS ? ntiles : (long long)NUM_SMS);
-  MACBF_CHECK_CUDA(cudaFuncSetAttribute(cbf_forward_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  MACBF_CHECK_CUDA(cudaFuncSetAttribute(cbf_forward_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)cbftc::smem_bytes));
-  cbf_forward_tc_kernel<false><<<grid, cbftc::THREADS, cbftc::smem_bytes, st>>>(
+  cbf_forward_tc_kernel<0><<<grid, cbftc::THREADS, cbftc::smem_bytes, st>>>(
       states, obstacles, idx, params, N, M, K, a_end, a_begin, TA, (float)dist_min, (float)obs_radius, h, 0, ntiles, nullptr,
-      nullptr, nullptr);
+      nullptr, nullptr, nullptr);
   MACBF_CHECK_LAUNCH("cbf_forward_tc_kernel");
   return 0;
 }
 
-// First kernel of the tensor-core backward: tiles [tile_begin, tile_end) -> records + dW4/db4 slices.
+// First kernel of the tensor-core backward: tiles [tile_begin, tile_end) -> records + dW4/db4 slices.  With grad_h ==
+// NULL it is the recording forward: h and a3buf are written, slices is not.
 int cbf_forward_tc_dump(const float* states, const float* obstacles, const int32_t* idx, const float* params, int N, int M,
                         int K, long long agents, double dist_min, double obs_radius, long long tile_begin,
-                        long long tile_end, const float* grad_h, unsigned char* rec, float* slices, cudaStream_t st) {
+                        long long tile_end, const float* grad_h, unsigned char* rec, float* slices, cudaStream_t st,
+                        float* h, float* a3buf) {
+  MACBF_CHECK_ARG((grad_h != nullptr) != (a3buf != nullptr) && (grad_h != nullptr) == (slices != nullptr) &&
+                      (grad_h != nullptr) == (h == nullptr),
+                  "cbf_forward_tc_dump: either (grad_h, slices) or (h, a3buf)");
   const int TA = max(1, cbftc::R / K);
   const long long nt = tile_end - tile_begin;
   const int grid = (int)(nt < NUM_SMS ? nt : (long long)NUM_SMS);
-  MACBF_CHECK_CUDA(cudaFuncSetAttribute(cbf_forward_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  if (grad_h == nullptr) {
+    MACBF_CHECK_CUDA(cudaFuncSetAttribute(cbf_forward_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)cbftc::smem_bytes));
+    cbf_forward_tc_kernel<2><<<grid, cbftc::THREADS, cbftc::smem_bytes, st>>>(
+        states, obstacles, idx, params, N, M, K, agents, 0, TA, (float)dist_min, (float)obs_radius, h, tile_begin, tile_end,
+        nullptr, rec, nullptr, a3buf);
+    MACBF_CHECK_LAUNCH("cbf_forward_tc_kernel<record>");
+    return 0;
+  }
+  MACBF_CHECK_CUDA(cudaFuncSetAttribute(cbf_forward_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)cbftc::smem_bytes));
-  cbf_forward_tc_kernel<true><<<grid, cbftc::THREADS, cbftc::smem_bytes, st>>>(
+  cbf_forward_tc_kernel<1><<<grid, cbftc::THREADS, cbftc::smem_bytes, st>>>(
       states, obstacles, idx, params, N, M, K, agents, 0, TA, (float)dist_min, (float)obs_radius, nullptr, tile_begin, tile_end,
-      grad_h, rec, slices);
+      grad_h, rec, slices, nullptr);
   MACBF_CHECK_LAUNCH("cbf_forward_tc_kernel<dump>");
   return 0;
 }

@@ -38,10 +38,26 @@ def _batched(t: torch.Tensor, last: int):
 class CBFFunction(torch.autograd.Function):
     """h = CBF(states) on a fixed neighbour graph (cbf.py:21-45)."""
 
+    # a differentiable REPAIRED forward writes the tile records of the backward (macbf_cbf_forward_record) when they
+    # fit this budget - the backward then skips the recompute; larger problems recompute (macbf_cbf_backward)
+    RECORD_BUDGET_BYTES = 2 << 30
+
     @staticmethod
-    def forward(ctx, states, obstacles, idx, semantics, *params):
+    def apply_auto(states, obstacles, idx, semantics, *params):
+        """apply(), with the recording decided by the caller's grad mode (inside forward() grad mode is always off)."""
+        wants_grad = torch.is_grad_enabled() and (states.requires_grad or any(p.requires_grad for p in params))
+        return CBFFunction.apply(states, obstacles, idx, semantics, wants_grad, *params)
+
+    @staticmethod
+    def forward(ctx, states, obstacles, idx, semantics, wants_grad, *params):
         flat = pack_params(params)
-        h = ops.cbf_forward(states, idx, flat, obstacles, semantics)
+        B, N, K = idx.shape
+        ctx.record = None
+        if (semantics == ops.REPAIRED and wants_grad and B * N * K < 2 ** 31
+                and ops.cbf_record_bytes(B, N, K) <= CBFFunction.RECORD_BUDGET_BYTES):
+            h, ctx.record = ops.cbf_forward_record(states, idx, flat, obstacles)
+        else:
+            h = ops.cbf_forward(states, idx, flat, obstacles, semantics)
         ctx.save_for_backward(states, idx, flat, obstacles if obstacles is not None else states.new_empty(0))
         ctx.has_obs = obstacles is not None
         ctx.semantics = semantics
@@ -55,13 +71,16 @@ class CBFFunction(torch.autograd.Function):
             raise RuntimeError("LITERAL semantics is forward-only (the reference's losses do not run; SURVEY App. A)")
         states, idx, flat, obs = ctx.saved_tensors
         obs = obs if ctx.has_obs else None
-        gp, gs = ops.cbf_backward(states, idx, flat, grad_h.contiguous(), obs, want_grad_states=ctx.needs_input_grad[0])
+        if ctx.record is not None:
+            gp, gs = ops.cbf_backward_record(idx, flat, grad_h.contiguous(), ctx.record, want_grad_states=ctx.needs_input_grad[0])
+        else:
+            gp, gs = ops.cbf_backward(states, idx, flat, grad_h.contiguous(), obs, want_grad_states=ctx.needs_input_grad[0])
         grads, off = [], 0
         for shp in ctx.param_shapes:
             n = int(torch.Size(shp).numel())
             grads.append(gp[off:off + n].view(shp))
             off += n
-        return (gs, None, None, None, *grads)
+        return (gs, None, None, None, None, *grads)
 
 
 class ControllerFunction(torch.autograd.Function):

@@ -64,6 +64,12 @@ SIGNATURES = {
     "macbf_step_forward_rows_b": (I, [c_f32p, c_f32p, c_f32p, c_f32p, c_f32p, I, I, I, I, D, D, D, D, D, I, I, c_i32p, c_i32p,
                                       c_f32p, c_f32p, c_f32p, c_u8p, c_f32p, c_void, SZ, c_void]),
     "macbf_step_forward_rows_c": (I, [c_f32p, I, I, c_f32p, c_void]),
+    "macbf_cbf_record_bytes": (SZ, [I, I, I]),
+    "macbf_cbf_backward_record_scratch_bytes": (SZ, []),
+    "macbf_cbf_forward_record": (I, [c_f32p, c_f32p, c_i32p, c_f32p, I, I, I, I, D, D, c_f32p, c_void, SZ, c_void]),
+    "macbf_cbf_backward_record": (I, [c_i32p, c_f32p, c_f32p, I, I, I, c_void, SZ, c_f32p, c_f32p, c_void, SZ, c_void]),
+    "macbf_step_forward_train": (I, [c_f32p, c_f32p, c_f32p, c_f32p, c_f32p, I, I, I, I, I, D, D, D, D, D, I, c_i32p, c_i32p,
+                                     c_f32p, c_f32p, c_f32p, c_f32p, c_u8p, c_f32p, c_void, SZ, c_void, c_void, SZ, c_void]),
     "macbf_step_forward": (I, [c_f32p, c_f32p, c_f32p, c_f32p, c_f32p, I, I, I, I, I, D, D, D, D, D, c_i32p, c_i32p,
                                c_f32p, c_f32p, c_f32p, c_f32p, c_u8p, c_f32p, c_void, SZ, c_void]),
     "macbf_step_forward_ex": (I, [c_f32p, c_f32p, c_f32p, c_f32p, c_f32p, I, I, I, I, I, D, D, D, D, D, I, c_i32p, c_i32p,

@@ -258,6 +258,49 @@ def cbf_backward(states, idx, cbf_params, grad_h, obstacles=None, dist_min_thres
     return grad_params, gs
 
 
+def cbf_record_bytes(B: int, N: int, K: int) -> int:
+    """Bytes of the record buffer of cbf_forward_record (173 KB per 128 edge rows)."""
+    return int(_lib.load().macbf_cbf_record_bytes(B, N, K))
+
+
+@_on_device_of
+def cbf_forward_record(states, idx, cbf_params, obstacles=None, dist_min_thres=DIST_MIN_THRES, obs_radius=OBS_RADIUS,
+                       record=None):
+    """h = CBF(states) as cbf_forward (REPAIRED), also writing the tile records cbf_backward_record starts from
+    (a training step then runs the CBF forward once instead of twice).  -> (h [B,N,K], record uint8 buffer)."""
+    _need_cuda(states, idx, cbf_params, obstacles, record)
+    states, idx, cbf_params, obstacles = map(_c, (states, idx, cbf_params, obstacles))
+    B, N, M, obstacles = _dims(states, obstacles)
+    K = idx.shape[2]
+    L = _lib.load()
+    nbytes = L.macbf_cbf_record_bytes(B, N, K)
+    if record is None:
+        record = torch.empty((nbytes,), dtype=torch.uint8, device=states.device)
+    h = torch.empty((B, N, K), dtype=torch.float32, device=states.device)
+    _lib.check(L.macbf_cbf_forward_record(_p(states), _p(obstacles), _p(idx), _p(cbf_params), B, N, M, K, dist_min_thres,
+                                          obs_radius, _p(h), _p(record), record.numel(), _stream()), "macbf_cbf_forward_record")
+    return h, record
+
+
+@_on_device_of
+def cbf_backward_record(idx, cbf_params, grad_h, record, grad_params=None, want_grad_states=False):
+    """Backward of cbf_forward_record's pass from its record (reusable) -> (grad_params [17089], grad_states | None)."""
+    _need_cuda(idx, cbf_params, grad_h, record, grad_params)
+    idx, cbf_params, grad_h = map(_c, (idx, cbf_params, grad_h))
+    B, N, K = idx.shape
+    dev = idx.device
+    if grad_params is None:
+        grad_params = torch.zeros((CBF_PARAMS,), dtype=torch.float32, device=dev)
+    gs = torch.zeros((B, N, 4), dtype=torch.float32, device=dev) if want_grad_states else None
+    L = _lib.load()
+    nbytes = L.macbf_cbf_backward_record_scratch_bytes()
+    scratch = torch.empty((nbytes,), dtype=torch.uint8, device=dev)
+    _lib.check(L.macbf_cbf_backward_record(_p(idx), _p(cbf_params), _p(grad_h), B, N, K, _p(record), record.numel(),
+                                           _p(grad_params), _p(gs), _p(scratch), nbytes, _stream()),
+               "macbf_cbf_backward_record")
+    return grad_params, gs
+
+
 @_on_device_of
 def controller_backward(states, goals, idx, ctrl_params, grad_u, grad_s_next=None, obstacles=None,
                         obs_radius=OBS_RADIUS, dt=TIME_STEP, grad_params=None, want_grad_states=False,
@@ -290,10 +333,15 @@ STEP_SAVE_WINNERS = 2    # MACBF_STEP_SAVE_WINNERS
 class StepBuffers:
     """Pre-allocated outputs + workspace for macbf_step_forward: the timed loop allocates nothing."""
 
-    def __init__(self, B: int, N: int, M: int, top_k: int, device):
+    def __init__(self, B: int, N: int, M: int, top_k: int, device, record: bool = False):
         L = _lib.load()
         self.B, self.N, self.M, self.top_k = B, N, M, top_k
         self.K = K = neighbor_count(N, M, top_k)
+        # record=True: tile records of the two CBF passes (training: step_forward(..., record=True), then
+        # macbf_cbf_backward_record instead of macbf_cbf_backward)
+        self.record_bytes = int(L.macbf_cbf_record_bytes(B, N, K)) if record else 0
+        self.record = torch.empty((self.record_bytes,), dtype=torch.uint8, device=device) if record else None
+        self.record_next = torch.empty((self.record_bytes,), dtype=torch.uint8, device=device) if record else None
         f32, dev = torch.float32, device
         self.idx = torch.empty((B, N, K), dtype=torch.int32, device=dev)
         self.idx_next = torch.empty((B, N, K), dtype=torch.int32, device=dev)
@@ -313,17 +361,27 @@ class StepBuffers:
 @_on_device_of
 def step_forward(states, goals, cbf_params, ctrl_params, buf: StepBuffers, obstacles=None, semantics=REPAIRED,
                  dist_min_thres=DIST_MIN_THRES, obs_radius=OBS_RADIUS, ttc=TIME_TO_COLLISION, dt=TIME_STEP,
-                 alpha=ALPHA_CBF, reuse_indices=False, save_winners=False):
+                 alpha=ALPHA_CBF, reuse_indices=False, save_winners=False, record=False):
     """The whole per-step path (graph -> u, S' -> graph' -> h, h' -> TTC mask -> scalars) in one C call.
-    reuse_indices=True evaluates h' on S's neighbour sets (MACBF_STEP_REUSE_INDICES; not the reference's default)."""
+    reuse_indices=True evaluates h' on S's neighbour sets (MACBF_STEP_REUSE_INDICES; not the reference's default).
+    record=True (buf made with record=True): the two CBF passes write their tile records (macbf_step_forward_train)."""
     _need_cuda(states, goals, cbf_params, ctrl_params, obstacles)
     B, N, M, obstacles = _dims(states, obstacles)
     assert (B, N, M) == (buf.B, buf.N, buf.M), "StepBuffers were sized for another problem"
     assert states.is_contiguous() and goals.is_contiguous() and cbf_params.is_contiguous() and ctrl_params.is_contiguous()
     L = _lib.load()
+    flags = (STEP_REUSE_INDICES if reuse_indices else 0) | (STEP_SAVE_WINNERS if save_winners else 0)
+    if record:
+        assert buf.record is not None, "StepBuffers were made without record=True"
+        _lib.check(L.macbf_step_forward_train(_p(states), _p(goals), _p(obstacles), _p(cbf_params), _p(ctrl_params), B, N, M,
+                                              buf.top_k, semantics, dist_min_thres, obs_radius, ttc, dt, alpha, flags,
+                                              _p(buf.idx), _p(buf.idx_next), _p(buf.u), _p(buf.s_next), _p(buf.h),
+                                              _p(buf.h_next), _p(buf.ttc_mask), _p(buf.scalars), _p(buf.workspace),
+                                              buf.workspace.numel(), _p(buf.record), _p(buf.record_next), buf.record_bytes,
+                                              _stream()), "macbf_step_forward_train")
+        return buf
     _lib.check(L.macbf_step_forward_ex(_p(states), _p(goals), _p(obstacles), _p(cbf_params), _p(ctrl_params), B, N, M,
-                                       buf.top_k, semantics, dist_min_thres, obs_radius, ttc, dt, alpha,
-                                       (STEP_REUSE_INDICES if reuse_indices else 0) | (STEP_SAVE_WINNERS if save_winners else 0),
+                                       buf.top_k, semantics, dist_min_thres, obs_radius, ttc, dt, alpha, flags,
                                        _p(buf.idx), _p(buf.idx_next),
                                        _p(buf.u), _p(buf.s_next), _p(buf.h), _p(buf.h_next), _p(buf.ttc_mask),
                                        _p(buf.scalars), _p(buf.workspace), buf.workspace.numel(), _stream()),

@@ -24,14 +24,22 @@ _LOSS_WEIGHTS = {0: 20.0, 1: 10.0, 4: 20.0, 5: 10.0, 8: 0.1}
 
 
 class TrainStep:
-    def __init__(self, B: int, N: int, M: int, top_k: int, device, world_size: int = 1, process_group=None):
+    # record_forward=None: the forward pass writes the CBF tile records (one CBF forward per pass less) whenever the two
+    # record buffers fit this budget; False: recompute in the backward (macbf_cbf_backward), no extra memory
+    RECORD_BUDGET_BYTES = 16 << 30
+
+    def __init__(self, B: int, N: int, M: int, top_k: int, device, world_size: int = 1, process_group=None,
+                 record_forward: Optional[bool] = None):
         self.B, self.N, self.M, self.top_k = B, N, M, top_k
         self.world_size = world_size
         self.group = process_group
         self.device = torch.device(device)
-        self.buf = ops.StepBuffers(B, N, M, top_k, device)
-        K = self.buf.K
         L = _lib.load()
+        K = ops.neighbor_count(N, M, top_k)
+        if record_forward is None:
+            record_forward = B * N * K < 2 ** 31 and 2 * L.macbf_cbf_record_bytes(B, N, K) <= self.RECORD_BUDGET_BYTES
+        self.record_forward = bool(record_forward)
+        self.buf = ops.StepBuffers(B, N, M, top_k, device, record=self.record_forward)
         f32 = torch.float32
         dev = device
         # one flat gradient buffer [cbf | ctrl] so a single collective moves everything
@@ -46,7 +54,8 @@ class TrainStep:
         for c, w in _LOSS_WEIGHTS.items():
             gsc[:, c] = w / (B * world_size)
         self.grad_scalars = gsc.to(dev)
-        nb = max(L.macbf_cbf_backward_scratch_bytes(B, N, K), L.macbf_controller_backward_scratch_bytes(B, N, K), 256)
+        nb_cbf = L.macbf_cbf_backward_record_scratch_bytes() if self.record_forward else L.macbf_cbf_backward_scratch_bytes(B, N, K)
+        nb = max(nb_cbf, L.macbf_controller_backward_scratch_bytes(B, N, K), 256)
         self.scratch = torch.empty((nb,), dtype=torch.uint8, device=dev)
         self.overlap_allreduce = True
         # optional probes (bench.py): recorded on the current stream after the last backward kernel / after the sync
@@ -65,7 +74,8 @@ class TrainStep:
         b = self.buf
         B, N, M, K = self.B, self.N, self.M, b.K
         ops.step_forward(states, goals, cbf_params, ctrl_params, b, obstacles, reuse_indices=reuse_indices,
-                         save_winners=True)   # the controller backward below reuses pool and the max-pool winners
+                         save_winners=True,   # the controller backward below reuses pool and the max-pool winners
+                         record=self.record_forward)
         st = torch.cuda.current_stream().cuda_stream
         p = ops._p
         obs = obstacles if (obstacles is not None and M > 0) else None
@@ -74,6 +84,24 @@ class TrainStep:
                                          p(self.ghn), p(self.gu), None, st), "macbf_loss_backward")
         self.grad.zero_()
         self.gs_next.zero_()
+        if self.record_forward:
+            # the forward wrote the tile records: the backward starts at the delta chain (h' first: parameter gradient +
+            # d/dS'; then h: S is the data of this step, only the parameter gradient is needed)
+            _lib.check(L.macbf_cbf_backward_record(p(b.idx_next), p(cbf_params), p(self.ghn), B, N, K, p(b.record_next),
+                                                   b.record_bytes, p(self.grad_cbf), p(self.gs_next), p(self.scratch),
+                                                   self.scratch.numel(), st), "macbf_cbf_backward_record(S')")
+            _lib.check(L.macbf_cbf_backward_record(p(b.idx), p(cbf_params), p(self.gh), B, N, K, p(b.record),
+                                                   b.record_bytes, p(self.grad_cbf), None, p(self.scratch),
+                                                   self.scratch.numel(), st), "macbf_cbf_backward_record(S)")
+        else:
+            self._cbf_backward_recompute(L, p, b, states, obs, cbf_params, B, N, M, K, st)
+        cbf_work = None
+        if all_reduce and self.world_size > 1 and self.overlap_allreduce:
+            import torch.distributed as dist
+            cbf_work = dist.all_reduce(self.grad_cbf, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+        return self._controller_backward_and_sync(L, p, b, states, goals, obs, ctrl_params, B, N, M, K, st, all_reduce, cbf_work)
+
+    def _cbf_backward_recompute(self, L, p, b, states, obs, cbf_params, B, N, M, K, st):
         # h' = CBF(S') on its own graph: parameter gradient + d/dS'
         _lib.check(L.macbf_cbf_backward(p(b.s_next), p(obs), p(b.idx_next), p(cbf_params), p(self.ghn), B, N, M, K,
                                         ops.DIST_MIN_THRES, ops.OBS_RADIUS, p(self.grad_cbf), p(self.gs_next),
@@ -82,13 +110,11 @@ class TrainStep:
         _lib.check(L.macbf_cbf_backward(p(states), p(obs), p(b.idx), p(cbf_params), p(self.gh), B, N, M, K,
                                         ops.DIST_MIN_THRES, ops.OBS_RADIUS, p(self.grad_cbf), None,
                                         p(self.scratch), self.scratch.numel(), st), "macbf_cbf_backward(S)")
-        # The CBF half of the flat gradient is final here: start its all-reduce now, on NCCL's own stream, so it runs
-        # under the controller backward (the controller half follows after it; SURVEY 8e's one collective, split in two
-        # messages so that only the second one is exposed).
-        cbf_work = None
-        if all_reduce and self.world_size > 1 and self.overlap_allreduce:
-            import torch.distributed as dist
-            cbf_work = dist.all_reduce(self.grad_cbf, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+
+    def _controller_backward_and_sync(self, L, p, b, states, goals, obs, ctrl_params, B, N, M, K, st, all_reduce, cbf_work):
+        # (The CBF half of the flat gradient was final before this call: its all-reduce was started there, on NCCL's own
+        # stream, so it runs under the controller backward; the controller half follows after it - SURVEY 8e's one
+        # collective, split in two messages so that only the second one is exposed.)
         # controller: d/du from the action loss, plus dt * d/dS'[v] through the Euler step
         ws = b.workspace.data_ptr()
         _lib.check(L.macbf_controller_backward_saved(p(states), p(goals), p(obs), p(b.idx), p(ctrl_params), p(self.gu),

@@ -137,3 +137,60 @@ def test_tensor_core_backward_matches_oracle_autograd(ops, K, N, n_obs):
     want[2] = torch.cat([pt[n].grad.reshape(-1) for n in O.CTRL_KEYS])
     for name, a, b in zip(NAMES, tc, want):
         assert _rel(a.cpu(), b) < GTOL, f"K={K}: {name} differs from oracle autograd by {_rel(a.cpu(), b):.2e}"
+
+
+@pytest.mark.parametrize("B,N,K,n_obs", [(2, 200, 12, 0), (1, 96, 5, 2), (2, 150, 64, 0), (1, 200, 128, 0), (3, 7, 12, 0), (1, 1000, 1, 0)])
+def test_recording_forward_and_its_backward_equal_the_recompute_path(ops, B, N, K, n_obs):
+    """macbf_cbf_forward_record + macbf_cbf_backward_record (the training step's pair: the forward writes the tile records,
+    the backward starts at the delta chain) against macbf_cbf_forward + macbf_cbf_backward (forward, then recompute):
+    same h bit for bit (a row's value does not depend on the tile it sits in), same gradients up to the summation
+    order of dW4 / db4 (which move from the dump kernel to the delta-chain kernel)."""
+    s, g, obs, idx, cf, tf, gh, gu, gs = _case(ops, B, N, K, n_obs, 21)
+    h_plain = ops.cbf_forward(s, idx, cf, obs)
+    h_rec, rec = ops.cbf_forward_record(s, idx, cf, obs)
+    assert rec.numel() == ops.cbf_record_bytes(B, N, idx.shape[2])
+    assert torch.equal(h_plain, h_rec)
+    gp1, gs1 = ops.cbf_backward(s, idx, cf, gh, obstacles=obs, want_grad_states=True)
+    gp2, gs2 = ops.cbf_backward_record(idx, cf, gh, rec, want_grad_states=True)
+    assert _rel(gp2, gp1) <= 2e-6, f"grad_params record vs recompute: {_rel(gp2, gp1):.2e}"
+    assert _rel(gs2, gs1) <= 2e-6, f"grad_states record vs recompute: {_rel(gs2, gs1):.2e}"
+    # W4 / b4 (the part computed by different code): tight on their own scale
+    from macbf_b200.ops import CBF_PARAMS
+    w4 = slice(CBF_PARAMS - 65, CBF_PARAMS)
+    assert _rel(gp2[w4], gp1[w4]) <= 2e-6, f"dW4/db4 record vs recompute: {_rel(gp2[w4], gp1[w4]):.2e}"
+
+
+def test_train_step_record_and_recompute_modes_agree(ops):
+    """TrainStep(record_forward=True) (default when the records fit) against record_forward=False on the same inputs:
+    same scalars bit for bit, same flat gradient to summation order."""
+    import oracle.macbf_oracle as O
+    from macbf_b200.step import TrainStep
+    B, N = 3, 300
+    s, g = O.synthetic_swarm(B, N, 4)
+    obs = dev(O.synthetic_obstacles(B, N, 2, 0, 5))
+    p_cbf, p_ctrl = O.init_params(4)
+    cf, tf = dev(O.flatten_params(p_cbf, O.CBF_KEYS)), dev(O.flatten_params(p_ctrl, O.CTRL_KEYS))
+    out = []
+    for rec in (True, False):
+        ts = TrainStep(B, N, obs.shape[1], 12, "cuda", record_forward=rec)
+        assert ts.record_forward is rec
+        sc, gr = ts.forward_backward(dev(s), dev(g), cf, tf, obs)
+        out.append((sc.clone(), gr.clone()))
+    assert TrainStep(B, N, obs.shape[1], 12, "cuda").record_forward is True
+    assert torch.equal(out[0][0], out[1][0])
+    assert _rel(out[0][1], out[1][1]) <= 2e-6, f"{_rel(out[0][1], out[1][1]):.2e}"
+
+
+def test_record_entry_points_reject_small_buffers(ops):
+    from macbf_b200 import lib
+    L = lib.load()
+    s, g, obs, idx, cf, tf, gh, gu, gs = _case(ops, 1, 64, 12, 0, 3)
+    h = torch.empty(1, 64, 12, device="cuda")
+    small = torch.empty(4096, dtype=torch.uint8, device="cuda")
+    rc = L.macbf_cbf_forward_record(s.data_ptr(), None, idx.data_ptr(), cf.data_ptr(), 1, 64, 0, 12, 0.07, 1.0, h.data_ptr(),
+                                    small.data_ptr(), small.numel(), None)
+    assert rc == 1 and b"record buffer too small" in L.macbf_last_error()
+    gp = torch.zeros(17089, device="cuda")
+    rc = L.macbf_cbf_backward_record(idx.data_ptr(), cf.data_ptr(), gh.data_ptr(), 1, 64, 12, small.data_ptr(), small.numel(),
+                                     gp.data_ptr(), None, small.data_ptr(), small.numel(), None)
+    assert rc == 1 and b"too small" in L.macbf_last_error()
