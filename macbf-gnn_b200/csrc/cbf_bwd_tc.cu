@@ -90,8 +90,15 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
     mbar_init(&dz_full[0], 16); mbar_init(&dz_full[1], 16);
     fence_mbar_init();
   }
-  fill_weight_sw128_strided<128, 64>(params + CBF_W3, 1, 128, W3Thi, W3Tlo);
-  fill_weight_sw128_strided<64, 128>(params + CBF_W2, 1, 64, W2Thi, W2Tlo);
+  {   // both transposed weights: all loads in flight, then the splits and stores
+    constexpr int NT = RECORD ? THREADS_RECORD : THREADS;
+    WeightFill<128, 64, NT> f3;
+    WeightFill<64, 128, NT> f2;
+    f3.template load<true>(params + CBF_W3, 1, 128);
+    f2.template load<true>(params + CBF_W2, 1, 64);
+    f3.template store<true>(W3Thi, W3Tlo);
+    f2.template store<true>(W2Thi, W2Tlo);
+  }
   for (int t = threadIdx.x; t < 64 * 8; t += THREADS) W1[t] = ((t & 7) < 6) ? __ldg(params + CBF_W1 + (t >> 3) * 6 + (t & 7)) : 0.f;
   for (int t = threadIdx.x; t < 64; t += THREADS) W4[t] = __ldg(params + CBF_W4 + t);
   fence_proxy_async_smem();

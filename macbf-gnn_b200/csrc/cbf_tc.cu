@@ -125,15 +125,30 @@ cbf_forward_tc_kernel(const float* __restrict__ states, const float* __restrict_
     for (int i = 0; i < 4; ++i) mbar_init(&gm_full[i], 4);
     fence_mbar_init();
   }
-  fill_weight_sw128<128, 64>(params + CBF_W2, 64, W2hi, W2lo);
-  fill_weight_sw128<64, 128>(params + CBF_W3, 128, W3hi, W3lo);
+  {   // both weight matrices: all loads in flight, then the splits and stores
+    WeightFill<128, 64, THREADS> f2;
+    WeightFill<64, 128, THREADS> f3;
+    f2.template load<false>(params + CBF_W2, 64, 1);
+    f3.template load<false>(params + CBF_W3, 128, 1);
+    f2.template store<false>(W2hi, W2lo);
+    f3.template store<false>(W3hi, W3lo);
+  }
   // W1 (64 x 6): channel n is one 128-B row; 16-B chunk c sits at position c ^ (n & 7); A1 likewise
-  for (int t = threadIdx.x; t < 64 * 32; t += THREADS) {
-    const int n = t >> 5, pos = (t >> 2) & 7, e = t & 3;
-    const int k = ((pos ^ (n & 7)) << 2) + e;
-    float hi = 0.f, lo = 0.f;
-    if (k < 6) tf32_split(__ldg(params + CBF_W1 + n * 6 + k), hi, lo);
-    W1hi[t] = hi; W1lo[t] = lo;
+  {
+    float w1 = 0.f;                                   // the 384 real entries: one load each, in flight with the rest
+    if (threadIdx.x < 64 * 6) w1 = __ldg(params + CBF_W1 + threadIdx.x);
+    for (int t = threadIdx.x; t < 64 * 32; t += THREADS) {
+      const int n = t >> 5, pos = (t >> 2) & 7, e = t & 3;
+      const int k = ((pos ^ (n & 7)) << 2) + e;
+      if (k >= 6) { W1hi[t] = 0.f; W1lo[t] = 0.f; }
+    }
+    if (threadIdx.x < 64 * 6) {
+      const int n = threadIdx.x / 6, k = threadIdx.x - n * 6;
+      float hi, lo;
+      tf32_split(w1, hi, lo);
+      const int t = n * 32 + ((((k >> 2) ^ (n & 7)) << 2) | (k & 3));
+      W1hi[t] = hi; W1lo[t] = lo;
+    }
   }
   for (int t = threadIdx.x; t < 128 * 32; t += THREADS) { A1hi[t] = 0.f; A1lo[t] = 0.f; }
   for (int t = threadIdx.x; t < 128; t += THREADS) B2[t] = __ldg(params + CBF_B2 + t);

@@ -67,7 +67,11 @@ ctrl_edge_bwd_tc_kernel(const float* __restrict__ states, const float* __restric
     mbar_init(&z_full, 8); mbar_init(&c_done, 1);
     fence_mbar_init();
   }
-  fill_weight_sw128_strided<64, 128>(params + CT_EW2, 1, 64, W2Thi, W2Tlo);
+  {
+    WeightFill<64, 128, THREADS> f2;
+    f2.template load<true>(params + CT_EW2, 1, 64);
+    f2.template store<true>(W2Thi, W2Tlo);
+  }
   for (int t = threadIdx.x; t < 64 * 8; t += THREADS) W1[t] = ((t & 7) < 5) ? __ldg(params + CT_EW1 + (t >> 3) * 5 + (t & 7)) : 0.f;
   for (int t = threadIdx.x; t < 64; t += THREADS) B1[t] = __ldg(params + CT_EB1 + t);
   fence_proxy_async_smem();

@@ -64,8 +64,14 @@ ctrl_node_dgrad_tc_kernel(const float* __restrict__ params, const float* __restr
     mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_init(&bar[2], 1);
     fence_mbar_init();
   }
-  fill_weight_sw128_strided<128, 64>(params + CT_NW3, 1, 128, W3Thi, W3Tlo);
-  fill_weight_sw128_strided<64, 128>(params + CT_NW2, 1, 64, W2Thi, W2Tlo);
+  {   // both transposed weights: all loads in flight, then the splits and stores
+    WeightFill<128, 64, THREADS> f3;
+    WeightFill<64, 128, THREADS> f2;
+    f3.template load<true>(params + CT_NW3, 1, 128);
+    f2.template load<true>(params + CT_NW2, 1, 64);
+    f3.template store<true>(W3Thi, W3Tlo);
+    f2.template store<true>(W2Thi, W2Tlo);
+  }
   // W1^T: element (n = input, k = output) = W1[k][n], inputs 132..143 are zero rows
   for (int t = threadIdx.x; t < N1 * 16; t += THREADS) {
     const int n = t % N1, k4 = t / N1;

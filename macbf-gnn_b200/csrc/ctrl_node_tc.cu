@@ -97,23 +97,18 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
     mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_init(&bar[2], 1);
     fence_mbar_init();
   }
-  // W1 (64 x 132) zero-padded to K = 160 in the SWIZZLE_128B K-major layout
-  for (int t = threadIdx.x; t < 64 * (K1P / 4); t += THREADS) {
-    const int n = t / (K1P / 4), k4 = t % (K1P / 4);
-    const int kb = k4 >> 3, c = k4 & 7;
-    float h[4], l[4];
-#pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const int k = 4 * k4 + e;
-      const float w = (k < 132) ? __ldg(params + CT_NW1 + n * 132 + k) : 0.f;
-      tf32_split(w, h[e], l[e]);
-    }
-    const int off = kb * (64 * 32) + n * 32 + ((c ^ (n & 7)) << 2);
-    *reinterpret_cast<float4*>(W1hi + off) = make_float4(h[0], h[1], h[2], h[3]);
-    *reinterpret_cast<float4*>(W1lo + off) = make_float4(l[0], l[1], l[2], l[3]);
+  {   // all three weight matrices: every load in flight before the first split / store.  W1 (64 x 132) is zero-padded
+      // to K = 160 in the SWIZZLE_128B K-major layout
+    WeightFill<64, K1P, THREADS> f1;
+    WeightFill<128, 64, THREADS> f2;
+    WeightFill<64, 128, THREADS> f3;
+    f1.template load<false>(params + CT_NW1, 132, 1, 132);
+    f2.template load<false>(params + CT_NW2, 64, 1);
+    f3.template load<false>(params + CT_NW3, 128, 1);
+    f1.template store<false>(W1hi, W1lo);
+    f2.template store<false>(W2hi, W2lo);
+    f3.template store<false>(W3hi, W3lo);
   }
-  fill_weight_sw128<128, 64>(params + CT_NW2, 64, W2hi, W2lo);
-  fill_weight_sw128<64, 128>(params + CT_NW3, 128, W3hi, W3lo);
   for (int t = threadIdx.x; t < 64; t += THREADS) {
     B1[t] = __ldg(params + CT_NB1 + t);
     B3[t] = __ldg(params + CT_NB3 + t);

@@ -273,6 +273,45 @@ __device__ __forceinline__ void fill_weight_sw128(const float* __restrict__ W, i
   }
 }
 
+// The same fill in two phases, so that a kernel prologue can put the loads of ALL its weight matrices in flight before the
+// first split / store (one memory round trip instead of one per loop iteration and matrix: the prologue of a persistent
+// kernel is serial time on every SM).  element (n, k) = W[n * stride_n + k * stride_k]; THREADS = blockDim.x.
+template <int N, int K, int THREADS>
+struct WeightFill {
+  static constexpr int CHUNKS = N * (K / 4);
+  static constexpr int IT = (CHUNKS + THREADS - 1) / THREADS;
+  float w[IT][4];
+  // consecutive threads -> consecutive k4 of a row (row-major weights, stride_k == 1) or consecutive n (NFAST: transposed views)
+  // k_valid < K: the matrix has only k_valid columns, the rest of the operand is zero padding
+  template <bool NFAST>
+  __device__ __forceinline__ void load(const float* __restrict__ W, int stride_n, int stride_k, int k_valid = K) {
+#pragma unroll
+    for (int i = 0; i < IT; ++i) {
+      const int t = (int)threadIdx.x + i * THREADS;
+      const int n = NFAST ? t % N : t / (K / 4), k4 = NFAST ? t / N : t % (K / 4);
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        w[i][q] = (t < CHUNKS && 4 * k4 + q < k_valid) ? __ldg(W + (size_t)n * stride_n + (size_t)(4 * k4 + q) * stride_k) : 0.f;
+    }
+  }
+  template <bool NFAST>
+  __device__ __forceinline__ void store(float* __restrict__ hi, float* __restrict__ lo) const {
+#pragma unroll
+    for (int i = 0; i < IT; ++i) {
+      const int t = (int)threadIdx.x + i * THREADS;
+      if (t >= CHUNKS) continue;
+      const int n = NFAST ? t % N : t / (K / 4), k4 = NFAST ? t / N : t % (K / 4);
+      const int kb = k4 >> 3, c = k4 & 7;
+      float h[4], l[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) tf32_split(w[i][q], h[q], l[q]);
+      const int off = kb * (N * 32) + n * 32 + ((c ^ (n & 7)) << 2);
+      *reinterpret_cast<float4*>(hi + off) = make_float4(h[0], h[1], h[2], h[3]);
+      *reinterpret_cast<float4*>(lo + off) = make_float4(l[0], l[1], l[2], l[3]);
+    }
+  }
+};
+
 // Same, for a strided view: element (n, k) = W[n * stride_n + k * stride_k]  (a transposed weight for dgrad).
 template <int N, int K>
 __device__ __forceinline__ void fill_weight_sw128_strided(const float* __restrict__ W, int stride_n, int stride_k,
