@@ -1,5 +1,6 @@
 """Summaries for profiles/: per-kernel table of an ncu launch list with metrics, and headline metrics of a --set full report.
-usage: python scripts/r2_profile_summary.py launches <csv>  |  full <ncu-rep>"""
+usage: python scripts/r2_profile_summary.py launches <csv>  |  full <ncu-rep>  |  json <out.json> <ncu-rep> [<ncu-rep> ...]
+(json: per-kernel DRAM bytes / tensor-pipe activity under bench.py's kernel labels, read by bench.py for `roofline.traffic`)"""
 import collections
 import csv
 import io
@@ -8,7 +9,52 @@ import subprocess
 import sys
 
 mode, path = sys.argv[1], sys.argv[2]
-if mode == "launches":
+
+
+def bench_label(name):
+    """ncu kernel name -> the label bench.py's live table uses (MACBF_CHECK_LAUNCH strings)."""
+    import re
+    name = name.replace("void ", "").replace("macbf::", "").strip()
+    m = re.match(r"(\w+)(<.*>)?", name)
+    base, targs = m.group(1), (m.group(2) or "")
+    first = re.sub(r"[<>()a-z ]", "", targs).split(",")[0] if targs else ""
+    if base == "cbf_forward_tc_kernel":
+        return base + {"0": "", "1": "<dump>", "2": "<record>"}.get(first, targs)
+    if base == "ctrl_node_tc_kernel":
+        return base + {"0": "", "1": "<dump>"}.get(first, targs)
+    if base == "wgrad_tc_kernel":
+        return base + {"1": "<ctrl>", "2": "<cbf>", "3": "<node>"}.get(first, targs)
+    return base
+
+
+if mode == "json":
+    out = {"workload": [1024, 64, 12, 0],
+           "how": "ncu --set full --clock-control none, one launch per kernel of `python bench.py` (scripts/r2_profiles.sh); per launch",
+           "kernels": {}}
+    for rep in sys.argv[3:]:
+        raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+        rows = list(csv.reader(io.StringIO(raw)))
+        hdr = rows[0]
+        col = {w: hdr.index(w) for w in ("Kernel Name", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+                                          "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed")}
+        unit = rows[1]
+
+        def val(r, w):
+            v = float(r[col[w]].replace(",", ""))
+            u = unit[col[w]].lower()
+            return v * {"gbyte": 1e9, "mbyte": 1e6, "kbyte": 1e3, "byte": 1.0, "ms": 1e3, "us": 1.0, "ns": 1e-3, "%": 1.0, "msecond": 1e3,
+                        "usecond": 1.0, "nsecond": 1e-3}.get(u, 1.0)
+        for r in rows[2:]:
+            lab = bench_label(r[col["Kernel Name"]].split("(")[0] if "<" not in r[col["Kernel Name"]] else r[col["Kernel Name"]])
+            if lab in out["kernels"]:
+                continue
+            rd, wr = val(r, "dram__bytes_read.sum"), val(r, "dram__bytes_write.sum")
+            out["kernels"][lab] = {"dram_bytes": rd + wr, "dram_read": rd, "dram_write": wr,
+                                   "tensor_active_pct": val(r, "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed"),
+                                   "duration_us_under_ncu": val(r, "gpu__time_duration.sum")}
+    json.dump(out, open(path, "w"), indent=1)
+    print(json.dumps({k: round(v["duration_us_under_ncu"], 1) for k, v in out["kernels"].items()}))
+elif mode == "launches":
     rows = [r for r in csv.reader(open(path)) if len(r) > 5]
     hdr = next(r for r in rows if "Kernel Name" in r)
     st = rows.index(hdr)
