@@ -31,6 +31,7 @@
 namespace macbf {
 
 int reduce_partials(const float* partial, int nslices, int P, float* out, cudaStream_t st);
+int wgrad_cbf_ring(const unsigned char* rec, long long ntiles, float* slices, const float* params, int grid, cudaStream_t st);
 int cbf_forward_tc_dump(const float* states, const float* obstacles, const int32_t* idx, const float* params, int N, int M,
                         int K, long long agents, double dist_min, double obs_radius, long long tile_begin,
                         long long tile_end, const float* grad_h, unsigned char* rec, float* slices, cudaStream_t st,
@@ -458,8 +459,6 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
   __shared__ uint32_t tmem_base_s;
   __shared__ __align__(16) float gW1[64 * 8];
   __shared__ float gB1[64];
-  __shared__ float gW4[64];
-  const bool gen3 = (NST == 2) && gen_w4 != nullptr && gen_w1 != nullptr;
   const bool genA = (NST == 1) && route.dpool != nullptr && gen_w1 != nullptr;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const bool gen = (NST != 3) && gen_w1 != nullptr;
@@ -475,8 +474,6 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
   if (gen) {
     for (int t = threadIdx.x; t < 64 * 8; t += blockDim.x) gW1[t] = ((t & 7) < gen_nf) ? __ldg(gen_w1 + (t >> 3) * gen_nf + (t & 7)) : 0.f;
     for (int t = threadIdx.x; t < 64; t += blockDim.x) gB1[t] = __ldg(gen_b1 + t);
-    if (gen3)
-      for (int t = threadIdx.x; t < 64; t += blockDim.x) gW4[t] = __ldg(gen_w4 + t);
   }
   for (int t = threadIdx.x; t < 1024; t += blockDim.x) reinterpret_cast<uint32_t*>(sm + ONES)[t] = 0x3f803f80u;   // bf16 1.0 pairs
   fence_proxy_async_smem();
@@ -494,7 +491,7 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
         if (elect_one()) {
           const unsigned char* src = rec + (size_t)tile * rec_stride + (size_t)s * rec_stage;   // bytes of a stage in the record
           // with `gen` the last third of a G2-type stage (the a1 images) is produced on chip
-          const int parts = genA ? 0 : ((gen && ((NST == 1) || s == 1)) || (gen3 && s == 0)) ? 2 : 3;
+          const int parts = genA ? 0 : (gen && ((NST == 1) || s == 1)) ? 2 : 3;
           mbar_expect_tx(&full[buf], parts * (STAGE / 3));
           for (int p = 0; p < parts; ++p) bulk_g2s(sm + buf * STAGE + p * (STAGE / 3), src + p * (STAGE / 3), STAGE / 3, &full[buf]);
         }
@@ -566,56 +563,34 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
           }
         }
       };
+      // Every global load of a stage is requested right AFTER the previous stage has been published (and, for the first
+      // stage, here): fence.proxy.async waits for the thread's outstanding global loads, so a load requested between the
+      // start of a stage and its fence puts a DRAM round trip on the hand-off of every stage.
+      float4 xa_n = make_float4(0.f, 0.f, 0.f, 0.f), xb_n = xa_n;
+      auto load_x = [&](long long t, int s0n) {          // edge features of this thread's row for stage (t, s0n), if it is a G2-type one
+        if (t < ntiles && ((NST == 1) || s0n == 1)) {
+          const float4* xr = reinterpret_cast<const float4*>(rec + (size_t)t * rec_stride + gen_xoff) + 2 * r;
+          xa_n = __ldg(xr); xb_n = __ldg(xr + 1);
+        }
+      };
       if (genA) load_route(blockIdx.x);
+      load_x(blockIdx.x, 0);
       for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         for (int s0 = 0; s0 < NST; ++s0, ++n) {
           const uint32_t buf = n & 1;
           const bool g2 = (NST == 1) || s0 == 1;
-          float4 xa = make_float4(0.f, 0.f, 0.f, 0.f), xb = xa;
-          if (g2) {
-            const float4* xr = reinterpret_cast<const float4*>(rec + (size_t)tile * rec_stride + gen_xoff) + 2 * r;
-            xa = __ldg(xr); xb = __ldg(xr + 1);
-          }
-          const bool g3 = gen3 && s0 == 0;
-          float gm = 0.f;
-          uint32_t m3[4] = {0u, 0u, 0u, 0u};
-          if (g3) {
-            const unsigned char* tr = rec + (size_t)tile * rec_stride;
-            gm = __ldg(reinterpret_cast<const float*>(tr + cbfrec::GM) + r);
-#pragma unroll
-            for (int cg = 0; cg < 4; ++cg) m3[cg] = __ldg(reinterpret_cast<const uint32_t*>(tr + cbfrec::MASKS) + (3 * 4 + cg) * 128 + r);
-          }
+          const float4 xa = xa_n, xb = xb_n;
           // dZ2 is sparse - per agent and channel ONE row (the max-pool winner) carries d/dpool, the rest is zero: the
           // image is zero-filled with wide stores and the winners are scattered into it (512 generator threads:
           // thread = (agent g >> 7 + 4 j of the tile, channel g & 127)); loads go out before the stage is waited for
           float sc_v[8];
           int sc_w[8];                                   // winner slot (255: none / no such agent)
           const int sc_n = genA ? (route.TA + 3) >> 2 : 0;
-          if (genA) {
-            // this tile's values were fetched one tile ago (nx_*); fetch the next tile's now
+          if (genA) {   // this tile's values were fetched one tile ago (nx_*)
 #pragma unroll
             for (int j = 0; j < 8; ++j) { sc_v[j] = nx_v[j]; sc_w[j] = nx_w[j]; }
-            load_route(tile + gridDim.x);
           }
           if (n >= 2) mbar_wait(&empty[buf], ((n >> 1) - 1) & 1);
-          if (g3) {
-            unsigned char* img_hi = sm + buf * STAGE + 4 * cbfrec::BLK;
-            unsigned char* img_lo = sm + buf * STAGE + 5 * cbfrec::BLK;
-            for (int c8 = part; c8 < 8; c8 += nparts) {
-              float x[8];
-#pragma unroll
-              for (int e = 0; e < 8; ++e) {
-                const int ch = c8 * 8 + e;
-                x[e] = ((m3[ch >> 4] >> (ch & 15)) & 1u) ? gm * gW4[ch] : 0.f;
-              }
-              uint4 bh, bl;
-              bf16_split8(x, bh, bl);
-              const uint32_t off = (uint32_t)r * 128u + (uint32_t)((c8 ^ (r & 7)) << 4);
-              *reinterpret_cast<uint4*>(img_hi + off) = bh;
-              *reinterpret_cast<uint4*>(img_lo + off) = bl;
-            }
-            fence_proxy_async_smem();
-          }
           if (genA) {
             unsigned char* a_hi = sm + buf * STAGE;
             unsigned char* a_lo = sm + buf * STAGE + 2 * cbfrec::BLK;
@@ -675,6 +650,10 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
           }
           __syncwarp();
           if (lane == 0) mbar_arrive(&full[buf]);
+          // the next stage's inputs
+          const bool last = s0 + 1 == NST;
+          if (genA && last) load_route(tile + gridDim.x);
+          load_x(last ? tile + gridDim.x : tile, last ? 0 : s0 + 1);
         }
       }
     }
@@ -793,7 +772,6 @@ int cbf_backward_tc(const float* states, const float* obstacles, const int32_t* 
   const long long nt = cbf_bwd_tiles(agents, K);
   MACBF_CHECK_CUDA(cudaMemsetAsync(slices, 0, slice_bytes, st));
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(cbf_dgrad_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfdg::smem_bytes));
-  MACBF_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfwg::smem_bytes));
   const long long CH = chunk_tiles();
   for (long long t0 = 0; t0 < nt; t0 += CH) {
     const long long t1 = (t0 + CH < nt) ? t0 + CH : nt;
@@ -805,11 +783,7 @@ int cbf_backward_tc(const float* states, const float* obstacles, const int32_t* 
     cbf_dgrad_tc_kernel<false><<<grid, cbfdg::THREADS, cbfdg::smem_bytes, st>>>(idx, params, N, K, agents, TA, t0, t1, rec, slices,
                                                                                grad_states, nullptr, nullptr);
     MACBF_CHECK_LAUNCH("cbf_dgrad_tc_kernel");
-    wgrad_tc_kernel<2><<<grid, 64 + 256, cbfwg::smem_bytes, st>>>(rec, cbfrec::BYTES, ct, slices, MACBF_CBF_PARAMS, CBF_W3,
-                                                                       CBF_B3, CBF_W2, CBF_B2, 0, 0, params + CBF_W1, params + CBF_B1,
-                                                                       6, cbfrec::XREC, params + CBF_W4, WgradRoute{},
-                                                                       cbfrec::REC_STAGE);
-    MACBF_CHECK_LAUNCH("wgrad_tc_kernel<cbf>");
+    if (int rc = wgrad_cbf_ring(rec, ct, slices, params, grid, st)) return rc;
   }
   return reduce_partials(slices, NUM_SMS, MACBF_CBF_PARAMS, grad_params, st);
 }
@@ -856,15 +830,11 @@ int cbf_backward_record(const int32_t* idx, const float* params, const float* gr
   float* slices = (float*)scratch;
   MACBF_CHECK_CUDA(cudaMemsetAsync(slices, 0, cbf_backward_record_scratch_bytes(), st));
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(cbf_dgrad_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfdg::smem_bytes));
-  MACBF_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfwg::smem_bytes));
   const int grid = (int)(nt < NUM_SMS ? nt : (long long)NUM_SMS);
   cbf_dgrad_tc_kernel<true><<<grid, cbfdg::THREADS_RECORD, cbfdg::smem_bytes, st>>>(idx, params, N, K, agents, TA, 0, nt, rec, slices,
                                                                             grad_states, grad_h, a3);
   MACBF_CHECK_LAUNCH("cbf_dgrad_tc_kernel");
-  wgrad_tc_kernel<2><<<grid, 64 + 256, cbfwg::smem_bytes, st>>>(rec, cbfrec::BYTES, nt, slices, MACBF_CBF_PARAMS, CBF_W3, CBF_B3,
-                                                                CBF_W2, CBF_B2, 0, 0, params + CBF_W1, params + CBF_B1, 6,
-                                                                cbfrec::XREC, params + CBF_W4, WgradRoute{}, cbfrec::REC_STAGE);
-  MACBF_CHECK_LAUNCH("wgrad_tc_kernel<cbf>");
+  if (int rc = wgrad_cbf_ring(rec, nt, slices, params, grid, st)) return rc;
   return reduce_partials(slices, NUM_SMS, MACBF_CBF_PARAMS, grad_params, st);
 }
 
