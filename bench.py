@@ -60,7 +60,7 @@ KERNEL_WORK = {
     # delta chain dA2 = dZ3 W3, dA1 = dZ2 W2 (2 x 16,384) + first/last layer pieces (dZ3, dW1, d/dstates)
     "cbf_dgrad_tc_kernel": ("tensor", 2 * (64 * 128 + 128 * 64) + 2 * 64 + 2 * 2 * 6 * 64, 0),
     # dW3 = A2^T dZ3, dW2 = dZ2^T A1
-    "wgrad_tc_kernel<cbf>": ("tensor", 2 * (128 * 64 + 64 * 128), 0),
+    "wgrad_cbf_ring_kernel": ("tensor", 2 * (128 * 64 + 64 * 128), 0),
     "wgrad_tc_kernel<ctrl>": ("tensor", 2 * 64 * 128, 0),
     "wgrad_tc_kernel<node>": ("tensor", 0, 2 * (64 * 128 + 128 * 64 + 128 * 64)),
     "ctrl_edge_bwd_tc_kernel": ("tensor", 2 * 128 * 64 + 2 * 2 * 5 * 64, 0),
@@ -673,7 +673,7 @@ def main():
                     "kernel": top["kernel"], "bound": "tensor", "achieved": top["tflops"],
                     "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
                     "frac": top["tflops"] / peaks["bf16_tflops_sustained"],
-                    "frac_of_3xtf32_ceiling": (None if top["kernel"].startswith("wgrad") else
+                    "frac_of_3xtf32_ceiling": (None if "wgrad" in top["kernel"] else
                                                top["tflops"] / (peaks["tf32_tflops"] / 3.0)),
                     "ms_per_launch": top["ms_per_launch"], "launches_per_step": top["launches_per_step"],
                     "traffic": ((prof.get("kernels", {}).get(top["kernel"], {}).get("dram_bytes")) if same_workload else None),

@@ -237,7 +237,7 @@ wgrad_cbf_ring_kernel(const unsigned char* __restrict__ rec, long long ntiles, f
 int wgrad_cbf_ring(const unsigned char* rec, long long ntiles, float* slices, const float* params, int grid, cudaStream_t st) {
   MACBF_CHECK_CUDA(cudaFuncSetAttribute(wgrad_cbf_ring_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cbfwr::smem_bytes));
   wgrad_cbf_ring_kernel<<<grid, cbfwr::THREADS, cbfwr::smem_bytes, st>>>(rec, ntiles, slices, params);
-  MACBF_CHECK_LAUNCH("wgrad_tc_kernel<cbf>");
+  MACBF_CHECK_LAUNCH("wgrad_cbf_ring_kernel");
   return 0;
 }
 
