@@ -26,7 +26,7 @@ _LOSS_WEIGHTS = {0: 20.0, 1: 10.0, 4: 20.0, 5: 10.0, 8: 0.1}
 class TrainStep:
     # record_forward=None: the forward pass writes the CBF tile records (one CBF forward per pass less) whenever the two
     # record buffers fit this budget; False: recompute in the backward (macbf_cbf_backward), no extra memory
-    RECORD_BUDGET_BYTES = 16 << 30
+    RECORD_BUDGET_BYTES = 48 << 30      # of 180 GB HBM; BASELINE C4's per-GPU share (32 envs x 16,384 agents) needs 18.6 GB
 
     def __init__(self, B: int, N: int, M: int, top_k: int, device, world_size: int = 1, process_group=None,
                  record_forward: Optional[bool] = None):
