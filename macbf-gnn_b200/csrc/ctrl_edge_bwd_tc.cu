@@ -40,7 +40,8 @@ constexpr int oXs = oDz1 + 64 * DZS;           // [8][128]: per feature (f0..f4,
 constexpr int oXpart = oXs + 128 * 8;          // [2][4][128]
 constexpr int oW1 = oXpart + 2 * 4 * 128;      // W1 plain [64][8] (5 used), b1 [64]
 constexpr int oB1 = oW1 + 64 * 8;
-constexpr int total_floats = oB1 + 64;
+constexpr int oW1T = oB1 + 64;                 // W1 feature-major [5][64]: four channels of one feature per LDS.128 (packed FMAs)
+constexpr int total_floats = oW1T + 5 * 64;
 constexpr size_t smem_bytes = (size_t)total_floats * 4 + 1024;
 static_assert(smem_bytes <= 113 * 1024, "two CTAs per SM must fit");
 }  // namespace cebtc
@@ -57,6 +58,7 @@ ctrl_edge_bwd_tc_kernel(const float* __restrict__ states, const float* __restric
   float* sm = reinterpret_cast<float*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
   float* W2Thi = sm + oW2THI; float* W2Tlo = sm + oW2TLO;
   float* dz1s = sm + oDz1; float* xs = sm + oXs; float* xpart = sm + oXpart; float* W1 = sm + oW1; float* B1 = sm + oB1;
+  float* W1T = sm + oW1T;
   // workers -> MMA: z_full (8 arrivals, once per chunk); MMA -> workers: c_done (chunk's MMAs retired, once per chunk)
   __shared__ uint64_t z_full, c_done;
   __shared__ uint32_t tmem_base_s;
@@ -74,6 +76,7 @@ ctrl_edge_bwd_tc_kernel(const float* __restrict__ states, const float* __restric
   }
   for (int t = threadIdx.x; t < 64 * 8; t += THREADS) W1[t] = ((t & 7) < 5) ? __ldg(params + CT_EW1 + (t >> 3) * 5 + (t & 7)) : 0.f;
   for (int t = threadIdx.x; t < 64; t += THREADS) B1[t] = __ldg(params + CT_EB1 + t);
+  for (int t = threadIdx.x; t < 5 * 64; t += THREADS) W1T[t] = __ldg(params + CT_EW1 + (t & 63) * 5 + (t >> 6));
   fence_proxy_async_smem();
   fence_before_sync();
   __syncthreads();
@@ -155,14 +158,24 @@ ctrl_edge_bwd_tc_kernel(const float* __restrict__ states, const float* __restric
         xr[1] = make_float4(f[4], 0.f, 0.f, 0.f);
       }
       // ---- ReLU bits of a1 = relu(W1 x + b1), channels c0 .. c0+31 ----
+      // (the forward's fmaf chain b1 + w0 f0 + .. + w4 f4 per channel, four channels at a time as packed f32x2 FMAs: the
+      // same roundings at half the instructions)
       uint32_t mb1 = 0;
 #pragma unroll
-      for (int e = 0; e < 32; ++e) {
-        const int ch = c0 + e;
-        const float4 wa = *reinterpret_cast<const float4*>(W1 + ch * 8);
-        float z = fmaf(wa.x, f[0], B1[ch]);
-        z = fmaf(wa.y, f[1], z); z = fmaf(wa.z, f[2], z); z = fmaf(wa.w, f[3], z); z = fmaf(W1[ch * 8 + 4], f[4], z);
-        mb1 |= (z > 0.f ? 1u : 0u) << e;
+      for (int e = 0; e < 32; e += 4) {
+        const float4 bb = *reinterpret_cast<const float4*>(B1 + c0 + e);
+        float2 za = make_float2(bb.x, bb.y), zb = make_float2(bb.z, bb.w);
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+          const float4 w = *reinterpret_cast<const float4*>(W1T + k * 64 + c0 + e);
+          const float2 fk = make_float2(f[k], f[k]);
+          za = __ffma2_rn(make_float2(w.x, w.y), fk, za);
+          zb = __ffma2_rn(make_float2(w.z, w.w), fk, zb);
+        }
+        mb1 |= (za.x > 0.f ? 1u : 0u) << e;
+        mb1 |= (za.y > 0.f ? 1u : 0u) << (e + 1);
+        mb1 |= (zb.x > 0.f ? 1u : 0u) << (e + 2);
+        mb1 |= (zb.y > 0.f ? 1u : 0u) << (e + 3);
       }
       // ---- per 64-channel chunk: dZ2 from the winners -> TMEM hi/lo + image; the MMA warp accumulates dA1 ----
 #pragma unroll
@@ -227,18 +240,20 @@ ctrl_edge_bwd_tc_kernel(const float* __restrict__ states, const float* __restric
         const float4* xr = reinterpret_cast<const float4*>(xs + wf * R);
         const int wf2 = wf + 4;                         // 4, 5 for wf = 0, 1; idle otherwise
         const float4* xr2 = reinterpret_cast<const float4*>(xs + (wf2 < 6 ? wf2 : wf) * R);
-        float s0 = 0.f, s1 = 0.f, t0 = 0.f, t1 = 0.f;
+        float2 s01 = make_float2(0.f, 0.f), t01 = s01;      // packed f32x2 FMAs: (even rows, odd rows) partial sums
 #pragma unroll 8
         for (int e4 = 0; e4 < R / 4; ++e4) {
           const float4 d = dzr[e4], x = xr[e4];
-          s0 = fmaf(d.x, x.x, s0); s1 = fmaf(d.y, x.y, s1); s0 = fmaf(d.z, x.z, s0); s1 = fmaf(d.w, x.w, s1);
+          s01 = __ffma2_rn(make_float2(d.x, d.y), make_float2(x.x, x.y), s01);
+          s01 = __ffma2_rn(make_float2(d.z, d.w), make_float2(x.z, x.w), s01);
           if (wf2 < 6) {
             const float4 y = xr2[e4];
-            t0 = fmaf(d.x, y.x, t0); t1 = fmaf(d.y, y.y, t1); t0 = fmaf(d.z, y.z, t0); t1 = fmaf(d.w, y.w, t1);
+            t01 = __ffma2_rn(make_float2(d.x, d.y), make_float2(y.x, y.y), t01);
+            t01 = __ffma2_rn(make_float2(d.z, d.w), make_float2(y.z, y.w), t01);
           }
         }
-        accw1a += s0 + s1;
-        accw1b += t0 + t1;
+        accw1a += s01.x + s01.y;
+        accw1b += t01.x + t01.y;
       }
       if (grad_states != nullptr && cgrp == 0 && live && gj != ga) {   // the self edge contributes +g - g = 0
         float d0[4];
