@@ -291,13 +291,14 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
       if (wf < 7) {     // dW1[c][f], db1[c] += sum over the tile's rows (rows without an edge have dZ1 = 0)
         const float4* dzr = reinterpret_cast<const float4*>(dzb + wc * DZS);
         const float4* xr = reinterpret_cast<const float4*>(xsb + wf * R);
-        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        float2 s01 = make_float2(0.f, 0.f), s23 = s01;    // packed f32x2 FMAs (same four partial sums)
 #pragma unroll 8
         for (int e4 = 0; e4 < R / 4; ++e4) {
           const float4 d = dzr[e4], x = xr[e4];
-          s0 = fmaf(d.x, x.x, s0); s1 = fmaf(d.y, x.y, s1); s2 = fmaf(d.z, x.z, s2); s3 = fmaf(d.w, x.w, s3);
+          s01 = __ffma2_rn(make_float2(d.x, d.y), make_float2(x.x, x.y), s01);
+          s23 = __ffma2_rn(make_float2(d.z, d.w), make_float2(x.z, x.w), s23);
         }
-        accw1 += (s0 + s1) + (s2 + s3);
+        accw1 += (s01.x + s01.y) + (s23.x + s23.y);
       }
       // features -> states (cbf.py:23-30): +grad to agent i, -grad to neighbour j
       if (grad_states != nullptr && cgrp == 0) {
@@ -378,19 +379,21 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
         float v[16];
         tmem_ld16(tlane + C_DA1 + c0, v);
         wait_ld();
-        float px[5] = {0.f, 0.f, 0.f, 0.f, 0.f};       // d/d(f0, f1, f2, f3, f5); the identity indicator f4 has no gradient
+        float2 p01 = make_float2(0.f, 0.f), p23 = p01;  // d/d(f0, f1), d/d(f2, f3) as packed f32x2 FMAs; p4 = d/df5
+        float p4 = 0.f;                                 // (the identity indicator f4 has no gradient)
         float* dzb = dz1s + buf * (64 * DZS);
 #pragma unroll
         for (int e = 0; e < 16; ++e) {
           const float dz = ((mb1 >> e) & 1u) ? v[e] : 0.f;
           dzb[(c0 + e) * DZS + r] = dz;
           const float4 wa = *reinterpret_cast<const float4*>(W1 + (c0 + e) * 8);
-          px[0] = fmaf(dz, wa.x, px[0]); px[1] = fmaf(dz, wa.y, px[1]); px[2] = fmaf(dz, wa.z, px[2]);
-          px[3] = fmaf(dz, wa.w, px[3]); px[4] = fmaf(dz, W1[(c0 + e) * 8 + 5], px[4]);
+          const float2 dz2 = make_float2(dz, dz);
+          p01 = __ffma2_rn(dz2, make_float2(wa.x, wa.y), p01); p23 = __ffma2_rn(dz2, make_float2(wa.z, wa.w), p23);
+          p4 = fmaf(dz, W1[(c0 + e) * 8 + 5], p4);
         }
         float* xpb = xpart + buf * (4 * 5 * 128);
 #pragma unroll
-        for (int f = 0; f < 5; ++f) xpb[(cgrp * 5 + f) * R + r] = px[f];
+        for (int f = 0; f < 5; ++f) xpb[(cgrp * 5 + f) * R + r] = f == 0 ? p01.x : f == 1 ? p01.y : f == 2 ? p23.x : f == 3 ? p23.y : p4;
         if (cgrp == 0) {
           float* xsb = xs + buf * (128 * 8);
           xsb[0 * R + r] = x0.x; xsb[1 * R + r] = x0.y; xsb[2 * R + r] = x0.z; xsb[3 * R + r] = x0.w;

@@ -171,12 +171,13 @@ wgrad_cbf_ring_kernel(const unsigned char* __restrict__ rec, long long ntiles, f
           for (int e = 0; e < 8; ++e) x[e] = ((bits >> e) & 1u) ? gm * w4r[e] : 0.f;
         } else {
           const float4 xa = reinterpret_cast<const float4*>(in)[2 * rl], xb = reinterpret_cast<const float4*>(in)[2 * rl + 1];
+          const float xf[6] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y};
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            float z = fmaf(w1r[e][0], xa.x, w1r[e][6]);
-            z = fmaf(w1r[e][1], xa.y, z); z = fmaf(w1r[e][2], xa.z, z); z = fmaf(w1r[e][3], xa.w, z);
-            z = fmaf(w1r[e][4], xb.x, z); z = fmaf(w1r[e][5], xb.y, z);
-            x[e] = fmaxf(z, 0.f);
+          for (int e = 0; e < 8; e += 2) {                // two channels per packed f32x2 FMA: the forward's chain, same roundings
+            float2 z = make_float2(w1r[e][6], w1r[e + 1][6]);
+#pragma unroll
+            for (int f = 0; f < 6; ++f) z = __ffma2_rn(make_float2(w1r[e][f], w1r[e + 1][f]), make_float2(xf[f], xf[f]), z);
+            x[e] = fmaxf(z.x, 0.f); x[e + 1] = fmaxf(z.y, 0.f);
           }
         }
         uint4 bh, bl;

@@ -215,7 +215,7 @@ ctrl_edge_bwd_tc_kernel(const float* __restrict__ states, const float* __restric
       mbar_wait(&c_done, (n - 1) & 1);
       fence_after_sync();
       {
-        float px[4] = {0.f, 0.f, 0.f, 0.f};
+        float2 p01 = make_float2(0.f, 0.f), p23 = p01;       // d/d(f0, f1), d/d(f2, f3): packed f32x2 FMAs
 #pragma unroll
         for (int part = 0; part < 2; ++part) {
           float v[16];
@@ -227,11 +227,12 @@ ctrl_edge_bwd_tc_kernel(const float* __restrict__ states, const float* __restric
             const float dz = ((mb1 >> (part * 16 + e)) & 1u) ? v[e] : 0.f;
             dz1s[ch * DZS + r] = dz;
             const float4 wa = *reinterpret_cast<const float4*>(W1 + ch * 8);
-            px[0] = fmaf(dz, wa.x, px[0]); px[1] = fmaf(dz, wa.y, px[1]); px[2] = fmaf(dz, wa.z, px[2]); px[3] = fmaf(dz, wa.w, px[3]);
+            const float2 dz2 = make_float2(dz, dz);
+            p01 = __ffma2_rn(dz2, make_float2(wa.x, wa.y), p01); p23 = __ffma2_rn(dz2, make_float2(wa.z, wa.w), p23);
           }
         }
 #pragma unroll
-        for (int ff = 0; ff < 4; ++ff) xpart[(cgrp * 4 + ff) * R + r] = px[ff];
+        for (int ff = 0; ff < 4; ++ff) xpart[(cgrp * 4 + ff) * R + r] = ff == 0 ? p01.x : ff == 1 ? p01.y : ff == 2 ? p23.x : p23.y;
       }
       fence_before_sync();
       named_bar_sync(1, WORKERS);

@@ -308,17 +308,18 @@ ctrl_node_tc_kernel(const float* __restrict__ states, const float* __restrict__ 
       float v[16];
       tmem_ld16(tlane + C_D3 + c0, v);
       wait_ld();
-      float o[4] = {0.f, 0.f, 0.f, 0.f};
+      float2 o01 = make_float2(0.f, 0.f), o23 = o01;   // the four outputs as two packed f32x2 accumulators (same roundings)
       [[maybe_unused]] uint32_t bits = 0;
 #pragma unroll
       for (int e = 0; e < 16; ++e) {
         const float a = fmaxf(v[e] + B3[c0 + e], 0.f);
         if constexpr (DUMP) bits |= (a > 0.f ? 1u : 0u) << e;
-#pragma unroll
-        for (int qq = 0; qq < 4; ++qq) o[qq] = fmaf(W4[qq * 64 + c0 + e], a, o[qq]);
+        const float2 a2 = make_float2(a, a);
+        o01 = __ffma2_rn(make_float2(W4[0 * 64 + c0 + e], W4[1 * 64 + c0 + e]), a2, o01);
+        o23 = __ffma2_rn(make_float2(W4[2 * 64 + c0 + e], W4[3 * 64 + c0 + e]), a2, o23);
       }
-#pragma unroll
-      for (int qq = 0; qq < 4; ++qq) part[(cgrp * 4 + qq) * R + r] = o[qq];
+      part[(cgrp * 4 + 0) * R + r] = o01.x; part[(cgrp * 4 + 1) * R + r] = o01.y;
+      part[(cgrp * 4 + 2) * R + r] = o23.x; part[(cgrp * 4 + 3) * R + r] = o23.y;
       if constexpr (DUMP) reinterpret_cast<uint32_t*>(tr + cnrec::MASKS)[(2 * 4 + cgrp) * R + r] = bits;
     }
     fence_before_sync();
