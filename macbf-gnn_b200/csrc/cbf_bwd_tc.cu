@@ -634,14 +634,18 @@ wgrad_tc_kernel(const unsigned char* __restrict__ rec, size_t rec_stride, long l
             for (int c8 = part; c8 < 8; c8 += nparts) {
               float x[8];
 #pragma unroll
-              for (int e = 0; e < 8; ++e) {
+              for (int e = 0; e < 8; e += 2) {           // two channels per packed f32x2 FMA: the forward's chain, same roundings
                 const int ch = c8 * 8 + e;
-                const float4 wa = *reinterpret_cast<const float4*>(gW1 + ch * 8);
-                const float4 wb = *reinterpret_cast<const float4*>(gW1 + ch * 8 + 4);
-                float z = fmaf(wa.x, xa.x, gB1[ch]);
-                z = fmaf(wa.y, xa.y, z); z = fmaf(wa.z, xa.z, z); z = fmaf(wa.w, xa.w, z);
-                z = fmaf(wb.x, xb.x, z); z = fmaf(wb.y, xb.y, z);
-                x[e] = fmaxf(z, 0.f);
+                const float4 wa0 = *reinterpret_cast<const float4*>(gW1 + ch * 8), wa1 = *reinterpret_cast<const float4*>(gW1 + ch * 8 + 8);
+                const float4 wb0 = *reinterpret_cast<const float4*>(gW1 + ch * 8 + 4), wb1 = *reinterpret_cast<const float4*>(gW1 + ch * 8 + 12);
+                float2 z = make_float2(gB1[ch], gB1[ch + 1]);
+                z = __ffma2_rn(make_float2(wa0.x, wa1.x), make_float2(xa.x, xa.x), z);
+                z = __ffma2_rn(make_float2(wa0.y, wa1.y), make_float2(xa.y, xa.y), z);
+                z = __ffma2_rn(make_float2(wa0.z, wa1.z), make_float2(xa.z, xa.z), z);
+                z = __ffma2_rn(make_float2(wa0.w, wa1.w), make_float2(xa.w, xa.w), z);
+                z = __ffma2_rn(make_float2(wb0.x, wb1.x), make_float2(xb.x, xb.x), z);
+                z = __ffma2_rn(make_float2(wb0.y, wb1.y), make_float2(xb.y, xb.y), z);
+                x[e] = fmaxf(z.x, 0.f); x[e + 1] = fmaxf(z.y, 0.f);
               }
               uint4 bh, bl;
               bf16_split8(x, bh, bl);
