@@ -270,8 +270,8 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
           x[e] = ((mb3 >> (half * 8 + e)) & 1u) ? gm * W4[c0 + half * 8 + e] : 0.f;
-          tf32_split(x[e], hi[e], lo[e]);
         }
+        tf32_split_trunc8(x, hi, lo);
         tmem_st8(tlane + C_Z3HI + c0 + half * 8, hi);
         tmem_st8(tlane + C_Z3LO + c0 + half * 8, lo);
       }
@@ -356,8 +356,8 @@ cbf_dgrad_tc_kernel(const int32_t* __restrict__ idx, const float* __restrict__ p
 #pragma unroll
           for (int e = 0; e < 8; ++e) {
             x[e] = ((mb2[c] >> (half * 8 + e)) & 1u) ? v[half * 8 + e] : 0.f;
-            tf32_split(x[e], hi[e], lo[e]);
           }
+          tf32_split_trunc8(x, hi, lo);
           tmem_st8(tlane + C_DA2 + c * 64 + c0 + half * 8, hi);
           tmem_st8(tlane + C_Z2LO + c * 64 + c0 + half * 8, lo);
           bf16_split8(x, bh[half], bl[half]);

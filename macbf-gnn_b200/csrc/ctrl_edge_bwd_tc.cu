@@ -202,8 +202,8 @@ ctrl_edge_bwd_tc_kernel(const float* __restrict__ states, const float* __restric
               const float4 d4 = dp[half * 2 + (e >> 2)];
               const float dv = (e & 3) == 0 ? d4.x : (e & 3) == 1 ? d4.y : (e & 3) == 2 ? d4.z : d4.w;
               x[e] = (wbyte == (uint32_t)k_loc) ? dv : 0.f;
-              tf32_split(x[e], hi[e], lo[e]);
             }
+            tf32_split_trunc8(x, hi, lo);
             tmem_st8(tlane + C_ZHI + c0 + pair * 16 + half * 8, hi);
             tmem_st8(tlane + C_ZLO + c0 + pair * 16 + half * 8, lo);
           }

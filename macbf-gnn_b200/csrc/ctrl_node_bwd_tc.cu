@@ -120,8 +120,8 @@ ctrl_node_dgrad_tc_kernel(const float* __restrict__ params, const float* __restr
           float sv = W4[c] * d_o.x;
           sv = fmaf(W4[64 + c], d_o.y, sv); sv = fmaf(W4[128 + c], d_o.z, sv); sv = fmaf(W4[192 + c], d_o.w, sv);
           x[e] = ((mb3 >> (half * 8 + e)) & 1u) ? sv : 0.f;
-          tf32_split(x[e], hi[e], lo[e]);
         }
+        tf32_split_trunc8(x, hi, lo);
         tmem_st8(tlane + C_Z3HI + c0 + half * 8, hi);
         tmem_st8(tlane + C_Z3LO + c0 + half * 8, lo);
         bf16_split8(x, bh[half], bl[half]);
@@ -151,8 +151,8 @@ ctrl_node_dgrad_tc_kernel(const float* __restrict__ params, const float* __restr
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
           x[e] = ((mb2 >> (half16 * 16 + half * 8 + e)) & 1u) ? v[half * 8 + e] : 0.f;
-          tf32_split(x[e], hi[e], lo[e]);
         }
+        tf32_split_trunc8(x, hi, lo);
         tmem_st8(tlane + C_DA2 + c0 + half * 8, hi);
         tmem_st8(tlane + C_Z2LO + c0 + half * 8, lo);
         bf16_split8(x, bh[half], bl[half]);
@@ -182,7 +182,6 @@ ctrl_node_dgrad_tc_kernel(const float* __restrict__ params, const float* __restr
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
           x[e] = ((mb1 >> (half * 8 + e)) & 1u) ? v[half * 8 + e] : 0.f;
-          tf32_split(x[e], hi[e], lo[e]);
           const float s0 = warp_sum(x[e] * ev.x), s1 = warp_sum(x[e] * ev.y), s2 = warp_sum(x[e] * ev.z),
                       s3 = warp_sum(x[e] * ev.w), s4 = warp_sum(x[e]);
           if (lane == 0) {
@@ -190,6 +189,7 @@ ctrl_node_dgrad_tc_kernel(const float* __restrict__ params, const float* __restr
             ws[0] = s0; ws[1] = s1; ws[2] = s2; ws[3] = s3; ws[4] = s4;
           }
         }
+        tf32_split_trunc8(x, hi, lo);
         tmem_st8(tlane + C_DA1 + c0 + half * 8, hi);
         tmem_st8(tlane + C_Z1LO + c0 + half * 8, lo);
         bf16_split8(x, bh[half], bl[half]);
