@@ -10,6 +10,7 @@ static thread_local long long g_launches = 0;
 thread_local const int* tl_skip_flag = nullptr;
 thread_local QueryPart tl_query_part = {0, 1};
 thread_local RowRange tl_row_range = {0, -1};
+thread_local GraphPair tl_graph_pair = {0, 0.f, nullptr};
 thread_local uint8_t* tl_save_winners = nullptr;
 
 void set_error(const char* fmt, ...) {
@@ -56,6 +57,9 @@ int rollout_forward(const float*, const float*, const float*, const float*, cons
 size_t neighbor_grid_workspace_bytes(int, int, int);
 bool neighbor_grid_applicable(int, int, int);
 int neighbor_topk_grid(const float*, const float*, int, int, int, int, int32_t*, void*, size_t, cudaStream_t);
+bool neighbor_grid_pair_applicable(int, int, int);
+size_t neighbor_grid_pair_workspace_bytes(int, int, int);
+int neighbor_topk_grid_pair(const float*, const float*, int, int, int, int, double, int32_t*, int32_t*, void*, size_t, cudaStream_t);
 
 // grid search when it applies (K <= 128, enough candidates) and workspace was given, else brute force
 static int neighbor_any(const float* states, const float* obstacles, int B, int N, int M, int top_k, int32_t* idx,
@@ -354,10 +358,16 @@ size_t macbf_step_workspace_bytes(int B, int N, int M, int top_k) {
   return macbf_step_workspace_winners_offset(B, N, M, top_k) + align256((size_t)B * N * MACBF_POOL_DIM);
 }
 
+// graph scratch of the fused step: both grids at once where that applies (neighbor_topk_grid_pair)
+static size_t step_graph_scratch_bytes(int B, int N, int M, int top_k) {
+  const size_t one = macbf_neighbor_workspace_bytes(B, N, M, top_k);
+  const size_t two = neighbor_grid_pair_applicable(N, M, top_k) ? neighbor_grid_pair_workspace_bytes(B, N, M) : 0;
+  return one > two ? one : two;
+}
 size_t macbf_step_workspace_winners_offset(int B, int N, int M, int top_k) {
   const int K = macbf_neighbor_count(N, M, top_k);
   return align256((size_t)B * N * MACBF_POOL_DIM * sizeof(float)) + align256(loss_scratch_bytes(B, N, K)) +
-         align256(macbf_neighbor_workspace_bytes(B, N, M, top_k));
+         align256(step_graph_scratch_bytes(B, N, M, top_k));
 }
 
 int macbf_step_forward(const float* states, const float* goals, const float* obstacles, const float* cbf_params,
@@ -409,10 +419,15 @@ int macbf_step_forward_train(const float* states, const float* goals, const floa
   cudaStream_t st = (cudaStream_t)stream;
   float* pool = (float*)workspace;
   void* lscratch = (char*)workspace + align256((size_t)B * N * MACBF_POOL_DIM * sizeof(float));
-  const size_t gbytes = macbf_neighbor_workspace_bytes(B, N, M, top_k);
+  const size_t gbytes = step_graph_scratch_bytes(B, N, M, top_k);
   void* gscratch = gbytes ? (char*)lscratch + align256(loss_scratch_bytes(B, N, K)) : nullptr;
   int rc;
-  if ((rc = neighbor_any(states, obstacles, B, N, M, top_k, idx, gscratch, gbytes, st))) return rc;
+  // graph(S') needs positions only and p' = p + v dt does not depend on the controller (core.py:137 with core.py:74-86): where
+  // the thread-per-query grid search applies, both graphs come from ONE build + ONE query launch here
+  const bool pair = !(flags & MACBF_STEP_REUSE_INDICES) && gscratch != nullptr && neighbor_grid_pair_applicable(N, M, top_k);
+  if (pair) rc = neighbor_topk_grid_pair(states, obstacles, B, N, M, K, dt, idx, idx_next, gscratch, gbytes, st);
+  else rc = neighbor_any(states, obstacles, B, N, M, top_k, idx, gscratch, gbytes, st);
+  if (rc) return rc;
   MACBF_CHECK_ARG(!(flags & MACBF_STEP_SAVE_WINNERS) || controller_forward_is_tensor_core(semantics),
                   "%s: MACBF_STEP_SAVE_WINNERS needs the tensor-core controller (REPAIRED semantics)", fn);
   if (flags & MACBF_STEP_SAVE_WINNERS)
@@ -422,6 +437,8 @@ int macbf_step_forward_train(const float* states, const float* goals, const floa
   if (rc) return rc;
   if (flags & MACBF_STEP_REUSE_INDICES) {   // h' on S's graph (the upstream `indices=` argument the reference dropped)
     MACBF_CHECK_CUDA(cudaMemcpyAsync(idx_next, idx, (size_t)B * N * K * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+    if ((rc = cbf_fwd(states, idx, h, record, K, st))) return rc;
+  } else if (pair) {
     if ((rc = cbf_fwd(states, idx, h, record, K, st))) return rc;
   } else {
     // graph(S') (core.py:137) on the side stream, under CBF(S) on the caller's stream

@@ -39,6 +39,10 @@ extern thread_local QueryPart tl_query_part;
 // Row range consulted by the launchers of the forward kernels (macbf_step_forward_rows_*): when active (end >= 0) only the
 // agents [begin, end) of a single env are processed as queries / rows - their neighbour search, controller, CBF and
 // loss partial sums - while every agent stays a candidate.  One large env row-sharded over several GPUs.
+// both neighbour graphs of a step in one launch (neighbor_grid.cu: neighbor_topk_grid_pair): grids [B_split, 2 B_split)
+// are the envs one Euler step (dt) later and write idx_next
+struct GraphPair { int B_split; float dt; int32_t* idx_next; };
+extern thread_local GraphPair tl_graph_pair;
 struct RowRange { int begin, end; };
 extern thread_local RowRange tl_row_range;
 inline bool rows_active() { return tl_row_range.end >= 0; }

@@ -37,13 +37,23 @@ __device__ __forceinline__ int cell_coord(float x, float o, float inv_cs, int G)
 __global__ void __launch_bounds__(GRID_BUILD_THREADS)
 grid_build_kernel(const float* __restrict__ states, const float* __restrict__ obstacles, int N, int M, int G,
                   float4* __restrict__ sorted, int* __restrict__ cell_start, GridHeader* __restrict__ header,
-                  const int* __restrict__ skip) {
+                  const int* __restrict__ skip, int Bs, float dt) {
   MACBF_SKIP_IF_SET(skip);
   extern __shared__ int cnt[];                  // G*G + 1: histogram -> cell starts -> scatter cursors
   __shared__ float red[4][32];
   __shared__ int wsum[32];
   __shared__ GridHeader hd;
   const int b = blockIdx.x, C = N + M, cells = G * G;
+  // Bs > 0 (both graphs of a step in one launch): grid b >= Bs is the grid of env b - Bs one Euler step later. The
+  // neighbour search sees positions only, and p' = p + v dt does not depend on the controller (core.py:133-137 with
+  // core.py:74-86): the same two ops as the controller's Euler epilogue, so the points are the s_next it writes bit for bit.
+  const bool adv = Bs > 0 && b >= Bs;
+  const int b_src = adv ? b - Bs : b;
+  auto cand = [&](int t) {
+    float4 sv = load_candidate(states, obstacles, b_src, t, N, M);
+    if (adv && t < N) { sv.x = xadd(sv.x, xmul(sv.z, dt)); sv.y = xadd(sv.y, xmul(sv.w, dt)); }
+    return sv;
+  };
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   // ---- bounding box ----
   float xmin = 3.0e38f, ymin = 3.0e38f, xmax = -3.0e38f, ymax = -3.0e38f;
@@ -52,7 +62,7 @@ grid_build_kernel(const float* __restrict__ states, const float* __restrict__ ob
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const int t = t0 + u * GRID_BUILD_THREADS;
-      sv[u] = load_candidate(states, obstacles, b, t < C ? t : t0, N, M);
+      sv[u] = cand(t < C ? t : t0);
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
@@ -89,7 +99,7 @@ grid_build_kernel(const float* __restrict__ states, const float* __restrict__ ob
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const int t = t0 + u * GRID_BUILD_THREADS;
-      sv[u] = load_candidate(states, obstacles, b, t < C ? t : t0, N, M);
+      sv[u] = cand(t < C ? t : t0);
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u)
@@ -137,7 +147,7 @@ grid_build_kernel(const float* __restrict__ states, const float* __restrict__ ob
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const int t = t0 + u * GRID_BUILD_THREADS;
-      sv[u] = load_candidate(states, obstacles, b, t < C ? t : t0, N, M);
+      sv[u] = cand(t < C ? t : t0);
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
@@ -486,9 +496,10 @@ template <int K, bool STAGE>
 __global__ void __launch_bounds__(128)
 knn_grid_tpq_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start,
                     const GridHeader* __restrict__ header, int N, int C, int G, int32_t* __restrict__ idx_out,
-                    const int* __restrict__ skip, int part, int nparts, int row_begin, int row_end) {
+                    const int* __restrict__ skip, int part, int nparts, int row_begin, int row_end, int Bs,
+                    int32_t* __restrict__ idx_out2) {
   MACBF_SKIP_IF_SET(skip);
-  const int b = blockIdx.y;
+  const int b = blockIdx.y;                            // Bs > 0: grids b >= Bs are the envs one Euler step later -> idx_out2
   const int p0 = blockIdx.x * blockDim.x + threadIdx.x;
   const GridHeader g = header[b];
   const int* cs = cell_start + (size_t)b * (GRID_GMAX * GRID_GMAX + 1);
@@ -565,7 +576,7 @@ knn_grid_tpq_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
     if (bound == __int_as_float(0x7f800000)) break;
     if (kK < bound * 0.9999f - 1e-5f * g.cs) break;
   }
-  int32_t* o = idx_out + ((size_t)b * N + i) * K;
+  int32_t* o = (Bs > 0 && b >= Bs) ? idx_out2 + ((size_t)(b - Bs) * N + i) * K : idx_out + ((size_t)b * N + i) * K;
 #pragma unroll
   for (int e = 0; e < K; ++e) o[e] = (int32_t)(unsigned)list[e];
 }
@@ -579,11 +590,11 @@ static int launch_tpq(const float4* sorted, const int* cell_start, const GridHea
     MACBF_CHECK_CUDA(cudaFuncSetAttribute(knn_grid_tpq_kernel<K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
     knn_grid_tpq_kernel<K, true><<<grid, 128, stage_bytes, st>>>(sorted, cell_start, header, N, C, G, idx, tl_skip_flag,
                                                                  tl_query_part.part, tl_query_part.nparts, tl_row_range.begin,
-                                                                 tl_row_range.end);
+                                                                 tl_row_range.end, tl_graph_pair.B_split, tl_graph_pair.idx_next);
   } else {
     knn_grid_tpq_kernel<K, false><<<grid, 128, 0, st>>>(sorted, cell_start, header, N, C, G, idx, tl_skip_flag,
                                                         tl_query_part.part, tl_query_part.nparts, tl_row_range.begin,
-                                                        tl_row_range.end);
+                                                        tl_row_range.end, tl_graph_pair.B_split, tl_graph_pair.idx_next);
   }
   MACBF_CHECK_LAUNCH("knn_grid_tpq_kernel");
   return 0;
@@ -640,7 +651,7 @@ int neighbor_topk_grid(const float* states, const float* obstacles, int B, int N
     MACBF_CHECK_LAUNCH("grid_big_scatter_kernel");
   } else {
     grid_build_kernel<<<B, GRID_BUILD_THREADS, build_smem, st>>>(states, obstacles, N, M, G, sorted, cell_start, header,
-                                                                 tl_skip_flag);
+                                                                 tl_skip_flag, tl_graph_pair.B_split, tl_graph_pair.dt);
     MACBF_CHECK_LAUNCH("grid_build_kernel");
   }
   {
@@ -669,6 +680,27 @@ int neighbor_topk_grid(const float* states, const float* obstacles, int B, int N
                                                             q_begin, q_end);
   MACBF_CHECK_LAUNCH("knn_grid_kernel");
   return 0;
+}
+
+// ---- both graphs of a step in ONE pair of launches -----------------------------------------------------------------
+// graph(S') needs the positions of S' only, and p' = p + v dt is known before the controller has run: the grid build
+// and the query kernel take 2B grids - env b from `states`, env B + b from the advanced positions - and write idx and
+// idx_next.  One build + one query launch at the start of the step instead of two of each (the second pair used to
+// run on a side stream under CBF(S), which it slowed down by about as much as it hid).
+bool neighbor_grid_pair_applicable(int N, int M, int top_k) {
+  const int C = N + M, K = C < top_k ? C : top_k;
+  const bool tpq = K == 4 || K == 8 || K == 12 || K == 16 || K == 24 || K == 32;
+  return neighbor_grid_applicable(N, M, top_k) && C < GRID_BIG_MIN_C && tpq && !rows_active() && tl_query_part.nparts == 1;
+}
+size_t neighbor_grid_pair_workspace_bytes(int B, int N, int M) { return neighbor_grid_workspace_bytes(2 * B, N, M); }
+
+int neighbor_topk_grid_pair(const float* states, const float* obstacles, int B, int N, int M, int K, double dt, int32_t* idx,
+                            int32_t* idx_next, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+  MACBF_CHECK_ARG(neighbor_grid_pair_applicable(N, M, K), "neighbor_topk_grid_pair: not applicable to N=%d M=%d K=%d", N, M, K);
+  tl_graph_pair = GraphPair{B, (float)dt, idx_next};
+  const int rc = neighbor_topk_grid(states, obstacles, 2 * B, N, M, K, idx, workspace, workspace_bytes, st);
+  tl_graph_pair = GraphPair{0, 0.f, nullptr};
+  return rc;
 }
 
 }  // namespace macbf
