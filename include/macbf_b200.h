@@ -224,9 +224,11 @@ int macbf_controller_backward_saved(const float* states, const float* goals, con
  * graph(S) -> u, S' -> graph(S') -> h(S), h(S') -> TTC mask -> scalars.  Workspace layout is
  * private; size it with macbf_step_workspace_bytes.  Outputs u, s_next, h, h_next, idx,
  * idx_next, ttc_mask, scalars as documented above (idx_next/h_next/ttc_mask may not be NULL).
- * The neighbour search on S' runs on a second, library-owned stream under CBF(S) (fork / join by events on
- * `stream`, so the call stays ordered on `stream` and can be captured); that stream and its two events are created on
- * the calling thread's first call per device and kept (the one exception to "the library holds no resources"). */
+ * graph(S') needs positions only and p' = p + v dt does not depend on the controller, so where the thread-per-query grid
+ * search applies both graphs come from one build + one query launch at the start of the call.  Otherwise the neighbour
+ * search on S' runs on a second, library-owned stream under CBF(S) (fork / join by events on `stream`, so the call stays
+ * ordered on `stream` and can be captured); that stream and its two events are created on the calling thread's first
+ * such call per device and kept (the one exception to "the library holds no resources"). */
 size_t macbf_step_workspace_bytes(int B, int N, int M, int top_k);
 /* flags for macbf_step_forward_ex.  MACBF_STEP_REUSE_INDICES: h' = CBF(S') is evaluated on the neighbour
  * sets of S instead of a fresh top-k on S' (the `indices=` argument of the code the reference derives
