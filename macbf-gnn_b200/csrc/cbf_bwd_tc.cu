@@ -10,7 +10,8 @@
 //      B = the TRANSPOSED weights resident in shared memory (same machinery as the forward's layers 2, 3).
 //      dZ2 is dumped as bf16 hi/lo images; dW1, db1 and d/dstates (6 features, fp32 atomics) are finished
 //      here on the CUDA cores.
-//   3. wgrad_tc_kernel   dW3^T = A2^T dZ3, dW2 = dZ2^T A1, db3, db2: GEMMs whose contraction index is the
+//   3. wgrad_cbf_ring_kernel (cbf_wgrad_ring.cu; the generic wgrad_tc_kernel below now serves the controller nets)
+//      dW3^T = A2^T dZ3, dW2 = dZ2^T A1, db3, db2: GEMMs whose contraction index is the
 //      EDGE, so both operands come from shared memory as MN-major bf16 images: the expensive ones (A2, dZ2) are
 //      staged by bulk copies (cp.async.bulk + mbarrier, two 96-KB stage buffers), the cheap ones (a1 from the
 //      edge features, dZ3 from gm and the ReLU bits) are rebuilt on chip by generator warps; 3 products (hi*hi,
@@ -436,6 +437,8 @@ struct WgradRoute {
   long long agents, tile0;   // total agents; global index of the record chunk's first tile
 };
 
+// (The CBF head's weight gradients moved to wgrad_cbf_ring_kernel, cbf_wgrad_ring.cu, in round 2; NST = 2 and gen_w4 below
+// describe that former instantiation and are no longer launched.)
 // NST = 2: CBF (stage 0 = G3: dW3^T, db3; stage 1 = G2: dW2, db2).  NST = 1: controller edge net (one G2-type stage
 // per tile: A = dZ2 (128 channels), B = A1 (64 channels) -> dW2[out][in], db2).  NST = 3: controller node net (G3, G2 and
 // a third stage A = pool (128 channels), B = dZ1 (64 channels) -> dW1[:, :128]^T, rows of W1 being `ldW1` floats long).
